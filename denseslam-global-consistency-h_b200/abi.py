@@ -1,0 +1,162 @@
+"""ctypes mirror of include/dsb200.h (POD structs + library loader).
+
+The product library is denseslam-global-consistency-h_b200/csrc/libdsb200.so (built by
+__graft_entry__.build()).  Loading fails loudly if it is missing: there is no CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libdsb200.so")
+
+BLOCK_SIZE = 8
+BLOCK_SIZE3 = 512
+DEFAULT_LOCAL_BLOCKS = 0x40000
+DEFAULT_BUCKETS = 0x100000
+DEFAULT_EXCESS = 0x60000
+
+OK = 0
+ERR_CUDA, ERR_INVALID, ERR_VBA_EXHAUSTED, ERR_EXCESS_EXHAUSTED, ERR_UNSUPPORTED, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6
+
+RENDER_SHADED_GREYSCALE, RENDER_COLOUR_FROM_VOLUME, RENDER_COLOUR_FROM_NORMAL, RENDER_COLOURCODED, RENDER_DEPTH_MAP = range(5)
+FRAME_ALLOCATE, FRAME_INTEGRATE, FRAME_EXPECTED_DEPTHS, FRAME_ICP_MAPS, FRAME_ALL = 1, 2, 4, 8, 15
+
+# numpy views of the two on-device record types (ITMHashEntry 20 B, ITMVoxel_s_rgb 8 B)
+HASH_DTYPE = np.dtype([("pos", "<i2", (3,)), ("pad", "<i2"), ("offset", "<i4"), ("ptr", "<i4"),
+                       ("allocated_time", "<i4")])
+VOXEL_DTYPE = np.dtype([("sdf", "<i2"), ("w_depth", "u1"), ("clr", "u1", (3,)), ("w_color", "u1"), ("pad", "u1")])
+assert HASH_DTYPE.itemsize == 20 and VOXEL_DTYPE.itemsize == 8
+
+
+class SceneParams(C.Structure):
+    _fields_ = [("voxel_size", C.c_float), ("mu", C.c_float), ("max_w", C.c_int32), ("vf_min", C.c_float),
+                ("vf_max", C.c_float), ("stop_integrating_at_max_w", C.c_int32)]
+
+
+class Scene(C.Structure):
+    _fields_ = [("voxels", C.c_void_p), ("hash", C.c_void_p), ("alloc_list", C.c_void_p), ("excess_list", C.c_void_p),
+                ("num_blocks", C.c_int32), ("bucket_num", C.c_int32), ("excess_size", C.c_int32),
+                ("last_free_block", C.c_int32), ("last_free_excess", C.c_int32), ("params", SceneParams),
+                ("use_swapping", C.c_int32)]
+
+    @property
+    def total_entries(self):
+        return self.bucket_num + self.excess_size
+
+
+class RenderState(C.Structure):
+    _fields_ = [("visible_ids", C.c_void_p), ("visible_type", C.c_void_p), ("visible_capacity", C.c_int32),
+                ("no_visible", C.c_int32), ("range_image", C.c_void_p), ("raycast_result", C.c_void_p),
+                ("raycast_image", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32)]
+
+
+class View(C.Structure):
+    _fields_ = [("depth", C.c_void_p), ("rgb", C.c_void_p), ("depth_w", C.c_int32), ("depth_h", C.c_int32),
+                ("rgb_w", C.c_int32), ("rgb_h", C.c_int32), ("intr_d", C.c_float * 4), ("intr_rgb", C.c_float * 4),
+                ("rgb_to_depth_inv", C.c_float * 16), ("timestamp", C.c_double)]
+
+
+class Tracking(C.Structure):
+    _fields_ = [("M_d", C.c_float * 16), ("invM_d", C.c_float * 16), ("requires_full_rendering", C.c_int32),
+                ("icp_points", C.c_void_p), ("icp_normals", C.c_void_p)]
+
+
+class WeightParams(C.Structure):
+    _fields_ = [("depth_weighting", C.c_int32), ("max_new_w", C.c_int32), ("max_distance", C.c_int32)]
+
+
+def f16(a):
+    """float[16] column-major ctypes array from any 16-element sequence."""
+    return (C.c_float * 16)(*[float(x) for x in np.asarray(a, dtype=np.float32).reshape(-1)])
+
+
+def f4(a):
+    return (C.c_float * 4)(*[float(x) for x in np.asarray(a, dtype=np.float32).reshape(-1)])
+
+
+IDENTITY16 = [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
+
+_P = C.POINTER
+_lib = None
+
+
+def load():
+    """Load libdsb200.so and declare every prototype of include/dsb200.h.  Raises if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "libdsb200.so not built (%s). Run `python -c 'import __graft_entry__ as g; g.build()'`. "
+            "There is no CPU fallback for the product path." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, cp = C.c_void_p, C.c_int32, C.c_char_p
+    sig = {
+        "dsb200_last_error": (cp, []),
+        "dsb200_device_count": (C.c_int, []),
+        "dsb200_recon_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
+        "dsb200_recon_destroy": (C.c_int, [vp]),
+        "dsb200_recon_set_async": (C.c_int, [vp, C.c_int]),
+        "dsb200_recon_sync": (C.c_int, [vp, _P(Scene), _P(RenderState)]),
+        "dsb200_reset_scene": (C.c_int, [vp, _P(Scene)]),
+        "dsb200_allocate_from_depth": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), C.c_int, C.c_int]),
+        "dsb200_integrate": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
+        "dsb200_deintegrate": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking)]),
+        "dsb200_decay": (C.c_int, [vp, _P(Scene), _P(RenderState), C.c_int, C.c_int, C.c_int]),
+        "dsb200_decay_defusion": (C.c_int, [vp, _P(Scene), _P(RenderState), C.c_int, C.c_int, C.c_int]),
+        "dsb200_slide_window": (C.c_int, [vp, _P(Scene), _P(RenderState), C.c_int]),
+        "dsb200_slide_window_defusion": (C.c_int, [vp, _P(Scene), _P(RenderState), C.c_int, C.c_int]),
+        "dsb200_decayed_block_count": (C.c_size_t, [vp]),
+        "dsb200_set_fusion_weight_params": (C.c_int, [vp, _P(WeightParams)]),
+        "dsb200_history_sizes": (C.c_int, [vp] + [_P(C.c_int)] * 5),
+        "dsb200_vis_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
+        "dsb200_vis_destroy": (C.c_int, [vp]),
+        "dsb200_find_visible_blocks": (C.c_int, [vp, _P(Scene), _P(C.c_float), _P(C.c_float), _P(RenderState)]),
+        "dsb200_count_visible_blocks": (C.c_int, [vp, _P(Scene), _P(RenderState), C.c_int, C.c_int, _P(C.c_int)]),
+        "dsb200_create_expected_depths": (C.c_int, [vp, _P(Scene), _P(C.c_float), _P(C.c_float), _P(RenderState)]),
+        "dsb200_find_surface": (C.c_int, [vp, _P(Scene), _P(C.c_float), _P(C.c_float), _P(RenderState)]),
+        "dsb200_create_icp_maps": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
+        "dsb200_render_image": (C.c_int, [vp, _P(Scene), _P(C.c_float), _P(C.c_float), _P(C.c_float), _P(RenderState), vp, vp, C.c_int]),
+        "dsb200_forward_render": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
+        "dsb200_create_point_cloud": (C.c_int, [vp]),
+        "dsb200_process_frame": (C.c_int, [vp, vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), C.c_int]),
+        "dsb200_scene_alloc": (C.c_int, [_P(Scene), i32, i32, i32]),
+        "dsb200_scene_free": (C.c_int, [_P(Scene)]),
+        "dsb200_render_state_alloc": (C.c_int, [_P(RenderState), i32, i32, i32, i32]),
+        "dsb200_render_state_free": (C.c_int, [_P(RenderState)]),
+        "dsb200_device_alloc": (C.c_int, [_P(vp), C.c_size_t]),
+        "dsb200_device_free": (C.c_int, [vp]),
+        "dsb200_host_alloc_pinned": (C.c_int, [_P(vp), C.c_size_t]),
+        "dsb200_host_free_pinned": (C.c_int, [vp]),
+        "dsb200_memcpy_h2d": (C.c_int, [vp, vp, C.c_size_t, vp]),
+        "dsb200_memcpy_d2h": (C.c_int, [vp, vp, C.c_size_t, vp]),
+        "dsb200_stream_synchronize": (C.c_int, [vp]),
+        "dsb200_mat4_inverse": (C.c_int, [_P(C.c_float), _P(C.c_float)]),
+        "dsb200_mat4_multiply": (None, [_P(C.c_float), _P(C.c_float), _P(C.c_float)]),
+        "dsb200_kernel_launch_count": (C.c_ulonglong, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)   # AttributeError here == header/library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    lib._declared = sorted(sig.keys())
+    _lib = lib
+    return lib
+
+
+class Dsb200Error(RuntimeError):
+    """Mirrors the reference's error behaviour: std::runtime_error with the reference's strings
+    (CUDA/ITMSceneReconstructionEngine_CUDA.cu:350-358) or a CUDA failure (ORcudaSafeCall)."""
+
+    def __init__(self, code, msg):
+        RuntimeError.__init__(self, "dsb200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def check(code):
+    if code != OK:
+        msg = load().dsb200_last_error()
+        raise Dsb200Error(code, msg.decode() if msg else "")
+    return code

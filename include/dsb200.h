@@ -1,0 +1,216 @@
+/* dsb200.h -- C ABI of the B200-native volumetric-fusion hot path.
+ *
+ * One entry point per virtual of the two InfiniTAM engine interfaces that DenseSLAM's
+ * InfiniTamDriver drives (paths relative to
+ * /root/reference/src/InfiniTAM-Global-Consistency-h/InfiniTAM/):
+ *   ITMLib/Engine/ITMSceneReconstructionEngine.h:45-96   (reconstruction engine)
+ *   ITMLib/Engine/ITMVisualisationEngine.h:71-124        (visualisation engine)
+ * The adapter subclasses shown in INTEGRATION.md pull raw DEVICE pointers out of the
+ * reference objects (ITMScene, ITMRenderState_VH, ITMView, ITMTrackingState) into the POD
+ * structs below and forward.  No torch / C++ types cross this boundary.
+ *
+ * Conventions (same as the reference): 4x4 matrices are column-major float[16]
+ * (ORUtils/Matrix.h:7-11); intrinsics are (fx, fy, cx, cy) (Objects/ITMIntrinsics.h:21-43);
+ * every call is synchronous on return unless dsb200_recon_set_async() was used; host mirrors
+ * (last_free_block, last_free_excess, no_visible) are valid on return.
+ * All functions return DSB200_OK (0) or a negative dsb200_status; dsb200_last_error() gives text.
+ */
+#ifndef DSB200_H
+#define DSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- data contract: byte-identical to the reference structs at default capacities ---- */
+#define DSB200_BLOCK_SIZE 8            /* SDF_BLOCK_SIZE   ITMLib/Utils/ITMLibDefines.h:36 */
+#define DSB200_BLOCK_SIZE3 512         /* SDF_BLOCK_SIZE3  :37 */
+#define DSB200_DEFAULT_LOCAL_BLOCKS 0x40000   /* SDF_LOCAL_BLOCK_NUM :38 */
+#define DSB200_DEFAULT_BUCKETS 0x100000       /* SDF_BUCKET_NUM :44 */
+#define DSB200_DEFAULT_EXCESS 0x60000         /* SDF_EXCESS_LIST_SIZE :46 */
+
+/* ITMHashEntry, ITMLibDefines.h:57-74 (20 bytes) */
+typedef struct dsb200_hash_entry {
+    int16_t pos[3];
+    int16_t pad_;
+    int32_t offset;         /* 0 = chain end, else next = bucket_num + offset - 1 */
+    int32_t ptr;            /* >=0 VBA block, -1 swapped out, -2 free */
+    int32_t allocated_time; /* never written by the reference allocators: we write 0 */
+} dsb200_hash_entry;
+
+/* ITMVoxel_s_rgb, ITMLibDefines.h:128-158 (8 bytes) */
+typedef struct dsb200_voxel {
+    int16_t sdf;       /* (short)(f*32767), init 32767 */
+    uint8_t w_depth;
+    uint8_t clr[3];
+    uint8_t w_color;
+    uint8_t pad_;
+} dsb200_voxel;
+
+typedef enum dsb200_status {
+    DSB200_OK = 0,
+    DSB200_ERR_CUDA = -1,
+    DSB200_ERR_INVALID = -2,
+    DSB200_ERR_VBA_EXHAUSTED = -3,    /* "run out of space in the Voxel Block Array"  (CUDA .cu:350-353) */
+    DSB200_ERR_EXCESS_EXHAUSTED = -4, /* "run out of slots in the hash table excess list" (.cu:354-358) */
+    DSB200_ERR_UNSUPPORTED = -5,
+    DSB200_ERR_NO_DEVICE = -6
+} dsb200_status;
+
+/* ITMSceneParams, Objects/ITMSceneParams.h:18-50 */
+typedef struct dsb200_scene_params {
+    float voxel_size, mu;
+    int32_t max_w;
+    float vf_min, vf_max;
+    int32_t stop_integrating_at_max_w;
+} dsb200_scene_params;
+
+/* Device pointers pulled from ITMScene (Objects/ITMScene.h, ITMLocalVBA.h:28-36, ITMVoxelBlockHash.h:70-84) */
+typedef struct dsb200_scene {
+    dsb200_voxel *voxels;          /* [num_blocks * 512] */
+    dsb200_hash_entry *hash;       /* [bucket_num + excess_size] */
+    int32_t *alloc_list;           /* [num_blocks] VBA free list, stack, pops from the high end */
+    int32_t *excess_list;          /* [excess_size] */
+    int32_t num_blocks, bucket_num /* power of two */, excess_size;
+    int32_t last_free_block;       /* host mirror (in/out) */
+    int32_t last_free_excess;      /* host mirror (in/out) */
+    dsb200_scene_params params;
+    int32_t use_swapping;          /* only changes visibility semantics (enlarged frustum), SURVEY A4/Q11 */
+} dsb200_scene;
+
+/* Device pointers pulled from ITMRenderState_VH (Objects/ITMRenderState.h:34-57, ITMRenderState_VH.h:26-65) */
+typedef struct dsb200_render_state {
+    int32_t *visible_ids;          /* [visible_capacity] hash-slot indices, ascending */
+    uint8_t *visible_type;         /* [bucket_num + excess_size] 0/1/2/3 */
+    int32_t visible_capacity;
+    int32_t no_visible;            /* host mirror (in/out) */
+    float *range_image;            /* Vector2f[W*H]; meaningful at 1/8 res with stride W */
+    float *raycast_result;         /* Vector4f[W*H], voxel units, w in {0,1} */
+    uint8_t *raycast_image;        /* Vector4u[W*H] grey rendering written by CreateICPMaps */
+    int32_t width, height;
+} dsb200_render_state;
+
+/* ITMView + calib (Objects/ITMView.h:20-36, ITMRGBDCalib.h) */
+typedef struct dsb200_view {
+    const float *depth;            /* float[W*H] metres, <=0 invalid */
+    const uint8_t *rgb;            /* Vector4u[Wrgb*Hrgb] */
+    int32_t depth_w, depth_h, rgb_w, rgb_h;
+    float intr_d[4], intr_rgb[4];
+    float rgb_to_depth_inv[16];    /* calib->trafo_rgb_to_depth.calib_inv */
+    double timestamp;              /* view->mTimeStamp, key of the de-fusion snapshot map */
+} dsb200_view;
+
+/* ITMTrackingState (Objects/ITMTrackingState.h:29-46) */
+typedef struct dsb200_tracking {
+    float M_d[16];                 /* pose_d->GetM(): world -> camera */
+    float invM_d[16];              /* pose_d->GetInvM() (host cofactor inverse, ORUtils/Matrix.h:175-246) */
+    int32_t requires_full_rendering;
+    float *icp_points;             /* pointCloud->locations Vector4f[W*H], metres, w=1 / -1 */
+    float *icp_normals;            /* pointCloud->colours   Vector4f[W*H], w=0 / -1 */
+} dsb200_tracking;
+
+/* WeightParams, Engine/ITMSceneReconstructionEngine.h:21-25 */
+typedef struct dsb200_weight_params { int32_t depth_weighting, max_new_w, max_distance; } dsb200_weight_params;
+
+/* IITMVisualisationEngine::RenderImageType, Engine/ITMVisualisationEngine.h */
+typedef enum dsb200_render_type {
+    DSB200_RENDER_SHADED_GREYSCALE = 0,
+    DSB200_RENDER_COLOUR_FROM_VOLUME = 1,
+    DSB200_RENDER_COLOUR_FROM_NORMAL = 2,
+    DSB200_RENDER_COLOURCODED = 3,
+    DSB200_RENDER_DEPTH_MAP = 4
+} dsb200_render_type;
+
+typedef struct dsb200_recon dsb200_recon;   /* engine-owned scratch + history queues */
+typedef struct dsb200_vis dsb200_vis;
+
+const char *dsb200_last_error(void);
+int dsb200_device_count(void);
+
+/* ---- reconstruction engine (ITMSceneReconstructionEngine.h:45-96) ---- */
+/* ctor: sizes the engine scratch (entriesAllocType/blockCoords equivalents) for these capacities. */
+int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_num, int32_t excess_size,
+                        void *cuda_stream /* cudaStream_t or NULL */);
+int dsb200_recon_destroy(dsb200_recon *e);
+/* async != 0: calls only enqueue work; host mirrors are refreshed by dsb200_recon_sync(). */
+int dsb200_recon_set_async(dsb200_recon *e, int async);
+int dsb200_recon_sync(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs);
+
+int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene);                                  /* ResetScene :50 */
+int dsb200_allocate_from_depth(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view,  /* AllocateSceneFromDepth :57 */
+                               const dsb200_tracking *tracking, dsb200_render_state *rs,
+                               int only_update_visible_list, int is_defusion);
+int dsb200_integrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view,            /* IntegrateIntoScene :63 */
+                     const dsb200_tracking *tracking, const dsb200_render_state *rs);
+int dsb200_deintegrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view,          /* DeIntegrateIntoScene :66 */
+                       const dsb200_tracking *tracking);
+int dsb200_decay(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs,                /* Decay :70 */
+                 int max_weight, int min_age, int force_all_voxels);
+int dsb200_decay_defusion(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs,       /* DecayDefusionPart :73 */
+                          int max_weight, int min_age, int force_all_voxels);
+int dsb200_slide_window(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs, int max_age);          /* SlideWindow :76 */
+int dsb200_slide_window_defusion(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs,               /* SlideWindowDefusionPart :77 */
+                                 int max_age, int max_size);
+size_t dsb200_decayed_block_count(const dsb200_recon *e);                                      /* GetDecayedBlockCount :79 */
+int dsb200_set_fusion_weight_params(dsb200_recon *e, const dsb200_weight_params *p);           /* SetFusionWeightParams :78-84 */
+/* introspection of the history queues (frameVisibleBlocks etc., CUDA/..._CUDA.h:41-48) */
+int dsb200_history_sizes(const dsb200_recon *e, int *decay_q, int *slide_q, int *decay_defusion_q,
+                         int *slide_defusion_q, int *snapshots);
+
+/* ---- visualisation engine (ITMVisualisationEngine.h:71-124) ---- */
+int dsb200_vis_create(dsb200_vis **out, int32_t max_visible, int32_t width, int32_t height, void *cuda_stream);
+int dsb200_vis_destroy(dsb200_vis *v);
+int dsb200_find_visible_blocks(dsb200_vis *v, const dsb200_scene *scene, const float *M, const float *intr,   /* FindVisibleBlocks :86 */
+                               dsb200_render_state *rs);
+int dsb200_count_visible_blocks(dsb200_vis *v, const dsb200_scene *scene, const dsb200_render_state *rs,      /* CountVisibleBlocks :91 */
+                                int min_block_id, int max_block_id, int *count);
+int dsb200_create_expected_depths(dsb200_vis *v, const dsb200_scene *scene, const float *M, const float *intr, /* CreateExpectedDepths :96 */
+                                  dsb200_render_state *rs);
+int dsb200_find_surface(dsb200_vis *v, const dsb200_scene *scene, const float *invM, const float *intr,       /* FindSurface :107 */
+                        dsb200_render_state *rs);
+int dsb200_create_icp_maps(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view,                 /* CreateICPMaps :117 */
+                           dsb200_tracking *tracking, dsb200_render_state *rs);
+int dsb200_render_image(dsb200_vis *v, const dsb200_scene *scene, const float *M, const float *invM,          /* RenderImage :101 */
+                        const float *intr, dsb200_render_state *rs, uint8_t *out_rgba, float *out_depth,
+                        int render_type);
+int dsb200_forward_render(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view,                  /* ForwardRender :122 */
+                          dsb200_tracking *tracking, dsb200_render_state *rs);
+int dsb200_create_point_cloud(dsb200_vis *v);                                                                 /* CreatePointCloud :112 -> UNSUPPORTED */
+
+/* ---- fused frame: ITMDenseMapper::ProcessFrame + ITMTrackingController::Prepare in one submission
+ *      (ITMLib/Engine/ITMDenseMapper.cpp:56-81, ITMTrackingController.cpp:21-58) ---- */
+#define DSB200_FRAME_ALLOCATE 1
+#define DSB200_FRAME_INTEGRATE 2
+#define DSB200_FRAME_EXPECTED_DEPTHS 4
+#define DSB200_FRAME_ICP_MAPS 8
+#define DSB200_FRAME_ALL 15
+int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, const dsb200_view *view,
+                         dsb200_tracking *tracking, dsb200_render_state *rs, int stages);
+
+/* ---- host helpers (what ITMScene / ITMRenderState_VH / ITMView ctors do with cudaMalloc) ---- */
+int dsb200_scene_alloc(dsb200_scene *scene, int32_t num_blocks, int32_t bucket_num, int32_t excess_size);
+int dsb200_scene_free(dsb200_scene *scene);
+int dsb200_render_state_alloc(dsb200_render_state *rs, int32_t total_entries, int32_t visible_capacity,
+                              int32_t width, int32_t height);
+int dsb200_render_state_free(dsb200_render_state *rs);
+int dsb200_device_alloc(void **ptr, size_t bytes);
+int dsb200_device_free(void *ptr);
+int dsb200_host_alloc_pinned(void **ptr, size_t bytes);
+int dsb200_host_free_pinned(void *ptr);
+int dsb200_memcpy_h2d(void *dst, const void *src, size_t bytes, void *cuda_stream);
+int dsb200_memcpy_d2h(void *dst, const void *src, size_t bytes, void *cuda_stream);
+int dsb200_stream_synchronize(void *cuda_stream);
+/* ORUtils Matrix4::inv restated (cofactor order preserved), ORUtils/Matrix.h:175-246 */
+int dsb200_mat4_inverse(const float *M, float *out);
+void dsb200_mat4_multiply(const float *A, const float *B, float *out);
+
+/* counters for bench.py: kernels launched by this library since process start */
+unsigned long long dsb200_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSB200_H */

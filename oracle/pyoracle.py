@@ -1,0 +1,280 @@
+"""oracle/pyoracle.py -- TEST INFRASTRUCTURE ONLY.
+
+ctypes wrappers for the two CPU checkers:
+  * Oracle    -> oracle/librestate.so   (our CPU restatement, oracle/restate.cpp)
+  * RefEngine -> oracle/_ref/libitmref.so (the unmodified reference CPU engines, oracle/ref_shim.cpp)
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes as C
+import importlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+abi = importlib.import_module("denseslam-global-consistency-h_b200.abi")
+
+RESTATE_PATH = os.path.join(HERE, "librestate.so")
+REF_PATH = os.path.join(HERE, "_ref", "libitmref.so")
+REF_FAST_PATH = os.path.join(HERE, "_ref", "libitmref_fast.so")
+
+
+def build(force=False):
+    """Compile librestate.so (always possible) and oracle/_ref (only where /root/reference exists)."""
+    if force or not os.path.exists(RESTATE_PATH) or \
+            os.path.getmtime(RESTATE_PATH) < os.path.getmtime(os.path.join(HERE, "restate.cpp")):
+        subprocess.check_call(["make", "-C", HERE, "librestate.so"])
+    subprocess.check_call(["make", "-C", HERE, "ref"])
+
+
+def ptr(a):
+    return a.ctypes.data_as(C.c_void_p).value
+
+
+class HostScene(object):
+    """Host-memory twin of ITMScene (numpy buffers behind a dsb200_scene struct)."""
+
+    def __init__(self, params, num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS,
+                 excess_size=abi.DEFAULT_EXCESS, use_swapping=False):
+        self.voxels = np.zeros(num_blocks * abi.BLOCK_SIZE3, dtype=abi.VOXEL_DTYPE)
+        self.hash = np.zeros(bucket_num + excess_size, dtype=abi.HASH_DTYPE)
+        self.alloc_list = np.zeros(num_blocks, dtype=np.int32)
+        self.excess_list = np.zeros(excess_size, dtype=np.int32)
+        self.c = abi.Scene(ptr(self.voxels), ptr(self.hash), ptr(self.alloc_list), ptr(self.excess_list),
+                           num_blocks, bucket_num, excess_size, num_blocks - 1, excess_size - 1, params,
+                           1 if use_swapping else 0)
+
+
+class HostRenderState(object):
+    def __init__(self, total_entries, width, height, visible_capacity=abi.DEFAULT_LOCAL_BLOCKS):
+        self.visible_ids = np.zeros(visible_capacity, dtype=np.int32)
+        self.visible_type = np.zeros(total_entries, dtype=np.uint8)
+        self.range_image = np.zeros((height, width, 2), dtype=np.float32)
+        self.raycast_result = np.zeros((height, width, 4), dtype=np.float32)
+        self.raycast_image = np.zeros((height, width, 4), dtype=np.uint8)
+        self.c = abi.RenderState(ptr(self.visible_ids), ptr(self.visible_type), visible_capacity, 0,
+                                 ptr(self.range_image), ptr(self.raycast_result), ptr(self.raycast_image),
+                                 width, height)
+
+    def visible(self):
+        return self.visible_ids[:self.c.no_visible].copy()
+
+
+def make_view(depth, rgb, intr_d, intr_rgb=None, rgb_to_depth_inv=None, timestamp=0.0, depth_ptr=None, rgb_ptr=None):
+    """dsb200_view over host arrays (or explicit device pointers)."""
+    h, w = depth.shape[:2] if depth is not None else (0, 0)
+    v = abi.View()
+    v.depth = depth_ptr if depth_ptr is not None else ptr(depth)
+    v.rgb = rgb_ptr if rgb_ptr is not None else ptr(rgb)
+    v.depth_w, v.depth_h, v.rgb_w, v.rgb_h = w, h, w, h
+    v.intr_d = abi.f4(intr_d)
+    v.intr_rgb = abi.f4(intr_rgb if intr_rgb is not None else intr_d)
+    v.rgb_to_depth_inv = abi.f16(rgb_to_depth_inv if rgb_to_depth_inv is not None else abi.IDENTITY16)
+    v.timestamp = timestamp
+    return v
+
+
+class Oracle(object):
+    """librestate.so: serial CPU restatement; all pointers are host pointers."""
+
+    def __init__(self):
+        if not os.path.exists(RESTATE_PATH):
+            build()
+        L = C.CDLL(RESTATE_PATH)
+        vp, P = C.c_void_p, C.POINTER
+        L.rst_recon_create.restype = vp
+        L.rst_recon_create.argtypes = [C.c_int] * 3
+        L.rst_recon_destroy.argtypes = [vp]
+        L.rst_set_fusion_weight_params.argtypes = [vp, P(abi.WeightParams)]
+        L.rst_decayed_block_count.restype = C.c_size_t
+        L.rst_decayed_block_count.argtypes = [vp]
+        L.rst_history_sizes.argtypes = [vp] + [P(C.c_int)] * 5
+        L.rst_reset_scene.argtypes = [vp, P(abi.Scene)]
+        L.rst_allocate_from_depth.restype = C.c_int
+        L.rst_allocate_from_depth.argtypes = [vp, P(abi.Scene), P(abi.View), P(abi.Tracking), P(abi.RenderState), C.c_int, C.c_int]
+        L.rst_integrate.argtypes = [vp, P(abi.Scene), P(abi.View), P(abi.Tracking), P(abi.RenderState)]
+        L.rst_deintegrate.argtypes = [vp, P(abi.Scene), P(abi.View), P(abi.Tracking)]
+        L.rst_decay.argtypes = [vp, P(abi.Scene), P(abi.RenderState), C.c_int, C.c_int, C.c_int]
+        L.rst_decay_defusion.argtypes = [vp, P(abi.Scene), P(abi.RenderState), C.c_int, C.c_int, C.c_int]
+        L.rst_slide_window.argtypes = [vp, P(abi.Scene), P(abi.RenderState), C.c_int]
+        L.rst_slide_window_defusion.argtypes = [vp, P(abi.Scene), P(abi.RenderState), C.c_int, C.c_int]
+        fp = P(C.c_float)
+        L.rst_find_visible_blocks.argtypes = [P(abi.Scene), fp, fp, P(abi.RenderState)]
+        L.rst_count_visible_blocks.restype = C.c_int
+        L.rst_count_visible_blocks.argtypes = [P(abi.Scene), P(abi.RenderState), C.c_int, C.c_int]
+        L.rst_create_expected_depths.argtypes = [P(abi.Scene), fp, fp, P(abi.RenderState)]
+        L.rst_find_surface.argtypes = [P(abi.Scene), fp, fp, P(abi.RenderState)]
+        L.rst_create_icp_maps.argtypes = [P(abi.Scene), P(abi.View), P(abi.Tracking), P(abi.RenderState)]
+        L.rst_render_image.argtypes = [P(abi.Scene), fp, fp, fp, P(abi.RenderState), vp, vp, C.c_int]
+        L.rst_forward_render.argtypes = [P(abi.Scene), P(abi.View), P(abi.Tracking), P(abi.RenderState), vp, vp, P(C.c_int)]
+        L.rst_mat4_inverse.restype = C.c_int
+        L.rst_mat4_inverse.argtypes = [fp, fp]
+        L.rst_mat4_multiply.argtypes = [fp, fp, fp]
+        self.L = L
+
+    def mat4_inverse(self, M):
+        out = (C.c_float * 16)()
+        ok = self.L.rst_mat4_inverse(abi.f16(M), out)
+        assert ok
+        return np.array(out[:], dtype=np.float32)
+
+    def mat4_multiply(self, A, B):
+        out = (C.c_float * 16)()
+        self.L.rst_mat4_multiply(abi.f16(A), abi.f16(B), out)
+        return np.array(out[:], dtype=np.float32)
+
+
+def make_tracking(M, invM, icp_points=None, icp_normals=None, requires_full_rendering=True,
+                  points_ptr=None, normals_ptr=None):
+    t = abi.Tracking()
+    t.M_d = abi.f16(M)
+    t.invM_d = abi.f16(invM)
+    t.requires_full_rendering = 1 if requires_full_rendering else 0
+    t.icp_points = points_ptr if points_ptr is not None else (ptr(icp_points) if icp_points is not None else None)
+    t.icp_normals = normals_ptr if normals_ptr is not None else (ptr(icp_normals) if icp_normals is not None else None)
+    return t
+
+
+class RefEngine(object):
+    """oracle/_ref/libitmref.so: the unmodified reference CPU engines at the reference's fixed capacities."""
+
+    def __init__(self, W, H, params, use_swapping=False, fast=False):
+        path = REF_FAST_PATH if fast else REF_PATH
+        if not os.path.exists(path):
+            raise RuntimeError("reference build %s absent (built only where /root/reference exists)" % path)
+        L = C.CDLL(path)
+        vp = C.c_void_p
+        L.itmref_create.restype = vp
+        L.itmref_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int]
+        for name in ("itmref_hash_table", "itmref_vba", "itmref_alloc_list", "itmref_excess_list", "itmref_visible_type",
+                     "itmref_icp_points", "itmref_icp_normals", "itmref_icp_rendering", "itmref_out_image"):
+            getattr(L, name).restype = vp
+            getattr(L, name).argtypes = [vp]
+        for name in ("itmref_visible_ids", "itmref_range_image", "itmref_raycast_result"):
+            getattr(L, name).restype = vp
+            getattr(L, name).argtypes = [vp, C.c_int]
+        L.itmref_no_visible.argtypes = [vp, C.c_int]
+        for name in ("itmref_destroy", "itmref_reset", "itmref_integrate", "itmref_create_expected_depths",
+                     "itmref_create_icp_maps", "itmref_find_surface", "itmref_last_free_block", "itmref_last_free_excess"):
+            getattr(L, name).argtypes = [vp]
+        L.itmref_set_calib.argtypes = [vp, vp, vp, vp]
+        L.itmref_set_view.argtypes = [vp, vp, vp, C.c_double]
+        L.itmref_set_pose.argtypes = [vp, vp]
+        L.itmref_get_pose.argtypes = [vp, vp, vp]
+        L.itmref_allocate.argtypes = [vp, C.c_int]
+        L.itmref_render_free_view.argtypes = [vp, vp, vp, C.c_int]
+        L.itmref_count_visible_blocks.argtypes = [vp, C.c_int, C.c_int]
+        L.itmref_mat4_inv.argtypes = [vp, vp]
+        L.itmref_mat4_mul.argtypes = [vp, vp, vp]
+        self.L, self.W, self.H = L, W, H
+        self.h = L.itmref_create(W, H, params.voxel_size, params.mu, params.max_w, params.vf_min, params.vf_max,
+                                 params.stop_integrating_at_max_w, 1 if use_swapping else 0)
+        self.total = L.itmref_no_total_entries()
+        self.num_blocks = L.itmref_local_block_num()
+        self.excess = L.itmref_excess_list_size()
+
+    def close(self):
+        if self.h:
+            self.L.itmref_destroy(self.h)
+            self.h = None
+
+    def _arr(self, p, dtype, count):
+        buf = (C.c_char * (np.dtype(dtype).itemsize * count)).from_address(p)
+        return np.frombuffer(buf, dtype=dtype, count=count)
+
+    def set_calib(self, intr_d, intr_rgb=None, rgb2depth=None):
+        a = np.asarray(intr_d, np.float32)
+        b = np.asarray(intr_rgb if intr_rgb is not None else intr_d, np.float32)
+        m = np.asarray(rgb2depth if rgb2depth is not None else abi.IDENTITY16, np.float32)
+        self.L.itmref_set_calib(self.h, ptr(a), ptr(b), ptr(m))
+
+    def set_view(self, depth, rgb, timestamp=0.0):
+        d = np.ascontiguousarray(depth, np.float32)
+        r = np.ascontiguousarray(rgb, np.uint8)
+        self.L.itmref_set_view(self.h, ptr(d), ptr(r), timestamp)
+
+    def set_pose(self, M):
+        m = np.ascontiguousarray(M, np.float32)
+        self.L.itmref_set_pose(self.h, ptr(m))
+
+    def get_pose(self):
+        M = np.zeros(16, np.float32)
+        iM = np.zeros(16, np.float32)
+        self.L.itmref_get_pose(self.h, ptr(M), ptr(iM))
+        return M, iM
+
+    def mat4_inv(self, M):
+        m = np.ascontiguousarray(M, np.float32)
+        o = np.zeros(16, np.float32)
+        self.L.itmref_mat4_inv(ptr(m), ptr(o))
+        return o
+
+    def mat4_mul(self, A, B):
+        a = np.ascontiguousarray(A, np.float32)
+        b = np.ascontiguousarray(B, np.float32)
+        o = np.zeros(16, np.float32)
+        self.L.itmref_mat4_mul(ptr(a), ptr(b), ptr(o))
+        return o
+
+    def allocate(self, only_visible=False):
+        self.L.itmref_allocate(self.h, 1 if only_visible else 0)
+
+    def integrate(self):
+        self.L.itmref_integrate(self.h)
+
+    def create_expected_depths(self):
+        self.L.itmref_create_expected_depths(self.h)
+
+    def create_icp_maps(self):
+        self.L.itmref_create_icp_maps(self.h)
+
+    def render_free_view(self, M, intr, render_type=0):
+        m = np.ascontiguousarray(M, np.float32)
+        i = np.ascontiguousarray(intr, np.float32)
+        self.L.itmref_render_free_view(self.h, ptr(m), ptr(i), render_type)
+
+    # state views (no copies)
+    def hash(self):
+        return self._arr(self.L.itmref_hash_table(self.h), abi.HASH_DTYPE, self.total)
+
+    def voxels(self):
+        return self._arr(self.L.itmref_vba(self.h), abi.VOXEL_DTYPE, self.num_blocks * abi.BLOCK_SIZE3)
+
+    def alloc_list(self):
+        return self._arr(self.L.itmref_alloc_list(self.h), np.int32, self.num_blocks)
+
+    def excess_list(self):
+        return self._arr(self.L.itmref_excess_list(self.h), np.int32, self.excess)
+
+    def last_free(self):
+        return self.L.itmref_last_free_block(self.h), self.L.itmref_last_free_excess(self.h)
+
+    def visible(self, free_view=False):
+        n = self.L.itmref_no_visible(self.h, int(free_view))
+        return self._arr(self.L.itmref_visible_ids(self.h, int(free_view)), np.int32, max(n, 1))[:n].copy()
+
+    def visible_type(self):
+        return self._arr(self.L.itmref_visible_type(self.h), np.uint8, self.total)
+
+    def range_image(self, free_view=False):
+        return self._arr(self.L.itmref_range_image(self.h, int(free_view)), np.float32, self.W * self.H * 2).reshape(self.H, self.W, 2)
+
+    def raycast_result(self, free_view=False):
+        return self._arr(self.L.itmref_raycast_result(self.h, int(free_view)), np.float32, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+    def icp_points(self):
+        return self._arr(self.L.itmref_icp_points(self.h), np.float32, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+    def icp_normals(self):
+        return self._arr(self.L.itmref_icp_normals(self.h), np.float32, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+    def icp_rendering(self):
+        return self._arr(self.L.itmref_icp_rendering(self.h), np.uint8, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+    def out_image(self):
+        return self._arr(self.L.itmref_out_image(self.h), np.uint8, self.W * self.H * 4).reshape(self.H, self.W, 4)

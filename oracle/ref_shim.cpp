@@ -1,0 +1,163 @@
+// oracle/ref_shim.cpp -- TEST INFRASTRUCTURE ONLY (never linked into the product).
+//
+// A thin C ABI around the UNMODIFIED reference CPU engines, compiled in place from
+// /root/reference by oracle/Makefile into oracle/_ref/libitmref.so.  It exists so the
+// tests can (1) pin oracle/restate.cpp against the real reference and (2) generate
+// the golden fixtures under tests/golden/.  No reference source is copied: this file
+// only #includes the reference headers and forwards calls.
+//
+// Reference classes driven here:
+//   ITMSceneReconstructionEngine_CPU<ITMVoxel,ITMVoxelBlockHash>
+//       ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.cpp:25-342
+//   ITMVisualisationEngine_CPU<ITMVoxel,ITMVoxelBlockHash>
+//       ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.cpp:27-180,296-459
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.h"
+#include "ITMLib/Objects/ITMRenderState_VH.h"
+
+#include <cstring>
+#include <cstdint>
+
+using namespace ITMLib::Engine;
+using namespace ITMLib::Objects;
+
+namespace {
+struct RefCtx {
+    ITMSceneParams params;
+    ITMScene<ITMVoxel, ITMVoxelBlockHash> *scene;
+    ITMSceneReconstructionEngine_CPU<ITMVoxel, ITMVoxelBlockHash> *recon;
+    ITMVisualisationEngine_CPU<ITMVoxel, ITMVoxelBlockHash> *vis;
+    ITMRGBDCalib calib;
+    ITMView *view;
+    ITMTrackingState *tracking;
+    ITMRenderState_VH *rs;       // tracking-path render state (visible list from Allocate)
+    ITMRenderState_VH *rsFree;   // free-view render state (FindVisibleBlocks)
+    ITMUChar4Image *outImg;
+    ITMFloatImage *outFloat;
+    Vector2i imgSize;
+};
+Matrix4f toM(const float *m) { Matrix4f M; for (int i = 0; i < 16; i++) M.m[i] = m[i]; return M; }
+}
+
+extern "C" {
+
+int itmref_sizeof_voxel() { return (int)sizeof(ITMVoxel); }
+int itmref_sizeof_hash_entry() { return (int)sizeof(ITMHashEntry); }
+int itmref_no_total_entries() { return ITMVoxelBlockHash::noTotalEntries; }
+int itmref_local_block_num() { return SDF_LOCAL_BLOCK_NUM; }
+int itmref_bucket_num() { return SDF_BUCKET_NUM; }
+int itmref_excess_list_size() { return SDF_EXCESS_LIST_SIZE; }
+
+void *itmref_create(int W, int H, float voxelSize, float mu, int maxW, float vfMin, float vfMax,
+                    int stopAtMaxW, int useSwapping)
+{
+    RefCtx *c = new RefCtx{ITMSceneParams(mu, maxW, voxelSize, vfMin, vfMax, stopAtMaxW != 0)};
+    c->imgSize = Vector2i(W, H);
+    c->scene = new ITMScene<ITMVoxel, ITMVoxelBlockHash>(&c->params, useSwapping != 0, MEMORYDEVICE_CPU);
+    c->recon = new ITMSceneReconstructionEngine_CPU<ITMVoxel, ITMVoxelBlockHash>();
+    c->vis = new ITMVisualisationEngine_CPU<ITMVoxel, ITMVoxelBlockHash>();
+    c->view = new ITMView(&c->calib, c->imgSize, c->imgSize, false);
+    c->tracking = new ITMTrackingState(c->imgSize, MEMORYDEVICE_CPU);
+    c->rs = c->vis->CreateRenderState(c->scene, c->imgSize);
+    c->rsFree = c->vis->CreateRenderState(c->scene, c->imgSize);
+    c->outImg = new ITMUChar4Image(c->imgSize, true, false);
+    c->outFloat = new ITMFloatImage(c->imgSize, true, false);
+    c->recon->ResetScene(c->scene);
+    return c;
+}
+
+void itmref_destroy(void *h)
+{
+    RefCtx *c = (RefCtx *)h;
+    delete c->outFloat; delete c->outImg; delete c->rsFree; delete c->rs; delete c->tracking;
+    delete c->view; delete c->vis; delete c->recon; delete c->scene; delete c;
+}
+
+void itmref_reset(void *h) { RefCtx *c = (RefCtx *)h; c->recon->ResetScene(c->scene); c->rs->noVisibleEntries = 0; }
+
+// intr = (fx, fy, cx, cy); rgb2depth = column-major 4x4 (trafo_rgb_to_depth.calib)
+void itmref_set_calib(void *h, const float *intrD, const float *intrRGB, const float *rgb2depth)
+{
+    RefCtx *c = (RefCtx *)h;
+    c->view->calib->intrinsics_d.SetFrom(intrD[0], intrD[1], intrD[2], intrD[3], c->imgSize.x, c->imgSize.y);
+    c->view->calib->intrinsics_rgb.SetFrom(intrRGB[0], intrRGB[1], intrRGB[2], intrRGB[3], c->imgSize.x, c->imgSize.y);
+    c->view->calib->trafo_rgb_to_depth.SetFrom(toM(rgb2depth));
+}
+
+void itmref_set_view(void *h, const float *depth, const uint8_t *rgba, double timestamp)
+{
+    RefCtx *c = (RefCtx *)h;
+    size_t n = (size_t)c->imgSize.x * c->imgSize.y;
+    memcpy(c->view->depth->GetData(MEMORYDEVICE_CPU), depth, n * sizeof(float));
+    memcpy(c->view->rgb->GetData(MEMORYDEVICE_CPU), rgba, n * 4);
+    c->view->mTimeStamp = timestamp;
+}
+
+void itmref_set_pose(void *h, const float *M) { ((RefCtx *)h)->tracking->pose_d->SetM(toM(M)); }
+void itmref_get_pose(void *h, float *M, float *invM)
+{
+    RefCtx *c = (RefCtx *)h;
+    Matrix4f m = c->tracking->pose_d->GetM(), im = c->tracking->pose_d->GetInvM();
+    memcpy(M, m.m, 64); memcpy(invM, im.m, 64);
+}
+int itmref_mat4_inv(const float *M, float *out) { Matrix4f o; bool ok = toM(M).inv(o); memcpy(out, o.m, 64); return ok; }
+void itmref_mat4_mul(const float *A, const float *B, float *out) { Matrix4f o = toM(A) * toM(B); memcpy(out, o.m, 64); }
+
+void itmref_allocate(void *h, int onlyUpdateVisibleList)
+{
+    RefCtx *c = (RefCtx *)h;
+    c->recon->AllocateSceneFromDepth(c->scene, c->view, c->tracking, c->rs, onlyUpdateVisibleList != 0, false);
+}
+void itmref_integrate(void *h) { RefCtx *c = (RefCtx *)h; c->recon->IntegrateIntoScene(c->scene, c->view, c->tracking, c->rs); }
+void itmref_create_expected_depths(void *h)
+{
+    RefCtx *c = (RefCtx *)h;
+    c->vis->CreateExpectedDepths(c->scene, c->tracking->pose_d, &c->view->calib->intrinsics_d, c->rs);
+}
+void itmref_create_icp_maps(void *h) { RefCtx *c = (RefCtx *)h; c->vis->CreateICPMaps(c->scene, c->view, c->tracking, c->rs); }
+void itmref_find_surface(void *h)
+{
+    RefCtx *c = (RefCtx *)h;
+    c->vis->FindSurface(c->scene, c->tracking->pose_d, &c->view->calib->intrinsics_d, c->rs);
+}
+
+// free-view path: ITMMainEngine::GetImage (ITMLib/Engine/ITMMainEngine.cpp:272-277)
+void itmref_render_free_view(void *h, const float *M, const float *intr, int renderType)
+{
+    RefCtx *c = (RefCtx *)h;
+    ITMPose pose; pose.SetM(toM(M));
+    ITMIntrinsics in; in.SetFrom(intr[0], intr[1], intr[2], intr[3], c->imgSize.x, c->imgSize.y);
+    c->vis->FindVisibleBlocks(c->scene, &pose, &in, c->rsFree);
+    c->vis->CreateExpectedDepths(c->scene, &pose, &in, c->rsFree);
+    c->vis->RenderImage(c->scene, &pose, &in, c->rsFree, c->outImg, c->outFloat,
+                        (IITMVisualisationEngine::RenderImageType)renderType);
+}
+int itmref_count_visible_blocks(void *h, int minId, int maxId)
+{
+    RefCtx *c = (RefCtx *)h; return c->vis->CountVisibleBlocks(c->scene, c->rs, minId, maxId);
+}
+
+// ---- state accessors (pointers into the reference's own buffers) ----
+void *itmref_hash_table(void *h) { return ((RefCtx *)h)->scene->index.GetEntries(); }
+void *itmref_vba(void *h) { return ((RefCtx *)h)->scene->localVBA.GetVoxelBlocks(); }
+int *itmref_alloc_list(void *h) { return ((RefCtx *)h)->scene->localVBA.GetAllocationList(); }
+int *itmref_excess_list(void *h) { return ((RefCtx *)h)->scene->index.GetExcessAllocationList(); }
+int itmref_last_free_block(void *h) { return ((RefCtx *)h)->scene->localVBA.lastFreeBlockId; }
+int itmref_last_free_excess(void *h) { return ((RefCtx *)h)->scene->index.GetLastFreeExcessListId(); }
+int itmref_no_visible(void *h, int freeView) { RefCtx *c = (RefCtx *)h; return (freeView ? c->rsFree : c->rs)->noVisibleEntries; }
+int *itmref_visible_ids(void *h, int freeView) { RefCtx *c = (RefCtx *)h; return (freeView ? c->rsFree : c->rs)->GetVisibleEntryIDs(); }
+uint8_t *itmref_visible_type(void *h) { return ((RefCtx *)h)->rs->GetEntriesVisibleType(); }
+float *itmref_range_image(void *h, int freeView)
+{
+    RefCtx *c = (RefCtx *)h; return (float *)(freeView ? c->rsFree : c->rs)->renderingRangeImage->GetData(MEMORYDEVICE_CPU);
+}
+float *itmref_raycast_result(void *h, int freeView)
+{
+    RefCtx *c = (RefCtx *)h; return (float *)(freeView ? c->rsFree : c->rs)->raycastResult->GetData(MEMORYDEVICE_CPU);
+}
+float *itmref_icp_points(void *h) { return (float *)((RefCtx *)h)->tracking->pointCloud->locations->GetData(MEMORYDEVICE_CPU); }
+float *itmref_icp_normals(void *h) { return (float *)((RefCtx *)h)->tracking->pointCloud->colours->GetData(MEMORYDEVICE_CPU); }
+uint8_t *itmref_icp_rendering(void *h) { return (uint8_t *)((RefCtx *)h)->rs->raycastImage->GetData(MEMORYDEVICE_CPU); }
+uint8_t *itmref_out_image(void *h) { return (uint8_t *)((RefCtx *)h)->outImg->GetData(MEMORYDEVICE_CPU); }
+
+} // extern "C"

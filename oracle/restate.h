@@ -1,0 +1,70 @@
+/* oracle/restate.h -- TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement ("oracle") of the reference's volumetric-fusion hot path.  Same POD
+ * structs as include/dsb200.h, but every pointer is a HOST pointer and every function is a
+ * serial loop.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this; the product (libdsb200.so) never does.
+ *
+ * Pinning: oracle/_ref/libitmref.so (the unmodified reference CPU engines) is compared
+ * bit-for-bit with this file by tests/test_oracle_vs_ref.py, and the committed fixtures under
+ * tests/golden/ were generated from the reference.  Decay / slide-window / de-integration have
+ * NO CPU implementation in the reference (CPU/ITMSceneReconstructionEngine_CPU.cpp:345-396
+ * throw) and no reference test: for those functions parity is UNPINNED by reference outputs;
+ * they restate CUDA/ITMSceneReconstructionEngine_CUDA.cu:426-1082 under the deterministic
+ * schedule described in DESIGN.md.
+ */
+#ifndef RESTATE_H
+#define RESTATE_H
+#include "../include/dsb200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rst_recon rst_recon;
+
+rst_recon *rst_recon_create(int num_blocks, int bucket_num, int excess_size);
+void rst_recon_destroy(rst_recon *e);
+void rst_set_fusion_weight_params(rst_recon *e, const dsb200_weight_params *p);
+size_t rst_decayed_block_count(const rst_recon *e);
+void rst_history_sizes(const rst_recon *e, int *decay_q, int *slide_q, int *decay_defusion_q,
+                       int *slide_defusion_q, int *snapshots);
+
+void rst_reset_scene(rst_recon *e, dsb200_scene *scene);
+int rst_allocate_from_depth(rst_recon *e, dsb200_scene *scene, const dsb200_view *view,
+                            const dsb200_tracking *tracking, dsb200_render_state *rs,
+                            int only_update_visible_list, int is_defusion);
+void rst_integrate(rst_recon *e, dsb200_scene *scene, const dsb200_view *view,
+                   const dsb200_tracking *tracking, const dsb200_render_state *rs);
+void rst_deintegrate(rst_recon *e, dsb200_scene *scene, const dsb200_view *view,
+                     const dsb200_tracking *tracking);
+void rst_decay(rst_recon *e, dsb200_scene *scene, dsb200_render_state *rs, int max_weight, int min_age,
+               int force_all_voxels);
+void rst_decay_defusion(rst_recon *e, dsb200_scene *scene, dsb200_render_state *rs, int max_weight,
+                        int min_age, int force_all_voxels);
+void rst_slide_window(rst_recon *e, dsb200_scene *scene, dsb200_render_state *rs, int max_age);
+void rst_slide_window_defusion(rst_recon *e, dsb200_scene *scene, dsb200_render_state *rs, int max_age,
+                               int max_size);
+
+void rst_find_visible_blocks(const dsb200_scene *scene, const float *M, const float *intr,
+                             dsb200_render_state *rs);
+int rst_count_visible_blocks(const dsb200_scene *scene, const dsb200_render_state *rs, int min_id, int max_id);
+void rst_create_expected_depths(const dsb200_scene *scene, const float *M, const float *intr,
+                                dsb200_render_state *rs);
+void rst_find_surface(const dsb200_scene *scene, const float *invM, const float *intr,
+                      dsb200_render_state *rs);
+void rst_create_icp_maps(const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *tracking,
+                         dsb200_render_state *rs);
+void rst_render_image(const dsb200_scene *scene, const float *M, const float *invM, const float *intr,
+                      dsb200_render_state *rs, uint8_t *out_rgba, float *out_depth, int render_type);
+void rst_forward_render(const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *tracking,
+                        dsb200_render_state *rs, float *forward_projection, int *missing_points,
+                        int *no_missing);
+
+int rst_mat4_inverse(const float *M, float *out);
+void rst_mat4_multiply(const float *A, const float *B, float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
