@@ -1,0 +1,666 @@
+// capi.cu -- the C ABI of include/dsb200.h: engine objects, history queues, host logic.
+//
+// Host-side control flow follows the reference's CUDA engines
+// (CUDA/ITMSceneReconstructionEngine_CUDA.cu:152-359, 363-489, 850-1082 and
+// CUDA/ITMVisualisationEngine_CUDA.cu:150-251, 351-484) with these structural changes:
+//  * counts (visible blocks, free-list tops) live on the device between stages; the host reads
+//    them once per call (or once per fused frame), not after every kernel;
+//  * the per-frame visible-list snapshots used by decay / slide-window / de-fusion live in a
+//    recycled device arena (no cudaMalloc per frame, no 4x over-allocation, no dangling aliases:
+//    SURVEY.md Appendix B Q2);
+//  * errors are returned as codes (+ dsb200_last_error) instead of exit(-1)/throw.
+#include "kernels.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace dsb {
+unsigned long long g_launches = 0;
+}
+using namespace dsb;
+
+static thread_local std::string g_error;
+
+static int fail(int code, const std::string &msg) { g_error = msg; return code; }
+static int cuda_fail(cudaError_t e, const char *what)
+{
+    return fail(e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? DSB200_ERR_NO_DEVICE : DSB200_ERR_CUDA,
+                std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                                     \
+    do {                                                             \
+        cudaError_t e_ = (call);                                     \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call);          \
+    } while (0)
+
+// ---------------------------------------------------------------- snapshot arena
+namespace {
+
+struct Chunk {
+    int *base = nullptr;
+    size_t capacity = 0, used = 0;   // in ints
+};
+
+struct Arena {
+    std::vector<Chunk *> freeChunks;
+    std::shared_ptr<Chunk> current;
+    size_t chunkInts = (size_t)8 << 20;   // 32 MiB
+
+    std::shared_ptr<Chunk> acquire(size_t minInts)
+    {
+        Chunk *c = nullptr;
+        for (size_t i = 0; i < freeChunks.size(); i++)
+            if (freeChunks[i]->capacity >= minInts) { c = freeChunks[i]; freeChunks.erase(freeChunks.begin() + i); break; }
+        if (!c) {
+            c = new Chunk();
+            c->capacity = minInts > chunkInts ? minInts : chunkInts;
+            if (cudaMalloc(&c->base, c->capacity * sizeof(int)) != cudaSuccess) { delete c; return nullptr; }
+        }
+        c->used = 0;
+        Arena *self = this;
+        return std::shared_ptr<Chunk>(c, [self](Chunk *p) { self->freeChunks.push_back(p); });
+    }
+    // reserve `ints` ints (64-int aligned); returns the owning chunk
+    std::shared_ptr<Chunk> reserve(size_t ints, int **out)
+    {
+        ints = (ints + 63) & ~(size_t)63;
+        if (!current || current->used + ints > current->capacity) current = acquire(ints);
+        if (!current) return nullptr;
+        *out = current->base + current->used;
+        current->used += ints;
+        return current;
+    }
+    void release_all()
+    {
+        current.reset();
+        for (Chunk *c : freeChunks) { cudaFree(c->base); delete c; }
+        freeChunks.clear();
+    }
+};
+
+struct Snapshot {
+    int *region = nullptr;     // arena reservation: [0] = device count, ids start at +64
+    size_t regionInts = 0;
+    int *ids = nullptr;        // device, in the arena
+    int *countDev = nullptr;   // device count (valid as soon as k_visible_list has run)
+    int countHost = -1;        // -1 until the host has synchronised
+    size_t frameIdx = 0;
+    std::shared_ptr<Chunk> chunk;
+};
+typedef std::shared_ptr<Snapshot> SnapPtr;
+
+void fill_mat(Mat4 &dst, const float *src) { memcpy(dst.m, src, 64); }
+
+} // namespace
+
+struct dsb200_recon {
+    cudaStream_t stream = nullptr;
+    int numBlocks = 0, bucketNum = 0, excessSize = 0, total = 0;
+    unsigned *reqKey = nullptr;       // order keys of allocation requests (entriesAllocType + blockCoords equivalent)
+    unsigned *slotMark = nullptr;     // pruning: per-slot rank marks, then per-bucket leaders
+    int *pruneScratch = nullptr; int pruneCap = 0;
+    FrameState fs{};
+    Counters *hostCounters = nullptr; // pinned
+    dsb200_weight_params weights{0, 10, 100};
+    bool async = false, deviceCountersValid = false;
+    // history (CUDA/ITMSceneReconstructionEngine_CUDA.h:41-48)
+    std::deque<SnapPtr> decayQ, slideQ, decayDefusionQ, slideDefusionQ;
+    std::map<double, SnapPtr> snapshots;   // mDefusionBlockDataBase
+    std::vector<SnapPtr> unsynced;         // snapshots whose host count is not known yet (async mode)
+    size_t frameIdx = 0;
+    long long totalDecayed = 0;
+    int lastFreeBeforePrune = 0; bool prunePending = false;
+    Arena arena;
+};
+
+struct dsb200_vis {
+    cudaStream_t stream = nullptr;
+    FrameState fs{};
+    int scanTilesAlloc = 0;
+    Counters *hostCounters = nullptr;
+    int *countScratch = nullptr;      // [0] visible count for stand-alone calls, [1] CountVisibleBlocks result
+    int *hostInts = nullptr;          // pinned [4]
+    float *fwdProjection = nullptr; int *fwdMissing = nullptr; int fwdPixels = 0;
+};
+
+extern "C" {
+
+const char *dsb200_last_error(void) { return g_error.c_str(); }
+
+int dsb200_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+unsigned long long dsb200_kernel_launch_count(void) { return g_launches; }
+
+// ---------------------------------------------------------------- engine lifetime
+int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_num, int32_t excess_size, void *stream)
+{
+    if (!out || num_blocks <= 0 || bucket_num <= 0 || (bucket_num & (bucket_num - 1)) || excess_size < 0)
+        return fail(DSB200_ERR_INVALID, "recon_create: capacities must be positive and bucket_num a power of two");
+    if (dsb200_device_count() == 0) return fail(DSB200_ERR_NO_DEVICE, "no CUDA device: libdsb200 has no CPU fallback");
+    dsb200_recon *e = new dsb200_recon();
+    e->stream = (cudaStream_t)stream;
+    e->numBlocks = num_blocks; e->bucketNum = bucket_num; e->excessSize = excess_size; e->total = bucket_num + excess_size;
+    e->fs.scanTiles = div_up(e->total, 1024);
+    const int pruneTiles = div_up(num_blocks, 1024);
+    size_t keyInts = (size_t)e->fs.scanTiles * 1024;
+    CU(cudaMalloc(&e->reqKey, keyInts * 4));
+    CU(cudaMemset(e->reqKey, 0, keyInts * 4));
+    CU(cudaMalloc(&e->slotMark, (keyInts + bucket_num) * 4));
+    CU(cudaMemset(e->slotMark, 0, (keyInts + bucket_num) * 4));
+    CU(cudaMalloc(&e->fs.counters, sizeof(Counters)));
+    CU(cudaMemset(e->fs.counters, 0, sizeof(Counters)));
+    CU(cudaMalloc(&e->fs.scanState, (size_t)(2 * e->fs.scanTiles + pruneTiles + 8) * 8));
+    CU(cudaMemset(e->fs.scanState, 0, (size_t)(2 * e->fs.scanTiles + pruneTiles + 8) * 8));
+    CU(cudaMalloc(&e->fs.tickets, 4 * sizeof(int)));
+    CU(cudaMemset(e->fs.tickets, 0, 4 * sizeof(int)));
+    CU(cudaMallocHost(&e->hostCounters, sizeof(Counters)));
+    memset(e->hostCounters, 0, sizeof(Counters));
+    e->pruneCap = num_blocks;
+    CU(cudaMalloc(&e->pruneScratch, (size_t)3 * e->pruneCap * 4));
+    *out = e;
+    return DSB200_OK;
+}
+
+int dsb200_recon_destroy(dsb200_recon *e)
+{
+    if (!e) return DSB200_OK;
+    cudaStreamSynchronize(e->stream);
+    e->decayQ.clear(); e->slideQ.clear(); e->decayDefusionQ.clear(); e->slideDefusionQ.clear();
+    e->snapshots.clear(); e->unsynced.clear();
+    e->arena.release_all();
+    cudaFree(e->reqKey); cudaFree(e->slotMark); cudaFree(e->pruneScratch); cudaFree(e->fs.counters);
+    cudaFree(e->fs.scanState); cudaFree(e->fs.tickets); cudaFreeHost(e->hostCounters);
+    delete e;
+    return DSB200_OK;
+}
+
+int dsb200_recon_set_async(dsb200_recon *e, int async) { e->async = async != 0; return DSB200_OK; }
+
+int dsb200_set_fusion_weight_params(dsb200_recon *e, const dsb200_weight_params *p) { e->weights = *p; return DSB200_OK; }
+size_t dsb200_decayed_block_count(const dsb200_recon *e) { return (size_t)e->totalDecayed; }
+int dsb200_history_sizes(const dsb200_recon *e, int *a, int *b, int *c, int *d, int *s)
+{
+    if (a) *a = (int)e->decayQ.size();
+    if (b) *b = (int)e->slideQ.size();
+    if (c) *c = (int)e->decayDefusionQ.size();
+    if (d) *d = (int)e->slideDefusionQ.size();
+    if (s) *s = (int)e->snapshots.size();
+    return DSB200_OK;
+}
+
+} // extern "C"
+
+// Pull the device counters to the host and refresh the caller's mirrors.
+static int sync_counters(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs)
+{
+    CU(cudaMemcpyAsync(e->hostCounters, e->fs.counters, sizeof(Counters), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (scene) { scene->last_free_block = e->hostCounters->lastFreeBlock; scene->last_free_excess = e->hostCounters->lastFreeExcess; }
+    if (rs) rs->no_visible = e->hostCounters->noVisible;
+    if (e->prunePending) {
+        e->totalDecayed += e->hostCounters->lastFreeBlock - e->lastFreeBeforePrune;
+        e->prunePending = false;
+    }
+    if (!e->unsynced.empty()) {
+        // host counts of snapshots taken since the last sync
+        std::vector<int> counts(e->unsynced.size());
+        for (size_t i = 0; i < e->unsynced.size(); i++)
+            CU(cudaMemcpyAsync(&counts[i], e->unsynced[i]->countDev, 4, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        for (size_t i = 0; i < e->unsynced.size(); i++) {
+            Snapshot &s = *e->unsynced[i];
+            s.countHost = counts[i];
+            // give back the unused tail if this snapshot is still the newest reservation of its chunk
+            size_t need = 64 + (((size_t)s.countHost + 63) & ~(size_t)63);
+            if (s.chunk && s.chunk->base + s.chunk->used == s.region + s.regionInts && need < s.regionInts) {
+                s.chunk->used -= (s.regionInts - need);
+                s.regionInts = need;
+            }
+        }
+        e->unsynced.clear();
+    }
+    e->deviceCountersValid = true;
+    return DSB200_OK;
+}
+
+extern "C" int dsb200_recon_sync(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs)
+{
+    return sync_counters(e, scene, rs);
+}
+
+// ---------------------------------------------------------------- reconstruction engine
+static void make_alloc_params(AllocParams &P, const dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk)
+{
+    fill_mat(P.invM, trk->invM_d);
+    P.invProj[0] = 1.0f / view->intr_d[0]; P.invProj[1] = 1.0f / view->intr_d[1];
+    P.invProj[2] = view->intr_d[2]; P.invProj[3] = view->intr_d[3];
+    P.mu = scene->params.mu;
+    P.oneOverBlock = 1.0f / (scene->params.voxel_size * DSB200_BLOCK_SIZE);
+    P.vfMin = scene->params.vf_min; P.vfMax = scene->params.vf_max;
+    P.W = view->depth_w; P.H = view->depth_h;
+    P.bucketNum = scene->bucket_num; P.bucketMask = scene->bucket_num - 1;
+}
+
+static void make_fuse_params(FuseParams &P, const dsb200_recon *e, const dsb200_scene *scene, const dsb200_view *view,
+                             const dsb200_tracking *trk)
+{
+    fill_mat(P.M_d, trk->M_d);
+    dsb200_mat4_multiply(view->rgb_to_depth_inv, trk->M_d, P.M_rgb.m);   // calib_inv * M_d (CPU .cpp:67)
+    memcpy(P.proj_d, view->intr_d, 16); memcpy(P.proj_rgb, view->intr_rgb, 16);
+    P.voxelSize = scene->params.voxel_size; P.mu = scene->params.mu; P.maxW = scene->params.max_w;
+    P.W = view->depth_w; P.H = view->depth_h; P.Wrgb = view->rgb_w; P.Hrgb = view->rgb_h;
+    P.stopMaxW = scene->params.stop_integrating_at_max_w;
+    P.approximate = trk->requires_full_rendering ? 0 : 1;
+    P.depthWeighting = e->weights.depth_weighting; P.maxNewW = e->weights.max_new_w; P.maxDistance = e->weights.max_distance;
+}
+
+static int check_scene(const dsb200_recon *e, const dsb200_scene *scene)
+{
+    if (!e || !scene || !scene->voxels || !scene->hash || !scene->alloc_list || !scene->excess_list)
+        return fail(DSB200_ERR_INVALID, "null engine/scene pointer");
+    if (scene->num_blocks != e->numBlocks || scene->bucket_num != e->bucketNum || scene->excess_size != e->excessSize)
+        return fail(DSB200_ERR_INVALID, "scene capacities differ from the capacities the engine was created with");
+    return DSB200_OK;
+}
+
+// enqueue: setToType3 + requests + ordered allocation + ordered visible list (+ snapshot)
+static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
+                            dsb200_render_state *rs, int onlyVisible, int isDefusion)
+{
+    AllocParams AP; make_alloc_params(AP, scene, view, trk);
+    if ((long long)AP.W * AP.H >= (1ll << 24)) return fail(DSB200_ERR_INVALID, "depth image too large for the 24-bit pixel order key");
+    // noSteps = ceil(2 * |segment| / blockSize) with |segment| = 2*mu (+ rounding): must fit the 8-bit step field
+    if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
+    const bool useHost = !(e->async && e->deviceCountersValid);
+    launch_begin_frame(e->stream, e->fs, scene->last_free_block, scene->last_free_excess, rs->no_visible, useHost ? 1 : 0,
+                       rs->visible_ids, rs->visible_type, useHost ? rs->no_visible : rs->visible_capacity);
+    launch_alloc_requests(e->stream, AP, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    launch_allocate(e->stream, AP, e->fs, view->depth, scene->hash, scene->alloc_list, scene->excess_list, rs->visible_type,
+                    e->reqKey, e->total, onlyVisible ? 0 : 1);
+    // snapshot reservation for decay / slide window / de-fusion (CUDA .cu:257-317)
+    SnapPtr snap = std::make_shared<Snapshot>();
+    snap->regionInts = 64 + (((size_t)rs->visible_capacity + 63) & ~(size_t)63);
+    snap->chunk = e->arena.reserve(snap->regionInts, &snap->region);
+    if (!snap->chunk) return fail(DSB200_ERR_CUDA, "out of device memory for the visible-list snapshot arena");
+    snap->countDev = snap->region; snap->ids = snap->region + 64;
+    VisParams VP; fill_mat(VP.M, trk->M_d); memcpy(VP.proj, view->intr_d, 16);
+    VP.voxelSize = scene->params.voxel_size; VP.W = AP.W; VP.H = AP.H;
+    VP.useSwapping = (scene->use_swapping && !onlyVisible) ? 1 : 0;
+    launch_visible_list(e->stream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, rs->visible_ids,
+                        rs->visible_capacity, snap->ids, snap->countDev, e->total);
+    e->unsynced.push_back(snap);
+    if (!isDefusion) {
+        snap->frameIdx = e->frameIdx;
+        e->snapshots[view->timestamp] = snap;
+        e->decayQ.push_back(snap); e->slideQ.push_back(snap);
+        e->frameIdx++;
+    } else {
+        std::map<double, SnapPtr>::iterator it = e->snapshots.find(view->timestamp);
+        if (it != e->snapshots.end()) {
+            snap->frameIdx = it->second->frameIdx;
+            e->decayDefusionQ.push_back(snap); e->slideDefusionQ.push_back(snap);
+            e->snapshots[view->timestamp] = snap;
+        }
+    }
+    return DSB200_OK;
+}
+
+static int finish_call(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs, bool checkExhaustion)
+{
+    CU(cudaGetLastError());
+    if (e->async) return DSB200_OK;
+    int rc = sync_counters(e, scene, rs);
+    if (rc != DSB200_OK) return rc;
+    if (checkExhaustion) {
+        if (scene->last_free_block < 0)
+            return fail(DSB200_ERR_VBA_EXHAUSTED, "Invalid free voxel block ID. InfiniTAM has run out of space in the Voxel Block Array.");
+        if (scene->last_free_excess < 0)
+            return fail(DSB200_ERR_EXCESS_EXHAUSTED, "Invalid free excess list slot ID. InfiniTAM has run out of slots in the hash table excess list. "
+                                                     "Consider increasing the size of the excess list or the number of buckets.");
+    }
+    return DSB200_OK;
+}
+
+extern "C" {
+
+int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
+{
+    int rc = check_scene(e, scene); if (rc) return rc;
+    e->totalDecayed = 0;
+    e->decayQ.clear(); e->slideQ.clear(); e->snapshots.clear();   // CUDA .cu:116-131
+    launch_reset_scene(e->stream, scene->voxels, (size_t)scene->num_blocks * DSB200_BLOCK_SIZE3, scene->hash, e->total,
+                       scene->alloc_list, scene->num_blocks, scene->excess_list, scene->excess_size, nullptr, e->reqKey,
+                       e->fs.counters);
+    CU(cudaGetLastError());
+    scene->last_free_block = scene->num_blocks - 1;
+    scene->last_free_excess = scene->excess_size - 1;
+    if (!e->async) CU(cudaStreamSynchronize(e->stream));
+    return DSB200_OK;
+}
+
+int dsb200_allocate_from_depth(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
+                               dsb200_render_state *rs, int onlyVisible, int isDefusion)
+{
+    int rc = check_scene(e, scene); if (rc) return rc;
+    if (!view || !trk || !rs || !view->depth) return fail(DSB200_ERR_INVALID, "allocate: null view/tracking/render state");
+    rc = enqueue_allocate(e, scene, view, trk, rs, onlyVisible, isDefusion); if (rc) return rc;
+    return finish_call(e, scene, rs, true);
+}
+
+int dsb200_integrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
+                     const dsb200_render_state *rs)
+{
+    int rc = check_scene(e, scene); if (rc) return rc;
+    FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
+    const int *countPtr = &e->fs.counters->noVisible;
+    if (!(e->async && e->deviceCountersValid)) {
+        // host mirror is authoritative between synchronous calls
+        e->hostCounters->noVisible = rs->no_visible;
+        CU(cudaMemcpyAsync(&e->fs.counters->noVisible, &e->hostCounters->noVisible, 4, cudaMemcpyHostToDevice, e->stream));
+    }
+    launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb);
+    CU(cudaGetLastError());
+    if (!e->async) CU(cudaStreamSynchronize(e->stream));
+    return DSB200_OK;
+}
+
+int dsb200_deintegrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk)
+{
+    int rc = check_scene(e, scene); if (rc) return rc;
+    std::map<double, SnapPtr>::iterator it = e->snapshots.find(view->timestamp);
+    if (it == e->snapshots.end()) return DSB200_OK;            // silent no-op, CUDA .cu:437-440
+    if (it->second->countHost == 0) return DSB200_OK;
+    FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
+    launch_fuse(e->stream, FP, true, scene->voxels, scene->hash, it->second->ids, it->second->countDev, view->depth, view->rgb);
+    CU(cudaGetLastError());
+    if (!e->async) CU(cudaStreamSynchronize(e->stream));
+    return DSB200_OK;
+}
+
+} // extern "C"
+
+// Decay / DecayDefusionPart / SlideWindow / SlideWindowDefusionPart share the queue policy of CUDA .cu:913-1077
+static int prune_from_queue(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs, std::deque<SnapPtr> &q,
+                            long threshold, bool slide, int minAge, int maxWeight)
+{
+    int rc = check_scene(e, scene); if (rc) return rc;
+    if ((long)q.size() > threshold) {
+        SnapPtr snap = q.front(); q.pop_front();
+        if (snap->countHost != 0) {
+            if (!(e->async && e->deviceCountersValid)) {
+                e->hostCounters->lastFreeBlock = scene->last_free_block;
+                CU(cudaMemcpyAsync(&e->fs.counters->lastFreeBlock, &e->hostCounters->lastFreeBlock, 4, cudaMemcpyHostToDevice, e->stream));
+            }
+            if (!e->prunePending) { e->lastFreeBeforePrune = scene->last_free_block; e->prunePending = true; }
+            int bound = snap->countHost >= 0 ? snap->countHost : (int)(snap->regionInts - 64);
+            if (bound > e->pruneCap) return fail(DSB200_ERR_INVALID, "snapshot larger than the pruning scratch");
+            launch_prune(e->stream, slide, scene->voxels, scene->hash, scene->bucket_num, snap->ids, snap->countDev, e->pruneCap,
+                         minAge, maxWeight, (int)e->frameIdx, scene->alloc_list, rs->visible_type, e->slotMark, e->pruneScratch,
+                         e->fs.counters, e->fs);
+        }
+    }
+    return finish_call(e, scene, rs, false);
+}
+
+extern "C" {
+
+int dsb200_decay(dsb200_recon *e, dsb200_scene *s, dsb200_render_state *rs, int maxWeight, int minAge, int)
+{ return prune_from_queue(e, s, rs, e->decayQ, minAge, false, minAge, maxWeight); }
+int dsb200_decay_defusion(dsb200_recon *e, dsb200_scene *s, dsb200_render_state *rs, int maxWeight, int minAge, int)
+{ return prune_from_queue(e, s, rs, e->decayDefusionQ, 0, false, minAge, maxWeight); }
+int dsb200_slide_window(dsb200_recon *e, dsb200_scene *s, dsb200_render_state *rs, int maxAge)
+{ return prune_from_queue(e, s, rs, e->slideQ, maxAge, true, 0, 0); }
+int dsb200_slide_window_defusion(dsb200_recon *e, dsb200_scene *s, dsb200_render_state *rs, int maxAge, int maxSize)
+{ (void)maxAge; return prune_from_queue(e, s, rs, e->slideDefusionQ, maxSize, true, 0, 0); }
+
+} // extern "C"
+
+// ---------------------------------------------------------------- visualisation engine
+static int vis_ensure_scan(dsb200_vis *v, int total)
+{
+    int tiles = div_up(total, 1024);
+    if (tiles <= v->scanTilesAlloc) { v->fs.scanTiles = tiles; return DSB200_OK; }
+    if (v->fs.scanState) CU(cudaFree(v->fs.scanState));
+    CU(cudaMalloc(&v->fs.scanState, (size_t)(2 * tiles + 8) * 8));
+    CU(cudaMemset(v->fs.scanState, 0, (size_t)(2 * tiles + 8) * 8));
+    v->scanTilesAlloc = tiles; v->fs.scanTiles = tiles;
+    return DSB200_OK;
+}
+
+static void make_ray_params(RayParams &P, const dsb200_scene *scene, const float *M, const float *invM, const float *intr,
+                            int W, int H)
+{
+    fill_mat(P.invM, invM);
+    if (M) fill_mat(P.M, M); else memset(P.M.m, 0, 64);
+    P.invProj[0] = 1.0f / intr[0]; P.invProj[1] = 1.0f / intr[1]; P.invProj[2] = intr[2]; P.invProj[3] = intr[3];
+    P.oneOverVoxel = 1.0f / scene->params.voxel_size; P.mu = scene->params.mu; P.voxelSize = scene->params.voxel_size;
+    P.light[0] = -invM[8]; P.light[1] = -invM[9]; P.light[2] = -invM[10];      // -invM.getColumn(2)
+    P.W = W; P.H = H; P.bucketNum = scene->bucket_num; P.bucketMask = scene->bucket_num - 1;
+}
+
+static void make_proj_params(ProjParams &P, const dsb200_scene *scene, const float *M, const float *intr, int W, int H)
+{
+    fill_mat(P.M, M); memcpy(P.proj, intr, 16);
+    P.voxelSize = scene->params.voxel_size; P.W = W; P.H = H; P.maxRenderBlocks = 65536 * 4;   // MAX_RENDERING_BLOCKS
+}
+
+// stand-alone (synchronous) vis calls take the visible count from the caller's host mirror
+static int vis_push_count(dsb200_vis *v, int n)
+{
+    v->hostInts[0] = n;
+    CU(cudaMemcpyAsync(&v->fs.counters->noVisible, &v->hostInts[0], 4, cudaMemcpyHostToDevice, v->stream));
+    return DSB200_OK;
+}
+
+extern "C" {
+
+int dsb200_vis_create(dsb200_vis **out, int32_t max_visible, int32_t width, int32_t height, void *stream)
+{
+    (void)max_visible;
+    if (!out || width <= 0 || height <= 0) return fail(DSB200_ERR_INVALID, "vis_create: bad arguments");
+    if (dsb200_device_count() == 0) return fail(DSB200_ERR_NO_DEVICE, "no CUDA device: libdsb200 has no CPU fallback");
+    dsb200_vis *v = new dsb200_vis();
+    v->stream = (cudaStream_t)stream;
+    CU(cudaMalloc(&v->fs.counters, sizeof(Counters)));
+    CU(cudaMemset(v->fs.counters, 0, sizeof(Counters)));
+    CU(cudaMalloc(&v->fs.tickets, 4 * sizeof(int)));
+    CU(cudaMemset(v->fs.tickets, 0, 4 * sizeof(int)));
+    CU(cudaMalloc(&v->countScratch, 4 * sizeof(int)));
+    CU(cudaMallocHost(&v->hostCounters, sizeof(Counters)));
+    CU(cudaMallocHost(&v->hostInts, 4 * sizeof(int)));
+    *out = v;
+    return DSB200_OK;
+}
+
+int dsb200_vis_destroy(dsb200_vis *v)
+{
+    if (!v) return DSB200_OK;
+    cudaStreamSynchronize(v->stream);
+    cudaFree(v->fs.counters); cudaFree(v->fs.tickets); cudaFree(v->fs.scanState); cudaFree(v->countScratch);
+    cudaFree(v->fwdProjection); cudaFree(v->fwdMissing);
+    cudaFreeHost(v->hostCounters); cudaFreeHost(v->hostInts);
+    delete v;
+    return DSB200_OK;
+}
+
+int dsb200_find_visible_blocks(dsb200_vis *v, const dsb200_scene *scene, const float *M, const float *intr, dsb200_render_state *rs)
+{
+    if (!v || !scene || !rs) return fail(DSB200_ERR_INVALID, "find_visible_blocks: null argument");
+    const int total = scene->bucket_num + scene->excess_size;
+    int rc = vis_ensure_scan(v, total); if (rc) return rc;
+    VisParams P; fill_mat(P.M, M); memcpy(P.proj, intr, 16);
+    P.voxelSize = scene->params.voxel_size; P.W = rs->width; P.H = rs->height; P.useSwapping = 0;
+    launch_find_visible(v->stream, P, v->fs, scene->hash, rs->visible_ids, rs->visible_capacity, total);
+    CU(cudaMemcpyAsync(v->hostCounters, v->fs.counters, sizeof(Counters), cudaMemcpyDeviceToHost, v->stream));
+    CU(cudaStreamSynchronize(v->stream));
+    rs->no_visible = v->hostCounters->noVisible;
+    return DSB200_OK;
+}
+
+int dsb200_count_visible_blocks(dsb200_vis *v, const dsb200_scene *scene, const dsb200_render_state *rs, int minId, int maxId, int *count)
+{
+    int rc = vis_push_count(v, rs->no_visible); if (rc) return rc;
+    launch_count_visible(v->stream, scene->hash, rs->visible_ids, &v->fs.counters->noVisible, minId, maxId, v->countScratch + 1);
+    CU(cudaMemcpyAsync(&v->hostInts[1], v->countScratch + 1, 4, cudaMemcpyDeviceToHost, v->stream));
+    CU(cudaStreamSynchronize(v->stream));
+    *count = v->hostInts[1];
+    return DSB200_OK;
+}
+
+int dsb200_create_expected_depths(dsb200_vis *v, const dsb200_scene *scene, const float *M, const float *intr, dsb200_render_state *rs)
+{
+    int rc = vis_push_count(v, rs->no_visible); if (rc) return rc;
+    ProjParams P; make_proj_params(P, scene, M, intr, rs->width, rs->height);
+    launch_expected_depths(v->stream, P, scene->hash, rs->visible_ids, &v->fs.counters->noVisible, rs->range_image, nullptr, v->fs.counters);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(v->stream));
+    return DSB200_OK;
+}
+
+int dsb200_find_surface(dsb200_vis *v, const dsb200_scene *scene, const float *invM, const float *intr, dsb200_render_state *rs)
+{
+    RayParams P; make_ray_params(P, scene, nullptr, invM, intr, rs->width, rs->height);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(v->stream));
+    return DSB200_OK;
+}
+
+int dsb200_create_icp_maps(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *trk, dsb200_render_state *rs)
+{
+    if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "create_icp_maps: tracking state has no point cloud buffers");
+    RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+    launch_icp_maps(v->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(v->stream));
+    return DSB200_OK;
+}
+
+int dsb200_render_image(dsb200_vis *v, const dsb200_scene *scene, const float *M, const float *invM, const float *intr,
+                        dsb200_render_state *rs, uint8_t *outRGBA, float *outDepth, int type)
+{
+    if (!outRGBA) return fail(DSB200_ERR_INVALID, "render_image: null output image");
+    if (type == DSB200_RENDER_COLOURCODED) type = DSB200_RENDER_SHADED_GREYSCALE;   // !TIndex::hasColorCoding
+    RayParams P; make_ray_params(P, scene, M, invM, intr, rs->width, rs->height);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+    launch_shade(v->stream, P, type, scene->voxels, scene->hash, rs->raycast_result, outRGBA, outDepth);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(v->stream));
+    return DSB200_OK;
+}
+
+int dsb200_forward_render(dsb200_vis *, const dsb200_scene *, const dsb200_view *, dsb200_tracking *, dsb200_render_state *)
+{
+    // only reachable with useApproximateRaycast, which DenseSLAM never sets
+    return fail(DSB200_ERR_UNSUPPORTED, "ForwardRender (approximate raycast) is not built yet");
+}
+
+int dsb200_create_point_cloud(dsb200_vis *)
+{
+    return fail(DSB200_ERR_UNSUPPORTED, "CreatePointCloud serves the colour tracker, which DenseSLAM never selects");
+}
+
+// ---------------------------------------------------------------- fused frame
+int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *trk,
+                         dsb200_render_state *rs, int stages)
+{
+    int rc = check_scene(e, scene); if (rc) return rc;
+    if ((stages & (DSB200_FRAME_EXPECTED_DEPTHS | DSB200_FRAME_ICP_MAPS)) && (!v || v->stream != e->stream))
+        return fail(DSB200_ERR_INVALID, "process_frame: the two engines must share one stream");
+    const int *countPtr = &e->fs.counters->noVisible;
+    if (stages & DSB200_FRAME_ALLOCATE) {
+        rc = enqueue_allocate(e, scene, view, trk, rs, 0, 0); if (rc) return rc;
+    } else if (!(e->async && e->deviceCountersValid)) {
+        e->hostCounters->noVisible = rs->no_visible;
+        CU(cudaMemcpyAsync(&e->fs.counters->noVisible, &e->hostCounters->noVisible, 4, cudaMemcpyHostToDevice, e->stream));
+    }
+    if (stages & DSB200_FRAME_INTEGRATE) {
+        FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
+        launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb);
+    }
+    if (stages & DSB200_FRAME_EXPECTED_DEPTHS) {
+        ProjParams P; make_proj_params(P, scene, trk->M_d, view->intr_d, rs->width, rs->height);
+        launch_expected_depths(e->stream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, nullptr, e->fs.counters);
+    }
+    if (stages & DSB200_FRAME_ICP_MAPS) {
+        if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "process_frame: tracking state has no point cloud buffers");
+        RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+        launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
+    }
+    return finish_call(e, scene, rs, (stages & DSB200_FRAME_ALLOCATE) != 0);
+}
+
+// ---------------------------------------------------------------- host helpers
+int dsb200_scene_alloc(dsb200_scene *s, int32_t num_blocks, int32_t bucket_num, int32_t excess_size)
+{
+    if (!s) return fail(DSB200_ERR_INVALID, "scene_alloc: null");
+    if (dsb200_device_count() == 0) return fail(DSB200_ERR_NO_DEVICE, "no CUDA device: libdsb200 has no CPU fallback");
+    s->num_blocks = num_blocks; s->bucket_num = bucket_num; s->excess_size = excess_size;
+    CU(cudaMalloc(&s->voxels, (size_t)num_blocks * DSB200_BLOCK_SIZE3 * sizeof(dsb200_voxel)));
+    CU(cudaMalloc(&s->hash, (size_t)(bucket_num + excess_size) * sizeof(dsb200_hash_entry)));
+    CU(cudaMalloc(&s->alloc_list, (size_t)num_blocks * 4));
+    CU(cudaMalloc(&s->excess_list, (size_t)(excess_size > 0 ? excess_size : 1) * 4));
+    s->last_free_block = num_blocks - 1; s->last_free_excess = excess_size - 1;
+    return DSB200_OK;
+}
+int dsb200_scene_free(dsb200_scene *s)
+{
+    if (!s) return DSB200_OK;
+    cudaFree(s->voxels); cudaFree(s->hash); cudaFree(s->alloc_list); cudaFree(s->excess_list);
+    s->voxels = nullptr; s->hash = nullptr; s->alloc_list = nullptr; s->excess_list = nullptr;
+    return DSB200_OK;
+}
+int dsb200_render_state_alloc(dsb200_render_state *rs, int32_t total_entries, int32_t visible_capacity, int32_t width, int32_t height)
+{
+    if (!rs) return fail(DSB200_ERR_INVALID, "render_state_alloc: null");
+    rs->visible_capacity = visible_capacity; rs->no_visible = 0; rs->width = width; rs->height = height;
+    const size_t px = (size_t)width * height;
+    CU(cudaMalloc(&rs->visible_ids, (size_t)visible_capacity * 4));
+    CU(cudaMalloc(&rs->visible_type, (size_t)((total_entries + 3) & ~3)));
+    CU(cudaMemset(rs->visible_type, 0, (size_t)((total_entries + 3) & ~3)));
+    CU(cudaMalloc(&rs->range_image, px * 8));
+    CU(cudaMalloc(&rs->raycast_result, px * 16));
+    CU(cudaMalloc(&rs->raycast_image, px * 4));
+    CU(cudaMemset(rs->raycast_result, 0, px * 16));
+    CU(cudaMemset(rs->raycast_image, 0, px * 4));
+    // ITMRenderState ctor pre-fills the range image with (vf_min, vf_max); callers overwrite it
+    CU(cudaMemset(rs->range_image, 0, px * 8));
+    return DSB200_OK;
+}
+int dsb200_render_state_free(dsb200_render_state *rs)
+{
+    if (!rs) return DSB200_OK;
+    cudaFree(rs->visible_ids); cudaFree(rs->visible_type); cudaFree(rs->range_image); cudaFree(rs->raycast_result);
+    cudaFree(rs->raycast_image);
+    memset(rs, 0, sizeof(*rs));
+    return DSB200_OK;
+}
+int dsb200_device_alloc(void **p, size_t bytes) { CU(cudaMalloc(p, bytes)); return DSB200_OK; }
+int dsb200_device_free(void *p) { CU(cudaFree(p)); return DSB200_OK; }
+int dsb200_host_alloc_pinned(void **p, size_t bytes) { CU(cudaMallocHost(p, bytes)); return DSB200_OK; }
+int dsb200_host_free_pinned(void *p) { CU(cudaFreeHost(p)); return DSB200_OK; }
+int dsb200_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream)
+{
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return DSB200_OK;
+}
+int dsb200_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream)
+{
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    return DSB200_OK;
+}
+int dsb200_stream_synchronize(void *stream) { CU(cudaStreamSynchronize((cudaStream_t)stream)); return DSB200_OK; }
+
+} // extern "C"

@@ -1,0 +1,96 @@
+// kernels.cuh -- parameter blocks and host-side launchers of every kernel in libdsb200.
+#pragma once
+#include "common.cuh"
+
+namespace dsb {
+
+// Engine scratch that several kernels of one frame share (device pointers, passed by value).
+struct FrameState {
+    Counters *counters;
+    unsigned long long *scanState;   // [2 * scanTiles]: look-back words of k_allocate, then k_visible_list
+    int *tickets;                    // [4] dynamic tile tickets
+    int scanTiles;                   // ceil(totalEntries / 1024)
+};
+
+struct AllocParams {
+    Mat4 invM;
+    float invProj[4];                // (1/fx, 1/fy, cx, cy)
+    float mu, oneOverBlock, vfMin, vfMax;
+    int W, H, bucketNum, bucketMask;
+};
+
+struct VisParams {                   // block visibility test
+    Mat4 M;
+    float proj[4];
+    float voxelSize;
+    int W, H, useSwapping;
+};
+
+struct FuseParams {                  // integrate / de-integrate
+    Mat4 M_d, M_rgb;
+    float proj_d[4], proj_rgb[4];
+    float voxelSize, mu;
+    int maxW, W, H, Wrgb, Hrgb;
+    int stopMaxW, approximate;       // template flags of the reference kernel (CUDA .cu:407-420)
+    int depthWeighting, maxNewW, maxDistance;
+};
+
+struct RayParams {                   // raycast (castRay) + ICP maps
+    Mat4 invM, M;
+    float invProj[4];
+    float oneOverVoxel, mu, voxelSize;
+    float light[3];
+    int W, H, bucketNum, bucketMask;
+};
+
+struct ProjParams {                  // CreateExpectedDepths
+    Mat4 M;
+    float proj[4];
+    float voxelSize;
+    int W, H, maxRenderBlocks;
+};
+
+// recon_alloc.cu
+void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeBlock, int hostLastFreeExcess,
+                        int hostNoVisible, int useHost, const int *visibleIds, uint8_t *visType, int prevUpperBound);
+void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const float *depth, const dsb200_hash_entry *hash,
+                           uint8_t *visType, unsigned *reqKey);
+void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
+                     dsb200_hash_entry *hash, const int *allocList, const int *excessList, uint8_t *visType,
+                     unsigned *reqKey, int total, int doAllocate);
+void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &fs, dsb200_hash_entry *hash,
+                         const int *allocList, uint8_t *visType, int *visibleIds, int visibleCapacity, int *snapshotIds,
+                         int *snapshotCount, int total);
+
+// recon_integrate.cu
+void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,
+                 const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth,
+                 const uint8_t *rgb);
+void launch_reset_scene(cudaStream_t st, dsb200_voxel *voxels, size_t numVoxels, dsb200_hash_entry *hash, int total,
+                        int *allocList, int numBlocks, int *excessList, int excessSize, uint8_t *visTypeOrNull,
+                        unsigned *reqKey, Counters *counters);
+
+// recon_prune.cu
+void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash_entry *hash, int bucketNum,
+                  const int *ids, const int *count, int countUpperBound, int minAge, int maxWeight, int currentFrame,
+                  int *allocList, uint8_t *visType, unsigned *slotMark, int *pendingList, Counters *counters,
+                  const FrameState &fs);
+
+// vis.cu
+void launch_find_visible(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
+                         int *visibleIds, int visibleCapacity, int total);
+void launch_count_visible(cudaStream_t st, const dsb200_hash_entry *hash, const int *ids, const int *count, int minId,
+                          int maxId, int *out);
+void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_hash_entry *hash, const int *ids,
+                            const int *count, float *rangeImage, int *blockTileCounts, Counters *counters);
+void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
+                    const float *rangeImage, float *raycastResult);
+void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,
+                     uint8_t *rendering);
+void launch_shade(cudaStream_t st, const RayParams &P, int renderType, const dsb200_voxel *voxels,
+                  const dsb200_hash_entry *hash, const float *raycastResult, uint8_t *outRGBA, float *outDepth);
+void launch_forward_render(cudaStream_t st, const RayParams &P, const float *proj, const dsb200_voxel *voxels,
+                           const dsb200_hash_entry *hash, const float *rangeImage, const float *raycastResult,
+                           const float *depth, float *fwd, int *missing, int *noMissing, uint8_t *rendering);
+
+} // namespace dsb

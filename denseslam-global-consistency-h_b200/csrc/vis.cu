@@ -1,0 +1,512 @@
+// vis.cu -- ITMVisualisationEngine for sm_100a: FindVisibleBlocks, CreateExpectedDepths,
+// raycast (castRay), ICP point/normal maps, free-view shading.
+//
+// Reference math: DeviceAgnostic/ITMVisualisationEngine.h:36-196,243-439 and
+// DeviceAgnostic/ITMRepresentationAccess.h:176-427; reference kernels:
+// CUDA/ITMVisualisationEngine_CUDA.cu:655-942.  Differences in structure (not in results):
+//  * visible-block compaction is ORDERED (ascending slot) like the CPU engine, via the look-back scan;
+//  * expected depths: no rendering-block list and no CAS-loop float atomics -- every visible block
+//    projects its 8 corners and min/max-es its bounding box straight into the range image with
+//    native integer atomics on the float bit patterns (all depths are >= 0.05 > 0, so integer
+//    order == float order); the reference's rendering-block cap is honoured by an exact serial
+//    fallback that only runs when the cap would be hit;
+//  * nothing returns to the host between stages (counts stay on the device).
+#include "kernels.cuh"
+#include "scan.cuh"
+#include "visibility.cuh"
+
+namespace dsb {
+
+
+constexpr float kFarAway = 999999.9f, kVeryClose = 0.05f;
+constexpr int kSubsample = 8;
+
+__global__ void k_reset_scan(FrameState fs, int region, int tiles, int ticket)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < tiles; i += gridDim.x * blockDim.x) fs.scanState[region + i] = 0ull;
+    if (blockIdx.x == 0 && threadIdx.x == 0) fs.tickets[ticket] = 0;
+}
+
+// FindVisibleBlocks (CPU/ITMVisualisationEngine_CPU.cpp:40-78): all allocated slots inside the frustum, ascending
+__global__ void __launch_bounds__(256) k_find_visible(VisParams P, FrameState fs, const dsb200_hash_entry *__restrict__ hash,
+                                                      int *visibleIds, int visibleCapacity, int total)
+{
+    __shared__ unsigned sScan[16];
+    __shared__ int sTile;
+    __shared__ unsigned sEx[2];
+    if (threadIdx.x == 0) sTile = atomicAdd(&fs.tickets[1], 1);
+    __syncthreads();
+    const int tile = sTile;
+    const int slot0 = tile * 1024 + threadIdx.x * 4;
+    bool v[4]; unsigned na = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        v[j] = false;
+        if (slot0 + j < total) {
+            HashEntry e = load_entry(hash, slot0 + j);
+            if (e.ptr >= 0) {
+                bool vis, visEnl;
+                block_visibility(vis, visEnl, e.px, e.py, e.pz, P.M, P.proj, P.voxelSize, P.W, P.H, false);
+                v[j] = vis;
+            }
+        }
+        na += v[j] ? 1 : 0;
+    }
+    unsigned exA, exB, totA, totB;
+    block_scan2(na, 0, sScan, exA, exB, totA, totB);
+    if (threadIdx.x < 32) {
+        unsigned ta, tb;
+        scan_lookback(fs.scanState + fs.scanTiles, tile, totA, 0, ta, tb);
+        if (threadIdx.x == 0) sEx[0] = ta;
+    }
+    __syncthreads();
+    unsigned r = sEx[0] + exA;
+#pragma unroll
+    for (int j = 0; j < 4; j++) if (v[j]) { if ((int)r < visibleCapacity) visibleIds[r] = slot0 + j; r++; }
+    if (threadIdx.x == 0 && tile == gridDim.x - 1) fs.counters->noVisible = (int)(sEx[0] + totA);
+}
+
+__global__ void k_count_visible(const dsb200_hash_entry *__restrict__ hash, const int *__restrict__ ids,
+                                const int *__restrict__ countPtr, int minId, int maxId, int *out)
+{
+    const int n = *countPtr;
+    int c = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int ptr = load_entry(hash, ids[i]).ptr;
+        c += (ptr >= minId && ptr <= maxId) ? 1 : 0;
+    }
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// ---------------------------------------------------------------- expected depths
+// ProjectSingleBlock, DeviceAgnostic/ITMVisualisationEngine.h:36-85
+__device__ __forceinline__ bool project_block(short bx, short by, short bz, const ProjParams &P, int ul[2], int lr[2], float zr[2])
+{
+    ul[0] = P.W / kSubsample; ul[1] = P.H / kSubsample; lr[0] = -1; lr[1] = -1; zr[0] = kFarAway; zr[1] = kVeryClose;
+#pragma unroll
+    for (int corner = 0; corner < 8; ++corner) {
+        short tx = bx + ((corner & 1) ? 1 : 0), ty = by + ((corner & 2) ? 1 : 0), tz = bz + ((corner & 4) ? 1 : 0);
+        Vec4 p = {(float)tx * (float)kBlock * P.voxelSize, (float)ty * (float)kBlock * P.voxelSize,
+                  (float)tz * (float)kBlock * P.voxelSize, 1.0f};
+        p = mul(P.M, p);
+        if ((double)p.z < 1e-6) continue;           // double literal in the reference
+        float px = (P.proj[0] * p.x / p.z + P.proj[2]) / (float)kSubsample;
+        float py = (P.proj[1] * p.y / p.z + P.proj[3]) / (float)kSubsample;
+        if (ul[0] > floorf(px)) ul[0] = (int)floorf(px);
+        if (lr[0] < ceilf(px)) lr[0] = (int)ceilf(px);
+        if (ul[1] > floorf(py)) ul[1] = (int)floorf(py);
+        if (lr[1] < ceilf(py)) lr[1] = (int)ceilf(py);
+        if (zr[0] > p.z) zr[0] = p.z;
+        if (zr[1] < p.z) zr[1] = p.z;
+    }
+    if (ul[0] < 0) ul[0] = 0;
+    if (ul[1] < 0) ul[1] = 0;
+    if (lr[0] >= P.W) lr[0] = P.W - 1;
+    if (lr[1] >= P.H) lr[1] = P.H - 1;
+    if (ul[0] > lr[0]) return false;
+    if (ul[1] > lr[1]) return false;
+    if (zr[0] < kVeryClose) zr[0] = kVeryClose;
+    if (zr[1] < kVeryClose) return false;
+    return true;
+}
+
+__global__ void __launch_bounds__(256) k_range_init(float2 *range, int n, Counters *counters)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) range[i] = make_float2(kFarAway, kVeryClose);
+    if (blockIdx.x == 0 && threadIdx.x == 0) counters->renderBlocks = 0;
+}
+
+__device__ __forceinline__ void range_minmax(float *range, int W, int x, int y, float zmin, float zmax)
+{
+    int *px = reinterpret_cast<int *>(range) + 2 * ((size_t)x + (size_t)y * W);
+    // positive floats: integer order == float order; skip the atomic when it cannot change the value
+    if (__float_as_int(zmin) < __ldcg(px)) atomicMin(px, __float_as_int(zmin));
+    if (__float_as_int(zmax) > __ldcg(px + 1)) atomicMax(px + 1, __float_as_int(zmax));
+}
+
+__global__ void __launch_bounds__(256) k_project_fill(ProjParams P, const dsb200_hash_entry *__restrict__ hash,
+                                                      const int *__restrict__ ids, const int *__restrict__ countPtr,
+                                                      float *range, Counters *counters)
+{
+    const int n = *countPtr;
+    int tiles = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        HashEntry e = load_entry(hash, __ldg(ids + i));
+        if (e.ptr < 0) continue;
+        int ul[2], lr[2]; float zr[2];
+        if (!project_block(e.px, e.py, e.pz, P, ul, lr, zr)) continue;
+        tiles += (int)ceilf((float)(lr[0] - ul[0] + 1) / 16.0f) * (int)ceilf((float)(lr[1] - ul[1] + 1) / 16.0f);
+        for (int y = ul[1]; y <= lr[1]; y++)
+            for (int x = ul[0]; x <= lr[0]; x++) range_minmax(range, P.W, x, y, zr[0], zr[1]);
+    }
+    for (int o = 16; o > 0; o >>= 1) tiles += __shfl_xor_sync(0xffffffffu, tiles, o);
+    if ((threadIdx.x & 31) == 0 && tiles) atomicAdd(&counters->renderBlocks, tiles);
+}
+
+// Exact fallback for the reference's MAX_RENDERING_BLOCKS rule (CPU .cpp:158: a block whose tiles
+// would push the running count to >= cap is skipped, later smaller blocks may still fit).  If the
+// grand total is below the cap no block can have been skipped and k_project_fill's result stands.
+__global__ void __launch_bounds__(1024) k_range_cap_fallback(ProjParams P, const dsb200_hash_entry *__restrict__ hash,
+                                                             const int *__restrict__ ids, const int *__restrict__ countPtr,
+                                                             float *range, Counters *counters)
+{
+    if (counters->renderBlocks < P.maxRenderBlocks) return;
+    __shared__ int sNum;
+    const int n = *countPtr;
+    for (int i = threadIdx.x; i < P.W * P.H; i += blockDim.x) { range[2 * i] = kFarAway; range[2 * i + 1] = kVeryClose; }
+    if (threadIdx.x == 0) sNum = 0;
+    __syncthreads();
+    for (int i = 0; i < n; i++) {
+        HashEntry e = load_entry(hash, ids[i]);
+        int ul[2], lr[2]; float zr[2];
+        bool ok = e.ptr >= 0 && project_block(e.px, e.py, e.pz, P, ul, lr, zr);
+        int req = 0;
+        if (ok) {
+            req = (int)ceilf((float)(lr[0] - ul[0] + 1) / 16.0f) * (int)ceilf((float)(lr[1] - ul[1] + 1) / 16.0f);
+            if (sNum + req >= P.maxRenderBlocks) ok = false;
+        }
+        __syncthreads();
+        if (ok) {
+            if (threadIdx.x == 0) sNum += req;
+            const int bw = lr[0] - ul[0] + 1, cells = bw * (lr[1] - ul[1] + 1);
+            for (int c = threadIdx.x; c < cells; c += blockDim.x) {
+                float *px = range + 2 * ((size_t)(ul[0] + c % bw) + (size_t)(ul[1] + c / bw) * P.W);
+                if (px[0] > zr[0]) px[0] = zr[0];
+                if (px[1] < zr[1]) px[1] = zr[1];
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) counters->renderBlocks = sNum;
+}
+
+// ---------------------------------------------------------------- raycast
+struct BlockCache { int bx, by, bz, base; };
+
+// readVoxel + pointToVoxelBlockPos (DeviceAgnostic/ITMRepresentationAccess.h:14-19,176-210); returns sdf as short
+__device__ __forceinline__ short read_sdf(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
+                                          int bucketNum, int bucketMask, int px, int py, int pz, bool &found, BlockCache &c)
+{
+    // floor division by 8 (arithmetic shift == the reference's ((p<0)?p-7:p)/8)
+    const int bx = px >> 3, by = py >> 3, bz = pz >> 3;
+    const int lin = (px & 7) + ((py & 7) << 3) + ((pz & 7) << 6);
+    if (bx == c.bx && by == c.by && bz == c.bz) { found = true; return __ldg(reinterpret_cast<const short *>(voxels + c.base + lin)); }
+    int h = hash_index(bx, by, bz, bucketMask);
+    while (true) {
+        HashEntry e = load_entry(hash, h);
+        if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= 0) {
+            found = true; c.bx = bx; c.by = by; c.bz = bz; c.base = e.ptr * kBlock3;
+            return __ldg(reinterpret_cast<const short *>(voxels + c.base + lin));
+        }
+        if (e.offset < 1) break;
+        h = bucketNum + e.offset - 1;
+    }
+    found = false;
+    return 32767;
+}
+
+__device__ __forceinline__ float round_half_away(float x) { return (x < 0) ? (x - 0.5f) : (x + 0.5f); }
+
+#define DSB_RD(X, Y, Z) ((float)read_sdf(voxels, hash, bucketNum, bucketMask, (X), (Y), (Z), found, cache))
+
+// readFromSDF_float_interpolated (:251-276)
+__device__ __forceinline__ float sdf_trilinear(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
+                                               int bucketNum, int bucketMask, float x, float y, float z, bool &found,
+                                               BlockCache &cache)
+{
+    float fx = floorf(x), fy = floorf(y), fz = floorf(z);
+    float cx = x - fx, cy = y - fy, cz = z - fz;
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    float res1, res2, v1, v2;
+    v1 = DSB_RD(ix, iy, iz); v2 = DSB_RD(ix + 1, iy, iz);
+    res1 = (1.0f - cx) * v1 + cx * v2;
+    v1 = DSB_RD(ix, iy + 1, iz); v2 = DSB_RD(ix + 1, iy + 1, iz);
+    res1 = (1.0f - cy) * res1 + cy * ((1.0f - cx) * v1 + cx * v2);
+    v1 = DSB_RD(ix, iy, iz + 1); v2 = DSB_RD(ix + 1, iy, iz + 1);
+    res2 = (1.0f - cx) * v1 + cx * v2;
+    v1 = DSB_RD(ix, iy + 1, iz + 1); v2 = DSB_RD(ix + 1, iy + 1, iz + 1);
+    res2 = (1.0f - cy) * res2 + cy * ((1.0f - cx) * v1 + cx * v2);
+    found = true;
+    return ((1.0f - cz) * res1 + cz * res2) / 32767.0f;
+}
+
+// castRay, DeviceAgnostic/ITMVisualisationEngine.h:124-196
+__device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const dsb200_voxel *__restrict__ voxels,
+                                         const dsb200_hash_entry *__restrict__ hash, const RayParams &P, float zmin, float zmax)
+{
+    const int bucketNum = P.bucketNum, bucketMask = P.bucketMask;
+    const float stepScale = P.mu * P.oneOverVoxel;
+    Vec4 pc;
+    pc.z = zmin;
+    pc.x = pc.z * (((float)x - P.invProj[2]) * P.invProj[0]);
+    pc.y = pc.z * (((float)y - P.invProj[3]) * P.invProj[1]);
+    pc.w = 1.0f;
+    float totalLength = sqrtf(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z) * P.oneOverVoxel;
+    Vec4 t = mul(P.invM, pc);
+    const float sx = t.x * P.oneOverVoxel, sy = t.y * P.oneOverVoxel, sz = t.z * P.oneOverVoxel;
+    pc.z = zmax;
+    pc.x = pc.z * (((float)x - P.invProj[2]) * P.invProj[0]);
+    pc.y = pc.z * (((float)y - P.invProj[3]) * P.invProj[1]);
+    pc.w = 1.0f;
+    const float totalLengthMax = sqrtf(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z) * P.oneOverVoxel;
+    t = mul(P.invM, pc);
+    float dx = t.x * P.oneOverVoxel - sx, dy = t.y * P.oneOverVoxel - sy, dz = t.z * P.oneOverVoxel - sz;
+    const float dn = 1.0f / sqrtf(dx * dx + dy * dy + dz * dz);
+    dx *= dn; dy *= dn; dz *= dn;
+    float rx = sx, ry = sy, rz = sz;
+    BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, -1};
+    float sdf = 1.0f, stepLength;
+    bool found, ptFound;
+    while (totalLength < totalLengthMax) {
+        sdf = (float)read_sdf(voxels, hash, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
+                              (int)round_half_away(rz), found, cache) / 32767.0f;
+        if (!found) stepLength = (float)kBlock;
+        else {
+            if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(voxels, hash, bucketNum, bucketMask, rx, ry, rz, found, cache);
+            if (!(sdf > 0.0f)) break;
+            stepLength = (sdf * stepScale < 1.0f) ? 1.0f : sdf * stepScale;
+        }
+        rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
+        totalLength += stepLength;
+    }
+    if (sdf <= 0.0f) {
+        stepLength = sdf * stepScale;
+        rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
+        sdf = sdf_trilinear(voxels, hash, bucketNum, bucketMask, rx, ry, rz, ptFound, cache);
+        stepLength = sdf * stepScale;
+        rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
+    } else ptFound = false;
+    out = make_float4(rx, ry, rz, ptFound ? 1.0f : 0.0f);
+    return ptFound;
+}
+
+// GenericRaycast (CPU .cpp:296-333; CUDA .cu:807-819)
+__global__ void __launch_bounds__(128) k_raycast(RayParams P, const dsb200_voxel *__restrict__ voxels,
+                                                 const dsb200_hash_entry *__restrict__ hash,
+                                                 const float2 *__restrict__ range, float4 *out)
+{
+    const int x = blockIdx.x * 16 + (threadIdx.x & 15), y = blockIdx.y * 8 + (threadIdx.x >> 4);
+    if (x >= P.W || y >= P.H) return;
+    const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
+    const float2 mm = __ldg(range + loc2);
+    float4 r;
+    cast_ray(r, x, y, voxels, hash, P, mm.x, mm.y);
+    out[x + y * P.W] = r;
+}
+
+// ---------------------------------------------------------------- ICP maps (processPixelICP<true>, DA/...:391-439)
+__device__ __forceinline__ void normal_from_image(bool &found, int x, int y, const float4 *__restrict__ pts, const RayParams &P,
+                                                  float n[3], float &angle)
+{   // computeNormalAndAngle<true>, DA/ITMVisualisationEngine.h:243-312
+    if (!found) return;
+    if (y <= 2 || y >= P.H - 3 || x <= 2 || x >= P.W - 3) { found = false; return; }
+    float4 xp = __ldg(pts + (x + 2) + y * P.W), yp = __ldg(pts + x + (y + 2) * P.W);
+    float4 xm = __ldg(pts + (x - 2) + y * P.W), ym = __ldg(pts + x + (y - 2) * P.W);
+    float dxx = 0, dxy = 0, dxz = 0, dyx = 0, dyy = 0, dyz = 0;
+    bool doPlus1 = false;
+    if (xp.w <= 0 || yp.w <= 0 || xm.w <= 0 || ym.w <= 0) doPlus1 = true;
+    else {
+        dxx = xp.x - xm.x; dxy = xp.y - xm.y; dxz = xp.z - xm.z;
+        dyx = yp.x - ym.x; dyy = yp.y - ym.y; dyz = yp.z - ym.z;
+        float a = dxx * dxx + dxy * dxy + dxz * dxz, b = dyx * dyx + dyy * dyy + dyz * dyz;
+        float lengthDiff = (a < b) ? b : a;
+        if (lengthDiff * P.voxelSize * P.voxelSize > (0.15f * 0.15f)) doPlus1 = true;
+    }
+    if (doPlus1) {
+        xp = __ldg(pts + (x + 1) + y * P.W); yp = __ldg(pts + x + (y + 1) * P.W);
+        xm = __ldg(pts + (x - 1) + y * P.W); ym = __ldg(pts + x + (y - 1) * P.W);
+        dxx = xp.x - xm.x; dxy = xp.y - xm.y; dxz = xp.z - xm.z;
+        dyx = yp.x - ym.x; dyy = yp.y - ym.y; dyz = yp.z - ym.z;
+        if (xp.w <= 0 || yp.w <= 0 || xm.w <= 0 || ym.w <= 0) { found = false; return; }
+    }
+    n[0] = -(dxy * dyz - dxz * dyy);
+    n[1] = -(dxz * dyx - dxx * dyz);
+    n[2] = -(dxx * dyy - dxy * dyx);
+    float sc = 1.0f / sqrtf(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    n[0] *= sc; n[1] *= sc; n[2] *= sc;
+    angle = n[0] * P.light[0] + n[1] * P.light[1] + n[2] * P.light[2];
+    if (!(angle > 0.0f)) found = false;
+}
+
+__global__ void __launch_bounds__(256) k_icp_maps(RayParams P, const float4 *__restrict__ pts, float4 *points, float4 *normals,
+                                                  uchar4 *rendering)
+{
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= P.W || y >= P.H) return;
+    const int loc = x + y * P.W;
+    const float4 pt = __ldg(pts + loc);
+    bool found = pt.w > 0.0f;
+    float n[3], angle = 0.0f;
+    normal_from_image(found, x, y, pts, P, n, angle);
+    if (found) {
+        unsigned char g = (unsigned char)((0.8f * angle + 0.2f) * 255.0f);
+        rendering[loc] = make_uchar4(g, g, g, g);
+        points[loc] = make_float4(pt.x * P.voxelSize, pt.y * P.voxelSize, pt.z * P.voxelSize, 1.0f);
+        normals[loc] = make_float4(n[0], n[1], n[2], 0.0f);
+    } else {
+        points[loc] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        normals[loc] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        rendering[loc] = make_uchar4(0, 0, 0, 0);
+    }
+}
+
+
+// ---------------------------------------------------------------- free-view shading (RenderImage)
+#define DSB_RV(DX, DY, DZ) ((float)read_sdf(voxels, hash, bucketNum, bucketMask, X + (DX), Y + (DY), Z + (DZ), f, cache))
+
+// computeSingleNormalFromSDF, DeviceAgnostic/ITMRepresentationAccess.h:314-427
+__device__ void normal_from_sdf(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
+                                int bucketNum, int bucketMask, float px, float py, float pz, float ret[3])
+{
+    bool f; BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, -1};
+    float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
+    float cx = px - flx, cy = py - fly, cz = pz - flz;
+    int X = (int)flx, Y = (int)fly, Z = (int)flz;
+    float nx = 1.0f - cx, ny = 1.0f - cy, nz = 1.0f - cz;
+    float fr0 = DSB_RV(0, 0, 0), fr1 = DSB_RV(1, 0, 0), fr2 = DSB_RV(0, 1, 0), fr3 = DSB_RV(1, 1, 0);
+    float bk0 = DSB_RV(0, 0, 1), bk1 = DSB_RV(1, 0, 1), bk2 = DSB_RV(0, 1, 1), bk3 = DSB_RV(1, 1, 1);
+    float t0, t1, t2, t3, p1, p2, v1;
+    p1 = fr0 * ny * nz + fr2 * cy * nz + bk0 * ny * cz + bk2 * cy * cz;
+    t0 = DSB_RV(-1, 0, 0); t1 = DSB_RV(-1, 1, 0); t2 = DSB_RV(-1, 0, 1); t3 = DSB_RV(-1, 1, 1);
+    p2 = t0 * ny * nz + t1 * cy * nz + t2 * ny * cz + t3 * cy * cz;
+    v1 = p1 * cx + p2 * nx;
+    p1 = fr1 * ny * nz + fr3 * cy * nz + bk1 * ny * cz + bk3 * cy * cz;
+    t0 = DSB_RV(2, 0, 0); t1 = DSB_RV(2, 1, 0); t2 = DSB_RV(2, 0, 1); t3 = DSB_RV(2, 1, 1);
+    p2 = t0 * ny * nz + t1 * cy * nz + t2 * ny * cz + t3 * cy * cz;
+    ret[0] = (p1 * nx + p2 * cx - v1) / 32767.0f;
+    p1 = fr0 * nx * nz + fr1 * cx * nz + bk0 * nx * cz + bk1 * cx * cz;
+    t0 = DSB_RV(0, -1, 0); t1 = DSB_RV(1, -1, 0); t2 = DSB_RV(0, -1, 1); t3 = DSB_RV(1, -1, 1);
+    p2 = t0 * nx * nz + t1 * cx * nz + t2 * nx * cz + t3 * cx * cz;
+    v1 = p1 * cy + p2 * ny;
+    p1 = fr2 * nx * nz + fr3 * cx * nz + bk2 * nx * cz + bk3 * cx * cz;
+    t0 = DSB_RV(0, 2, 0); t1 = DSB_RV(1, 2, 0); t2 = DSB_RV(0, 2, 1); t3 = DSB_RV(1, 2, 1);
+    p2 = t0 * nx * nz + t1 * cx * nz + t2 * nx * cz + t3 * cx * cz;
+    ret[1] = (p1 * ny + p2 * cy - v1) / 32767.0f;
+    p1 = fr0 * nx * ny + fr1 * cx * ny + fr2 * nx * cy + fr3 * cx * cy;
+    t0 = DSB_RV(0, 0, -1); t1 = DSB_RV(1, 0, -1); t2 = DSB_RV(0, 1, -1); t3 = DSB_RV(1, 1, -1);
+    p2 = t0 * nx * ny + t1 * cx * ny + t2 * nx * cy + t3 * cx * cy;
+    v1 = p1 * cz + p2 * nz;
+    p1 = bk0 * nx * ny + bk1 * cx * ny + bk2 * nx * cy + bk3 * cx * cy;
+    t0 = DSB_RV(0, 0, 2); t1 = DSB_RV(1, 0, 2); t2 = DSB_RV(0, 1, 2); t3 = DSB_RV(1, 1, 2);
+    p2 = t0 * nx * ny + t1 * cx * ny + t2 * nx * cy + t3 * cx * cy;
+    ret[2] = (p1 * nz + p2 * cz - v1) / 32767.0f;
+}
+
+// full voxel read for colour rendering
+__device__ __forceinline__ uchar4 read_clr(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
+                                           int bucketNum, int bucketMask, int px, int py, int pz, BlockCache &c)
+{
+    bool found;
+    read_sdf(voxels, hash, bucketNum, bucketMask, px, py, pz, found, c);   // positions the cache
+    if (!found) return make_uchar4(0, 0, 0, 0);
+    const int lin = (px & 7) + ((py & 7) << 3) + ((pz & 7) << 6);
+    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(voxels + c.base + lin));
+    return make_uchar4(raw.x >> 24, raw.y & 0xff, (raw.y >> 8) & 0xff, 0);
+}
+
+// RenderImage shading pass: CPU/ITMVisualisationEngine_CPU.cpp:339-405, CUDA .cu:405-435 (depth falls through to grey)
+__global__ void __launch_bounds__(128) k_shade(RayParams P, int type, const dsb200_voxel *__restrict__ voxels,
+                                               const dsb200_hash_entry *__restrict__ hash, const float4 *__restrict__ pts,
+                                               uchar4 *out, float *outDepth)
+{
+    const int x = blockIdx.x * 16 + (threadIdx.x & 15), y = blockIdx.y * 8 + (threadIdx.x >> 4);
+    if (x >= P.W || y >= P.H) return;
+    const int loc = x + y * P.W;
+    const float4 pt = __ldg(pts + loc);
+    bool found = pt.w > 0;
+    if (type == DSB200_RENDER_DEPTH_MAP && outDepth) {
+        // processPixelColourDepth / drawPixelDepth, DeviceAgnostic/ITMVisualisationEngine.h:340-357,527-540
+        float d = 0.0f;
+        if (found) {
+            Vec4 ph = {pt.x * P.voxelSize, pt.y * P.voxelSize, pt.z * P.voxelSize, 1.0f};
+            Vec4 pc = mul(P.M, ph);
+            d = pc.z / pc.w;
+        }
+        outDepth[loc] = d;
+    }
+    float n[3] = {0, 0, 0}, angle = 0.0f;
+    if (found) {   // computeNormalAndAngle<TVoxel,TIndex>, DA/...:220-234
+        normal_from_sdf(voxels, hash, P.bucketNum, P.bucketMask, pt.x, pt.y, pt.z, n);
+        float sc = 1.0f / sqrtf(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        n[0] *= sc; n[1] *= sc; n[2] *= sc;
+        angle = n[0] * P.light[0] + n[1] * P.light[1] + n[2] * P.light[2];
+        if (!(angle > 0.0f)) found = false;
+    }
+    if (!found) { out[loc] = make_uchar4(0, 0, 0, 0); return; }
+    if (type == DSB200_RENDER_COLOUR_FROM_VOLUME) {
+        // readFromSDF_color4u_interpolated, DeviceAgnostic/ITMRepresentationAccess.h:278-312
+        BlockCache c = {0x7fffffff, 0x7fffffff, 0x7fffffff, -1};
+        float flx = floorf(pt.x), fly = floorf(pt.y), flz = floorf(pt.z);
+        float cx = pt.x - flx, cy = pt.y - fly, cz = pt.z - flz;
+        int X = (int)flx, Y = (int)fly, Z = (int)flz;
+        float r0 = 0.0f, r1 = 0.0f, r2 = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int ox = i & 1, oy = (i >> 1) & 1, oz = i >> 2;
+            uchar4 v = read_clr(voxels, hash, P.bucketNum, P.bucketMask, X + ox, Y + oy, Z + oz, c);
+            float w = (ox ? cx : (1.0f - cx)) * (oy ? cy : (1.0f - cy)) * (oz ? cz : (1.0f - cz));
+            r0 += w * (float)v.x; r1 += w * (float)v.y; r2 += w * (float)v.z;
+        }
+        out[loc] = make_uchar4((unsigned char)((r0 / 255.0f) * 255.0f), (unsigned char)((r1 / 255.0f) * 255.0f),
+                               (unsigned char)((r2 / 255.0f) * 255.0f), 255);
+    } else if (type == DSB200_RENDER_COLOUR_FROM_NORMAL) {
+        uchar4 o = out[loc];   // drawPixelNormal leaves alpha untouched
+        o.x = (unsigned char)((0.3f + (-n[0] + 1.0f) * 0.35f) * 255.0f);
+        o.y = (unsigned char)((0.3f + (-n[1] + 1.0f) * 0.35f) * 255.0f);
+        o.z = (unsigned char)((0.3f + (-n[2] + 1.0f) * 0.35f) * 255.0f);
+        out[loc] = o;
+    } else {
+        unsigned char g = (unsigned char)((0.8f * angle + 0.2f) * 255.0f);
+        out[loc] = make_uchar4(g, g, g, g);
+    }
+}
+
+// ---------------------------------------------------------------- host launchers
+void launch_find_visible(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
+                         int *visibleIds, int visibleCapacity, int total)
+{
+    DSB_LAUNCH(k_reset_scan, 8, 256, 0, st, fs, fs.scanTiles, fs.scanTiles, 1);
+    DSB_LAUNCH(k_find_visible, fs.scanTiles, 256, 0, st, P, fs, hash, visibleIds, visibleCapacity, total);
+}
+
+void launch_count_visible(cudaStream_t st, const dsb200_hash_entry *hash, const int *ids, const int *count, int minId,
+                          int maxId, int *out)
+{
+    cudaMemsetAsync(out, 0, sizeof(int), st);
+    DSB_LAUNCH(k_count_visible, kNumSMs, 256, 0, st, hash, ids, count, minId, maxId, out);
+}
+
+void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_hash_entry *hash, const int *ids,
+                            const int *count, float *rangeImage, int *, Counters *counters)
+{
+    DSB_LAUNCH(k_range_init, kNumSMs * 4, 256, 0, st, reinterpret_cast<float2 *>(rangeImage), P.W * P.H, counters);
+    DSB_LAUNCH(k_project_fill, kNumSMs * 4, 256, 0, st, P, hash, ids, count, rangeImage, counters);
+    DSB_LAUNCH(k_range_cap_fallback, 1, 1024, 0, st, P, hash, ids, count, rangeImage, counters);
+}
+
+void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
+                    const float *rangeImage, float *raycastResult)
+{
+    dim3 grid(div_up(P.W, 16), div_up(P.H, 8));
+    DSB_LAUNCH(k_raycast, grid, 128, 0, st, P, voxels, hash, reinterpret_cast<const float2 *>(rangeImage),
+               reinterpret_cast<float4 *>(raycastResult));
+}
+
+void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,
+                     uint8_t *rendering)
+{
+    dim3 grid(div_up(P.W, 32), div_up(P.H, 8));
+    DSB_LAUNCH(k_icp_maps, grid, 256, 0, st, P, reinterpret_cast<const float4 *>(raycastResult),
+               reinterpret_cast<float4 *>(points), reinterpret_cast<float4 *>(normals), reinterpret_cast<uchar4 *>(rendering));
+}
+
+void launch_shade(cudaStream_t st, const RayParams &P, int renderType, const dsb200_voxel *voxels,
+                  const dsb200_hash_entry *hash, const float *raycastResult, uint8_t *outRGBA, float *outDepth)
+{
+    dim3 grid(div_up(P.W, 16), div_up(P.H, 8));
+    DSB_LAUNCH(k_shade, grid, 128, 0, st, P, renderType, voxels, hash, reinterpret_cast<const float4 *>(raycastResult),
+               reinterpret_cast<uchar4 *>(outRGBA), outDepth);
+}
+
+} // namespace dsb

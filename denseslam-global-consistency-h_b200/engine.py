@@ -1,0 +1,267 @@
+"""Host-side mirror of the reference's engine call surface, on top of the C ABI (libdsb200.so).
+
+Class / method names follow the reference so call sites read the same:
+  ITMSceneReconstructionEngine  (ITMLib/Engine/ITMSceneReconstructionEngine.h:45-96)
+  ITMVisualisationEngine        (ITMLib/Engine/ITMVisualisationEngine.h:71-124)
+  ITMScene / ITMRenderState_VH / ITMView / ITMTrackingState  (ITMLib/Objects/*.h)
+All heavy state lives in device memory owned through the C ABI helpers; numpy is used only to
+move data in and out.  Errors surface as abi.Dsb200Error carrying the reference's messages.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+def _lib():
+    return abi.load()
+
+
+class DeviceBuffer(object):
+    def __init__(self, nbytes):
+        self.nbytes = int(nbytes)
+        p = C.c_void_p()
+        abi.check(_lib().dsb200_device_alloc(C.byref(p), max(self.nbytes, 4)))
+        self.ptr = p.value
+
+    def upload(self, arr, stream=None):
+        a = np.ascontiguousarray(arr)
+        assert a.nbytes <= self.nbytes
+        abi.check(_lib().dsb200_memcpy_h2d(self.ptr, a.ctypes.data, a.nbytes, stream))
+        abi.check(_lib().dsb200_stream_synchronize(stream))
+
+    def download(self, dtype, count, stream=None):
+        out = np.empty(count, dtype=dtype)
+        abi.check(_lib().dsb200_memcpy_d2h(out.ctypes.data, self.ptr, out.nbytes, stream))
+        abi.check(_lib().dsb200_stream_synchronize(stream))
+        return out
+
+    def free(self):
+        if self.ptr:
+            _lib().dsb200_device_free(self.ptr)
+            self.ptr = None
+
+
+def _download(ptr, dtype, count):
+    out = np.empty(count, dtype=dtype)
+    if count:
+        abi.check(_lib().dsb200_memcpy_d2h(out.ctypes.data, ptr, out.nbytes, None))
+        abi.check(_lib().dsb200_stream_synchronize(None))
+    return out
+
+
+class ITMScene(object):
+    """Device-resident voxel-block-hash scene (Objects/ITMScene.h)."""
+
+    def __init__(self, params, num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS,
+                 excess_size=abi.DEFAULT_EXCESS, use_swapping=False):
+        self.c = abi.Scene()
+        abi.check(_lib().dsb200_scene_alloc(C.byref(self.c), num_blocks, bucket_num, excess_size))
+        self.c.params = params
+        self.c.use_swapping = 1 if use_swapping else 0
+
+    def free(self):
+        _lib().dsb200_scene_free(C.byref(self.c))
+
+    # state downloads (tests / checkpoints)
+    def hash(self):
+        return _download(self.c.hash, abi.HASH_DTYPE, self.c.total_entries)
+
+    def voxels(self, block_ptrs=None):
+        if block_ptrs is None:
+            return _download(self.c.voxels, abi.VOXEL_DTYPE, self.c.num_blocks * abi.BLOCK_SIZE3)
+        out = np.empty((len(block_ptrs), abi.BLOCK_SIZE3), dtype=abi.VOXEL_DTYPE)
+        for i, p in enumerate(block_ptrs):
+            out[i] = _download(self.c.voxels + int(p) * abi.BLOCK_SIZE3 * 8, abi.VOXEL_DTYPE, abi.BLOCK_SIZE3)
+        return out
+
+    def alloc_list(self):
+        return _download(self.c.alloc_list, np.int32, self.c.num_blocks)
+
+    def excess_list(self):
+        return _download(self.c.excess_list, np.int32, self.c.excess_size)
+
+
+class ITMRenderState_VH(object):
+    def __init__(self, total_entries, width, height, visible_capacity=abi.DEFAULT_LOCAL_BLOCKS):
+        self.c = abi.RenderState()
+        self.total_entries = total_entries
+        abi.check(_lib().dsb200_render_state_alloc(C.byref(self.c), total_entries, visible_capacity, width, height))
+
+    def free(self):
+        _lib().dsb200_render_state_free(C.byref(self.c))
+
+    def visible(self):
+        return _download(self.c.visible_ids, np.int32, min(self.c.no_visible, self.c.visible_capacity))
+
+    def visible_type(self):
+        return _download(self.c.visible_type, np.uint8, self.total_entries)
+
+    def range_image(self):
+        return _download(self.c.range_image, np.float32, self.c.width * self.c.height * 2).reshape(self.c.height, self.c.width, 2)
+
+    def raycast_result(self):
+        return _download(self.c.raycast_result, np.float32, self.c.width * self.c.height * 4).reshape(self.c.height, self.c.width, 4)
+
+    def raycast_image(self):
+        return _download(self.c.raycast_image, np.uint8, self.c.width * self.c.height * 4).reshape(self.c.height, self.c.width, 4)
+
+
+class ITMView(object):
+    """Depth + rgb on the device with calibration (Objects/ITMView.h)."""
+
+    def __init__(self, width, height, intr_d, intr_rgb=None, rgb_to_depth_inv=None):
+        self.W, self.H = width, height
+        self.depth = DeviceBuffer(width * height * 4)
+        self.rgb = DeviceBuffer(width * height * 4)
+        self.c = abi.View()
+        self.c.depth, self.c.rgb = self.depth.ptr, self.rgb.ptr
+        self.c.depth_w, self.c.depth_h, self.c.rgb_w, self.c.rgb_h = width, height, width, height
+        self.c.intr_d = abi.f4(intr_d)
+        self.c.intr_rgb = abi.f4(intr_rgb if intr_rgb is not None else intr_d)
+        self.c.rgb_to_depth_inv = abi.f16(rgb_to_depth_inv if rgb_to_depth_inv is not None else abi.IDENTITY16)
+
+    def update(self, depth, rgb, timestamp=0.0):
+        self.depth.upload(np.asarray(depth, np.float32))
+        self.rgb.upload(np.asarray(rgb, np.uint8))
+        self.c.timestamp = timestamp
+
+    def free(self):
+        self.depth.free()
+        self.rgb.free()
+
+
+class ITMTrackingState(object):
+    def __init__(self, width, height):
+        self.W, self.H = width, height
+        self.points = DeviceBuffer(width * height * 16)
+        self.normals = DeviceBuffer(width * height * 16)
+        self.c = abi.Tracking()
+        self.c.icp_points, self.c.icp_normals = self.points.ptr, self.normals.ptr
+        self.c.requires_full_rendering = 1
+        self.set_pose(abi.IDENTITY16)
+
+    def set_pose(self, M, invM=None):
+        """pose_d->SetM: M is world->camera, column-major. invM defaults to the cofactor inverse."""
+        self.c.M_d = abi.f16(M)
+        if invM is None:
+            out = (C.c_float * 16)()
+            if not _lib().dsb200_mat4_inverse(self.c.M_d, out):
+                raise ValueError("singular pose matrix")
+            self.c.invM_d = out
+        else:
+            self.c.invM_d = abi.f16(invM)
+
+    def icp_points(self):
+        return self.points.download(np.float32, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+    def icp_normals(self):
+        return self.normals.download(np.float32, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+    def free(self):
+        self.points.free()
+        self.normals.free()
+
+
+class ITMSceneReconstructionEngine(object):
+    def __init__(self, num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS, excess_size=abi.DEFAULT_EXCESS,
+                 stream=None):
+        self.h = C.c_void_p()
+        abi.check(_lib().dsb200_recon_create(C.byref(self.h), num_blocks, bucket_num, excess_size, stream))
+
+    def close(self):
+        if self.h:
+            _lib().dsb200_recon_destroy(self.h)
+            self.h = None
+
+    def SetAsync(self, flag):
+        abi.check(_lib().dsb200_recon_set_async(self.h, 1 if flag else 0))
+
+    def Sync(self, scene, renderState):
+        abi.check(_lib().dsb200_recon_sync(self.h, C.byref(scene.c), C.byref(renderState.c)))
+
+    def ResetScene(self, scene):
+        abi.check(_lib().dsb200_reset_scene(self.h, C.byref(scene.c)))
+
+    def AllocateSceneFromDepth(self, scene, view, trackingState, renderState, onlyUpdateVisibleList=False, isDefusion=False):
+        abi.check(_lib().dsb200_allocate_from_depth(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c),
+                                                    C.byref(renderState.c), int(onlyUpdateVisibleList), int(isDefusion)))
+
+    def IntegrateIntoScene(self, scene, view, trackingState, renderState):
+        abi.check(_lib().dsb200_integrate(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c), C.byref(renderState.c)))
+
+    def DeIntegrateIntoScene(self, scene, view, trackingState):
+        abi.check(_lib().dsb200_deintegrate(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c)))
+
+    def Decay(self, scene, renderState, maxWeight, minAge, forceAllVoxels=False):
+        abi.check(_lib().dsb200_decay(self.h, C.byref(scene.c), C.byref(renderState.c), maxWeight, minAge, int(forceAllVoxels)))
+
+    def DecayDefusionPart(self, scene, renderState, maxWeight, minAge, forceAllVoxels=False):
+        abi.check(_lib().dsb200_decay_defusion(self.h, C.byref(scene.c), C.byref(renderState.c), maxWeight, minAge, int(forceAllVoxels)))
+
+    def SlideWindow(self, scene, renderState, maxAge):
+        abi.check(_lib().dsb200_slide_window(self.h, C.byref(scene.c), C.byref(renderState.c), maxAge))
+
+    def SlideWindowDefusionPart(self, scene, renderState, maxAge, maxSize):
+        abi.check(_lib().dsb200_slide_window_defusion(self.h, C.byref(scene.c), C.byref(renderState.c), maxAge, maxSize))
+
+    def GetDecayedBlockCount(self):
+        return int(_lib().dsb200_decayed_block_count(self.h))
+
+    def SetFusionWeightParams(self, depthWeighting, maxNewW=10, maxDistance=100):
+        wp = abi.WeightParams(int(depthWeighting), maxNewW, maxDistance)
+        abi.check(_lib().dsb200_set_fusion_weight_params(self.h, C.byref(wp)))
+
+    def HistorySizes(self):
+        v = [C.c_int() for _ in range(5)]
+        _lib().dsb200_history_sizes(self.h, *[C.byref(x) for x in v])
+        return tuple(x.value for x in v)
+
+    def ProcessFrame(self, vis, scene, view, trackingState, renderState, stages=abi.FRAME_ALL):
+        """ITMDenseMapper::ProcessFrame + ITMTrackingController::Prepare as one submission."""
+        abi.check(_lib().dsb200_process_frame(self.h, vis.h if vis is not None else None, C.byref(scene.c), C.byref(view.c),
+                                              C.byref(trackingState.c), C.byref(renderState.c), stages))
+
+
+class ITMVisualisationEngine(object):
+    def __init__(self, width, height, max_visible=abi.DEFAULT_LOCAL_BLOCKS, stream=None):
+        self.h = C.c_void_p()
+        abi.check(_lib().dsb200_vis_create(C.byref(self.h), max_visible, width, height, stream))
+
+    def close(self):
+        if self.h:
+            _lib().dsb200_vis_destroy(self.h)
+            self.h = None
+
+    def CreateRenderState(self, scene, imgSize, visible_capacity=None):
+        return ITMRenderState_VH(scene.c.total_entries, imgSize[0], imgSize[1],
+                                 visible_capacity if visible_capacity else scene.c.num_blocks)
+
+    def FindVisibleBlocks(self, scene, M, intrinsics, renderState):
+        abi.check(_lib().dsb200_find_visible_blocks(self.h, C.byref(scene.c), abi.f16(M), abi.f4(intrinsics), C.byref(renderState.c)))
+
+    def CountVisibleBlocks(self, scene, renderState, minBlockId, maxBlockId):
+        n = C.c_int()
+        abi.check(_lib().dsb200_count_visible_blocks(self.h, C.byref(scene.c), C.byref(renderState.c), minBlockId, maxBlockId, C.byref(n)))
+        return n.value
+
+    def CreateExpectedDepths(self, scene, M, intrinsics, renderState):
+        abi.check(_lib().dsb200_create_expected_depths(self.h, C.byref(scene.c), abi.f16(M), abi.f4(intrinsics), C.byref(renderState.c)))
+
+    def FindSurface(self, scene, invM, intrinsics, renderState):
+        abi.check(_lib().dsb200_find_surface(self.h, C.byref(scene.c), abi.f16(invM), abi.f4(intrinsics), C.byref(renderState.c)))
+
+    def CreateICPMaps(self, scene, view, trackingState, renderState):
+        abi.check(_lib().dsb200_create_icp_maps(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c), C.byref(renderState.c)))
+
+    def RenderImage(self, scene, M, invM, intrinsics, renderState, outImage, outFloat, renderType=abi.RENDER_SHADED_GREYSCALE):
+        abi.check(_lib().dsb200_render_image(self.h, C.byref(scene.c), abi.f16(M), abi.f16(invM), abi.f4(intrinsics),
+                                             C.byref(renderState.c), outImage.ptr, outFloat.ptr if outFloat is not None else None,
+                                             renderType))
+
+    def ForwardRender(self, scene, view, trackingState, renderState):
+        abi.check(_lib().dsb200_forward_render(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c), C.byref(renderState.c)))
+
+    def CreatePointCloud(self):
+        abi.check(_lib().dsb200_create_point_cloud(self.h))

@@ -374,7 +374,9 @@ int rst_allocate_from_depth(rst_recon *e, dsb200_scene *scene, const dsb200_view
 namespace {
 
 inline float sdfToFloat(float x) { return (float)(x) / 32767.0f; }        // SDF_valueToFloat, ITMLibDefines.h:131
-inline short sdfToShort(float x) { return (short)((x) * 32767.0f); }       // SDF_floatToValue, :132
+// SDF_floatToValue, :132.  gcc lowers (short)(float) to cvttss2si + truncation, i.e. (short)(int); spelled out so
+// the GPU (whose direct float->short conversion saturates) can be written identically.
+inline short sdfToShort(float x) { return (short)(int)((x) * 32767.0f); }
 
 // ROUND (ORUtils/MathUtils.h:24) then (int), then CLAMP 0..255: Vector3::toUChar, ORUtils/Vector.h:245-247
 inline unsigned char toUChar(float v)
@@ -456,11 +458,14 @@ inline void updateColour(dsb200_voxel &vox, V4 pt, const float *Mrgb, const floa
         newC[k] = DE ? (oldC[k] * oldW - meas * newW) : (oldC[k] * oldW + meas * newW);
     }
     newW = DE ? (oldW - newW) : (oldW + newW);
+    if (DE && newW == 0.0f) {   // reference divides by zero and casts inf/NaN to uchar (UB): defined as "no colour left"
+        vox.clr[0] = vox.clr[1] = vox.clr[2] = 0; vox.w_color = 0; return;
+    }
     for (int k = 0; k < 3; k++) newC[k] /= newW;
     newW = (newW < maxW) ? newW : (float)maxW;
     // float->uchar of NaN/inf (DE with oldW==1) is UB in the reference; our definition: via toUChar's int cast
     for (int k = 0; k < 3; k++) vox.clr[k] = toUChar(newC[k] * 255.0f);
-    vox.w_color = (unsigned char)newW;
+    vox.w_color = (unsigned char)(int)newW;
 }
 
 template <bool DE>

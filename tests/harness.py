@@ -1,0 +1,300 @@
+"""Two interchangeable back ends behind one interface, so parity tests read as
+`run the same calls on both, compare the state`:
+
+  OracleBackend  -> oracle/librestate.so   (CPU restatement; the checker)
+  GpuBackend     -> libdsb200.so via the package's engine mirror (the product; needs a B200)
+  RefBackend     -> oracle/_ref/libitmref.so (unmodified reference CPU engines; fixed capacities,
+                    no decay / slide window / de-integration -- the reference CPU engine throws)
+"""
+import ctypes as C
+import importlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+PKG = "denseslam-global-consistency-h_b200"
+abi = importlib.import_module(PKG + ".abi")
+synth = importlib.import_module(PKG + ".synth")
+import pyoracle as po  # noqa: E402
+
+SMALL_CAPS = dict(num_blocks=0x4000, bucket_num=0x8000, excess_size=0x2000)
+
+
+def has_ref():
+    return os.path.exists(po.REF_PATH)
+
+
+def has_gpu():
+    try:
+        return abi.load().dsb200_device_count() > 0
+    except Exception:
+        return False
+
+
+class OracleBackend(object):
+    name = "oracle"
+
+    def __init__(self, cfg, caps=None, use_swapping=False):
+        caps = caps or {}
+        self.cfg = cfg
+        self.o = po.Oracle()
+        self.scene = po.HostScene(cfg.params(), use_swapping=use_swapping, **caps)
+        vis_cap = caps.get("num_blocks", abi.DEFAULT_LOCAL_BLOCKS)
+        self.rs = po.HostRenderState(self.scene.c.total_entries, cfg.W, cfg.H, vis_cap)
+        self.rs_free = po.HostRenderState(self.scene.c.total_entries, cfg.W, cfg.H, vis_cap)
+        self.e = self.o.L.rst_recon_create(self.scene.c.num_blocks, self.scene.c.bucket_num, self.scene.c.excess_size)
+        self.pts = np.zeros((cfg.H, cfg.W, 4), np.float32)
+        self.nrm = np.zeros((cfg.H, cfg.W, 4), np.float32)
+        self.out_img = np.zeros((cfg.H, cfg.W, 4), np.uint8)
+        self.out_depth = np.zeros((cfg.H, cfg.W), np.float32)
+        self.view = None
+        self.trk = None
+        self.requires_full_rendering = True
+        self.reset()
+
+    def close(self):
+        self.o.L.rst_recon_destroy(self.e)
+
+    def reset(self):
+        self.o.L.rst_reset_scene(self.e, C.byref(self.scene.c))
+
+    def set_weights(self, depth_weighting, max_new_w=10, max_distance=100):
+        wp = abi.WeightParams(int(depth_weighting), max_new_w, max_distance)
+        self.o.L.rst_set_fusion_weight_params(self.e, C.byref(wp))
+
+    def set_frame(self, f, M=None):
+        self._f = f
+        M = f.M if M is None else M
+        self.view = po.make_view(f.depth, f.rgb, self.cfg.intr, timestamp=f.timestamp)
+        self.trk = po.make_tracking(M, self.o.mat4_inverse(M), self.pts, self.nrm, self.requires_full_rendering)
+
+    def allocate(self, only_visible=False, is_defusion=False):
+        return self.o.L.rst_allocate_from_depth(self.e, C.byref(self.scene.c), C.byref(self.view), C.byref(self.trk),
+                                                C.byref(self.rs.c), int(only_visible), int(is_defusion))
+
+    def integrate(self):
+        self.o.L.rst_integrate(self.e, C.byref(self.scene.c), C.byref(self.view), C.byref(self.trk), C.byref(self.rs.c))
+
+    def deintegrate(self):
+        self.o.L.rst_deintegrate(self.e, C.byref(self.scene.c), C.byref(self.view), C.byref(self.trk))
+
+    def decay(self, max_weight, min_age):
+        self.o.L.rst_decay(self.e, C.byref(self.scene.c), C.byref(self.rs.c), max_weight, min_age, 0)
+
+    def decay_defusion(self, max_weight, min_age):
+        self.o.L.rst_decay_defusion(self.e, C.byref(self.scene.c), C.byref(self.rs.c), max_weight, min_age, 0)
+
+    def slide_window(self, max_age):
+        self.o.L.rst_slide_window(self.e, C.byref(self.scene.c), C.byref(self.rs.c), max_age)
+
+    def slide_window_defusion(self, max_age, max_size):
+        self.o.L.rst_slide_window_defusion(self.e, C.byref(self.scene.c), C.byref(self.rs.c), max_age, max_size)
+
+    def decayed_blocks(self):
+        return int(self.o.L.rst_decayed_block_count(self.e))
+
+    def history_sizes(self):
+        v = [C.c_int() for _ in range(5)]
+        self.o.L.rst_history_sizes(self.e, *[C.byref(x) for x in v])
+        return tuple(x.value for x in v)
+
+    def expected_depths(self):
+        self.o.L.rst_create_expected_depths(C.byref(self.scene.c), self.trk.M_d, self.view.intr_d, C.byref(self.rs.c))
+
+    def icp_maps(self):
+        self.o.L.rst_create_icp_maps(C.byref(self.scene.c), C.byref(self.view), C.byref(self.trk), C.byref(self.rs.c))
+
+    def process_frame(self):
+        rc = self.allocate()
+        self.integrate()
+        self.expected_depths()
+        self.icp_maps()
+        return rc
+
+    def free_view(self, M, intr, render_type=0):
+        Mc, iM, ic = abi.f16(M), abi.f16(self.o.mat4_inverse(M)), abi.f4(intr)
+        self.o.L.rst_find_visible_blocks(C.byref(self.scene.c), Mc, ic, C.byref(self.rs_free.c))
+        self.o.L.rst_create_expected_depths(C.byref(self.scene.c), Mc, ic, C.byref(self.rs_free.c))
+        self.o.L.rst_render_image(C.byref(self.scene.c), Mc, iM, ic, C.byref(self.rs_free.c), self.out_img.ctypes.data,
+                                  self.out_depth.ctypes.data, render_type)
+
+    def count_visible(self, lo, hi):
+        return self.o.L.rst_count_visible_blocks(C.byref(self.scene.c), C.byref(self.rs.c), lo, hi)
+
+    # ---- state
+    def state(self, voxels=True):
+        s = dict(hash=self.scene.hash.copy(), visible=self.rs.visible(), visible_type=self.rs.visible_type.copy(),
+                 last_free=(self.scene.c.last_free_block, self.scene.c.last_free_excess),
+                 alloc_list=self.scene.alloc_list.copy(), excess_list=self.scene.excess_list.copy())
+        if voxels:
+            s["voxels"] = self.scene.voxels.copy()
+        return s
+
+    def images(self):
+        return dict(range=self.rs.range_image.copy(), raycast=self.rs.raycast_result.copy(), points=self.pts.copy(),
+                    normals=self.nrm.copy(), rendering=self.rs.raycast_image.copy())
+
+    def free_images(self):
+        return dict(visible=self.rs_free.visible(), range=self.rs_free.range_image.copy(),
+                    raycast=self.rs_free.raycast_result.copy(), image=self.out_img.copy(), depth=self.out_depth.copy())
+
+
+class GpuBackend(object):
+    name = "gpu"
+
+    def __init__(self, cfg, caps=None, use_swapping=False):
+        eng = importlib.import_module(PKG + ".engine")
+        caps = caps or {}
+        self.cfg, self.eng = cfg, eng
+        nb = caps.get("num_blocks", abi.DEFAULT_LOCAL_BLOCKS)
+        bn = caps.get("bucket_num", abi.DEFAULT_BUCKETS)
+        ex = caps.get("excess_size", abi.DEFAULT_EXCESS)
+        self.scene = eng.ITMScene(cfg.params(), nb, bn, ex, use_swapping)
+        self.recon = eng.ITMSceneReconstructionEngine(nb, bn, ex)
+        self.vis = eng.ITMVisualisationEngine(cfg.W, cfg.H)
+        self.rs = self.vis.CreateRenderState(self.scene, (cfg.W, cfg.H))
+        self.rs_free = self.vis.CreateRenderState(self.scene, (cfg.W, cfg.H))
+        self.view = eng.ITMView(cfg.W, cfg.H, cfg.intr)
+        self.trk = eng.ITMTrackingState(cfg.W, cfg.H)
+        self.out_img = eng.DeviceBuffer(cfg.W * cfg.H * 4)
+        self.out_depth = eng.DeviceBuffer(cfg.W * cfg.H * 4)
+        self.out_img.upload(np.zeros(cfg.W * cfg.H * 4, np.uint8))
+        self.out_depth.upload(np.zeros(cfg.W * cfg.H, np.float32))
+        self.reset()
+
+    def close(self):
+        self.recon.close(); self.vis.close()
+        for o in (self.scene, self.rs, self.rs_free, self.view, self.trk, self.out_img, self.out_depth):
+            o.free()
+
+    requires_full_rendering = True
+
+    def reset(self):
+        self.recon.ResetScene(self.scene)
+
+    def set_weights(self, depth_weighting, max_new_w=10, max_distance=100):
+        self.recon.SetFusionWeightParams(depth_weighting, max_new_w, max_distance)
+
+    def set_frame(self, f, M=None):
+        self.view.update(f.depth, f.rgb, f.timestamp)
+        self.trk.set_pose(f.M if M is None else M)
+        self.trk.c.requires_full_rendering = 1 if self.requires_full_rendering else 0
+
+    def _rc(self, fn, *a, **k):
+        try:
+            fn(*a, **k)
+            return 0
+        except abi.Dsb200Error as e:
+            if e.code in (abi.ERR_VBA_EXHAUSTED, abi.ERR_EXCESS_EXHAUSTED):
+                return e.code
+            raise
+
+    def allocate(self, only_visible=False, is_defusion=False):
+        return self._rc(self.recon.AllocateSceneFromDepth, self.scene, self.view, self.trk, self.rs, only_visible, is_defusion)
+
+    def integrate(self):
+        self.recon.IntegrateIntoScene(self.scene, self.view, self.trk, self.rs)
+
+    def deintegrate(self):
+        self.recon.DeIntegrateIntoScene(self.scene, self.view, self.trk)
+
+    def decay(self, max_weight, min_age):
+        self.recon.Decay(self.scene, self.rs, max_weight, min_age)
+
+    def decay_defusion(self, max_weight, min_age):
+        self.recon.DecayDefusionPart(self.scene, self.rs, max_weight, min_age)
+
+    def slide_window(self, max_age):
+        self.recon.SlideWindow(self.scene, self.rs, max_age)
+
+    def slide_window_defusion(self, max_age, max_size):
+        self.recon.SlideWindowDefusionPart(self.scene, self.rs, max_age, max_size)
+
+    def decayed_blocks(self):
+        return self.recon.GetDecayedBlockCount()
+
+    def history_sizes(self):
+        return self.recon.HistorySizes()
+
+    def expected_depths(self):
+        self.vis.CreateExpectedDepths(self.scene, self.trk.c.M_d, self.cfg.intr, self.rs)
+
+    def icp_maps(self):
+        self.vis.CreateICPMaps(self.scene, self.view, self.trk, self.rs)
+
+    def process_frame(self):
+        return self._rc(self.recon.ProcessFrame, self.vis, self.scene, self.view, self.trk, self.rs)
+
+    def free_view(self, M, intr, render_type=0):
+        lib = abi.load()
+        Mc = abi.f16(M)
+        iM = (C.c_float * 16)()
+        lib.dsb200_mat4_inverse(Mc, iM)
+        self.vis.FindVisibleBlocks(self.scene, M, intr, self.rs_free)
+        self.vis.CreateExpectedDepths(self.scene, M, intr, self.rs_free)
+        self.vis.RenderImage(self.scene, M, iM, intr, self.rs_free, self.out_img, self.out_depth, render_type)
+
+    def count_visible(self, lo, hi):
+        return self.vis.CountVisibleBlocks(self.scene, self.rs, lo, hi)
+
+    def state(self, voxels=True):
+        s = dict(hash=self.scene.hash(), visible=self.rs.visible(), visible_type=self.rs.visible_type(),
+                 last_free=(self.scene.c.last_free_block, self.scene.c.last_free_excess),
+                 alloc_list=self.scene.alloc_list(), excess_list=self.scene.excess_list())
+        if voxels:
+            s["voxels"] = self.scene.voxels()
+        return s
+
+    def images(self):
+        return dict(range=self.rs.range_image(), raycast=self.rs.raycast_result(), points=self.trk.icp_points(),
+                    normals=self.trk.icp_normals(), rendering=self.rs.raycast_image())
+
+    def free_images(self):
+        n = self.cfg.W * self.cfg.H
+        return dict(visible=self.rs_free.visible(), range=self.rs_free.range_image(), raycast=self.rs_free.raycast_result(),
+                    image=self.out_img.download(np.uint8, n * 4).reshape(self.cfg.H, self.cfg.W, 4),
+                    depth=self.out_depth.download(np.float32, n).reshape(self.cfg.H, self.cfg.W))
+
+
+# ---------------------------------------------------------------- comparators
+def bits(a):
+    a = np.ascontiguousarray(a)
+    return a.view(np.uint32) if a.dtype == np.float32 else a
+
+
+def assert_state_equal(a, b, what="", voxels=True, free_lists=True):
+    """Bit-exact: hash (pos, offset, ptr; allocated_time excluded per SURVEY A9), visible list,
+    visibility flags, free-list tops (+ the live part of the free lists), voxels."""
+    for k in ("pos", "offset", "ptr"):
+        bad = np.nonzero(np.any(a["hash"][k] != b["hash"][k], axis=-1) if k == "pos" else (a["hash"][k] != b["hash"][k]))[0]
+        assert bad.size == 0, "%s hash.%s differs at %d slots, first %s: %s vs %s" % (
+            what, k, bad.size, bad[:5], a["hash"][k][bad[:5]], b["hash"][k][bad[:5]])
+    assert a["last_free"] == b["last_free"], "%s free-list tops %s vs %s" % (what, a["last_free"], b["last_free"])
+    assert np.array_equal(a["visible"], b["visible"]), "%s visible list differs (%d vs %d)" % (what, len(a["visible"]), len(b["visible"]))
+    assert np.array_equal(a["visible_type"], b["visible_type"]), "%s visible_type differs at %d slots" % (
+        what, int((a["visible_type"] != b["visible_type"]).sum()))
+    if free_lists:
+        n = a["last_free"][0] + 1
+        assert np.array_equal(a["alloc_list"][:max(n, 0)], b["alloc_list"][:max(n, 0)]), "%s VBA free list differs" % what
+    if voxels and "voxels" in a and "voxels" in b:
+        va, vb = a["voxels"].view(np.uint64), b["voxels"].view(np.uint64)
+        if not np.array_equal(va, vb):
+            bad = np.nonzero(va != vb)[0]
+            d = np.abs(a["voxels"]["sdf"][bad].astype(np.int32) - b["voxels"]["sdf"][bad].astype(np.int32))
+            raise AssertionError("%s voxels differ at %d of %d (max |dsdf| %d LSB), first idx %s: %s vs %s" % (
+                what, bad.size, va.size, int(d.max()), bad[:3], a["voxels"][bad[:3]], b["voxels"][bad[:3]]))
+
+
+def assert_images_equal(a, b, what=""):
+    for k in sorted(a.keys()):
+        x, y = bits(a[k]), bits(b[k])
+        if not np.array_equal(x, y):
+            bad = np.nonzero(x.reshape(-1) != y.reshape(-1))[0]
+            raise AssertionError("%s image '%s' differs at %d of %d elements; first %s: %s vs %s" % (
+                what, k, bad.size, x.size, bad[:4], a[k].reshape(-1)[bad[:4]], b[k].reshape(-1)[bad[:4]]))

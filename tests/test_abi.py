@@ -1,0 +1,67 @@
+"""The C-ABI library loads and exports every symbol include/dsb200.h declares (no GPU needed)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+import harness as hz
+from harness import abi
+
+HEADER = os.path.join(hz.ROOT, "include", "dsb200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(dsb200_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(abi.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    return abi.load()
+
+
+def test_header_symbols_exported(lib):
+    syms = declared_symbols()
+    assert len(syms) >= 40
+    missing = [s for s in syms if not hasattr(lib, s)]
+    assert not missing, "declared in dsb200.h but not exported: %s" % missing
+    # and the ctypes mirror declares a prototype for each of them
+    assert sorted(lib._declared) == syms
+
+
+def test_struct_layouts_match_reference_sizes():
+    assert abi.HASH_DTYPE.itemsize == 20      # sizeof(ITMHashEntry), SURVEY 2.4
+    assert abi.VOXEL_DTYPE.itemsize == 8      # sizeof(ITMVoxel_s_rgb)
+    assert C.sizeof(abi.SceneParams) == 24
+    assert C.sizeof(abi.WeightParams) == 12
+    assert abi.DEFAULT_BUCKETS + abi.DEFAULT_EXCESS == 1441792   # ITMVoxelBlockHash::noTotalEntries
+
+
+def test_product_fails_loudly_without_gpu(lib):
+    if lib.dsb200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    h = C.c_void_p()
+    rc = lib.dsb200_recon_create(C.byref(h), 1024, 1024, 256, None)
+    assert rc == abi.ERR_NO_DEVICE
+    assert b"no CPU fallback" in lib.dsb200_last_error()
+    with pytest.raises(abi.Dsb200Error):
+        abi.check(rc)
+
+
+def test_host_matrix_helpers_match_oracle(lib):
+    import numpy as np
+    o = hz.po.Oracle()
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        M = rng.normal(size=16).astype(np.float32)
+        out = (C.c_float * 16)()
+        assert lib.dsb200_mat4_inverse(abi.f16(M), out)
+        assert np.array_equal(np.array(out[:], np.float32).view(np.uint32), o.mat4_inverse(M).view(np.uint32))
+        B = rng.normal(size=16).astype(np.float32)
+        lib.dsb200_mat4_multiply(abi.f16(M), abi.f16(B), out)
+        assert np.array_equal(np.array(out[:], np.float32).view(np.uint32), o.mat4_multiply(M, B).view(np.uint32))

@@ -1,0 +1,97 @@
+"""GPU parity tests proper: libdsb200 (through the C ABI) vs the CPU oracle on the same seeded inputs.
+Bit-exact on everything (the north star only asks +-1 LSB on voxels and 1e-3 on raycast depth)."""
+import numpy as np
+import pytest
+
+import harness as hz
+from harness import abi, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def run_sequence(cfg_name, n_frames, caps, fused=True, use_swapping=False, weights=None, check_every=1, seed=0):
+    cfg, frames = synth.make_sequence(cfg_name, n_frames, seed=seed)
+    gpu, ora = hz.GpuBackend(cfg, caps, use_swapping), hz.OracleBackend(cfg, caps, use_swapping)
+    if weights:
+        gpu.set_weights(*weights); ora.set_weights(*weights)
+    for i, f in enumerate(frames):
+        gpu.set_frame(f); ora.set_frame(f)
+        if fused:
+            rg, ro = gpu.process_frame(), ora.process_frame()
+        else:
+            rg, ro = gpu.allocate(), ora.allocate()
+            gpu.integrate(); ora.integrate()
+            gpu.expected_depths(); ora.expected_depths()
+            gpu.icp_maps(); ora.icp_maps()
+        assert rg == ro
+        if i % check_every == 0 or i == n_frames - 1:
+            hz.assert_state_equal(ora.state(), gpu.state(), "%s frame %d" % (cfg_name, i))
+            hz.assert_images_equal(ora.images(), gpu.images(), "%s frame %d" % (cfg_name, i))
+    return cfg, frames, gpu, ora
+
+
+def test_tiny_room_fused_sequence():
+    cfg, frames, gpu, ora = run_sequence("tiny", 12, hz.SMALL_CAPS)
+    assert gpu.rs.c.no_visible > 200
+    gpu.close(); ora.close()
+
+
+def test_tiny_room_stagewise_calls():
+    cfg, frames, gpu, ora = run_sequence("tiny", 4, hz.SMALL_CAPS, fused=False)
+    gpu.close(); ora.close()
+
+
+def test_tiny_street_depth_weighting():
+    cfg, frames, gpu, ora = run_sequence("tiny_street", 8, hz.SMALL_CAPS, weights=(True, 10, 100))
+    gpu.close(); ora.close()
+
+
+def test_use_swapping_enlarged_frustum():
+    cfg, frames, gpu, ora = run_sequence("tiny", 6, hz.SMALL_CAPS, use_swapping=True)
+    gpu.close(); ora.close()
+
+
+def test_heavy_hash_collisions_excess_chains():
+    # 256 buckets for thousands of blocks: almost every allocation goes through the excess list
+    caps = dict(num_blocks=0x4000, bucket_num=256, excess_size=0x4000)
+    cfg, frames, gpu, ora = run_sequence("tiny", 6, caps)
+    h = gpu.scene.hash()
+    assert (h["offset"] > 0).sum() > 500
+    gpu.close(); ora.close()
+
+
+def test_vba_exhaustion_reports_reference_error():
+    caps = dict(num_blocks=256, bucket_num=0x8000, excess_size=0x2000)
+    cfg, frames = synth.make_sequence("tiny", 2)
+    gpu, ora = hz.GpuBackend(cfg, caps), hz.OracleBackend(cfg, caps)
+    gpu.set_frame(frames[0]); ora.set_frame(frames[0])
+    rg, ro = gpu.allocate(), ora.allocate()
+    assert rg == ro == abi.ERR_VBA_EXHAUSTED
+    hz.assert_state_equal(ora.state(voxels=False), gpu.state(voxels=False), "exhausted", free_lists=False)
+    gpu.close(); ora.close()
+
+
+def test_free_view_render_all_types():
+    cfg, frames, gpu, ora = run_sequence("tiny", 6, hz.SMALL_CAPS, check_every=100)
+    M = frames[2].M
+    for rtype in (abi.RENDER_SHADED_GREYSCALE, abi.RENDER_COLOUR_FROM_VOLUME, abi.RENDER_COLOUR_FROM_NORMAL, abi.RENDER_DEPTH_MAP):
+        gpu.free_view(M, cfg.intr, rtype); ora.free_view(M, cfg.intr, rtype)
+        a, b = ora.free_images(), gpu.free_images()
+        assert np.array_equal(a.pop("visible"), b.pop("visible"))
+        hz.assert_images_equal(a, b, "free view type %d" % rtype)
+    assert gpu.count_visible(0, 1 << 30) == ora.count_visible(0, 1 << 30) > 0
+    assert gpu.count_visible(100, 200) == ora.count_visible(100, 200)
+    gpu.close(); ora.close()
+
+
+def test_c1_full_size_frames():
+    # BASELINE configs[0]: 640x480, 5 mm voxels, reference capacities
+    cfg, frames, gpu, ora = run_sequence("C1", 3, None)
+    assert gpu.rs.c.no_visible > 5000
+    gpu.close(); ora.close()
+
+
+def test_c2_kitti_shaped_frames():
+    cfg, frames, gpu, ora = run_sequence("C2", 3, None, weights=(True, 10, 100))
+    assert gpu.rs.c.no_visible > 5000
+    gpu.close(); ora.close()

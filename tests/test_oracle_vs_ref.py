@@ -1,0 +1,62 @@
+"""Pin the CPU restatement (oracle/restate.cpp) against the UNMODIFIED reference CPU engines
+compiled from /root/reference (oracle/_ref).  Bit-exact on every output.  Skipped where the
+reference build is absent; the committed fixtures (test_golden.py) carry the same evidence."""
+import numpy as np
+import pytest
+
+import harness as hz
+from harness import abi, synth, po
+
+pytestmark = pytest.mark.skipif(not hz.has_ref(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+def run_pair(cfg_name, n_frames, use_swapping=False, weights=False):
+    cfg, frames = synth.make_sequence(cfg_name, n_frames)
+    ref = po.RefEngine(cfg.W, cfg.H, cfg.params(), use_swapping=use_swapping)
+    ref.set_calib(cfg.intr)
+    ora = hz.OracleBackend(cfg, use_swapping=use_swapping)
+    for i, f in enumerate(frames):
+        ref.set_view(f.depth, f.rgb, f.timestamp); ref.set_pose(f.M)
+        Mr, iMr = ref.get_pose()
+        assert np.array_equal(Mr, f.M)
+        assert np.array_equal(iMr.view(np.uint32), ora.o.mat4_inverse(f.M).view(np.uint32))
+        ref.allocate(); ref.integrate(); ref.create_expected_depths(); ref.create_icp_maps()
+        ora.set_frame(f); ora.process_frame()
+        s = ora.state()
+        rstate = dict(hash=ref.hash(), visible=ref.visible(), visible_type=ref.visible_type(), last_free=ref.last_free(),
+                      alloc_list=ref.alloc_list(), excess_list=ref.excess_list(), voxels=ref.voxels())
+        hz.assert_state_equal(rstate, s, "frame %d ref-vs-oracle" % i)
+        hz.assert_images_equal(dict(range=ref.range_image(), raycast=ref.raycast_result(), points=ref.icp_points(),
+                                    normals=ref.icp_normals(), rendering=ref.icp_rendering()), ora.images(), "frame %d" % i)
+    return cfg, frames, ref, ora
+
+
+def test_c1_sequence_bit_exact():
+    cfg, frames, ref, ora = run_pair("C1", 3)
+    assert ora.rs.c.no_visible > 1000
+    ref.close(); ora.close()
+
+
+def test_tiny_sequence_and_free_view_bit_exact():
+    cfg, frames, ref, ora = run_pair("tiny", 8)
+    # free-view render path (ITMMainEngine::GetImage): FindVisibleBlocks + CreateExpectedDepths + RenderImage
+    M = frames[3].M
+    for rtype in (abi.RENDER_SHADED_GREYSCALE, abi.RENDER_COLOUR_FROM_VOLUME, abi.RENDER_COLOUR_FROM_NORMAL):
+        ref.render_free_view(M, cfg.intr, rtype)
+        ora.out_img[:] = 0
+        ref.out_image()[:] = 0 if rtype == abi.RENDER_COLOUR_FROM_NORMAL else ref.out_image()
+        if rtype == abi.RENDER_COLOUR_FROM_NORMAL:
+            ref.render_free_view(M, cfg.intr, rtype)
+        ora.free_view(M, cfg.intr, rtype)
+        fi = ora.free_images()
+        assert np.array_equal(ref.visible(True), fi["visible"])
+        hz.assert_images_equal(dict(range=ref.range_image(True), raycast=ref.raycast_result(True), image=ref.out_image()),
+                               dict(range=fi["range"], raycast=fi["raycast"], image=fi["image"]), "free view type %d" % rtype)
+    assert (fi["raycast"][..., 3] > 0).sum() > 1000
+    ref.close(); ora.close()
+
+
+def test_use_swapping_visibility_bit_exact():
+    # app default useSwapping=true enlarges the visibility frustum
+    cfg, frames, ref, ora = run_pair("tiny", 6, use_swapping=True)
+    ref.close(); ora.close()
