@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py -- frames/s of the fused volumetric-fusion step (allocate + integrate + expected depths +
+raycast/ICP maps) on the KITTI-stereo-shaped workload of BASELINE.json configs[1]
+(1242x375 synthetic disparity depth, 2 cm voxels, depth weighting on).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+ours:      one step = one depth frame through dsb200_process_frame.  `value` = frames/s with the
+           frames already resident in HBM (device time, CUDA events, L2 flushed between steps);
+           `e2e` = the same through the C ABI with pinned HOST buffers (H2D of depth+rgb and a
+           D2H of the rendered map + counters inside the timed region).
+reference: the reference's own CPU engines (oracle/_ref, compiled from the unmodified reference
+           sources) on the host cores, on a bounded sample of the same workload.
+N > 1:     the path shards by independent scenes ("replicas only"): every rank fuses its
+           own sequence (seed = rank), no data-path collective; value = total frames / max time.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+PKG = "denseslam-global-consistency-h_b200"
+
+WORKLOAD = "C2"
+CAPS = dict(num_blocks=1 << 21, bucket_num=1 << 22, excess_size=1 << 20)   # 8 GiB VBA: 1000 street frames fit
+REF_SAMPLE_FRAMES = 12      # bounded CPU sample: the reference's capacities are compile-time (262144 blocks)
+METRIC = "frames/s alloc+integrate+raycast (1242x375, 2 cm voxels)"
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 9 for i in range(4) if r[5 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def make_frames(n, seed):
+    synth = importlib.import_module(PKG + ".synth")
+    return synth.make_sequence(WORKLOAD, n, seed=seed)
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank, world):
+    if rank != 0:
+        return None
+    import pyoracle as po
+    abi = importlib.import_module(PKG + ".abi")
+    cfg, frames = make_frames(REF_SAMPLE_FRAMES, 0)
+    kind, path_ok = "reference", os.path.exists(po.REF_FAST_PATH)
+    cores = 1
+    if path_ok:
+        eng = po.RefEngine(cfg.W, cfg.H, cfg.params(), fast=True)
+        eng.set_calib(cfg.intr)
+
+        def reset():
+            eng.L.itmref_reset(eng.h)
+
+        def step(f):
+            eng.set_view(f.depth, f.rgb, f.timestamp); eng.set_pose(f.M)
+            eng.allocate(); eng.integrate(); eng.create_expected_depths(); eng.create_icp_maps()
+    else:   # the oracle port is the only CPU implementation available on this box
+        import harness as hz
+        kind = "port"
+        ora = hz.OracleBackend(cfg, dict(num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS, excess_size=abi.DEFAULT_EXCESS))
+        ora.set_weights(True, 10, 100)
+        reset = ora.reset
+
+        def step(f):
+            ora.set_frame(f); ora.process_frame()
+    idx = 0
+
+    def next_frame():
+        nonlocal idx
+        if idx % REF_SAMPLE_FRAMES == 0:
+            reset()     # untimed: the sample wraps, so the map restarts with it
+        f = frames[idx % REF_SAMPLE_FRAMES]
+        idx += 1
+        return f
+    for _ in range(args.warmup):
+        step(next_frame())
+    total = 0.0
+    for _ in range(args.steps):
+        f = next_frame()
+        t0 = time.perf_counter()
+        step(f)
+        total += time.perf_counter() - t0
+    fps = args.steps / total
+    sample = "first %d frames of the %s sequence, cycled (scene reset untimed at wrap); %s" % (
+        REF_SAMPLE_FRAMES, WORKLOAD, "reference CPU engines -O3 -march=x86-64-v3, OpenMP off (reference default; its OpenMP build races on "
+        "allocation and was slower in the survey probe); depth weighting is ignored by the reference CPU integrator" if kind == "reference"
+        else "oracle/restate.cpp port")
+    return {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1000.0 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32->i16/u8 voxels", "data": "synthetic",
+            "config": {"workload": "C2 KITTI-stereo-shaped 1242x375, 2 cm voxels, CPU sample"},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    abi = importlib.import_module(PKG + ".abi")
+    eng = importlib.import_module(PKG + ".engine")
+    lib = abi.load()          # raises if libdsb200.so is missing: no fallback
+    if lib.dsb200_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
+    abi.check(lib.dsb200_set_device(local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    K, Wm = args.steps, args.warmup
+    cfg, frames = make_frames(K + Wm, seed=rank)
+    W, H = cfg.W, cfg.H
+    npx = W * H
+
+    scene = eng.ITMScene(cfg.params(), CAPS["num_blocks"], CAPS["bucket_num"], CAPS["excess_size"])
+    recon = eng.ITMSceneReconstructionEngine(CAPS["num_blocks"], CAPS["bucket_num"], CAPS["excess_size"])
+    recon.SetFusionWeightParams(cfg.depth_weighting, 10, 100)
+    vis = eng.ITMVisualisationEngine(W, H)
+    rs = vis.CreateRenderState(scene, (W, H))
+    trk = eng.ITMTrackingState(W, H)
+    view = eng.ITMView(W, H, cfg.intr)          # staging view for the e2e leg
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+
+    # ---- leg 1: inputs resident in HBM
+    d_depth = torch.from_numpy(np.stack([f.depth for f in frames])).to(dev)
+    d_rgb = torch.from_numpy(np.stack([f.rgb for f in frames])).to(dev)
+    views = []
+    for i, f in enumerate(frames):
+        v = abi.View()
+        C.memmove(C.byref(v), C.byref(view.c), C.sizeof(abi.View))
+        v.depth, v.rgb, v.timestamp = d_depth[i].data_ptr(), d_rgb[i].data_ptr(), f.timestamp
+        views.append(v)
+
+    def frame_async(i):
+        trk.set_pose(frames[i].M)
+        abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views[i]), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
+
+    recon.ResetScene(scene)
+    recon.SetAsync(True)
+    abi.check(lib.dsb200_profile_enable(recon.h, 1))
+    stage_ms = np.zeros(abi.PROFILE_STAGES)
+    stage_buf = (C.c_float * abi.PROFILE_STAGES)()
+    vis_counts = []
+    for i in range(Wm):
+        frame_async(i)
+    recon.Sync(scene, rs)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = lib.dsb200_kernel_launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    torch.cuda.synchronize()
+    for k in range(K):
+        flush.zero_()                      # L2 flush between timed iterations (outside the event pair)
+        evs[k][0].record()
+        frame_async(Wm + k)
+        evs[k][1].record()
+        abi.check(lib.dsb200_profile_read(recon.h, stage_buf))      # synchronises; device-side stage times
+        stage_ms += np.array(stage_buf[:])
+        recon.Sync(scene, rs)
+        vis_counts.append(rs.c.no_visible)
+    torch.cuda.synchronize()
+    launches = int(lib.dsb200_kernel_launch_count() - launches0)
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop()
+    dev_ms = float(sum(a.elapsed_time(b) for a, b in evs))
+    abi.check(lib.dsb200_profile_enable(recon.h, 0))
+    recon.SetAsync(False)
+    blocks_used = CAPS["num_blocks"] - 1 - scene.c.last_free_block
+
+    # ---- leg 2: end to end through the C ABI with pinned host buffers
+    h_depth = torch.empty((H, W), dtype=torch.float32).pin_memory()
+    h_rgb = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    h_out = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    recon.ResetScene(scene)
+    rs.c.no_visible = 0
+    abi.check(lib.dsb200_memcpy_h2d(rs.c.visible_type, np.zeros(scene.c.total_entries, np.uint8).ctypes.data, scene.c.total_entries, None))
+    abi.check(lib.dsb200_stream_synchronize(None))
+
+    def frame_e2e(i):
+        f = frames[i]
+        h_depth.numpy()[:] = f.depth            # the caller's frame lands in its pinned buffers (not timed as GPU work,
+        h_rgb.numpy()[:] = f.rgb                # but inside the bracket, as in the reference's UpdateView)
+        abi.check(lib.dsb200_memcpy_h2d(view.c.depth, h_depth.data_ptr(), npx * 4, None))
+        abi.check(lib.dsb200_memcpy_h2d(view.c.rgb, h_rgb.data_ptr(), npx * 4, None))
+        view.c.timestamp = f.timestamp
+        trk.set_pose(f.M)
+        abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(view.c), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
+        abi.check(lib.dsb200_memcpy_d2h(h_out.data_ptr(), rs.c.raycast_image, npx * 4, None))
+        abi.check(lib.dsb200_stream_synchronize(None))
+
+    for i in range(Wm):
+        frame_e2e(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for k in range(K):
+        frame_e2e(Wm + k)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_wall = time.perf_counter() - t0
+    e2e_ms = max(float(e0.elapsed_time(e1)), 1000.0 * e2e_wall)
+    if world > 1:
+        dist.barrier()
+        t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return None
+
+    pk, pk_kind = peaks()
+    V = float(np.mean(vis_counts))
+    stage_names = ["allocate+visible_list", "integrate", "expected_depths", "raycast", "icp_maps"]
+    per_stage = stage_ms / K
+    # algorithmic bytes per frame (SURVEY.md section 8d / DESIGN.md), each datum counted once
+    alg = [4.0 * npx + 4.0 * 2 * (CAPS["bucket_num"] + CAPS["excess_size"]) + 24.0 * V,    # keys+visType scans, depth, lists
+           8216.0 * V + 8.0 * npx, 24.0 * V + 16.0 * (W // 8 + 1) * (H // 8 + 1) + 8.0 * npx,
+           4116.0 * V + 16.0 * npx, 52.0 * npx]
+    dom = int(np.argmax(per_stage))
+    achieved = alg[dom] / (per_stage[dom] * 1e-3) / 1e9
+    stages = {stage_names[i]: {"ms": float(per_stage[i]), "alg_MB": alg[i] / 1e6,
+                               "GBps": alg[i] / (per_stage[i] * 1e-3) / 1e9 if per_stage[i] > 0 else None} for i in range(5)}
+    out = {"metric": METRIC, "value": world * K / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+           "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic",
+           "config": {"workload": "C2 KITTI-stereo-shaped 1242x375 synthetic disparity depth, 2 cm voxels, mu 8 cm, depth weighting on; "
+                                  "one scene per GPU (replicas only)", "frames": K, "mean_visible_blocks": V,
+                      "blocks_allocated": int(blocks_used), "capacity_blocks": CAPS["num_blocks"], "l2": "flushed (256 MiB write) between timed steps"},
+           "e2e": {"value": world * K / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": 8 * npx + 128,
+                   "d2h_bytes_per_step": 4 * npx + 32, "ms_per_step": e2e_ms / K},
+           "gpu_launches": launches, "clocks": clocks,
+           "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                        "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"},
+           "stages": stages}
+    if world == 1:
+        a2 = argparse.Namespace(gpus=1, steps=REF_SAMPLE_FRAMES, warmup=1)
+        ref = run_reference(a2, 0, 1)
+        out["cpu_baseline"] = ref["cpu_baseline"]
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    out = run_reference(args, rank, world) if args.impl == "reference" else run_ours(args, rank, world, local_rank)
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -21,6 +21,7 @@ OK = 0
 ERR_CUDA, ERR_INVALID, ERR_VBA_EXHAUSTED, ERR_EXCESS_EXHAUSTED, ERR_UNSUPPORTED, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6
 
 RENDER_SHADED_GREYSCALE, RENDER_COLOUR_FROM_VOLUME, RENDER_COLOUR_FROM_NORMAL, RENDER_COLOURCODED, RENDER_DEPTH_MAP = range(5)
+PROFILE_STAGES = 5
 FRAME_ALLOCATE, FRAME_INTEGRATE, FRAME_EXPECTED_DEPTHS, FRAME_ICP_MAPS, FRAME_ALL = 1, 2, 4, 8, 15
 
 # numpy views of the two on-device record types (ITMHashEntry 20 B, ITMVoxel_s_rgb 8 B)
@@ -96,6 +97,7 @@ def load():
     sig = {
         "dsb200_last_error": (cp, []),
         "dsb200_device_count": (C.c_int, []),
+        "dsb200_set_device": (C.c_int, [C.c_int]),
         "dsb200_recon_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
         "dsb200_recon_destroy": (C.c_int, [vp]),
         "dsb200_recon_set_async": (C.c_int, [vp, C.c_int]),
@@ -135,6 +137,8 @@ def load():
         "dsb200_stream_synchronize": (C.c_int, [vp]),
         "dsb200_mat4_inverse": (C.c_int, [_P(C.c_float), _P(C.c_float)]),
         "dsb200_mat4_multiply": (None, [_P(C.c_float), _P(C.c_float), _P(C.c_float)]),
+        "dsb200_profile_enable": (C.c_int, [vp, C.c_int]),
+        "dsb200_profile_read": (C.c_int, [vp, _P(C.c_float)]),
         "dsb200_kernel_launch_count": (C.c_ulonglong, []),
     }
     for name, (res, args) in sig.items():

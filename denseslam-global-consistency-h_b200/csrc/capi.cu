@@ -116,6 +116,7 @@ struct dsb200_recon {
     long long totalDecayed = 0;
     int lastFreeBeforePrune = 0; bool prunePending = false;
     Arena arena;
+    bool profile = false; cudaEvent_t ev[DSB200_PROFILE_STAGES + 1] = {}; bool evRecorded[DSB200_PROFILE_STAGES + 1] = {};
 };
 
 struct dsb200_vis {
@@ -140,6 +141,8 @@ int dsb200_device_count(void)
 }
 
 unsigned long long dsb200_kernel_launch_count(void) { return g_launches; }
+
+int dsb200_set_device(int device) { CU(cudaSetDevice(device)); return DSB200_OK; }
 
 // ---------------------------------------------------------------- engine lifetime
 int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_num, int32_t excess_size, void *stream)
@@ -579,27 +582,49 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     if ((stages & (DSB200_FRAME_EXPECTED_DEPTHS | DSB200_FRAME_ICP_MAPS)) && (!v || v->stream != e->stream))
         return fail(DSB200_ERR_INVALID, "process_frame: the two engines must share one stream");
     const int *countPtr = &e->fs.counters->noVisible;
+#define DSB_MARK(i) do { if (e->profile) { cudaEventRecord(e->ev[i], e->stream); e->evRecorded[i] = true; } } while (0)
+    if (e->profile) for (int i = 0; i <= DSB200_PROFILE_STAGES; i++) e->evRecorded[i] = false;
+    DSB_MARK(0);
     if (stages & DSB200_FRAME_ALLOCATE) {
         rc = enqueue_allocate(e, scene, view, trk, rs, 0, 0); if (rc) return rc;
     } else if (!(e->async && e->deviceCountersValid)) {
         e->hostCounters->noVisible = rs->no_visible;
         CU(cudaMemcpyAsync(&e->fs.counters->noVisible, &e->hostCounters->noVisible, 4, cudaMemcpyHostToDevice, e->stream));
     }
+    DSB_MARK(1);
     if (stages & DSB200_FRAME_INTEGRATE) {
         FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
         launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb);
     }
+    DSB_MARK(2);
     if (stages & DSB200_FRAME_EXPECTED_DEPTHS) {
         ProjParams P; make_proj_params(P, scene, trk->M_d, view->intr_d, rs->width, rs->height);
         launch_expected_depths(e->stream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, nullptr, e->fs.counters);
     }
+    DSB_MARK(3);
     if (stages & DSB200_FRAME_ICP_MAPS) {
         if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "process_frame: tracking state has no point cloud buffers");
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
         launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+        DSB_MARK(4);
         launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
-    }
+    } else DSB_MARK(4);
+    DSB_MARK(5);
     return finish_call(e, scene, rs, (stages & DSB200_FRAME_ALLOCATE) != 0);
+}
+
+int dsb200_profile_enable(dsb200_recon *e, int on)
+{
+    if (on && !e->ev[0]) for (int i = 0; i <= DSB200_PROFILE_STAGES; i++) CU(cudaEventCreate(&e->ev[i]));
+    e->profile = on != 0;
+    return DSB200_OK;
+}
+int dsb200_profile_read(dsb200_recon *e, float *ms)
+{
+    if (!e->profile || !e->evRecorded[DSB200_PROFILE_STAGES]) return fail(DSB200_ERR_INVALID, "profile_read: nothing recorded");
+    CU(cudaEventSynchronize(e->ev[DSB200_PROFILE_STAGES]));
+    for (int i = 0; i < DSB200_PROFILE_STAGES; i++) CU(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
+    return DSB200_OK;
 }
 
 // ---------------------------------------------------------------- host helpers

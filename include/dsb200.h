@@ -129,6 +129,8 @@ typedef struct dsb200_vis dsb200_vis;
 
 const char *dsb200_last_error(void);
 int dsb200_device_count(void);
+/* selects the CUDA device for this thread's subsequent calls (one process per GPU under torchrun) */
+int dsb200_set_device(int device);
 
 /* ---- reconstruction engine (ITMSceneReconstructionEngine.h:45-96) ---- */
 /* ctor: sizes the engine scratch (entriesAllocType/blockCoords equivalents) for these capacities. */
@@ -206,6 +208,12 @@ int dsb200_stream_synchronize(void *cuda_stream);
 /* ORUtils Matrix4::inv restated (cofactor order preserved), ORUtils/Matrix.h:175-246 */
 int dsb200_mat4_inverse(const float *M, float *out);
 void dsb200_mat4_multiply(const float *A, const float *B, float *out);
+
+/* per-stage device timing of dsb200_process_frame (CUDA events on the engine's stream).  Stage order:
+ * 0 allocate(+visible list) 1 integrate 2 expected depths 3 raycast 4 ICP maps.  read() synchronises. */
+#define DSB200_PROFILE_STAGES 5
+int dsb200_profile_enable(dsb200_recon *e, int on);
+int dsb200_profile_read(dsb200_recon *e, float *stage_ms /* [DSB200_PROFILE_STAGES] */);
 
 /* counters for bench.py: kernels launched by this library since process start */
 unsigned long long dsb200_kernel_launch_count(void);
