@@ -1,0 +1,23 @@
+// compile_check.cpp -- instantiates both adapters against the UNMODIFIED reference headers (run where
+// /root/reference exists: `make -C adapters check`).  Proves the adapters override every pure virtual of the
+// two interfaces with matching signatures, and that the reference's struct layouts match include/dsb200.h.
+#include "ITMSceneReconstructionEngine_B200.h"
+#include "ITMVisualisationEngine_B200.h"
+
+using namespace ITMLib::Engine;
+
+template class ITMLib::Engine::ITMSceneReconstructionEngine_B200<ITMVoxel, ITMVoxelIndex>;
+template class ITMLib::Engine::ITMVisualisationEngine_B200<ITMVoxel, ITMVoxelIndex>;
+
+static_assert(sizeof(ITMVoxel) == 8, "ITMVoxel_s_rgb");
+static_assert(sizeof(ITMHashEntry) == 20, "ITMHashEntry");
+static_assert(SDF_LOCAL_BLOCK_NUM == DSB200_DEFAULT_LOCAL_BLOCKS && SDF_BUCKET_NUM == DSB200_DEFAULT_BUCKETS &&
+              SDF_EXCESS_LIST_SIZE == DSB200_DEFAULT_EXCESS, "default capacities");
+static_assert((int)IITMVisualisationEngine::RENDER_SHADED_GREYSCALE == DSB200_RENDER_SHADED_GREYSCALE &&
+              (int)IITMVisualisationEngine::RENDER_COLOUR_FROM_VOLUME == DSB200_RENDER_COLOUR_FROM_VOLUME &&
+              (int)IITMVisualisationEngine::RENDER_COLOUR_FROM_NORMAL == DSB200_RENDER_COLOUR_FROM_NORMAL &&
+              (int)IITMVisualisationEngine::RENDER_DEPTH_MAP == DSB200_RENDER_DEPTH_MAP, "RenderImageType values");
+
+// what ITMDenseMapper / ITMMainEngine would do with deviceType == DEVICE_B200 (never executed here: no GPU)
+ITMSceneReconstructionEngine<ITMVoxel, ITMVoxelIndex> *make_recon() { return new ITMSceneReconstructionEngine_B200<ITMVoxel, ITMVoxelIndex>(); }
+IITMVisualisationEngine *make_vis(Vector2i imgSize) { return new ITMVisualisationEngine_B200<ITMVoxel, ITMVoxelIndex>(imgSize); }

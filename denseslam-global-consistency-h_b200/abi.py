@@ -20,7 +20,7 @@ DEFAULT_EXCESS = 0x60000
 OK = 0
 ERR_CUDA, ERR_INVALID, ERR_VBA_EXHAUSTED, ERR_EXCESS_EXHAUSTED, ERR_UNSUPPORTED, ERR_NO_DEVICE = -1, -2, -3, -4, -5, -6
 
-RENDER_SHADED_GREYSCALE, RENDER_COLOUR_FROM_VOLUME, RENDER_COLOUR_FROM_NORMAL, RENDER_COLOURCODED, RENDER_DEPTH_MAP = range(5)
+RENDER_SHADED_GREYSCALE, RENDER_COLOUR_FROM_VOLUME, RENDER_COLOUR_FROM_NORMAL, RENDER_DEPTH_MAP, RENDER_COLOURCODED = range(5)
 PROFILE_STAGES = 5
 FRAME_ALLOCATE, FRAME_INTEGRATE, FRAME_EXPECTED_DEPTHS, FRAME_ICP_MAPS, FRAME_ALL = 1, 2, 4, 8, 15
 

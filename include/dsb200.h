@@ -115,13 +115,13 @@ typedef struct dsb200_tracking {
 /* WeightParams, Engine/ITMSceneReconstructionEngine.h:21-25 */
 typedef struct dsb200_weight_params { int32_t depth_weighting, max_new_w, max_distance; } dsb200_weight_params;
 
-/* IITMVisualisationEngine::RenderImageType, Engine/ITMVisualisationEngine.h */
+/* IITMVisualisationEngine::RenderImageType, Engine/ITMVisualisationEngine.h:21-28 (same values) */
 typedef enum dsb200_render_type {
     DSB200_RENDER_SHADED_GREYSCALE = 0,
     DSB200_RENDER_COLOUR_FROM_VOLUME = 1,
     DSB200_RENDER_COLOUR_FROM_NORMAL = 2,
-    DSB200_RENDER_COLOURCODED = 3,
-    DSB200_RENDER_DEPTH_MAP = 4
+    DSB200_RENDER_DEPTH_MAP = 3,      /* the fork inserts the depth mode before COLOURCODED (:21-28) */
+    DSB200_RENDER_COLOURCODED = 4
 } dsb200_render_type;
 
 typedef struct dsb200_recon dsb200_recon;   /* engine-owned scratch + history queues */
