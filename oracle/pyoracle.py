@@ -26,9 +26,9 @@ REF_FAST_PATH = os.path.join(HERE, "_ref", "libitmref_fast.so")
 
 def build(force=False):
     """Compile librestate.so (always possible) and oracle/_ref (only where /root/reference exists)."""
-    if force or not os.path.exists(RESTATE_PATH) or \
-            os.path.getmtime(RESTATE_PATH) < os.path.getmtime(os.path.join(HERE, "restate.cpp")):
-        subprocess.check_call(["make", "-C", HERE, "librestate.so"])
+    if force and os.path.exists(RESTATE_PATH):
+        os.remove(RESTATE_PATH)
+    subprocess.check_call(["make", "-C", HERE, "librestate.so"])   # make tracks restate.cpp / restate.h / dsb200.h
     subprocess.check_call(["make", "-C", HERE, "ref"])
 
 
