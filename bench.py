@@ -184,57 +184,72 @@ def run_ours(args, rank, world, local_rank):
         trk.set_pose(frames[i].M)
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views[i]), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
 
-    recon.ResetScene(scene)
-    recon.SetAsync(True)
-    abi.check(lib.dsb200_profile_enable(recon.h, 1))
-    stage_ms = np.zeros(abi.PROFILE_STAGES)
+    def reset_all():
+        recon.ResetScene(scene)
+        rs.c.no_visible = 0
+        abi.check(lib.dsb200_memcpy_h2d(rs.c.visible_type, zeros_vt.ctypes.data, scene.c.total_entries, None))
+        abi.check(lib.dsb200_stream_synchronize(None))
+
+    zeros_vt = np.zeros(scene.c.total_entries, np.uint8)
+    alloc_stage = np.zeros(5)
     stage_buf = (C.c_float * abi.PROFILE_STAGES)()
-    vis_counts = []
-    for i in range(Wm):
-        frame_async(i)
-    recon.Sync(scene, rs)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
+
+    def resident_pass(profile):
+        """W warm-up + K timed frames from a fresh scene.  profile=False: the product configuration (expected depths
+        overlapped with integration); profile=True: stages serialised and timed one by one with CUDA events."""
+        reset_all()
+        recon.SetAsync(True)
+        abi.check(lib.dsb200_profile_enable(recon.h, 1 if profile else 0))
+        stage = np.zeros(abi.PROFILE_STAGES)
+        counts = []
+        for i in range(Wm):
+            frame_async(i)
+        recon.Sync(scene, rs)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        l0 = lib.dsb200_kernel_launch_count()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        torch.cuda.synchronize()
+        for k in range(K):
+            flush.zero_()                      # L2 flush between timed iterations (outside the event pair)
+            evs[k][0].record()
+            frame_async(Wm + k)
+            evs[k][1].record()
+            if profile:
+                abi.check(lib.dsb200_profile_read(recon.h, stage_buf))      # synchronises; device-side stage times
+                stage += np.array(stage_buf[:])
+                abi.check(lib.dsb200_profile_read_allocate(recon.h, stage_buf))
+                alloc_stage += np.array(stage_buf[:])
+            recon.Sync(scene, rs)
+            counts.append(rs.c.no_visible)
+        torch.cuda.synchronize()
+        n_launch = int(lib.dsb200_kernel_launch_count() - l0)
+        if world > 1:
+            dist.barrier()
+        ms = float(sum(a.elapsed_time(b) for a, b in evs))
+        abi.check(lib.dsb200_profile_enable(recon.h, 0))
+        recon.SetAsync(False)
+        return ms, stage, counts, n_launch
+
     sampler = ClockSampler(local_rank)
     sampler.start()
-    launches0 = lib.dsb200_kernel_launch_count()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    torch.cuda.synchronize()
-    for k in range(K):
-        flush.zero_()                      # L2 flush between timed iterations (outside the event pair)
-        evs[k][0].record()
-        frame_async(Wm + k)
-        evs[k][1].record()
-        abi.check(lib.dsb200_profile_read(recon.h, stage_buf))      # synchronises; device-side stage times
-        stage_ms += np.array(stage_buf[:])
-        recon.Sync(scene, rs)
-        vis_counts.append(rs.c.no_visible)
-    torch.cuda.synchronize()
-    launches = int(lib.dsb200_kernel_launch_count() - launches0)
-    if world > 1:
-        dist.barrier()
+    dev_ms, _, vis_counts, launches = resident_pass(False)
     clocks = sampler.stop()
-    dev_ms = float(sum(a.elapsed_time(b) for a, b in evs))
-    abi.check(lib.dsb200_profile_enable(recon.h, 0))
-    recon.SetAsync(False)
     blocks_used = CAPS["num_blocks"] - 1 - scene.c.last_free_block
+    _, stage_ms, _, _ = resident_pass(True)
 
     # ---- leg 2: end to end through the C ABI with pinned host buffers
-    h_depth = torch.empty((H, W), dtype=torch.float32).pin_memory()
-    h_rgb = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    # the caller's frames live in pinned host memory (as a camera driver / decoder would deliver them)
+    h_depth = torch.from_numpy(np.stack([f.depth for f in frames])).pin_memory()
+    h_rgb = torch.from_numpy(np.stack([f.rgb for f in frames])).pin_memory()
     h_out = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
-    recon.ResetScene(scene)
-    rs.c.no_visible = 0
-    abi.check(lib.dsb200_memcpy_h2d(rs.c.visible_type, np.zeros(scene.c.total_entries, np.uint8).ctypes.data, scene.c.total_entries, None))
-    abi.check(lib.dsb200_stream_synchronize(None))
+    reset_all()
 
     def frame_e2e(i):
         f = frames[i]
-        h_depth.numpy()[:] = f.depth            # the caller's frame lands in its pinned buffers (not timed as GPU work,
-        h_rgb.numpy()[:] = f.rgb                # but inside the bracket, as in the reference's UpdateView)
-        abi.check(lib.dsb200_memcpy_h2d(view.c.depth, h_depth.data_ptr(), npx * 4, None))
-        abi.check(lib.dsb200_memcpy_h2d(view.c.rgb, h_rgb.data_ptr(), npx * 4, None))
+        abi.check(lib.dsb200_memcpy_h2d(view.c.depth, h_depth[i].data_ptr(), npx * 4, None))
+        abi.check(lib.dsb200_memcpy_h2d(view.c.rgb, h_rgb[i].data_ptr(), npx * 4, None))
         view.c.timestamp = f.timestamp
         trk.set_pose(f.M)
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(view.c), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
@@ -288,7 +303,9 @@ def run_ours(args, rank, world, local_rank):
            "gpu_launches": launches, "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"},
-           "stages": stages}
+           "stages": stages,
+           "allocate_kernels_ms": dict(zip(["begin_frame", "alloc_requests", "allocate", "recheck_visibility", "visible_list"],
+                                           [float(x) / K for x in alloc_stage]))}
     if world == 1:
         a2 = argparse.Namespace(gpus=1, steps=REF_SAMPLE_FRAMES, warmup=1)
         ref = run_reference(a2, 0, 1)

@@ -11,6 +11,7 @@
 //  * errors are returned as codes (+ dsb200_last_error) instead of exit(-1)/throw.
 #include "kernels.cuh"
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <deque>
@@ -108,6 +109,9 @@ struct dsb200_recon {
     Counters *hostCounters = nullptr; // pinned
     dsb200_weight_params weights{0, 10, 100};
     bool async = false, deviceCountersValid = false;
+    const uint8_t *visBitsOwner = nullptr;   // the render state's visibility-flag array that fs.visBits currently describes
+    cudaStream_t sideStream = nullptr; cudaEvent_t evFork = nullptr, evJoin = nullptr;   // fused frame: expected depths || integration
+    bool forceSlowDiv = false;        // debug: run the plain-division kernel variants (dsb200_debug_force_plain_division)
     // history (CUDA/ITMSceneReconstructionEngine_CUDA.h:41-48)
     std::deque<SnapPtr> decayQ, slideQ, decayDefusionQ, slideDefusionQ;
     std::map<double, SnapPtr> snapshots;   // mDefusionBlockDataBase
@@ -116,6 +120,7 @@ struct dsb200_recon {
     long long totalDecayed = 0;
     int lastFreeBeforePrune = 0; bool prunePending = false;
     Arena arena;
+    cudaEvent_t evAlloc[DSB200_PROFILE_ALLOC_STAGES + 1] = {}; bool evAllocRecorded = false;
     bool profile = false; cudaEvent_t ev[DSB200_PROFILE_STAGES + 1] = {}; bool evRecorded[DSB200_PROFILE_STAGES + 1] = {};
 };
 
@@ -154,6 +159,12 @@ int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_n
     e->stream = (cudaStream_t)stream;
     e->numBlocks = num_blocks; e->bucketNum = bucket_num; e->excessSize = excess_size; e->total = bucket_num + excess_size;
     e->fs.scanTiles = div_up(e->total, 1024);
+    e->fs.bitTiles = div_up(e->total, 32768);
+    CU(cudaMalloc(&e->fs.reqBits, (size_t)e->fs.bitTiles * 8192));
+    CU(cudaMemset(e->fs.reqBits, 0, (size_t)e->fs.bitTiles * 8192));
+    e->fs.reqExBits = e->fs.reqBits + (size_t)e->fs.bitTiles * 1024;
+    CU(cudaMalloc(&e->fs.visBits, (size_t)e->fs.bitTiles * 4096));
+    CU(cudaMemset(e->fs.visBits, 0, (size_t)e->fs.bitTiles * 4096));
     const int pruneTiles = div_up(num_blocks, 1024);
     size_t keyInts = (size_t)e->fs.scanTiles * 1024;
     CU(cudaMalloc(&e->reqKey, keyInts * 4));
@@ -168,6 +179,9 @@ int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_n
     CU(cudaMemset(e->fs.tickets, 0, 4 * sizeof(int)));
     CU(cudaMallocHost(&e->hostCounters, sizeof(Counters)));
     memset(e->hostCounters, 0, sizeof(Counters));
+    CU(cudaStreamCreateWithFlags(&e->sideStream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e->evJoin, cudaEventDisableTiming));
     e->pruneCap = num_blocks;
     CU(cudaMalloc(&e->pruneScratch, (size_t)3 * e->pruneCap * 4));
     *out = e;
@@ -178,11 +192,13 @@ int dsb200_recon_destroy(dsb200_recon *e)
 {
     if (!e) return DSB200_OK;
     cudaStreamSynchronize(e->stream);
+    if (e->sideStream) { cudaStreamSynchronize(e->sideStream); cudaStreamDestroy(e->sideStream); cudaEventDestroy(e->evFork); cudaEventDestroy(e->evJoin); }
     e->decayQ.clear(); e->slideQ.clear(); e->decayDefusionQ.clear(); e->slideDefusionQ.clear();
     e->snapshots.clear(); e->unsynced.clear();
     e->arena.release_all();
     cudaFree(e->reqKey); cudaFree(e->slotMark); cudaFree(e->pruneScratch); cudaFree(e->fs.counters);
     cudaFree(e->fs.scanState); cudaFree(e->fs.tickets); cudaFreeHost(e->hostCounters);
+    cudaFree(e->fs.reqBits); cudaFree(e->fs.visBits);
     delete e;
     return DSB200_OK;
 }
@@ -254,6 +270,10 @@ static void make_alloc_params(AllocParams &P, const dsb200_scene *scene, const d
     P.bucketNum = scene->bucket_num; P.bucketMask = scene->bucket_num - 1;
 }
 
+static bool in_window(float v, int loExp, int hiExp) { float a = fabsf(v); return a >= ldexpf(1.0f, loExp) && a <= ldexpf(1.0f, hiExp); }
+static bool zero_or_in_window(float v, int loExp, int hiExp) { return v == 0.0f || in_window(v, loExp, hiExp); }
+static bool significand_all_ones(float v) { unsigned u; memcpy(&u, &v, 4); return (u & 0x7fffffu) == 0x7fffffu; }
+
 static void make_fuse_params(FuseParams &P, const dsb200_recon *e, const dsb200_scene *scene, const dsb200_view *view,
                              const dsb200_tracking *trk)
 {
@@ -265,6 +285,14 @@ static void make_fuse_params(FuseParams &P, const dsb200_recon *e, const dsb200_
     P.stopMaxW = scene->params.stop_integrating_at_max_w;
     P.approximate = trk->requires_full_rendering ? 0 : 1;
     P.depthWeighting = e->weights.depth_weighting; P.maxNewW = e->weights.max_new_w; P.maxDistance = e->weights.max_distance;
+    // exact-division support (exactdiv.cuh).  Host IEEE divisions give the correctly rounded reciprocals; fastDiv states
+    // that no intermediate of the FMA correction sequences can overflow or go denormal for ANY voxel of ANY block:
+    // |pt| <= 2^18 * voxelSize, so with these windows |proj * pc.xy| stays inside [2^-84, 2^68] or is exactly 0.
+    P.rcpMu = 1.0f / P.mu; P.rcp255 = 1.0f / 255.0f; P.rcp32767 = 1.0f / 32767.0f;
+    bool ok = in_window(P.voxelSize, -20, 10) && in_window(P.mu, -20, 20) && !significand_all_ones(P.mu);
+    for (int i = 0; i < 16 && ok; i++) ok = zero_or_in_window(P.M_d.m[i], -30, 20) && zero_or_in_window(P.M_rgb.m[i], -30, 20);
+    for (int i = 0; i < 4 && ok; i++) ok = zero_or_in_window(P.proj_d[i], -10, 20) && zero_or_in_window(P.proj_rgb[i], -10, 20);
+    P.fastDiv = (ok && !e->forceSlowDiv) ? 1 : 0;
 }
 
 static int check_scene(const dsb200_recon *e, const dsb200_scene *scene)
@@ -285,11 +313,20 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     // noSteps = ceil(2 * |segment| / blockSize) with |segment| = 2*mu (+ rounding): must fit the 8-bit step field
     if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
     const bool useHost = !(e->async && e->deviceCountersValid);
+    if (rs->visible_type != e->visBitsOwner) {     // a render state this engine has not been tracking: derive its bitmap
+        launch_rebuild_visbits(e->stream, e->fs, rs->visible_type, e->total);
+        e->visBitsOwner = rs->visible_type;
+    }
+#define DSB_MARK_A(i) do { if (e->profile) cudaEventRecord(e->evAlloc[i], e->stream); } while (0)
+    DSB_MARK_A(0);
     launch_begin_frame(e->stream, e->fs, scene->last_free_block, scene->last_free_excess, rs->no_visible, useHost ? 1 : 0,
                        rs->visible_ids, rs->visible_type, useHost ? rs->no_visible : rs->visible_capacity);
-    launch_alloc_requests(e->stream, AP, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    DSB_MARK_A(1);
+    launch_alloc_requests(e->stream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    DSB_MARK_A(2);
     launch_allocate(e->stream, AP, e->fs, view->depth, scene->hash, scene->alloc_list, scene->excess_list, rs->visible_type,
                     e->reqKey, e->total, onlyVisible ? 0 : 1);
+    DSB_MARK_A(3);
     // snapshot reservation for decay / slide window / de-fusion (CUDA .cu:257-317)
     SnapPtr snap = std::make_shared<Snapshot>();
     snap->regionInts = 64 + (((size_t)rs->visible_capacity + 63) & ~(size_t)63);
@@ -299,8 +336,12 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     VisParams VP; fill_mat(VP.M, trk->M_d); memcpy(VP.proj, view->intr_d, 16);
     VP.voxelSize = scene->params.voxel_size; VP.W = AP.W; VP.H = AP.H;
     VP.useSwapping = (scene->use_swapping && !onlyVisible) ? 1 : 0;
+    launch_recheck_visibility(e->stream, VP, e->fs, scene->hash, rs->visible_ids, rs->visible_type);
+    DSB_MARK_A(4);
     launch_visible_list(e->stream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, rs->visible_ids,
                         rs->visible_capacity, snap->ids, snap->countDev, e->total);
+    DSB_MARK_A(5);
+    if (e->profile) e->evAllocRecorded = true;
     e->unsynced.push_back(snap);
     if (!isDefusion) {
         snap->frameIdx = e->frameIdx;
@@ -344,6 +385,7 @@ int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
     launch_reset_scene(e->stream, scene->voxels, (size_t)scene->num_blocks * DSB200_BLOCK_SIZE3, scene->hash, e->total,
                        scene->alloc_list, scene->num_blocks, scene->excess_list, scene->excess_size, nullptr, e->reqKey,
                        e->fs.counters);
+    CU(cudaMemsetAsync(e->fs.reqBits, 0, (size_t)e->fs.bitTiles * 8192, e->stream));   // the keys were cleared: so are their bits
     CU(cudaGetLastError());
     scene->last_free_block = scene->num_blocks - 1;
     scene->last_free_excess = scene->excess_size - 1;
@@ -408,7 +450,8 @@ static int prune_from_queue(dsb200_recon *e, dsb200_scene *scene, dsb200_render_
             int bound = snap->countHost >= 0 ? snap->countHost : (int)(snap->regionInts - 64);
             if (bound > e->pruneCap) return fail(DSB200_ERR_INVALID, "snapshot larger than the pruning scratch");
             launch_prune(e->stream, slide, scene->voxels, scene->hash, scene->bucket_num, snap->ids, snap->countDev, e->pruneCap,
-                         minAge, maxWeight, (int)e->frameIdx, scene->alloc_list, rs->visible_type, e->slotMark, e->pruneScratch,
+                         minAge, maxWeight, (int)e->frameIdx, scene->alloc_list, rs->visible_type,
+                         rs->visible_type == e->visBitsOwner ? e->fs.visBits : nullptr, e->slotMark, e->pruneScratch,
                          e->fs.counters, e->fs);
         }
     }
@@ -533,7 +576,7 @@ int dsb200_create_expected_depths(dsb200_vis *v, const dsb200_scene *scene, cons
 int dsb200_find_surface(dsb200_vis *v, const dsb200_scene *scene, const float *invM, const float *intr, dsb200_render_state *rs)
 {
     RayParams P; make_ray_params(P, scene, nullptr, invM, intr, rs->width, rs->height);
-    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(v->stream));
     return DSB200_OK;
@@ -543,7 +586,7 @@ int dsb200_create_icp_maps(dsb200_vis *v, const dsb200_scene *scene, const dsb20
 {
     if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "create_icp_maps: tracking state has no point cloud buffers");
     RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
     launch_icp_maps(v->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(v->stream));
@@ -556,7 +599,7 @@ int dsb200_render_image(dsb200_vis *v, const dsb200_scene *scene, const float *M
     if (!outRGBA) return fail(DSB200_ERR_INVALID, "render_image: null output image");
     if (type == DSB200_RENDER_COLOURCODED) type = DSB200_RENDER_SHADED_GREYSCALE;   // !TIndex::hasColorCoding
     RayParams P; make_ray_params(P, scene, M, invM, intr, rs->width, rs->height);
-    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
     launch_shade(v->stream, P, type, scene->voxels, scene->hash, rs->raycast_result, outRGBA, outDepth);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(v->stream));
@@ -592,12 +635,24 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
         CU(cudaMemcpyAsync(&e->fs.counters->noVisible, &e->hostCounters->noVisible, 4, cudaMemcpyHostToDevice, e->stream));
     }
     DSB_MARK(1);
+    // Integration (writes voxels) and the expected-depth image (reads hash + visible list, writes the range image) are
+    // independent: outside profiling mode the latter runs on a side stream, forked after the visible list and joined
+    // before the raycast.
+    const bool fork = !e->profile && (stages & DSB200_FRAME_INTEGRATE) && (stages & DSB200_FRAME_EXPECTED_DEPTHS) && e->sideStream;
+    if (fork) {
+        CU(cudaEventRecord(e->evFork, e->stream));
+        CU(cudaStreamWaitEvent(e->sideStream, e->evFork, 0));
+        ProjParams P; make_proj_params(P, scene, trk->M_d, view->intr_d, rs->width, rs->height);
+        launch_expected_depths(e->sideStream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, nullptr, e->fs.counters);
+        CU(cudaEventRecord(e->evJoin, e->sideStream));
+    }
     if (stages & DSB200_FRAME_INTEGRATE) {
         FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
         launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb);
     }
     DSB_MARK(2);
-    if (stages & DSB200_FRAME_EXPECTED_DEPTHS) {
+    if (fork) CU(cudaStreamWaitEvent(e->stream, e->evJoin, 0));
+    else if (stages & DSB200_FRAME_EXPECTED_DEPTHS) {
         ProjParams P; make_proj_params(P, scene, trk->M_d, view->intr_d, rs->width, rs->height);
         launch_expected_depths(e->stream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, nullptr, e->fs.counters);
     }
@@ -605,7 +660,7 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     if (stages & DSB200_FRAME_ICP_MAPS) {
         if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "process_frame: tracking state has no point cloud buffers");
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
         DSB_MARK(4);
         launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
     } else DSB_MARK(4);
@@ -613,10 +668,36 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     return finish_call(e, scene, rs, (stages & DSB200_FRAME_ALLOCATE) != 0);
 }
 
+int dsb200_debug_force_plain_division(dsb200_recon *e, int on) { e->forceSlowDiv = on != 0; return DSB200_OK; }
+
+int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches)
+{
+    if (!mismatches) return fail(DSB200_ERR_INVALID, "selftest_division: null output");
+    if (dsb200_device_count() == 0) return fail(DSB200_ERR_NO_DEVICE, "no CUDA device: libdsb200 has no CPU fallback");
+    unsigned long long *d = nullptr;
+    CU(cudaMalloc(&d, 8));
+    CU(cudaMemset(d, 0, 8));
+    launch_selftest_division(nullptr, n, seed, d);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(mismatches, d, 8, cudaMemcpyDeviceToHost));
+    CU(cudaFree(d));
+    return DSB200_OK;
+}
+
 int dsb200_profile_enable(dsb200_recon *e, int on)
 {
-    if (on && !e->ev[0]) for (int i = 0; i <= DSB200_PROFILE_STAGES; i++) CU(cudaEventCreate(&e->ev[i]));
+    if (on && !e->ev[0]) {
+        for (int i = 0; i <= DSB200_PROFILE_STAGES; i++) CU(cudaEventCreate(&e->ev[i]));
+        for (int i = 0; i <= DSB200_PROFILE_ALLOC_STAGES; i++) CU(cudaEventCreate(&e->evAlloc[i]));
+    }
     e->profile = on != 0;
+    return DSB200_OK;
+}
+int dsb200_profile_read_allocate(dsb200_recon *e, float *ms)
+{
+    if (!e->profile || !e->evAllocRecorded) return fail(DSB200_ERR_INVALID, "profile_read_allocate: nothing recorded");
+    CU(cudaEventSynchronize(e->evAlloc[DSB200_PROFILE_ALLOC_STAGES]));
+    for (int i = 0; i < DSB200_PROFILE_ALLOC_STAGES; i++) CU(cudaEventElapsedTime(&ms[i], e->evAlloc[i], e->evAlloc[i + 1]));
     return DSB200_OK;
 }
 int dsb200_profile_read(dsb200_recon *e, float *ms)

@@ -10,6 +10,11 @@ struct FrameState {
     unsigned long long *scanState;   // [2 * scanTiles]: look-back words of k_allocate, then k_visible_list
     int *tickets;                    // [4] dynamic tile tickets
     int scanTiles;                   // ceil(totalEntries / 1024)
+    // slot bitmaps (reconstruction engine only), padded to bitTiles * 1024 words
+    unsigned *reqBits;               // slots holding an allocation request this frame (all zero between frames)
+    unsigned *reqExBits;             // ... of which excess-list requests
+    unsigned *visBits;               // superset of the slots whose visibility flag may be non-zero
+    int bitTiles;                    // ceil(totalEntries / 32768)
 };
 
 struct AllocParams {
@@ -33,6 +38,9 @@ struct FuseParams {                  // integrate / de-integrate
     int maxW, W, H, Wrgb, Hrgb;
     int stopMaxW, approximate;       // template flags of the reference kernel (CUDA .cu:407-420)
     int depthWeighting, maxNewW, maxDistance;
+    // exact-division support (exactdiv.cuh): host-computed correctly rounded reciprocals and the operand-range verdict
+    float rcpMu, rcp255, rcp32767;
+    int fastDiv;
 };
 
 struct RayParams {                   // raycast (castRay) + ICP maps
@@ -53,8 +61,11 @@ struct ProjParams {                  // CreateExpectedDepths
 // recon_alloc.cu
 void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeBlock, int hostLastFreeExcess,
                         int hostNoVisible, int useHost, const int *visibleIds, uint8_t *visType, int prevUpperBound);
-void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const float *depth, const dsb200_hash_entry *hash,
-                           uint8_t *visType, unsigned *reqKey);
+void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
+                           const dsb200_hash_entry *hash, uint8_t *visType, unsigned *reqKey);
+void launch_recheck_visibility(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
+                               const int *prevVisibleIds, uint8_t *visType);
+void launch_rebuild_visbits(cudaStream_t st, const FrameState &fs, const uint8_t *visType, int total);
 void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
                      dsb200_hash_entry *hash, const int *allocList, const int *excessList, uint8_t *visType,
                      unsigned *reqKey, int total, int doAllocate);
@@ -70,11 +81,13 @@ void launch_reset_scene(cudaStream_t st, dsb200_voxel *voxels, size_t numVoxels,
                         int *allocList, int numBlocks, int *excessList, int excessSize, uint8_t *visTypeOrNull,
                         unsigned *reqKey, Counters *counters);
 
+void launch_selftest_division(cudaStream_t st, unsigned long long n, unsigned long long seed, unsigned long long *mismatches);
+
 // recon_prune.cu
 void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash_entry *hash, int bucketNum,
                   const int *ids, const int *count, int countUpperBound, int minAge, int maxWeight, int currentFrame,
-                  int *allocList, uint8_t *visType, unsigned *slotMark, int *pendingList, Counters *counters,
-                  const FrameState &fs);
+                  int *allocList, uint8_t *visType, unsigned *visBitsOrNull, unsigned *slotMark, int *pendingList,
+                  Counters *counters, const FrameState &fs);
 
 // vis.cu
 void launch_find_visible(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
@@ -84,7 +97,7 @@ void launch_count_visible(cudaStream_t st, const dsb200_hash_entry *hash, const 
 void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_hash_entry *hash, const int *ids,
                             const int *count, float *rangeImage, int *blockTileCounts, Counters *counters);
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
-                    const float *rangeImage, float *raycastResult);
+                    const float *rangeImage, float *raycastResult, int *ticketPair /* two zeroed ints, re-armed by the kernel */);
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,
                      uint8_t *rendering);
 void launch_shade(cudaStream_t st, const RayParams &P, int renderType, const dsb200_voxel *voxels,

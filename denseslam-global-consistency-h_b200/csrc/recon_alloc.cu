@@ -17,6 +17,8 @@
 namespace dsb {
 
 // ---------------------------------------------------------------- shared ray set-up
+constexpr unsigned kVerified = 0x80u;   // transient marker on a visibility flag: "type 3, frustum test passed this frame"
+
 struct RaySeg { float px, py, pz, dx, dy, dz; int noSteps; };
 
 __device__ __forceinline__ bool ray_segment(RaySeg &r, int x, int y, float d, const AllocParams &P)
@@ -50,7 +52,11 @@ __global__ void __launch_bounds__(256) k_begin_frame(FrameState fs, int hostLast
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
     // every thread derives the previous count the same way (no intra-kernel dependency)
     const int nPrev = useHostCounters ? hostNoVisible : fs.counters->noVisible;
-    for (int i = tid; i < nPrev; i += stride) visType[visibleIds[i]] = 3;
+    for (int i = tid; i < nPrev; i += stride) {
+        const int h = visibleIds[i];
+        visType[h] = 3;
+        atomicOr(&fs.visBits[h >> 5], 1u << (h & 31));   // normally already set by the previous build; makes any caller-supplied list safe
+    }
     for (int i = tid; i < nScanWords; i += stride) fs.scanState[i] = 0ull;
     if (tid == 0) {
         fs.tickets[0] = 0; fs.tickets[1] = 0;
@@ -65,7 +71,10 @@ __global__ void __launch_bounds__(256) k_begin_frame(FrameState fs, int hostLast
     }
 }
 
-__global__ void __launch_bounds__(256) k_alloc_requests(AllocParams P, const float *__restrict__ depth,
+// One thread per depth pixel.  A hit writes the visibility flag (and the bitmap bit when the flag was 0: the flag read is
+// issued together with the hash-entry load, so it adds no latency); a miss races for the slot with an ORDER KEY and the
+// first requester records the request (and whether it is an excess-list request: a function of the slot alone).
+__global__ void __launch_bounds__(256) k_alloc_requests(AllocParams P, FrameState fs, const float *__restrict__ depth,
                                                         const dsb200_hash_entry *__restrict__ hash,
                                                         uint8_t *visType, unsigned *reqKey)
 {
@@ -81,22 +90,29 @@ __global__ void __launch_bounds__(256) k_alloc_requests(AllocParams P, const flo
         short bx = (short)floorf(px), by = (short)floorf(py), bz = (short)floorf(pz);
         if (lastH >= 0 && bx == lbx && by == lby && bz == lbz) {
             // same block as the previous step: a hit re-writes the same value; a miss must still
-            // raise the order key to this later step
+            // raise the order key to this later step (its request bit was set by the first miss)
             if (lastMiss) atomicMax(&reqKey[lastH], (unsigned)loc * 256u + (unsigned)i + 1u);
         } else {
             int h = hash_index(bx, by, bz, P.bucketMask);
+            unsigned char oldVis = visType[h];
             HashEntry e = load_entry(hash, h);
-            bool found = false;
-            if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= -1) { visType[h] = (e.ptr == -1) ? 2 : 1; found = true; }
-            if (!found) {
-                if (e.ptr >= -1) {
-                    while (e.offset >= 1) {
-                        h = P.bucketNum + e.offset - 1;
-                        e = load_entry(hash, h);
-                        if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= -1) { visType[h] = (e.ptr == -1) ? 2 : 1; found = true; break; }
-                    }
+            const bool headOccupied = e.ptr >= -1;
+            bool found = e.px == bx && e.py == by && e.pz == bz && headOccupied;
+            if (!found && headOccupied) {
+                while (e.offset >= 1) {
+                    h = P.bucketNum + e.offset - 1;
+                    oldVis = visType[h];
+                    e = load_entry(hash, h);
+                    if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= -1) { found = true; break; }
                 }
-                if (!found) atomicMax(&reqKey[h], (unsigned)loc * 256u + (unsigned)i + 1u);
+            }
+            if (found) {
+                const unsigned char v = (e.ptr == -1) ? 2 : 1;
+                if (oldVis != v) visType[h] = v;
+                if (oldVis == 0) atomicOr(&fs.visBits[h >> 5], 1u << (h & 31));   // a stale 0 only costs a redundant RED
+            } else if (atomicMax(&reqKey[h], (unsigned)loc * 256u + (unsigned)i + 1u) == 0u) {
+                atomicOr(&fs.reqBits[h >> 5], 1u << (h & 31));                    // first request for this slot
+                if (headOccupied) atomicOr(&fs.reqExBits[h >> 5], 1u << (h & 31));
             }
             lastH = h; lbx = bx; lby = by; lbz = bz; lastMiss = !found;
         }
@@ -104,7 +120,19 @@ __global__ void __launch_bounds__(256) k_alloc_requests(AllocParams P, const flo
     }
 }
 
-// One CTA = one tile of 1024 consecutive slots (4 per thread, 16 B key loads).
+// The ordered passes below scan BITMAPS (1 bit per hash slot) instead of the slot arrays: reqBits / reqExBits mark the slots
+// that received an (excess-list) allocation request this frame; visBits is a superset of the slots whose visibility flag is
+// non-zero.  One CTA = one tile of 1024 bitmap words = 32768 consecutive slots (4 words per thread, one 16 B load), so the
+// 5 M-slot table of the bench configuration is 160 co-resident tiles whose look-back chain resolves in a few round trips,
+// and the per-thread first pass is pure popcount (k_allocate) or at most eight independent 16 B flag loads (k_visible_list):
+// no thread walks a serial chain of dependent loads before the scan.
+
+// iterate over the set bits of the thread's 4 words in ascending slot order
+#define DSB_FOR_EACH_BIT(words, wordBase, slotVar, jVar, bitVar)                                  \
+    for (int jVar = 0; jVar < 4; jVar++)                                                          \
+        for (unsigned rem_ = (words)[jVar]; rem_;)                                                \
+            for (int bitVar = __ffs(rem_) - 1, slotVar = (((wordBase) + jVar) << 5) + bitVar, once_ = 1; once_; once_ = 0, rem_ &= rem_ - 1)
+
 __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, const float *__restrict__ depth,
                                                   dsb200_hash_entry *hash, const int *__restrict__ allocList,
                                                   const int *__restrict__ excessList, uint8_t *visType,
@@ -116,26 +144,16 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
     if (threadIdx.x == 0) sTile = atomicAdd(&fs.tickets[0], 1);
     __syncthreads();
     const int tile = sTile;
-    const int slot0 = tile * 1024 + threadIdx.x * 4;
-    unsigned key[4] = {0, 0, 0, 0};
-    if (slot0 + 3 < total) {
-        uint4 k = *reinterpret_cast<const uint4 *>(reqKey + slot0);
-        key[0] = k.x; key[1] = k.y; key[2] = k.z; key[3] = k.w;
-    } else {
-        for (int j = 0; j < 4; j++) if (slot0 + j < total) key[j] = reqKey[slot0 + j];
+    const int word0 = tile * 1024 + threadIdx.x * 4;
+    unsigned bits[4], excess[4];
+    {
+        const uint4 w = *reinterpret_cast<const uint4 *>(fs.reqBits + word0);   // padded to whole tiles
+        const uint4 x = *reinterpret_cast<const uint4 *>(fs.reqExBits + word0);
+        bits[0] = w.x; bits[1] = w.y; bits[2] = w.z; bits[3] = w.w;
+        excess[0] = x.x; excess[1] = x.y; excess[2] = x.z; excess[3] = x.w;
     }
-    unsigned na = 0, nb = 0; unsigned char type[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-        if (key[j]) {
-            int h = slot0 + j;
-            // the request's type is a function of the slot alone: free bucket head -> 1, else
-            // (occupied head with no chain, or chain tail in the excess area) -> 2
-            bool ordered = (h < P.bucketNum) && (load_entry_cg(hash, h).ptr < -1);
-            type[j] = ordered ? 1 : 2;
-            na++; nb += ordered ? 0 : 1;
-        }
-    }
+    const unsigned na = __popc(bits[0]) + __popc(bits[1]) + __popc(bits[2]) + __popc(bits[3]);
+    const unsigned nb = __popc(excess[0]) + __popc(excess[1]) + __popc(excess[2]) + __popc(excess[3]);
     unsigned exA, exB, totA, totB;
     block_scan2(na, nb, sScan, exA, exB, totA, totB);
     if (threadIdx.x < 32) {
@@ -145,16 +163,19 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
     }
     __syncthreads();
     const int lastFreeBlock0 = fs.counters->lastFreeBlock, lastFreeExcess0 = fs.counters->lastFreeExcess;
-    unsigned ra = sEx[0] + exA, rb = sEx[1] + exB;
     if (na) {
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            if (!key[j]) continue;
-            const int h = slot0 + j;
-            if (type[j] == 1) visType[h] = 1;             // new ordered entry is visible (DA/...:391)
+        unsigned ra = sEx[0] + exA, rb = sEx[1] + exB;
+        DSB_FOR_EACH_BIT(bits, word0, h, j, bit) {
+            const bool isExcess = (excess[j] >> bit) & 1u;
+            const unsigned key = reqKey[h];
+            reqKey[h] = 0;                                    // keys are consumed: the array stays zeroed between frames
+            if (!isExcess) {                                  // new ordered entry is visible (DA/...:391)
+                visType[h] = 1;
+                atomicOr(&fs.visBits[h >> 5], 1u << (h & 31));
+            }
             if (doAllocate) {
                 // recompute the winning request's block: pixel = key/256, step = key%256 - 1
-                const unsigned ord = key[j] - 1u;
+                const unsigned ord = key - 1u;
                 const int loc = (int)(ord >> 8), step = (int)(ord & 255u);
                 const int y = loc / P.W, x = loc - y * P.W;
                 RaySeg r; ray_segment(r, x, y, __ldg(depth + loc), P);
@@ -162,24 +183,25 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
                 for (int s = 0; s < step; s++) { px += r.dx; py += r.dy; pz += r.dz; }
                 const short bx = (short)floorf(px), by = (short)floorf(py), bz = (short)floorf(pz);
                 const int vbaIdx = lastFreeBlock0 - (int)ra;
-                if (type[j] == 1) {
+                if (!isExcess) {
                     if (vbaIdx >= 0) store_entry(hash, h, bx, by, bz, 0, allocList[vbaIdx], 0);
                 } else {
                     const int exlIdx = lastFreeExcess0 - (int)rb;
                     if (vbaIdx >= 0 && exlIdx >= 0) {
                         const int exlOffset = excessList[exlIdx];
+                        const int child = P.bucketNum + exlOffset;
                         reinterpret_cast<int *>(hash)[(size_t)h * 5 + 2] = exlOffset + 1;       // parent.offset
-                        store_entry(hash, P.bucketNum + exlOffset, bx, by, bz, 0, allocList[vbaIdx], 0);
-                        visType[P.bucketNum + exlOffset] = 1;
+                        store_entry(hash, child, bx, by, bz, 0, allocList[vbaIdx], 0);
+                        visType[child] = 1;
+                        atomicOr(&fs.visBits[child >> 5], 1u << (child & 31));
                     }
                     rb++;
                 }
                 ra++;
             }
         }
-        // keys are consumed: leave the array zeroed for the next frame (no per-frame memset)
-        if (slot0 + 3 < total) *reinterpret_cast<uint4 *>(reqKey + slot0) = make_uint4(0, 0, 0, 0);
-        else for (int j = 0; j < 4; j++) if (slot0 + j < total) reqKey[slot0 + j] = 0;
+        *reinterpret_cast<uint4 *>(fs.reqBits + word0) = make_uint4(0, 0, 0, 0);
+        if (nb) *reinterpret_cast<uint4 *>(fs.reqExBits + word0) = make_uint4(0, 0, 0, 0);
     }
     // the tile holding the last slot knows the grand totals
     // (written to separate fields: other tiles may still be reading lastFreeBlock / lastFreeExcess)
@@ -187,6 +209,47 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
         fs.counters->lastFreeBlockNew = doAllocate ? lastFreeBlock0 - (int)(sEx[0] + totA) : lastFreeBlock0;
         fs.counters->lastFreeExcessNew = doAllocate ? lastFreeExcess0 - (int)(sEx[1] + totB) : lastFreeExcess0;
     }
+    (void)total;
+}
+
+// Frustum re-test of the slots that were visible last frame and were not re-observed by this frame's depth rays (flag 3;
+// CPU .cpp:268-285).  One thread per entry of the previous visible list = perfectly balanced, and the ordered compaction
+// that follows only has to look at flags.  Runs after k_allocate (a freed slot of the old list may just have been
+// re-allocated -> flag 1, no re-test, as in the serial engine).
+__global__ void __launch_bounds__(256) k_recheck_visibility(VisParams P, FrameState fs, const dsb200_hash_entry *__restrict__ hash,
+                                                            const int *__restrict__ prevVisibleIds, uint8_t *visType)
+{
+    const int nPrev = fs.counters->noVisiblePrev;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nPrev; i += gridDim.x * blockDim.x) {
+        const int h = __ldg(prevVisibleIds + i);
+        if (visType[h] != 3) continue;
+        const HashEntry e = load_entry(hash, h);
+        bool vis, visEnl;
+        block_visibility(vis, visEnl, e.px, e.py, e.pz, P.M, P.proj, P.voxelSize, P.W, P.H, P.useSwapping != 0);
+        // verified entries carry a marker bit until k_visible_list emits them; a flag 3 WITHOUT the marker can only come from
+        // outside the list (pruning moves flags between slots, .cu:574-579) and is re-tested there
+        visType[h] = (P.useSwapping ? visEnl : vis) ? (uint8_t)(3 | kVerified) : (uint8_t)0;
+    }
+}
+
+// non-zero bytes of the 32 visibility flags of bitmap word w -> mask
+__device__ __forceinline__ unsigned flag_mask32(const uint8_t *visType, int w, int total)
+{
+    const int s0 = w << 5;
+    unsigned m = 0;
+    if (s0 + 31 < total) {
+        const uint4 a = *reinterpret_cast<const uint4 *>(visType + s0), b = *reinterpret_cast<const uint4 *>(visType + s0 + 16);
+        const unsigned v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            // byte != 0 -> bit: fold each byte onto its low bit
+            unsigned t = v[k]; t |= t >> 4; t |= t >> 2; t |= t >> 1; t &= 0x01010101u;
+            m |= ((t & 1u) | ((t >> 7) & 2u) | ((t >> 14) & 4u) | ((t >> 21) & 8u)) << (4 * k);
+        }
+    } else {
+        for (int k = 0; k < 32; k++) if (s0 + k < total && visType[s0 + k]) m |= 1u << k;
+    }
+    return m;
 }
 
 // Ordered visible-list build (CPU .cpp:261-336).  Counter a = visible slots, counter b = visible
@@ -202,28 +265,67 @@ __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs
     if (threadIdx.x == 0) sTile = atomicAdd(&fs.tickets[1], 1);
     __syncthreads();
     const int tile = sTile;
-    const int slot0 = tile * 1024 + threadIdx.x * 4;
-    unsigned char vt[4] = {0, 0, 0, 0};
-    if (slot0 + 3 < total) {
-        unsigned w = *reinterpret_cast<const unsigned *>(visType + slot0);
-        vt[0] = w & 0xff; vt[1] = (w >> 8) & 0xff; vt[2] = (w >> 16) & 0xff; vt[3] = w >> 24;
-    } else {
-        for (int j = 0; j < 4; j++) if (slot0 + j < total) vt[j] = visType[slot0 + j];
+    const int word0 = tile * 1024 + threadIdx.x * 4;
+    unsigned bits[4], keep[4], swapIn[4] = {0, 0, 0, 0};
+    {
+        const uint4 w = *reinterpret_cast<const uint4 *>(fs.visBits + word0);
+        bits[0] = w.x; bits[1] = w.y; bits[2] = w.z; bits[3] = w.w;
     }
-    unsigned na = 0, nb = 0; bool swapIn[4] = {false, false, false, false};
-    if (vt[0] | vt[1] | vt[2] | vt[3]) {
+    // the bitmap is a superset: confirm against the flags (independent vector loads, only for non-empty words)
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            if (vt[j] == 3) {
-                HashEntry e = load_entry_cg(hash, slot0 + j);
+    for (int j = 0; j < 4; j++) {
+        keep[j] = 0;
+        if (!bits[j]) continue;
+        const int s0 = (word0 + j) << 5;
+        if (s0 + 31 < total) {
+            uint4 *fp = reinterpret_cast<uint4 *>(visType + s0);
+            uint4 a = fp[0], b = fp[1];
+            unsigned v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+            unsigned nz = 0, marked = 0, raw3 = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                unsigned t = v[k]; t |= t >> 4; t |= t >> 2; t |= t >> 1; t &= 0x01010101u;
+                nz |= ((t & 1u) | ((t >> 7) & 2u) | ((t >> 14) & 4u) | ((t >> 21) & 8u)) << (4 * k);
+                unsigned m = (v[k] >> 7) & 0x01010101u;
+                marked |= ((m & 1u) | ((m >> 7) & 2u) | ((m >> 14) & 4u) | ((m >> 21) & 8u)) << (4 * k);
+                unsigned x = v[k] ^ 0x03030303u; x |= x >> 4; x |= x >> 2; x |= x >> 1; x = ~x & 0x01010101u;   // byte == 3
+                raw3 |= ((x & 1u) | ((x >> 7) & 2u) | ((x >> 14) & 4u) | ((x >> 21) & 8u)) << (4 * k);
+            }
+            keep[j] = bits[j] & nz;
+            if (marked) {                                   // strip the markers: the stored flag is the reference's 3
+                a.x &= 0x7f7f7f7fu; a.y &= 0x7f7f7f7fu; a.z &= 0x7f7f7f7fu; a.w &= 0x7f7f7f7fu;
+                b.x &= 0x7f7f7f7fu; b.y &= 0x7f7f7f7fu; b.z &= 0x7f7f7f7fu; b.w &= 0x7f7f7f7fu;
+                fp[0] = a; fp[1] = b;
+            }
+            for (unsigned rem = keep[j] & raw3; rem; rem &= rem - 1) {       // rare: flag 3 that k_recheck_visibility did not see
+                const int bit = __ffs(rem) - 1, h = s0 + bit;
+                const HashEntry e = load_entry_cg(hash, h);
                 bool vis, visEnl;
                 block_visibility(vis, visEnl, e.px, e.py, e.pz, P.M, P.proj, P.voxelSize, P.W, P.H, P.useSwapping != 0);
-                if (!(P.useSwapping ? visEnl : vis)) { vt[j] = 0; visType[slot0 + j] = 0; }
+                if (!(P.useSwapping ? visEnl : vis)) { visType[h] = 0; keep[j] &= ~(1u << bit); }
             }
-            if (vt[j] > 0) {
-                na++;
-                if (P.useSwapping && load_entry_cg(hash, slot0 + j).ptr == -1) { swapIn[j] = true; nb++; }
+        } else {
+            for (int k = 0; k < 32 && s0 + k < total; k++) {
+                if (!((bits[j] >> k) & 1u)) continue;
+                unsigned char f = visType[s0 + k];
+                if (f == 3) {
+                    const HashEntry e = load_entry_cg(hash, s0 + k);
+                    bool vis, visEnl;
+                    block_visibility(vis, visEnl, e.px, e.py, e.pz, P.M, P.proj, P.voxelSize, P.W, P.H, P.useSwapping != 0);
+                    if (!(P.useSwapping ? visEnl : vis)) f = 0;
+                }
+                if (f & kVerified) f &= 0x7f;
+                visType[s0 + k] = f;
+                if (f) keep[j] |= 1u << k;
             }
+        }
+    }
+    if (bits[0] != keep[0] || bits[1] != keep[1] || bits[2] != keep[2] || bits[3] != keep[3])
+        *reinterpret_cast<uint4 *>(fs.visBits + word0) = make_uint4(keep[0], keep[1], keep[2], keep[3]);
+    unsigned na = __popc(keep[0]) + __popc(keep[1]) + __popc(keep[2]) + __popc(keep[3]), nb = 0;
+    if (P.useSwapping && na) {
+        DSB_FOR_EACH_BIT(keep, word0, h, j, bit) {
+            if (load_entry_cg(hash, h).ptr == -1) { swapIn[j] |= 1u << bit; nb++; }
         }
     }
     unsigned exA, exB, totA, totB;
@@ -237,17 +339,15 @@ __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs
     if (na) {
         unsigned ra = sEx[0] + exA, rb = sEx[1] + exB;
         const int lastFreeBlock0 = fs.counters->lastFreeBlockNew;   // result of k_allocate (previous launch)
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            if (vt[j] == 0) continue;
+        DSB_FOR_EACH_BIT(keep, word0, h, j, bit) {
             if ((int)ra < visibleCapacity) {
-                visibleIds[ra] = slot0 + j;
-                if (snapshotIds) snapshotIds[ra] = slot0 + j;
+                visibleIds[ra] = h;
+                if (snapshotIds) snapshotIds[ra] = h;
             }
             ra++;
-            if (swapIn[j]) {
+            if ((swapIn[j] >> bit) & 1u) {
                 int vbaIdx = lastFreeBlock0 - (int)rb;
-                if (vbaIdx >= 0) reinterpret_cast<int *>(hash)[(size_t)(slot0 + j) * 5 + 3] = allocList[vbaIdx];
+                if (vbaIdx >= 0) reinterpret_cast<int *>(hash)[(size_t)h * 5 + 3] = allocList[vbaIdx];
                 rb++;
             }
         }
@@ -262,6 +362,13 @@ __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs
     }
 }
 
+// visBits <- (visType != 0): run when an engine meets a render state it has not been tracking
+__global__ void __launch_bounds__(256) k_rebuild_visbits(const uint8_t *__restrict__ visType, unsigned *visBits, int total, int words)
+{
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < words; w += gridDim.x * blockDim.x)
+        visBits[w] = ((w << 5) < total) ? flag_mask32(visType, w, total) : 0u;
+}
+
 // ---------------------------------------------------------------- host launchers
 void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeBlock, int hostLastFreeExcess,
                         int hostNoVisible, int useHost, const int *visibleIds, uint8_t *visType, int prevUpperBound)
@@ -273,17 +380,17 @@ void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeB
                visibleIds, visType, 2 * fs.scanTiles);
 }
 
-void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const float *depth, const dsb200_hash_entry *hash,
-                           uint8_t *visType, unsigned *reqKey)
+void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
+                           const dsb200_hash_entry *hash, uint8_t *visType, unsigned *reqKey)
 {
-    DSB_LAUNCH(k_alloc_requests, div_up(P.W * P.H, 256), 256, 0, st, P, depth, hash, visType, reqKey);
+    DSB_LAUNCH(k_alloc_requests, div_up(P.W * P.H, 256), 256, 0, st, P, fs, depth, hash, visType, reqKey);
 }
 
 void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
                      dsb200_hash_entry *hash, const int *allocList, const int *excessList, uint8_t *visType,
                      unsigned *reqKey, int total, int doAllocate)
 {
-    DSB_LAUNCH(k_allocate, fs.scanTiles, 256, 0, st, P, fs, depth, hash, allocList, excessList, visType, reqKey, total,
+    DSB_LAUNCH(k_allocate, fs.bitTiles, 256, 0, st, P, fs, depth, hash, allocList, excessList, visType, reqKey, total,
                doAllocate);
 }
 
@@ -291,8 +398,20 @@ void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &
                          const int *allocList, uint8_t *visType, int *visibleIds, int visibleCapacity, int *snapshotIds,
                          int *snapshotCount, int total)
 {
-    DSB_LAUNCH(k_visible_list, fs.scanTiles, 256, 0, st, P, fs, hash, allocList, visType, visibleIds, visibleCapacity,
+    DSB_LAUNCH(k_visible_list, fs.bitTiles, 256, 0, st, P, fs, hash, allocList, visType, visibleIds, visibleCapacity,
                snapshotIds, snapshotCount, total);
+}
+
+// must run between launch_allocate and launch_visible_list: visibleIds still holds the PREVIOUS list at that point
+void launch_recheck_visibility(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
+                               const int *prevVisibleIds, uint8_t *visType)
+{
+    DSB_LAUNCH(k_recheck_visibility, kNumSMs * 2, 256, 0, st, P, fs, hash, prevVisibleIds, visType);
+}
+
+void launch_rebuild_visbits(cudaStream_t st, const FrameState &fs, const uint8_t *visType, int total)
+{
+    DSB_LAUNCH(k_rebuild_visbits, kNumSMs * 4, 256, 0, st, visType, fs.visBits, total, fs.bitTiles * 1024);
 }
 
 } // namespace dsb

@@ -8,8 +8,11 @@
 // vector load/store (two voxels per thread, fully coalesced), stores only for lanes whose voxels
 // changed.  Arithmetic order is the reference's (no FMA contraction, IEEE division).
 #include "kernels.cuh"
+#include "exactdiv.cuh"
 
 namespace dsb {
+
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 struct VoxelRegs { short sdf; unsigned char w, r, g, b, wc; };
 
@@ -34,30 +37,50 @@ __device__ __forceinline__ unsigned char to_uchar(float v)
     return (unsigned char)((0 < lo) ? lo : 0);
 }
 
-template <bool DE>
-__device__ __forceinline__ void fuse_voxel(VoxelRegs &vox, float ptx, float pty, float ptz, const FuseParams &P,
-                                           const float *__restrict__ depth, const uchar4 *__restrict__ rgb)
+// Shared look-up tables: reciprocals of the integer voxel weights and c/255 for the colour bytes,
+// both produced with IEEE division at kernel start (3 divisions per thread).
+struct FuseTables { float rcp[kRcpTable]; float byte255[256]; };
+
+__device__ __forceinline__ void fill_tables(FuseTables &T)
 {
-    if (P.stopMaxW && vox.w == P.maxW) return;
-    if (P.approximate && vox.w != 0) return;
-    // computeUpdatedVoxelDepthInfo / computeDeUpdatedVoxelDepthInfo
+    for (int i = threadIdx.x; i < kRcpTable; i += blockDim.x) T.rcp[i] = 1.0f / (float)(i > 0 ? i : 1);
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) T.byte255[i] = (float)i / 255.0f;
+}
+
+// Depth part of ComputeUpdatedVoxelInfo (computeUpdatedVoxelDepthInfo / computeDeUpdatedVoxelDepthInfo,
+// DeviceAgnostic/ITMSceneReconstructionEngine.h:17-77, 117-181).  Returns true when the colour part
+// (:80-113, 184-217) must run for this voxel; that part is executed later by k_fuse on a CTA-wide
+// compacted list, so that a warp does not pay for it when only a few of its voxels are near the surface.
+template <bool DE, bool FAST>
+__device__ __forceinline__ bool fuse_depth(VoxelRegs &vox, float ptx, float pty, float ptz, const FuseParams &P,
+                                           const float *__restrict__ depth, const FuseTables &T)
+{
+    typedef Exact<FAST> X;
+    if (P.stopMaxW && vox.w == P.maxW) return false;
+    if (P.approximate && vox.w != 0) return false;
     Vec4 pt = {ptx, pty, ptz, 1.0f};
     Vec4 pc = mul(P.M_d, pt);
-    if (pc.z <= 0) return;
-    float u = P.proj_d[0] * pc.x / pc.z + P.proj_d[2];
-    float v = P.proj_d[1] * pc.y / pc.z + P.proj_d[3];
-    if ((u < 1) || (u > P.W - 2) || (v < 1) || (v > P.H - 2)) return;
+    if (pc.z <= 0) return false;
+    float qu, qv;
+    X::pair(P.proj_d[0] * pc.x, P.proj_d[1] * pc.y, pc.z, qu, qv);
+    float u = qu + P.proj_d[2];
+    float v = qv + P.proj_d[3];
+    if ((u < 1) || (u > P.W - 2) || (v < 1) || (v > P.H - 2)) return false;
     float dm = __ldg(depth + (int)(u + 0.5f) + (int)(v + 0.5f) * P.W);
-    if (dm <= 0.0f) return;
+    if (dm <= 0.0f) return false;
     float eta = dm - pc.z;
-    if (eta < -P.mu) return;
+    if (eta < -P.mu) return false;
+    const float q = X::by_host_rcp(eta, P.mu, P.rcpMu);
     {
-        float oldF = (float)vox.sdf / 32767.0f; int oldW = vox.w;
-        float q = eta / P.mu;
+        float oldF = X::by_int((float)vox.sdf, 32767.0f, P.rcp32767); int oldW = vox.w;
         float newF = (1.0f < q) ? 1.0f : q;
         int newW;
         if (P.depthWeighting) {
-            newW = (int)((double)((float)P.maxDistance / dm) + 0.5);   // "+ 0.5" is a double add in the reference
+            // (int)((float)maxDistance / dm + 0.5) with a DOUBLE add in the reference: the sum is exact in double, so
+            // the result is trunc(x) + (frac(x) >= 0.5), computed exactly in float (0 < x < 2^23 when it matters)
+            float x = X::one((float)P.maxDistance, dm);
+            if (x < 8388608.0f) { float tr = truncf(x); newW = (int)tr + ((x - tr >= 0.5f) ? 1 : 0); }
+            else newW = 0x7fffffff;
             if (newW < 1) newW = 1;
             if (newW > P.maxNewW) newW = P.maxNewW;
         } else newW = 1;
@@ -65,20 +88,30 @@ __device__ __forceinline__ void fuse_voxel(VoxelRegs &vox, float ptx, float pty,
         else     { newF = oldW * oldF - newW * newF; newW = oldW - newW; }
         if (DE && newW == 0) { reset(vox); }      // defined behaviour for the reference's 0/0
         else {
-            newF /= newW;
+            if ((unsigned)newW - 1u < (unsigned)(kRcpTable - 1)) newF = X::by_int(newF, (float)newW, T.rcp[newW]);
+            else newF /= newW;
             newW = (newW < P.maxW) ? newW : P.maxW;
             vox.sdf = (short)(int)(newF * 32767.0f);
             vox.w = (unsigned char)newW;
             if (DE && vox.w == 0) reset(vox);
         }
     }
-    if ((eta > P.mu) || (fabsf(eta / P.mu) > 0.25f)) return;
-    // computeUpdatedVoxelColorInfo / computeDeUpdatedVoxelColorInfo
+    return !((eta > P.mu) || (fabsf(q) > 0.25f));
+}
+
+template <bool DE, bool FAST>
+__device__ __forceinline__ void fuse_colour(VoxelRegs &vox, float ptx, float pty, float ptz, const FuseParams &P,
+                                            const uchar4 *__restrict__ rgb, const FuseTables &T)
+{
+    typedef Exact<FAST> X;
     float oldWc = (float)vox.wc;
-    float oc0 = (float)vox.r / 255.0f, oc1 = (float)vox.g / 255.0f, oc2 = (float)vox.b / 255.0f;
+    float oc0 = T.byte255[vox.r], oc1 = T.byte255[vox.g], oc2 = T.byte255[vox.b];
+    Vec4 pt = {ptx, pty, ptz, 1.0f};
     Vec4 pr = mul(P.M_rgb, pt);
-    float ur = P.proj_rgb[0] * pr.x / pr.z + P.proj_rgb[2];
-    float vr = P.proj_rgb[1] * pr.y / pr.z + P.proj_rgb[3];
+    float ur, vr;   // no z > 0 gate here in the reference; pair() falls back to plain division outside its window
+    X::pair(P.proj_rgb[0] * pr.x, P.proj_rgb[1] * pr.y, pr.z, ur, vr);
+    ur = ur + P.proj_rgb[2];
+    vr = vr + P.proj_rgb[3];
     if ((ur < 1) || (ur > P.Wrgb - 2) || (vr < 1) || (vr > P.Hrgb - 2)) return;
     // interpolateBilinear (DeviceAgnostic/ITMPixelUtils.h:11-39)
     int ix = (int)floorf(ur), iy = (int)floorf(vr);
@@ -90,42 +123,98 @@ __device__ __forceinline__ void fuse_voxel(VoxelRegs &vox, float ptx, float pty,
     float m0 = ((float)a.x * (1.0f - dx) * (1.0f - dy) + (float)b.x * dx * (1.0f - dy) + (float)c.x * (1.0f - dx) * dy + (float)d.x * dx * dy);
     float m1 = ((float)a.y * (1.0f - dx) * (1.0f - dy) + (float)b.y * dx * (1.0f - dy) + (float)c.y * (1.0f - dx) * dy + (float)d.y * dx * dy);
     float m2 = ((float)a.z * (1.0f - dx) * (1.0f - dy) + (float)b.z * dx * (1.0f - dy) + (float)c.z * (1.0f - dx) * dy + (float)d.z * dx * dy);
-    m0 = m0 / 255.0f; m1 = m1 / 255.0f; m2 = m2 / 255.0f;
+    m0 = X::by_int(m0, 255.0f, P.rcp255); m1 = X::by_int(m1, 255.0f, P.rcp255); m2 = X::by_int(m2, 255.0f, P.rcp255);
     float newWc = 1;
     float n0, n1, n2;
     if (!DE) { n0 = oc0 * oldWc + m0 * newWc; n1 = oc1 * oldWc + m1 * newWc; n2 = oc2 * oldWc + m2 * newWc; newWc = oldWc + newWc; }
     else     { n0 = oc0 * oldWc - m0 * newWc; n1 = oc1 * oldWc - m1 * newWc; n2 = oc2 * oldWc - m2 * newWc; newWc = oldWc - newWc; }
     if (DE && newWc == 0.0f) { vox.r = vox.g = vox.b = 0; vox.wc = 0; return; }   // defined behaviour for x/0
-    n0 /= newWc; n1 /= newWc; n2 /= newWc;
+    if (newWc >= 1.0f) {      // integer-valued, <= 256
+        const float y = T.rcp[(int)newWc];
+        n0 = X::by_int(n0, newWc, y); n1 = X::by_int(n1, newWc, y); n2 = X::by_int(n2, newWc, y);
+    } else { n0 /= newWc; n1 /= newWc; n2 /= newWc; }
     float mw = (float)(unsigned char)P.maxW;
     newWc = (newWc < mw) ? newWc : mw;
     vox.r = to_uchar(n0 * 255.0f); vox.g = to_uchar(n1 * 255.0f); vox.b = to_uchar(n2 * 255.0f);
     vox.wc = (unsigned char)(int)newWc;
 }
 
-template <bool DE>
+// One 4 KiB voxel block per CTA iteration.  Phase A: every thread loads 16 B (two voxels), runs the depth part in
+// registers and queues the voxels that need the colour part; phase B: the CTA drains the queue densely (a voxel per
+// thread, whatever warp it came from) on the shared-memory copy of the block; phase C: 16 B stores where anything changed.
+template <bool DE, bool FAST>
 __global__ void __launch_bounds__(256) k_fuse(FuseParams P, dsb200_voxel *voxels,
                                               const dsb200_hash_entry *__restrict__ hash,
                                               const int *__restrict__ ids, const int *__restrict__ countPtr,
                                               const float *__restrict__ depth, const uchar4 *__restrict__ rgb)
 {
+    __shared__ FuseTables T;
+    __shared__ uint4 sVox[256];
+    __shared__ unsigned short sQueue[kBlock3];
+    __shared__ int sCount[2];
     const int n = *countPtr;
-    const int t = threadIdx.x;
+    const int t = threadIdx.x, lane = t & 31;
     const int lx = (2 * t) & 7, ly = (t >> 2) & 7, lz = t >> 5;     // voxel 2t: x even, same y/z for 2t+1
-    for (int i = blockIdx.x; i < n; i += gridDim.x) {
-        const int slot = __ldg(ids + i);
-        const HashEntry e = load_entry(hash, slot);
-        if (e.ptr < 0) continue;
-        uint4 *p = reinterpret_cast<uint4 *>(voxels + (size_t)e.ptr * kBlock3) + t;
-        uint4 raw = *p;
-        const float pty = (float)(e.py * kBlock + ly) * P.voxelSize, ptz = (float)(e.pz * kBlock + lz) * P.voxelSize;
-        const int gx = e.px * kBlock + lx;
-        VoxelRegs v0 = unpack(raw.x, raw.y), v1 = unpack(raw.z, raw.w);
-        fuse_voxel<DE>(v0, (float)gx * P.voxelSize, pty, ptz, P, depth, rgb);
-        fuse_voxel<DE>(v1, (float)(gx + 1) * P.voxelSize, pty, ptz, P, depth, rgb);
-        uint4 out = raw;
-        pack(v0, out.x, out.y); pack(v1, out.z, out.w);
-        if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) *p = out;
+    fill_tables(T);
+    if (t < 2) sCount[t] = 0;
+    __syncthreads();
+    int par = 0;
+    // Software pipeline over the CTA's blocks: the chain ids[i] -> hash entry -> voxel block is three dependent global
+    // loads (~2 us); each stage is issued one iteration ahead of its consumer so the chain hides behind the arithmetic.
+    const int stride = gridDim.x;
+    const HashEntry none = {0, 0, 0, 0, 0, -2, 0};
+    int i = blockIdx.x;
+    int slot2 = (i + 2 * stride < n) ? __ldg(ids + i + 2 * stride) : -1;
+    HashEntry e1 = (i + stride < n) ? load_entry(hash, __ldg(ids + i + stride)) : none;
+    HashEntry e0 = (i < n) ? load_entry(hash, __ldg(ids + i)) : none;
+    for (; i < n; i += stride) {
+        const int slot3 = (i + 3 * stride < n) ? __ldg(ids + i + 3 * stride) : -1;      // stage A: list entry, 3 ahead
+        const HashEntry e2 = (slot2 >= 0) ? load_entry(hash, slot2) : none;              // stage B: hash entry, 2 ahead
+        if (e1.ptr >= 0) prefetch_l2(voxels + (size_t)e1.ptr * kBlock3 + 2 * t);         // stage C: voxel block -> L2, 1 ahead
+        if (e0.ptr >= 0) {
+            const HashEntry e = e0;
+            uint4 *p = reinterpret_cast<uint4 *>(voxels + (size_t)e.ptr * kBlock3) + t;
+            const uint4 raw = *p;
+            const float pty = (float)(e.py * kBlock + ly) * P.voxelSize, ptz = (float)(e.pz * kBlock + lz) * P.voxelSize;
+            const int gx = e.px * kBlock + lx;
+            VoxelRegs v0 = unpack(raw.x, raw.y), v1 = unpack(raw.z, raw.w);
+            const bool c0 = fuse_depth<DE, FAST>(v0, (float)gx * P.voxelSize, pty, ptz, P, depth, T);
+            const bool c1 = fuse_depth<DE, FAST>(v1, (float)(gx + 1) * P.voxelSize, pty, ptz, P, depth, T);
+            uint4 out = raw;
+            pack(v0, out.x, out.y); pack(v1, out.z, out.w);
+            // queue the colour work (warp-aggregated)
+            const unsigned m0 = __ballot_sync(0xffffffffu, c0), m1 = __ballot_sync(0xffffffffu, c1);
+            const int cnt = __popc(m0) + __popc(m1);
+            if (cnt) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&sCount[par], cnt);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const unsigned lt = (1u << lane) - 1u;
+                if (c0) sQueue[base + __popc(m0 & lt)] = (unsigned short)(2 * t);
+                if (c1) sQueue[base + __popc(m0) + __popc(m1 & lt)] = (unsigned short)(2 * t + 1);
+            }
+            sVox[t] = out;
+            if (t == 0) sCount[par ^ 1] = 0;
+            __syncthreads();
+            const int nq = sCount[par];
+            par ^= 1;
+            if (nq) {
+                uint2 *sv = reinterpret_cast<uint2 *>(sVox);
+                for (int k = t; k < nq; k += 256) {
+                    const int vi = sQueue[k];
+                    uint2 w = sv[vi];
+                    VoxelRegs vx = unpack(w.x, w.y);
+                    fuse_colour<DE, FAST>(vx, (float)(e.px * kBlock + (vi & 7)) * P.voxelSize, (float)(e.py * kBlock + ((vi >> 3) & 7)) * P.voxelSize,
+                                          (float)(e.pz * kBlock + (vi >> 6)) * P.voxelSize, P, rgb, T);
+                    pack(vx, w.x, w.y);
+                    sv[vi] = w;
+                }
+                __syncthreads();
+                out = sVox[t];
+            }
+            if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) *p = out;
+        }
+        e0 = e1; e1 = e2; slot2 = slot3;
     }
 }
 
@@ -133,10 +222,75 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
                  const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth, const uint8_t *rgb)
 {
     const int grid = kNumSMs * 8;
-    if (deintegrate)
-        DSB_LAUNCH(k_fuse<true>, grid, 256, 0, st, P, voxels, hash, ids, count, depth, reinterpret_cast<const uchar4 *>(rgb));
-    else
-        DSB_LAUNCH(k_fuse<false>, grid, 256, 0, st, P, voxels, hash, ids, count, depth, reinterpret_cast<const uchar4 *>(rgb));
+    const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
+    if (deintegrate) {
+        if (P.fastDiv) DSB_LAUNCH((k_fuse<true, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+        else DSB_LAUNCH((k_fuse<true, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+    } else {
+        if (P.fastDiv) DSB_LAUNCH((k_fuse<false, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+        else DSB_LAUNCH((k_fuse<false, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+    }
+}
+
+// ---------------------------------------------------------------- exact-division self test
+__device__ __forceinline__ unsigned long long splitmix(unsigned long long &x)
+{
+    unsigned long long z = (x += 0x9e3779b97f4a7c15ull);
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull; z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+// float with a uniformly random significand and sign, exponent uniform in [loExp, hiExp]
+__device__ __forceinline__ float random_float(unsigned long long &st, int loExp, int hiExp)
+{
+    unsigned long long r = splitmix(st);
+    unsigned mant = (unsigned)r & 0x7fffffu, sign = (unsigned)(r >> 23) & 1u;
+    int ex = loExp + (int)((r >> 24) % (unsigned long long)(hiExp - loExp + 1));
+    return __uint_as_float((sign << 31) | ((unsigned)(ex + 127) << 23) | mant);
+}
+__device__ __forceinline__ bool same_bits(float a, float b) { return __float_as_uint(a) == __float_as_uint(b); }
+
+__global__ void __launch_bounds__(256) k_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches)
+{
+    typedef Exact<true> X;
+    unsigned long long bad = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned long long st = seed * 0x2545f4914f6cdd1dull + i * 0x9e3779b97f4a7c15ull;
+        // (1) shared run-time divisor: numerators in [2^-84, 2^68] or 0, divisor anywhere in [2^-30, 2^30] (window + fall-back)
+        float a0 = random_float(st, -84, 68), a1 = random_float(st, -84, 68), b = random_float(st, -30, 30);
+        if ((i & 63) == 0) a0 = 0.0f;
+        if ((i & 1023) == 1) b = 0.0f;
+        float q0, q1;
+        X::pair(a0, a1, b, q0, q1);
+        bad += !same_bits(q0, a0 / b); bad += !same_bits(q1, a1 / b);
+        bad += !same_bits(X::one(a1, b), a1 / b);
+        // realistic projection operands: z in [0.05, 400], numerators up to 1e6
+        float z = fabsf(random_float(st, -5, 8)), nx = random_float(st, -20, 20);
+        X::pair(nx, a1, z, q0, q1);
+        bad += !same_bits(q0, nx / z);
+        // (2) host reciprocal, two steps: any divisor whose significand is not all ones
+        float mu = fabsf(random_float(st, -20, 20));
+        if ((__float_as_uint(mu) & 0x7fffffu) == 0x7fffffu) mu = 0.08f;
+        float eta = random_float(st, -40, 10);
+        bad += !same_bits(X::by_host_rcp(eta, mu, 1.0f / mu), eta / mu);
+        // (3) integer divisors with one correction step
+        unsigned long long r = splitmix(st);
+        float w = (float)(1 + (int)(r % 511ull)), num = random_float(st, -60, 20);
+        bad += !same_bits(X::by_int(num, w, 1.0f / w), num / w);
+        bad += !same_bits(X::by_int(num, 255.0f, 1.0f / 255.0f), num / 255.0f);
+        float s16 = (float)((int)((r >> 16) & 0xffffull) - 32768);
+        bad += !same_bits(X::by_int(s16, 32767.0f, 1.0f / 32767.0f), s16 / 32767.0f);
+        // (4) depth weighting rounding: trunc + frac test == (int)((double)x + 0.5)
+        float x = fabsf(random_float(st, -10, 22));
+        float tr = truncf(x); int fastW = (int)tr + ((x - tr >= 0.5f) ? 1 : 0);
+        bad += fastW != (int)((double)x + 0.5);
+    }
+    for (int o = 16; o > 0; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(mismatches, bad);
+}
+
+void launch_selftest_division(cudaStream_t st, unsigned long long n, unsigned long long seed, unsigned long long *mismatches)
+{
+    DSB_LAUNCH(k_selftest_division, kNumSMs * 8, 256, 0, st, n, seed, mismatches);
 }
 
 // ResetScene (CPU .cpp:25-45; CUDA .cu:111-148): pure store bandwidth, 16-byte stores.

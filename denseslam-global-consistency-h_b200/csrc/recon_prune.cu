@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(256) k_prune_rank(const dsb200_hash_entry *has
 
 __global__ void __launch_bounds__(128) k_prune_unlink(dsb200_hash_entry *hash, int bucketNum, const int *compactSlot,
                                                       const int *compactBucket, unsigned *slotMark,
-                                                      unsigned *bucketLeader, uint8_t *visType, FrameState fs)
+                                                      unsigned *bucketLeader, uint8_t *visType, unsigned *visBits, FrameState fs)
 {
     const int total = fs.counters->freedBlocks;
     int *hw = reinterpret_cast<int *>(hash);
@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(128) k_prune_unlink(dsb200_hash_entry *hash, i
 #pragma unroll
                     for (int k = 0; k < 5; k++) hw[(size_t)idx * 5 + k] = hw[(size_t)next * 5 + k];
                     visType[idx] = visType[next]; visType[next] = 0;
+                    if (visBits && visType[idx]) atomicOr(&visBits[idx >> 5], 1u << (idx & 31));
                     slotMark[idx] = slotMark[next]; slotMark[next] = 0;
                     hw[(size_t)next * 5 + 2] = 0; hw[(size_t)next * 5 + 3] = -2;
                 } else {               // bucket head, no successor
@@ -184,6 +185,7 @@ __global__ void __launch_bounds__(128) k_prune_unlink(dsb200_hash_entry *hash, i
                 hw[(size_t)bestPrev * 5 + 2] = hw[(size_t)idx * 5 + 2];
                 hw[(size_t)idx * 5 + 2] = 0; hw[(size_t)idx * 5 + 3] = -2;
                 visType[bestPrev] = visType[idx]; visType[idx] = 0;
+                if (visBits && visType[bestPrev]) atomicOr(&visBits[bestPrev >> 5], 1u << (bestPrev & 31));
             }
         }
         bucketLeader[b] = 0;
@@ -199,7 +201,7 @@ __global__ void k_prune_cleanup(const int *compactSlot, unsigned *slotMark, Fram
 
 void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash_entry *hash, int bucketNum,
                   const int *ids, const int *count, int countUpperBound, int minAge, int maxWeight, int currentFrame,
-                  int *allocList, uint8_t *visType, unsigned *slotMark, int *scratch, Counters *counters,
+                  int *allocList, uint8_t *visType, unsigned *visBits, unsigned *slotMark, int *scratch, Counters *counters,
                   const FrameState &fs)
 {
     (void)counters;
@@ -219,7 +221,7 @@ void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash
     DSB_LAUNCH(k_prune_rank, rankGrid, 256, 0, st, hash, bucketNum, ids, count, flags, compactSlot, compactBucket,
                allocList, slotMark, bucketLeader, fs);
     DSB_LAUNCH(k_prune_unlink, kNumSMs * 2, 128, 0, st, hash, bucketNum, compactSlot, compactBucket, slotMark,
-               bucketLeader, visType, fs);
+               bucketLeader, visType, visBits, fs);
     DSB_LAUNCH(k_prune_cleanup, kNumSMs, 256, 0, st, compactSlot, slotMark, fs);
 }
 

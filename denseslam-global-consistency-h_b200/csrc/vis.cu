@@ -125,23 +125,62 @@ __device__ __forceinline__ void range_minmax(float *range, int W, int x, int y, 
     if (__float_as_int(zmax) > __ldcg(px + 1)) atomicMax(px + 1, __float_as_int(zmax));
 }
 
+// One WARP per visible block: lanes 0-7 project one corner each (same arithmetic as project_block; min/max are
+// order-independent, so the warp reduction gives the identical bounding box and depth range), then all 32 lanes spread
+// over the bounding-box cells.  A thread-per-block version serialises the (up to ~30x30 cell) boxes of near blocks.
 __global__ void __launch_bounds__(256) k_project_fill(ProjParams P, const dsb200_hash_entry *__restrict__ hash,
                                                       const int *__restrict__ ids, const int *__restrict__ countPtr,
                                                       float *range, Counters *counters)
 {
     const int n = *countPtr;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nWarps = (gridDim.x * blockDim.x) >> 5;
     int tiles = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (int i = warp; i < n; i += nWarps) {
         HashEntry e = load_entry(hash, __ldg(ids + i));
         if (e.ptr < 0) continue;
-        int ul[2], lr[2]; float zr[2];
-        if (!project_block(e.px, e.py, e.pz, P, ul, lr, zr)) continue;
-        tiles += (int)ceilf((float)(lr[0] - ul[0] + 1) / 16.0f) * (int)ceilf((float)(lr[1] - ul[1] + 1) / 16.0f);
-        for (int y = ul[1]; y <= lr[1]; y++)
-            for (int x = ul[0]; x <= lr[0]; x++) range_minmax(range, P.W, x, y, zr[0], zr[1]);
+        // corner `lane & 7` (lanes 8-31 duplicate corners: harmless for min/max)
+        const int corner = lane & 7;
+        int ulx = P.W / kSubsample, uly = P.H / kSubsample, lrx = -1, lry = -1;
+        float zmin = kFarAway, zmax = kVeryClose;
+        {
+            short tx = e.px + ((corner & 1) ? 1 : 0), ty = e.py + ((corner & 2) ? 1 : 0), tz = e.pz + ((corner & 4) ? 1 : 0);
+            Vec4 p = {(float)tx * (float)kBlock * P.voxelSize, (float)ty * (float)kBlock * P.voxelSize,
+                      (float)tz * (float)kBlock * P.voxelSize, 1.0f};
+            p = mul(P.M, p);
+            if (!((double)p.z < 1e-6)) {
+                float px = (P.proj[0] * p.x / p.z + P.proj[2]) / (float)kSubsample;
+                float py = (P.proj[1] * p.y / p.z + P.proj[3]) / (float)kSubsample;
+                if (ulx > floorf(px)) ulx = (int)floorf(px);
+                if (lrx < ceilf(px)) lrx = (int)ceilf(px);
+                if (uly > floorf(py)) uly = (int)floorf(py);
+                if (lry < ceilf(py)) lry = (int)ceilf(py);
+                if (zmin > p.z) zmin = p.z;
+                if (zmax < p.z) zmax = p.z;
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            ulx = min(ulx, __shfl_xor_sync(0xffffffffu, ulx, o)); uly = min(uly, __shfl_xor_sync(0xffffffffu, uly, o));
+            lrx = max(lrx, __shfl_xor_sync(0xffffffffu, lrx, o)); lry = max(lry, __shfl_xor_sync(0xffffffffu, lry, o));
+            zmin = fminf(zmin, __shfl_xor_sync(0xffffffffu, zmin, o)); zmax = fmaxf(zmax, __shfl_xor_sync(0xffffffffu, zmax, o));
+        }
+        if (ulx < 0) ulx = 0;
+        if (uly < 0) uly = 0;
+        if (lrx >= P.W) lrx = P.W - 1;
+        if (lry >= P.H) lry = P.H - 1;
+        if (ulx > lrx || uly > lry) continue;
+        if (zmin < kVeryClose) zmin = kVeryClose;
+        if (zmax < kVeryClose) continue;
+        const int bw = lrx - ulx + 1, bh = lry - uly + 1;
+        if (lane == 0) tiles += (int)ceilf((float)bw / 16.0f) * (int)ceilf((float)bh / 16.0f);
+        for (int c = lane; c < bw * bh; c += 32) {
+            const int cy = c / bw;
+            range_minmax(range, P.W, ulx + (c - cy * bw), uly + cy, zmin, zmax);
+        }
     }
     for (int o = 16; o > 0; o >>= 1) tiles += __shfl_xor_sync(0xffffffffu, tiles, o);
-    if ((threadIdx.x & 31) == 0 && tiles) atomicAdd(&counters->renderBlocks, tiles);
+    if (lane == 0 && tiles) atomicAdd(&counters->renderBlocks, tiles);
 }
 
 // Exact fallback for the reference's MAX_RENDERING_BLOCKS rule (CPU .cpp:158: a block whose tiles
@@ -281,18 +320,35 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const dsb200
     return ptFound;
 }
 
-// GenericRaycast (CPU .cpp:296-333; CUDA .cu:807-819)
+// GenericRaycast (CPU .cpp:296-333; CUDA .cu:807-819).  Ray lengths differ by orders of magnitude across the image (sky
+// pixels do not march at all, grazing road pixels cross hundreds of voxels), so a static pixel-tile -> CTA map leaves
+// most of the machine idle behind a few long tiles (41 % achieved occupancy in profiles/r01a).  Here every WARP pulls
+// the next 8x4 pixel tile from a device ticket; the last warp to run dry re-arms the ticket pair for the next launch.
 __global__ void __launch_bounds__(128) k_raycast(RayParams P, const dsb200_voxel *__restrict__ voxels,
                                                  const dsb200_hash_entry *__restrict__ hash,
-                                                 const float2 *__restrict__ range, float4 *out)
+                                                 const float2 *__restrict__ range, float4 *out, int *ticket)
 {
-    const int x = blockIdx.x * 16 + (threadIdx.x & 15), y = blockIdx.y * 8 + (threadIdx.x >> 4);
-    if (x >= P.W || y >= P.H) return;
-    const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
-    const float2 mm = __ldg(range + loc2);
-    float4 r;
-    cast_ray(r, x, y, voxels, hash, P, mm.x, mm.y);
-    out[x + y * P.W] = r;
+    const int lane = threadIdx.x & 31;
+    const int tilesX = (P.W + 7) >> 3, tilesY = (P.H + 3) >> 2, nTiles = tilesX * tilesY;
+    while (true) {
+        int tile = 0;
+        if (lane == 0) tile = atomicAdd(&ticket[0], 1);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= nTiles) break;
+        const int ty = tile / tilesX, tx = tile - ty * tilesX;
+        const int x = tx * 8 + (lane & 7), y = ty * 4 + (lane >> 3);
+        if (x < P.W && y < P.H) {
+            const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
+            const float2 mm = __ldg(range + loc2);
+            float4 r;
+            cast_ray(r, x, y, voxels, hash, P, mm.x, mm.y);
+            out[x + y * P.W] = r;
+        }
+    }
+    if (lane == 0) {
+        const int nWarps = gridDim.x * (blockDim.x >> 5);
+        if (atomicAdd(&ticket[1], 1) == nWarps - 1) { ticket[1] = 0; ticket[0] = 0; }   // all tickets were handed out: re-arm
+    }
 }
 
 // ---------------------------------------------------------------- ICP maps (processPixelICP<true>, DA/...:391-439)
@@ -486,11 +542,13 @@ void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_h
 }
 
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
-                    const float *rangeImage, float *raycastResult)
+                    const float *rangeImage, float *raycastResult, int *ticketPair)
 {
-    dim3 grid(div_up(P.W, 16), div_up(P.H, 8));
+    const int nTiles = div_up(P.W, 8) * div_up(P.H, 4);
+    int grid = div_up(nTiles, 4);
+    if (grid > kNumSMs * 12) grid = kNumSMs * 12;
     DSB_LAUNCH(k_raycast, grid, 128, 0, st, P, voxels, hash, reinterpret_cast<const float2 *>(rangeImage),
-               reinterpret_cast<float4 *>(raycastResult));
+               reinterpret_cast<float4 *>(raycastResult), ticketPair);
 }
 
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,

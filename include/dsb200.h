@@ -214,6 +214,17 @@ void dsb200_mat4_multiply(const float *A, const float *B, float *out);
 #define DSB200_PROFILE_STAGES 5
 int dsb200_profile_enable(dsb200_recon *e, int on);
 int dsb200_profile_read(dsb200_recon *e, float *stage_ms /* [DSB200_PROFILE_STAGES] */);
+/* kernels of the last AllocateSceneFromDepth: 0 begin-frame 1 requests 2 ordered allocation 3 visibility re-test 4 visible list */
+#define DSB200_PROFILE_ALLOC_STAGES 5
+int dsb200_profile_read_allocate(dsb200_recon *e, float *stage_ms /* [DSB200_PROFILE_ALLOC_STAGES] */);
+
+/* ---- diagnostics of the exact-division fast paths (csrc/exactdiv.cuh) ----
+ * force_plain_division: run the integrate / de-integrate kernel variants that use the compiler's `/` everywhere.
+ * selftest_division: evaluates every fast-path helper against `/` on n pseudo-random operand tuples drawn from
+ * the operand windows the kernels guarantee (plus the out-of-window fall-backs); *mismatches = number of
+ * bit-level disagreements (must be 0). */
+int dsb200_debug_force_plain_division(dsb200_recon *e, int on);
+int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches);
 
 /* counters for bench.py: kernels launched by this library since process start */
 unsigned long long dsb200_kernel_launch_count(void);
