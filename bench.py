@@ -220,7 +220,7 @@ def run_ours(args, rank, world, local_rank):
                 abi.check(lib.dsb200_profile_read(recon.h, stage_buf))      # synchronises; device-side stage times
                 stage += np.array(stage_buf[:])
                 abi.check(lib.dsb200_profile_read_allocate(recon.h, stage_buf))
-                alloc_stage += np.array(stage_buf[:])
+                np.add(alloc_stage, np.array(stage_buf[:])[:5], out=alloc_stage)
             recon.Sync(scene, rs)
             counts.append(rs.c.no_visible)
         torch.cuda.synchronize()
