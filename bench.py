@@ -315,17 +315,95 @@ def run_ours(args, rank, world, local_rank):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ sharded scene
+def run_sharded(args, rank, world, local_rank):
+    """BASELINE configs[3]: ONE scene partitioned by block ownership across the N GPUs (sharded.py).  Rank 0 owns the camera
+    stream (frames resident in its HBM); a step = NCCL broadcast of the frame + per-shard allocate / integrate / expected
+    depths + whole-scene raycast over peer memory + ICP maps on the root.  value = frames/s of the one scene (strong scaling)."""
+    import torch
+    import torch.distributed as dist
+    abi = importlib.import_module(PKG + ".abi")
+    sharded = importlib.import_module(PKG + ".sharded")
+    lib = abi.load()
+    if lib.dsb200_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
+    abi.check(lib.dsb200_set_device(local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist.init_process_group("nccl", device_id=dev) if world > 1 else None
+    if world == 1:     # single process: still goes through DistShardedScene (count = 1) so the code path is the same
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29555")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    K, Wm = args.steps, args.warmup
+    cfg, frames = make_frames(K + Wm, seed=0)          # every rank knows the trajectory; only rank 0 uses the images
+    sc = sharded.DistShardedScene(cfg, CAPS, brick_log2=args.brick_log2, mode=args.shard_mode)
+    sc.m.recon.SetFusionWeightParams(cfg.depth_weighting, 10, 100)
+    packed = [sc.pack_frame(f).to(dev) for f in frames] if rank == 0 else [None] * len(frames)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    sc.m.recon.SetAsync(True)
+    for i in range(Wm):
+        sc.process_frame(packed[i], M=frames[i].M, timestamp=frames[i].timestamp)
+    sc.m.recon.Sync(sc.m.scene, sc.m.rs)
+    torch.cuda.synchronize(); dist.barrier()
+    l0 = lib.dsb200_kernel_launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    sampler = ClockSampler(local_rank); sampler.start()
+    vis_counts = []
+    for k in range(K):
+        flush.zero_()
+        evs[k][0].record()
+        sc.process_frame(packed[Wm + k], M=frames[Wm + k].M, timestamp=frames[Wm + k].timestamp)
+        evs[k][1].record()
+        sc.m.recon.Sync(sc.m.scene, sc.m.rs)
+        vis_counts.append(sc.m.rs.c.no_visible)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    launches = int(lib.dsb200_kernel_launch_count() - l0)
+    dist.barrier()
+    ms = float(sum(a.elapsed_time(b) for a, b in evs))
+    blocks = CAPS["num_blocks"] - 1 - sc.m.scene.c.last_free_block
+    t = torch.tensor([ms, float(blocks), float(np.mean(vis_counts))], dtype=torch.float64, device=dev)
+    tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    sc.m.recon.SetAsync(False)
+    sc.close()
+    dist.destroy_process_group()
+    if rank != 0:
+        return None
+    ms = float(tmax[0])
+    npx = cfg.W * cfg.H
+    return {"metric": METRIC, "value": K / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic", "mode": "sharded",
+            "config": {"workload": "C2 street sequence fused into ONE scene sharded by block ownership over %d GPU(s) "
+                                   "(bricks of %d^3 blocks, raycast mode '%s'); camera stream on rank 0" % (world, 1 << args.brick_log2, args.shard_mode),
+                       "frames": K, "visible_blocks_per_shard_mean": float(tsum[2]) / world, "visible_blocks_max_shard": float(tmax[2]),
+                       "blocks_allocated_total": int(tsum[1]), "blocks_allocated_max_shard": int(tmax[1]),
+                       "l2": "flushed (256 MiB write) between timed steps"},
+            "collectives_per_step": {"broadcast_bytes": 8 * npx + 72, "rendezvous_allreduce": 2 if args.shard_mode == "lookup" else 1},
+            "gpu_launches": launches, "clocks": clocks}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="replicas", choices=["replicas", "sharded"],
+                    help="N > 1: independent scenes per GPU (default, weak scaling) or ONE scene sharded by block ownership")
+    ap.add_argument("--shard-mode", default="lookup", choices=["lookup", "composite"])
+    ap.add_argument("--brick-log2", type=int, default=2)
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    out = run_reference(args, rank, world) if args.impl == "reference" else run_ours(args, rank, world, local_rank)
+    if args.impl == "reference":
+        out = run_reference(args, rank, world)
+    elif args.mode == "sharded":
+        out = run_sharded(args, rank, world, local_rank)
+    else:
+        out = run_ours(args, rank, world, local_rank)
     if out is not None:
         print(json.dumps(out))
 

@@ -23,6 +23,9 @@ ERR_CUDA, ERR_INVALID, ERR_VBA_EXHAUSTED, ERR_EXCESS_EXHAUSTED, ERR_UNSUPPORTED,
 RENDER_SHADED_GREYSCALE, RENDER_COLOUR_FROM_VOLUME, RENDER_COLOUR_FROM_NORMAL, RENDER_DEPTH_MAP, RENDER_COLOURCODED = range(5)
 PROFILE_STAGES = 5
 FRAME_ALLOCATE, FRAME_INTEGRATE, FRAME_EXPECTED_DEPTHS, FRAME_ICP_MAPS, FRAME_ALL = 1, 2, 4, 8, 15
+FRAME_RAYCAST = 16
+IPC_HANDLE_BYTES = 64
+MAX_SHARDS = 16
 
 # numpy views of the two on-device record types (ITMHashEntry 20 B, ITMVoxel_s_rgb 8 B)
 HASH_DTYPE = np.dtype([("pos", "<i2", (3,)), ("pad", "<i2"), ("offset", "<i4"), ("ptr", "<i4"),
@@ -66,6 +69,15 @@ class Tracking(C.Structure):
 
 class WeightParams(C.Structure):
     _fields_ = [("depth_weighting", C.c_int32), ("max_new_w", C.c_int32), ("max_distance", C.c_int32)]
+
+
+class Shard(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("count", C.c_int32), ("brick_log2", C.c_int32), ("halo", C.c_int32)]
+
+
+class ShardTables(C.Structure):
+    _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("brick_log2", C.c_int32), ("pad_", C.c_int32),
+                ("hash", C.c_void_p * 16), ("voxels", C.c_void_p * 16), ("range_image", C.c_void_p * 16)]
 
 
 def f16(a):
@@ -124,6 +136,15 @@ def load():
         "dsb200_forward_render": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
         "dsb200_create_point_cloud": (C.c_int, [vp]),
         "dsb200_process_frame": (C.c_int, [vp, vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), C.c_int]),
+        "dsb200_recon_set_shard": (C.c_int, [vp, _P(Shard)]),
+        "dsb200_shard_owner": (C.c_int, [C.c_int] * 5),
+        "dsb200_shard_holds": (C.c_int, [C.c_int] * 3 + [_P(Shard)]),
+        "dsb200_raycast_sharded": (C.c_int, [vp, _P(Scene), _P(ShardTables), _P(C.c_float), _P(C.c_float), C.c_int, C.c_int, vp, vp]),
+        "dsb200_composite_nearest": (C.c_int, [vp, C.c_int, _P(vp), _P(C.c_float), C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+        "dsb200_icp_maps_from_raycast": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), vp, vp, C.c_int, C.c_int]),
+        "dsb200_ipc_export": (C.c_int, [vp, C.c_char_p]),
+        "dsb200_ipc_open": (C.c_int, [C.c_char_p, _P(vp)]),
+        "dsb200_ipc_close": (C.c_int, [vp]),
         "dsb200_scene_alloc": (C.c_int, [_P(Scene), i32, i32, i32]),
         "dsb200_scene_free": (C.c_int, [_P(Scene)]),
         "dsb200_render_state_alloc": (C.c_int, [_P(RenderState), i32, i32, i32, i32]),

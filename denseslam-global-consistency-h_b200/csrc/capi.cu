@@ -111,6 +111,7 @@ struct dsb200_recon {
     bool async = false, deviceCountersValid = false;
     const uint8_t *visBitsOwner = nullptr;   // the render state's visibility-flag array that fs.visBits currently describes
     cudaStream_t sideStream = nullptr; cudaEvent_t evFork = nullptr, evJoin = nullptr;   // fused frame: expected depths || integration
+    dsb200_shard shard{0, 1, 2, 0};      // sharded scene: this engine's block ownership (count <= 1: everything)
     bool forceSlowDiv = false;        // debug: run the plain-division kernel variants (dsb200_debug_force_plain_division)
     // history (CUDA/ITMSceneReconstructionEngine_CUDA.h:41-48)
     std::deque<SnapPtr> decayQ, slideQ, decayDefusionQ, slideDefusionQ;
@@ -206,6 +207,23 @@ int dsb200_recon_destroy(dsb200_recon *e)
 int dsb200_recon_set_async(dsb200_recon *e, int async) { e->async = async != 0; return DSB200_OK; }
 
 int dsb200_set_fusion_weight_params(dsb200_recon *e, const dsb200_weight_params *p) { e->weights = *p; return DSB200_OK; }
+int dsb200_recon_set_shard(dsb200_recon *e, const dsb200_shard *s)
+{
+    if (!e || !s) return fail(DSB200_ERR_INVALID, "set_shard: null argument");
+    if (s->count > 1 && (s->rank < 0 || s->rank >= s->count || s->brick_log2 < 0 || s->brick_log2 > 12 || s->count > kMaxShards))
+        return fail(DSB200_ERR_INVALID, "set_shard: need 0 <= rank < count <= 16 and 0 <= brick_log2 <= 12");
+    e->shard = *s;
+    if (e->shard.count < 1) e->shard.count = 1;
+    return DSB200_OK;
+}
+int dsb200_shard_owner(int bx, int by, int bz, int count, int brick_log2)
+{
+    return count > 1 ? shard_owner(bx, by, bz, count, brick_log2) : 0;
+}
+int dsb200_shard_holds(int bx, int by, int bz, const dsb200_shard *s)
+{
+    return (s->count <= 1 || shard_holds(bx, by, bz, s->rank, s->count, s->brick_log2, s->halo)) ? 1 : 0;
+}
 size_t dsb200_decayed_block_count(const dsb200_recon *e) { return (size_t)e->totalDecayed; }
 int dsb200_history_sizes(const dsb200_recon *e, int *a, int *b, int *c, int *d, int *s)
 {
@@ -258,8 +276,10 @@ extern "C" int dsb200_recon_sync(dsb200_recon *e, dsb200_scene *scene, dsb200_re
 }
 
 // ---------------------------------------------------------------- reconstruction engine
-static void make_alloc_params(AllocParams &P, const dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk)
+static void make_alloc_params(AllocParams &P, const dsb200_recon *e, const dsb200_scene *scene, const dsb200_view *view,
+                              const dsb200_tracking *trk)
 {
+    P.shardRank = e->shard.rank; P.shardCount = e->shard.count; P.shardBrickLog2 = e->shard.brick_log2; P.shardHalo = e->shard.halo;
     fill_mat(P.invM, trk->invM_d);
     P.invProj[0] = 1.0f / view->intr_d[0]; P.invProj[1] = 1.0f / view->intr_d[1];
     P.invProj[2] = view->intr_d[2]; P.invProj[3] = view->intr_d[3];
@@ -308,7 +328,7 @@ static int check_scene(const dsb200_recon *e, const dsb200_scene *scene)
 static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
                             dsb200_render_state *rs, int onlyVisible, int isDefusion)
 {
-    AllocParams AP; make_alloc_params(AP, scene, view, trk);
+    AllocParams AP; make_alloc_params(AP, e, scene, view, trk);
     if ((long long)AP.W * AP.H >= (1ll << 24)) return fail(DSB200_ERR_INVALID, "depth image too large for the 24-bit pixel order key");
     // noSteps = ceil(2 * |segment| / blockSize) with |segment| = 2*mu (+ rounding): must fit the 8-bit step field
     if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
@@ -606,6 +626,63 @@ int dsb200_render_image(dsb200_vis *v, const dsb200_scene *scene, const float *M
     return DSB200_OK;
 }
 
+int dsb200_composite_nearest(dsb200_vis *v, int n, const float *const *results, const float *invM, float voxel_size,
+                             int width, int height, int row_begin, int row_end, float *out)
+{
+    if (!v || !results || !invM || !out || n < 1 || n > kMaxShards) return fail(DSB200_ERR_INVALID, "composite_nearest: bad arguments (1 <= n <= 16)");
+    if (row_begin < 0 || row_end > height || row_begin > row_end) return fail(DSB200_ERR_INVALID, "composite_nearest: bad row range");
+    for (int i = 0; i < n; i++) if (!results[i]) return fail(DSB200_ERR_INVALID, "composite_nearest: null raycast result");
+    // camera centre in voxel units, as castRay forms its points: (invM * p) * (1 / voxelSize)
+    const float oneOverVoxel = 1.0f / voxel_size;
+    launch_composite_nearest(v->stream, n, results, invM[12] * oneOverVoxel, invM[13] * oneOverVoxel, invM[14] * oneOverVoxel,
+                             width, row_begin, row_end, out);
+    CU(cudaGetLastError());
+    return DSB200_OK;     // stream-ordered: the caller synchronises (the sharded path keeps the frame in flight)
+}
+
+int dsb200_raycast_sharded(dsb200_vis *v, const dsb200_scene *scene, const dsb200_shard_tables *t, const float *invM,
+                           const float *intr, int width, int height, float *merged_range, float *out_raycast)
+{
+    if (!v || !scene || !t || !invM || !intr || !merged_range || !out_raycast) return fail(DSB200_ERR_INVALID, "raycast_sharded: null argument");
+    if (t->count < 1 || t->count > kMaxShards || t->rank < 0 || t->rank >= t->count || t->brick_log2 < 0 || t->brick_log2 > 12)
+        return fail(DSB200_ERR_INVALID, "raycast_sharded: need 0 <= rank < count <= 16 and 0 <= brick_log2 <= 12");
+    for (int i = 0; i < t->count; i++)
+        if (!t->hash[i] || !t->voxels[i] || !t->range_image[i]) return fail(DSB200_ERR_INVALID, "raycast_sharded: null table pointer");
+    RayParams P; make_ray_params(P, scene, nullptr, invM, intr, width, height);
+    launch_raycast_sharded(v->stream, P, t->count, t->rank, t->brick_log2, t->hash, t->voxels, t->range_image, merged_range,
+                           out_raycast, v->fs.tickets + 2);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
+int dsb200_icp_maps_from_raycast(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *trk,
+                                 const float *raycast_result, uint8_t *out_rendering, int width, int height)
+{
+    if (!v || !scene || !view || !trk || !raycast_result || !out_rendering) return fail(DSB200_ERR_INVALID, "icp_maps_from_raycast: null argument");
+    if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "icp_maps_from_raycast: tracking state has no point cloud buffers");
+    RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, width, height);
+    launch_icp_maps(v->stream, P, raycast_result, trk->icp_points, trk->icp_normals, out_rendering);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
+int dsb200_ipc_export(void *p, uint8_t handle[DSB200_IPC_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == DSB200_IPC_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, p));
+    memcpy(handle, &h, sizeof(h));
+    return DSB200_OK;
+}
+int dsb200_ipc_open(const uint8_t handle[DSB200_IPC_HANDLE_BYTES], void **p)
+{
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    CU(cudaIpcOpenMemHandle(p, h, cudaIpcMemLazyEnablePeerAccess));
+    return DSB200_OK;
+}
+int dsb200_ipc_close(void *p) { CU(cudaIpcCloseMemHandle(p)); return DSB200_OK; }
+
 int dsb200_forward_render(dsb200_vis *, const dsb200_scene *, const dsb200_view *, dsb200_tracking *, dsb200_render_state *)
 {
     // only reachable with useApproximateRaycast, which DenseSLAM never sets
@@ -622,7 +699,7 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
                          dsb200_render_state *rs, int stages)
 {
     int rc = check_scene(e, scene); if (rc) return rc;
-    if ((stages & (DSB200_FRAME_EXPECTED_DEPTHS | DSB200_FRAME_ICP_MAPS)) && (!v || v->stream != e->stream))
+    if ((stages & (DSB200_FRAME_EXPECTED_DEPTHS | DSB200_FRAME_ICP_MAPS | DSB200_FRAME_RAYCAST)) && (!v || v->stream != e->stream))
         return fail(DSB200_ERR_INVALID, "process_frame: the two engines must share one stream");
     const int *countPtr = &e->fs.counters->noVisible;
 #define DSB_MARK(i) do { if (e->profile) { cudaEventRecord(e->ev[i], e->stream); e->evRecorded[i] = true; } } while (0)
@@ -663,6 +740,10 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
         launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
         DSB_MARK(4);
         launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
+    } else if (stages & DSB200_FRAME_RAYCAST) {
+        RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
+        DSB_MARK(4);
     } else DSB_MARK(4);
     DSB_MARK(5);
     return finish_call(e, scene, rs, (stages & DSB200_FRAME_ALLOCATE) != 0);

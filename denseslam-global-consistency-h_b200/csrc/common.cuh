@@ -20,6 +20,7 @@ namespace dsb {
 constexpr int kBlock = DSB200_BLOCK_SIZE;     // 8
 constexpr int kBlock3 = DSB200_BLOCK_SIZE3;   // 512
 constexpr int kNumSMs = 148;                  // B200
+constexpr int kMaxShards = 16;                // sharded scene: at most this many raycast results per composite
 
 struct Mat4 { float m[16]; };                 // column-major, ORUtils/Matrix.h:7-11
 struct Vec4 { float x, y, z, w; };
@@ -40,6 +41,32 @@ __host__ __device__ __forceinline__ Vec4 mul(const Mat4 &M, Vec4 v)
 __host__ __device__ __forceinline__ int hash_index(int x, int y, int z, int bucketMask)
 {
     return (int)((((unsigned)x * 73856093u) ^ ((unsigned)y * 19349669u) ^ ((unsigned)z * 83492791u)) & (unsigned)bucketMask);
+}
+
+// Shard ownership of a voxel block (include/dsb200.h, dsb200_shard): bricks of 2^brickLog2 blocks per axis
+// (arithmetic shift = floor division), brick coordinate hashed with the table's primes and a murmur3 finaliser.
+__host__ __device__ __forceinline__ int shard_owner(int bx, int by, int bz, int count, int brickLog2)
+{
+    unsigned h = ((unsigned)(bx >> brickLog2) * 73856093u) ^ ((unsigned)(by >> brickLog2) * 19349669u) ^
+                 ((unsigned)(bz >> brickLog2) * 83492791u);
+    h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+    return (int)(h % (unsigned)count);
+}
+
+// holds = owned, or (halo) one of the blocks b - {0,1}^3 is owned.  b - d lies in another brick only when b sits on the
+// low face of its brick along every axis where d is 1, so interior blocks cost one owner evaluation.
+__host__ __device__ __forceinline__ bool shard_holds(int bx, int by, int bz, int rank, int count, int brickLog2, int halo)
+{
+    if (shard_owner(bx, by, bz, count, brickLog2) == rank) return true;
+    if (!halo) return false;
+    const int mask = (1 << brickLog2) - 1;
+    const int fx = (bx & mask) == 0, fy = (by & mask) == 0, fz = (bz & mask) == 0;
+    for (int d = 1; d < 8; d++) {
+        const int dx = d & 1, dy = (d >> 1) & 1, dz = d >> 2;
+        if ((dx && !fx) || (dy && !fy) || (dz && !fz)) continue;
+        if (shard_owner(bx - dx, by - dy, bz - dz, count, brickLog2) == rank) return true;
+    }
+    return false;
 }
 
 // 20-byte hash entry viewed as 5 ints: {pos.x|pos.y<<16, pos.z|pad<<16, offset, ptr, allocatedTime}

@@ -22,6 +22,7 @@ struct AllocParams {
     float invProj[4];                // (1/fx, 1/fy, cx, cy)
     float mu, oneOverBlock, vfMin, vfMax;
     int W, H, bucketNum, bucketMask;
+    int shardRank, shardCount, shardBrickLog2, shardHalo;   // shardCount <= 1: unsharded
 };
 
 struct VisParams {                   // block visibility test
@@ -98,8 +99,13 @@ void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_h
                             const int *count, float *rangeImage, int *blockTileCounts, Counters *counters);
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
                     const float *rangeImage, float *raycastResult, int *ticketPair /* two zeroed ints, re-armed by the kernel */);
+void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank, int brickLog2,
+                            const dsb200_hash_entry *const *hash, const dsb200_voxel *const *voxels,
+                            const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair);
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,
                      uint8_t *rendering);
+void launch_composite_nearest(cudaStream_t st, int n, const float *const *resultsDev, float cx, float cy, float cz, int W,
+                              int rowBegin, int rowEnd, float *out);
 void launch_shade(cudaStream_t st, const RayParams &P, int renderType, const dsb200_voxel *voxels,
                   const dsb200_hash_entry *hash, const float *raycastResult, uint8_t *outRGBA, float *outDepth);
 void launch_forward_render(cudaStream_t st, const RayParams &P, const float *proj, const dsb200_voxel *voxels,

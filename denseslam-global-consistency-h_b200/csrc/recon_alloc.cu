@@ -88,7 +88,11 @@ __global__ void __launch_bounds__(256) k_alloc_requests(AllocParams P, FrameStat
     short lbx = 0, lby = 0, lbz = 0; bool lastMiss = false;
     for (int i = 0; i < r.noSteps; i++) {
         short bx = (short)floorf(px), by = (short)floorf(py), bz = (short)floorf(pz);
-        if (lastH >= 0 && bx == lbx && by == lby && bz == lbz) {
+        if (P.shardCount > 1 && !shard_holds(bx, by, bz, P.shardRank, P.shardCount, P.shardBrickLog2, P.shardHalo)) {
+            // another shard's block: no probe, no request (and it breaks the same-block run, as in the serial loop
+            // where the next owned step is simply processed on its own)
+            lastH = -1;
+        } else if (lastH >= 0 && bx == lbx && by == lby && bz == lbz) {
             // same block as the previous step: a hit re-writes the same value; a miss must still
             // raise the order key to this later step (its request bit was set by the first miss)
             if (lastMiss) atomicMax(&reqKey[lastH], (unsigned)loc * 256u + (unsigned)i + 1u);

@@ -221,22 +221,43 @@ __global__ void __launch_bounds__(1024) k_range_cap_fallback(ProjParams P, const
 }
 
 // ---------------------------------------------------------------- raycast
-struct BlockCache { int bx, by, bz, base; };
+struct BlockCache { int bx, by, bz; const dsb200_voxel *blk; };
+
+// Where a block's hash table and voxel array live.  One scene: the two pointers.  Sharded scene (dsb200_raycast_sharded):
+// the tables of the shard that OWNS the block, which may be peer-GPU memory mapped with CUDA IPC -- the probe and the
+// voxel read then travel over NVLink, and the march is the single-scene march probe for probe.
+struct SceneTables {
+    const dsb200_voxel *voxels; const dsb200_hash_entry *hash;
+    __device__ __forceinline__ void resolve(int, int, int, const dsb200_hash_entry *&h, const dsb200_voxel *&v) const { h = hash; v = voxels; }
+};
+struct ShardTables {
+    int n, brickLog2;
+    const dsb200_hash_entry *hash[kMaxShards];
+    const dsb200_voxel *voxels[kMaxShards];
+    __device__ __forceinline__ void resolve(int bx, int by, int bz, const dsb200_hash_entry *&h, const dsb200_voxel *&v) const
+    {
+        const int o = shard_owner(bx, by, bz, n, brickLog2);
+        h = hash[o]; v = voxels[o];
+    }
+};
 
 // readVoxel + pointToVoxelBlockPos (DeviceAgnostic/ITMRepresentationAccess.h:14-19,176-210); returns sdf as short
-__device__ __forceinline__ short read_sdf(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
-                                          int bucketNum, int bucketMask, int px, int py, int pz, bool &found, BlockCache &c)
+template <class Tables>
+__device__ __forceinline__ short read_sdf(const Tables &T, int bucketNum, int bucketMask, int px, int py, int pz, bool &found,
+                                          BlockCache &c)
 {
     // floor division by 8 (arithmetic shift == the reference's ((p<0)?p-7:p)/8)
     const int bx = px >> 3, by = py >> 3, bz = pz >> 3;
     const int lin = (px & 7) + ((py & 7) << 3) + ((pz & 7) << 6);
-    if (bx == c.bx && by == c.by && bz == c.bz) { found = true; return __ldg(reinterpret_cast<const short *>(voxels + c.base + lin)); }
+    if (bx == c.bx && by == c.by && bz == c.bz) { found = true; return __ldg(reinterpret_cast<const short *>(c.blk + lin)); }
+    const dsb200_hash_entry *hash; const dsb200_voxel *voxels;
+    T.resolve(bx, by, bz, hash, voxels);
     int h = hash_index(bx, by, bz, bucketMask);
     while (true) {
         HashEntry e = load_entry(hash, h);
         if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= 0) {
-            found = true; c.bx = bx; c.by = by; c.bz = bz; c.base = e.ptr * kBlock3;
-            return __ldg(reinterpret_cast<const short *>(voxels + c.base + lin));
+            found = true; c.bx = bx; c.by = by; c.bz = bz; c.blk = voxels + (size_t)e.ptr * kBlock3;
+            return __ldg(reinterpret_cast<const short *>(c.blk + lin));
         }
         if (e.offset < 1) break;
         h = bucketNum + e.offset - 1;
@@ -247,11 +268,11 @@ __device__ __forceinline__ short read_sdf(const dsb200_voxel *__restrict__ voxel
 
 __device__ __forceinline__ float round_half_away(float x) { return (x < 0) ? (x - 0.5f) : (x + 0.5f); }
 
-#define DSB_RD(X, Y, Z) ((float)read_sdf(voxels, hash, bucketNum, bucketMask, (X), (Y), (Z), found, cache))
+#define DSB_RD(X, Y, Z) ((float)read_sdf(T, bucketNum, bucketMask, (X), (Y), (Z), found, cache))
 
 // readFromSDF_float_interpolated (:251-276)
-__device__ __forceinline__ float sdf_trilinear(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
-                                               int bucketNum, int bucketMask, float x, float y, float z, bool &found,
+template <class Tables>
+__device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, int bucketMask, float x, float y, float z, bool &found,
                                                BlockCache &cache)
 {
     float fx = floorf(x), fy = floorf(y), fz = floorf(z);
@@ -271,8 +292,8 @@ __device__ __forceinline__ float sdf_trilinear(const dsb200_voxel *__restrict__ 
 }
 
 // castRay, DeviceAgnostic/ITMVisualisationEngine.h:124-196
-__device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const dsb200_voxel *__restrict__ voxels,
-                                         const dsb200_hash_entry *__restrict__ hash, const RayParams &P, float zmin, float zmax)
+template <class Tables>
+__device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables &T, const RayParams &P, float zmin, float zmax)
 {
     const int bucketNum = P.bucketNum, bucketMask = P.bucketMask;
     const float stepScale = P.mu * P.oneOverVoxel;
@@ -294,15 +315,15 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const dsb200
     const float dn = 1.0f / sqrtf(dx * dx + dy * dy + dz * dz);
     dx *= dn; dy *= dn; dz *= dn;
     float rx = sx, ry = sy, rz = sz;
-    BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, -1};
+    BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
     float sdf = 1.0f, stepLength;
     bool found, ptFound;
     while (totalLength < totalLengthMax) {
-        sdf = (float)read_sdf(voxels, hash, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
+        sdf = (float)read_sdf(T, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
                               (int)round_half_away(rz), found, cache) / 32767.0f;
         if (!found) stepLength = (float)kBlock;
         else {
-            if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(voxels, hash, bucketNum, bucketMask, rx, ry, rz, found, cache);
+            if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(T, bucketNum, bucketMask, rx, ry, rz, found, cache);
             if (!(sdf > 0.0f)) break;
             stepLength = (sdf * stepScale < 1.0f) ? 1.0f : sdf * stepScale;
         }
@@ -312,7 +333,7 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const dsb200
     if (sdf <= 0.0f) {
         stepLength = sdf * stepScale;
         rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
-        sdf = sdf_trilinear(voxels, hash, bucketNum, bucketMask, rx, ry, rz, ptFound, cache);
+        sdf = sdf_trilinear(T, bucketNum, bucketMask, rx, ry, rz, ptFound, cache);
         stepLength = sdf * stepScale;
         rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
     } else ptFound = false;
@@ -324,16 +345,19 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const dsb200
 // pixels do not march at all, grazing road pixels cross hundreds of voxels), so a static pixel-tile -> CTA map leaves
 // most of the machine idle behind a few long tiles (41 % achieved occupancy in profiles/r01a).  Here every WARP pulls
 // the next 8x4 pixel tile from a device ticket; the last warp to run dry re-arms the ticket pair for the next launch.
-__global__ void __launch_bounds__(128) k_raycast(RayParams P, const dsb200_voxel *__restrict__ voxels,
-                                                 const dsb200_hash_entry *__restrict__ hash,
-                                                 const float2 *__restrict__ range, float4 *out, int *ticket)
+// Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
+// root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
+template <class Tables>
+__global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_constant__ Tables T,
+                                                 const float2 *__restrict__ range, float4 *out, int *ticket, int tileFirst,
+                                                 int tileStride)
 {
     const int lane = threadIdx.x & 31;
     const int tilesX = (P.W + 7) >> 3, tilesY = (P.H + 3) >> 2, nTiles = tilesX * tilesY;
     while (true) {
         int tile = 0;
         if (lane == 0) tile = atomicAdd(&ticket[0], 1);
-        tile = __shfl_sync(0xffffffffu, tile, 0);
+        tile = __shfl_sync(0xffffffffu, tile, 0) * tileStride + tileFirst;
         if (tile >= nTiles) break;
         const int ty = tile / tilesX, tx = tile - ty * tilesX;
         const int x = tx * 8 + (lane & 7), y = ty * 4 + (lane >> 3);
@@ -341,7 +365,7 @@ __global__ void __launch_bounds__(128) k_raycast(RayParams P, const dsb200_voxel
             const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
             const float2 mm = __ldg(range + loc2);
             float4 r;
-            cast_ray(r, x, y, voxels, hash, P, mm.x, mm.y);
+            cast_ray(r, x, y, T, P, mm.x, mm.y);
             out[x + y * P.W] = r;
         }
     }
@@ -408,14 +432,53 @@ __global__ void __launch_bounds__(256) k_icp_maps(RayParams P, const float4 *__r
 }
 
 
+// ---------------------------------------------------------------- sharded scene: nearest-hit composite
+// Every shard raycasts the blocks it owns; the surface a camera ray sees is the hit closest to the camera among the
+// shards.  One thread per pixel loads the n candidate points (16 B each; peers' images are read in place over NVLink
+// when the pointers are IPC mappings) and keeps the one with the smallest squared distance to the camera centre
+// (ties: lowest shard index).  Replaces an all-reduce(min) on packed keys + a second collective for the winner's point.
+struct PeerImages { const float4 *p[kMaxShards]; };
+
+__global__ void __launch_bounds__(256) k_composite_nearest(PeerImages imgs, int n, float cx, float cy, float cz, int begin,
+                                                           int end, float4 *out)
+{
+    for (int i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
+        float4 best = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float bestD = 0.0f;
+        bool have = false;
+#pragma unroll 4
+        for (int r = 0; r < n; r++) {
+            const float4 q = __ldcg(imgs.p[r] + i);        // produced by another kernel / another GPU: bypass L1
+            if (q.w > 0.0f) {
+                const float dx = q.x - cx, dy = q.y - cy, dz = q.z - cz;
+                const float d = dx * dx + dy * dy + dz * dz;
+                if (!have || d < bestD) { best = q; bestD = d; have = true; }
+            }
+        }
+        out[i] = best;
+    }
+}
+
+void launch_composite_nearest(cudaStream_t st, int n, const float *const *results, float cx, float cy, float cz, int W,
+                              int rowBegin, int rowEnd, float *out)
+{
+    PeerImages imgs;
+    for (int r = 0; r < kMaxShards; r++) imgs.p[r] = reinterpret_cast<const float4 *>(results[r < n ? r : 0]);
+    const int begin = rowBegin * W, end = rowEnd * W;
+    int grid = div_up(end - begin > 0 ? end - begin : 1, 256);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    DSB_LAUNCH(k_composite_nearest, grid, 256, 0, st, imgs, n, cx, cy, cz, begin, end, reinterpret_cast<float4 *>(out));
+}
+
 // ---------------------------------------------------------------- free-view shading (RenderImage)
-#define DSB_RV(DX, DY, DZ) ((float)read_sdf(voxels, hash, bucketNum, bucketMask, X + (DX), Y + (DY), Z + (DZ), f, cache))
+#define DSB_RV(DX, DY, DZ) ((float)read_sdf(T, bucketNum, bucketMask, X + (DX), Y + (DY), Z + (DZ), f, cache))
 
 // computeSingleNormalFromSDF, DeviceAgnostic/ITMRepresentationAccess.h:314-427
 __device__ void normal_from_sdf(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
                                 int bucketNum, int bucketMask, float px, float py, float pz, float ret[3])
 {
-    bool f; BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, -1};
+    const SceneTables T = {voxels, hash};
+    bool f; BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
     float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
     float cx = px - flx, cy = py - fly, cz = pz - flz;
     int X = (int)flx, Y = (int)fly, Z = (int)flz;
@@ -454,10 +517,11 @@ __device__ __forceinline__ uchar4 read_clr(const dsb200_voxel *__restrict__ voxe
                                            int bucketNum, int bucketMask, int px, int py, int pz, BlockCache &c)
 {
     bool found;
-    read_sdf(voxels, hash, bucketNum, bucketMask, px, py, pz, found, c);   // positions the cache
+    const SceneTables T = {voxels, hash};
+    read_sdf(T, bucketNum, bucketMask, px, py, pz, found, c);   // positions the cache
     if (!found) return make_uchar4(0, 0, 0, 0);
     const int lin = (px & 7) + ((py & 7) << 3) + ((pz & 7) << 6);
-    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(voxels + c.base + lin));
+    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(c.blk + lin));
     return make_uchar4(raw.x >> 24, raw.y & 0xff, (raw.y >> 8) & 0xff, 0);
 }
 
@@ -492,7 +556,7 @@ __global__ void __launch_bounds__(128) k_shade(RayParams P, int type, const dsb2
     if (!found) { out[loc] = make_uchar4(0, 0, 0, 0); return; }
     if (type == DSB200_RENDER_COLOUR_FROM_VOLUME) {
         // readFromSDF_color4u_interpolated, DeviceAgnostic/ITMRepresentationAccess.h:278-312
-        BlockCache c = {0x7fffffff, 0x7fffffff, 0x7fffffff, -1};
+        BlockCache c = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
         float flx = floorf(pt.x), fly = floorf(pt.y), flz = floorf(pt.z);
         float cx = pt.x - flx, cy = pt.y - fly, cz = pt.z - flz;
         int X = (int)flx, Y = (int)fly, Z = (int)flz;
@@ -547,8 +611,44 @@ void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *vox
     const int nTiles = div_up(P.W, 8) * div_up(P.H, 4);
     int grid = div_up(nTiles, 4);
     if (grid > kNumSMs * 12) grid = kNumSMs * 12;
-    DSB_LAUNCH(k_raycast, grid, 128, 0, st, P, voxels, hash, reinterpret_cast<const float2 *>(rangeImage),
-               reinterpret_cast<float4 *>(raycastResult), ticketPair);
+    const SceneTables T = {voxels, hash};
+    DSB_LAUNCH(k_raycast<SceneTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(rangeImage),
+               reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1);
+}
+
+// Expected-depth image of the whole sharded scene = element-wise (min of mins, max of maxes) of the shards' images: what
+// CreateExpectedDepths computes over the union of the visible lists (min / max are order-independent).
+__global__ void __launch_bounds__(256) k_range_merge(PeerImages imgs, int n, int count, float2 *out)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        float2 m = make_float2(kFarAway, kVeryClose);
+#pragma unroll 4
+        for (int r = 0; r < n; r++) {
+            const float2 q = __ldcg(reinterpret_cast<const float2 *>(imgs.p[r]) + i);
+            m.x = fminf(m.x, q.x); m.y = fmaxf(m.y, q.y);
+        }
+        out[i] = m;
+    }
+}
+
+void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank, int brickLog2,
+                            const dsb200_hash_entry *const *hash, const dsb200_voxel *const *voxels,
+                            const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair)
+{
+    // only rows [0, H/8] of the full-stride range image are ever read
+    PeerImages imgs;
+    for (int r = 0; r < kMaxShards; r++) imgs.p[r] = reinterpret_cast<const float4 *>(rangeImages[r < n ? r : 0]);
+    const int count = P.W * (P.H / kSubsample + 1);
+    DSB_LAUNCH(k_range_merge, div_up(count, 256) < kNumSMs * 4 ? div_up(count, 256) : kNumSMs * 4, 256, 0, st, imgs, n, count,
+               reinterpret_cast<float2 *>(mergedRange));
+    ShardTables T;
+    T.n = n; T.brickLog2 = brickLog2;
+    for (int r = 0; r < kMaxShards; r++) { T.hash[r] = hash[r < n ? r : 0]; T.voxels[r] = voxels[r < n ? r : 0]; }
+    const int nTiles = div_up(div_up(P.W, 8) * div_up(P.H, 4), n);
+    int grid = div_up(nTiles, 4);
+    if (grid > kNumSMs * 12) grid = kNumSMs * 12;
+    DSB_LAUNCH(k_raycast<ShardTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(mergedRange),
+               reinterpret_cast<float4 *>(raycastResult), ticketPair, rank, n);
 }
 
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,

@@ -213,6 +213,11 @@ class ITMSceneReconstructionEngine(object):
         wp = abi.WeightParams(int(depthWeighting), maxNewW, maxDistance)
         abi.check(_lib().dsb200_set_fusion_weight_params(self.h, C.byref(wp)))
 
+    def SetShard(self, rank, count, brick_log2=2, halo=True):
+        """sharded scene (include/dsb200.h, dsb200_shard): this engine allocates only the blocks shard `rank` owns"""
+        sh = abi.Shard(rank, count, brick_log2, 1 if halo else 0)
+        abi.check(_lib().dsb200_recon_set_shard(self.h, C.byref(sh)))
+
     def HistorySizes(self):
         v = [C.c_int() for _ in range(5)]
         _lib().dsb200_history_sizes(self.h, *[C.byref(x) for x in v])

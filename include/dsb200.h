@@ -192,6 +192,60 @@ int dsb200_create_point_cloud(dsb200_vis *v);                                   
 int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, const dsb200_view *view,
                          dsb200_tracking *tracking, dsb200_render_state *rs, int stages);
 
+/* raycast only (FindSurface with the tracking pose), no ICP maps: the sharded path composites first */
+#define DSB200_FRAME_RAYCAST 16
+
+/* ---- sharded scene (no counterpart in the reference, which is single-GPU) ----
+ * The voxel-block space is partitioned by block-coordinate ownership: bricks of 2^brick_log2 blocks
+ * per axis are dealt to `count` shards by a hash of the brick coordinate.  A reconstruction engine
+ * with a shard set only raises allocation requests for blocks it owns
+ * (buildHashAllocAndVisibleTypePP, DeviceAgnostic/ITMSceneReconstructionEngine.h:328-396, with one
+ * extra `continue`); everything downstream (ordered allocation, visible list, integration, expected
+ * depths, raycast) then works on the shard's own hash table unchanged.  count <= 1 disables. */
+typedef struct dsb200_shard {
+    int32_t rank, count, brick_log2;
+    int32_t halo;   /* 1: also hold (allocate + integrate) the blocks b with an owned block among b - {0,1}^3, i.e. the +1
+                       neighbours the trilinear reads of castRay touch (ITMRepresentationAccess.h:258-272), so a ray inside
+                       an owned block never reads a missing neighbour; replication factor ((B+1)/B)^3 for bricks of B blocks */
+} dsb200_shard;
+int dsb200_recon_set_shard(dsb200_recon *e, const dsb200_shard *s);
+/* owner of block (bx,by,bz): the same function the kernels evaluate (host helper for tests / routing) */
+int dsb200_shard_owner(int bx, int by, int bz, int count, int brick_log2);
+/* does shard s hold block (bx,by,bz): owned, or (halo) a +1 neighbour of an owned block */
+int dsb200_shard_holds(int bx, int by, int bz, const dsb200_shard *s);
+/* Raycast of the WHOLE sharded scene, split by image tiles: this shard marches the 8x4-pixel tiles t with
+ * t % count == rank; every block lookup goes to the hash table / voxel array of the shard that owns the block
+ * (tables[] entries of the other shards are peer-GPU memory mapped with dsb200_ipc_open, so probes and voxel reads
+ * travel over NVLink).  The march is castRay (DeviceAgnostic/ITMVisualisationEngine.h:124-196) probe for probe, so with
+ * equal block sets the image equals the single-scene raycast bit for bit.  The expected-depth image used is the
+ * element-wise min/max merge of the shards' range images (written to merged_range, Vector2f[W*H] scratch).
+ * out_raycast (Vector4f[W*H]) may be the root shard's buffer: each shard stores only its own tiles.
+ * Stream-ordered (no host sync): the caller orders it after every shard's integration and before the next frame. */
+typedef struct dsb200_shard_tables {
+    int32_t count, rank, brick_log2, pad_;
+    const dsb200_hash_entry *hash[16];
+    const dsb200_voxel *voxels[16];
+    const float *range_image[16];
+} dsb200_shard_tables;
+int dsb200_raycast_sharded(dsb200_vis *v, const dsb200_scene *scene /* params + capacities, same on every shard */,
+                           const dsb200_shard_tables *tables, const float *invM, const float *intr, int width, int height,
+                           float *merged_range, float *out_raycast);
+/* Per-pixel nearest-hit composite of n raycast results (Vector4f[W*H] each, voxel units, w = found):
+ * out[p] = the hit closest to the camera centre (-> invM * (0,0,0,1) / voxel_size) among results[0..n),
+ * ties to the lowest index, (0,0,0,0) when no shard hit.  results[i] may be peer-GPU memory mapped with
+ * dsb200_ipc_open (the loads then travel over NVLink); row_begin/row_end restrict the rows written. */
+int dsb200_composite_nearest(dsb200_vis *v, int n, const float *const *results, const float *invM,
+                             float voxel_size, int width, int height, int row_begin, int row_end, float *out);
+/* CreateICPMaps' second half (processPixelICP<true>) on an already raycast / composited point image */
+int dsb200_icp_maps_from_raycast(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view,
+                                 dsb200_tracking *tracking, const float *raycast_result, uint8_t *out_rendering,
+                                 int width, int height);
+/* CUDA IPC plumbing for the peer-memory composite: export a device allocation, map a peer's */
+#define DSB200_IPC_HANDLE_BYTES 64
+int dsb200_ipc_export(void *device_ptr, uint8_t handle[DSB200_IPC_HANDLE_BYTES]);
+int dsb200_ipc_open(const uint8_t handle[DSB200_IPC_HANDLE_BYTES], void **device_ptr);
+int dsb200_ipc_close(void *device_ptr);
+
 /* ---- host helpers (what ITMScene / ITMRenderState_VH / ITMView ctors do with cudaMalloc) ---- */
 int dsb200_scene_alloc(dsb200_scene *scene, int32_t num_blocks, int32_t bucket_num, int32_t excess_size);
 int dsb200_scene_free(dsb200_scene *scene);

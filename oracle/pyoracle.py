@@ -112,6 +112,14 @@ class Oracle(object):
         L.rst_create_icp_maps.argtypes = [P(abi.Scene), P(abi.View), P(abi.Tracking), P(abi.RenderState)]
         L.rst_render_image.argtypes = [P(abi.Scene), fp, fp, fp, P(abi.RenderState), vp, vp, C.c_int]
         L.rst_forward_render.argtypes = [P(abi.Scene), P(abi.View), P(abi.Tracking), P(abi.RenderState), vp, vp, P(C.c_int)]
+        L.rst_set_shard.argtypes = [vp, P(abi.Shard)]
+        L.rst_shard_owner.restype = C.c_int
+        L.rst_shard_owner.argtypes = [C.c_int] * 5
+        L.rst_shard_holds.restype = C.c_int
+        L.rst_shard_holds.argtypes = [C.c_int] * 3 + [P(abi.Shard)]
+        L.rst_raycast_sharded.argtypes = [C.c_int, P(vp), P(vp), C.c_int, fp, fp, C.c_int, C.c_int, vp, vp]
+        L.rst_composite_nearest.argtypes = [C.c_int, P(vp), fp, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+        L.rst_icp_maps_from_raycast.argtypes = [P(abi.Scene), P(abi.View), P(abi.Tracking), vp, vp, C.c_int, C.c_int]
         L.rst_mat4_inverse.restype = C.c_int
         L.rst_mat4_inverse.argtypes = [fp, fp]
         L.rst_mat4_multiply.argtypes = [fp, fp, fp]

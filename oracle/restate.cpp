@@ -64,6 +64,7 @@ struct rst_recon {
     std::map<double, SnapPtr> snapshots;    // mDefusionBlockDataBase
     size_t frameIdx;
     long long totalDecayed;
+    dsb200_shard shard;                     // sharded scene (include/dsb200.h): count <= 1 = unsharded
 };
 
 extern "C" {
@@ -77,11 +78,30 @@ rst_recon *rst_recon_create(int num_blocks, int bucket_num, int excess_size)
     e->blockCoords.assign((size_t)e->total * 4, 0);
     e->weights.depth_weighting = 0; e->weights.max_new_w = 10; e->weights.max_distance = 100;
     e->frameIdx = 0; e->totalDecayed = 0;
+    e->shard.rank = 0; e->shard.count = 1; e->shard.brick_log2 = 2; e->shard.halo = 0;
     return e;
 }
 void rst_recon_destroy(rst_recon *e) { delete e; }
 void rst_set_fusion_weight_params(rst_recon *e, const dsb200_weight_params *p) { e->weights = *p; }
 size_t rst_decayed_block_count(const rst_recon *e) { return (size_t)e->totalDecayed; }
+void rst_set_shard(rst_recon *e, const dsb200_shard *s) { e->shard = *s; if (e->shard.count < 1) e->shard.count = 1; }
+// block ownership of the sharded scene (no reference counterpart; definition in include/dsb200.h)
+int rst_shard_owner(int bx, int by, int bz, int count, int brickLog2)
+{
+    if (count <= 1) return 0;
+    unsigned h = ((unsigned)(bx >> brickLog2) * 73856093u) ^ ((unsigned)(by >> brickLog2) * 19349669u) ^
+                 ((unsigned)(bz >> brickLog2) * 83492791u);
+    h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+    return (int)(h % (unsigned)count);
+}
+// held = owned, or (halo) a +1 neighbour of an owned block: some b - d, d in {0,1}^3, is owned
+int rst_shard_holds(int bx, int by, int bz, const dsb200_shard *s)
+{
+    if (s->count <= 1) return 1;
+    for (int d = 0; d < (s->halo ? 8 : 1); d++)
+        if (rst_shard_owner(bx - (d & 1), by - ((d >> 1) & 1), bz - (d >> 2), s->count, s->brick_log2) == s->rank) return 1;
+    return 0;
+}
 void rst_history_sizes(const rst_recon *e, int *a, int *b, int *c, int *d, int *s)
 {
     if (a) *a = (int)e->decayQ.size();
@@ -200,7 +220,7 @@ inline void blockVisibility(bool &vis, bool &visEnl, const int16_t *pos, const f
 inline void allocRequestForPixel(unsigned char *allocType, unsigned char *visType, short *blockCoords, int x, int y,
                                  const float *depth, const float *invM, const float *invProj, float mu, int W,
                                  float oneOverBlock, const dsb200_hash_entry *hash, int bucketNum, float vfMin,
-                                 float vfMax)
+                                 float vfMax, const dsb200_shard &shard)
 {
     float d = depth[x + y * W];
     if (d <= 0 || (d - mu) < 0 || (d - mu) < vfMin || (d + mu) > vfMax) return;
@@ -224,6 +244,10 @@ inline void allocRequestForPixel(unsigned char *allocType, unsigned char *visTyp
 
     for (int i = 0; i < noSteps; i++) {
         short bx = (short)floorf(point.x), by = (short)floorf(point.y), bz = (short)floorf(point.z);
+        if (!rst_shard_holds(bx, by, bz, &shard)) {
+            point.x += dir.x; point.y += dir.y; point.z += dir.z;      // another shard's block
+            continue;
+        }
         int h = hashIndex(bx, by, bz, bucketNum);
         bool found = false;
         dsb200_hash_entry e = hash[h];
@@ -276,7 +300,7 @@ int rst_allocate_from_depth(rst_recon *e, dsb200_scene *scene, const dsb200_view
     for (int loc = 0; loc < W * H; loc++) {
         int y = loc / W, x = loc - y * W;
         allocRequestForPixel(allocType, visType, blockCoords, x, y, view->depth, invM, invProj, mu, W, oneOverBlock,
-                             hash, bucketNum, scene->params.vf_min, scene->params.vf_max);
+                             hash, bucketNum, scene->params.vf_min, scene->params.vf_max, e->shard);
     }
 
     if (onlyUpdateVisibleList) useSwapping = false;
@@ -528,11 +552,16 @@ const int SUBSAMPLE = 8;                                 // minmaximg_subsample 
 
 struct BlockCache { int bx, by, bz, ptr; BlockCache() : bx(0x7fffffff), by(0x7fffffff), bz(0x7fffffff), ptr(-1) {} };
 
+// Sharded scene (rst_raycast_sharded): while set, every voxel read goes to the scene of the shard that owns the block.
+struct ShardSet { int n, brickLog2; const dsb200_scene *const *scenes; };
+static ShardSet g_shardSet = {0, 0, nullptr};
+
 // pointToVoxelBlockPos + readVoxel (cached), DA/ITMRepresentationAccess.h:14-19,176-210
 inline dsb200_voxel readVoxel(const dsb200_scene *s, int px, int py, int pz, bool &found, BlockCache &c)
 {
     int bx = ((px < 0) ? px - 8 + 1 : px) / 8, by = ((py < 0) ? py - 8 + 1 : py) / 8, bz = ((pz < 0) ? pz - 8 + 1 : pz) / 8;
     int lin = (px - bx * 8) + (py - by * 8) * 8 + (pz - bz * 8) * 64;
+    if (g_shardSet.n > 1) s = g_shardSet.scenes[rst_shard_owner(bx, by, bz, g_shardSet.n, g_shardSet.brickLog2)];
     if (bx == c.bx && by == c.by && bz == c.bz) { found = true; return s->voxels[c.ptr + lin]; }
     int h = hashIndex(bx, by, bz, s->bucket_num);
     while (true) {
@@ -860,19 +889,26 @@ extern "C" {
 void rst_create_icp_maps(const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *tracking,
                          dsb200_render_state *rs)
 {
-    const int W = rs->width, H = rs->height;
+    genericRaycast(scene, rs->width, rs->height, tracking->invM_d, view->intr_d, rs);
+    rst_icp_maps_from_raycast(scene, view, tracking, rs->raycast_result, rs->raycast_image, rs->width, rs->height);
+}
+
+// second half of CreateICPMaps on a given point image (the sharded path composites the shards' raycasts first)
+void rst_icp_maps_from_raycast(const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *tracking,
+                               const float *raycastResult, uint8_t *outRendering, int W, int H)
+{
+    (void)view;
     const float *invM = tracking->invM_d;
-    genericRaycast(scene, W, H, invM, view->intr_d, rs);
     float light[3] = {-invM[8], -invM[9], -invM[10]};     // -invM.getColumn(2)
     float vs = scene->params.voxel_size;
     for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
         int loc = x + y * W;
-        const float *pt = rs->raycast_result + 4 * (size_t)loc;
+        const float *pt = raycastResult + 4 * (size_t)loc;
         bool found = pt[3] > 0.0f;
         float n[3], angle = 0.0f;
-        normalAndAngleImage<true>(found, x, y, rs->raycast_result, light, vs, W, H, n, angle);
+        normalAndAngleImage<true>(found, x, y, raycastResult, light, vs, W, H, n, angle);
         float *P = tracking->icp_points + 4 * (size_t)loc, *N = tracking->icp_normals + 4 * (size_t)loc;
-        uint8_t *R = rs->raycast_image + 4 * (size_t)loc;
+        uint8_t *R = outRendering + 4 * (size_t)loc;
         if (found) {
             unsigned char g = greyOf(angle);
             R[0] = R[1] = R[2] = R[3] = g;
@@ -883,6 +919,50 @@ void rst_create_icp_maps(const dsb200_scene *scene, const dsb200_view *view, dsb
             N[0] = N[1] = N[2] = 0.0f; N[3] = -1.0f;
             R[0] = R[1] = R[2] = R[3] = 0;
         }
+    }
+}
+
+// Raycast of the whole sharded scene (definition in include/dsb200.h, dsb200_raycast_sharded): expected depths merged
+// by min / max over the shards' range images, then the unchanged castRay with owner-routed voxel reads.
+void rst_raycast_sharded(int n, const dsb200_scene *const *scenes, const float *const *rangeImages, int brickLog2,
+                         const float *invM, const float *intr, int W, int H, float *mergedRange, float *out)
+{
+    const int count = W * (H / SUBSAMPLE + 1);
+    for (int i = 0; i < count; i++) {
+        float lo = FAR_AWAY, hi = VERY_CLOSE;
+        for (int r = 0; r < n; r++) {
+            float a = rangeImages[r][2 * i], b = rangeImages[r][2 * i + 1];
+            if (a < lo) lo = a;
+            if (b > hi) hi = b;
+        }
+        mergedRange[2 * i] = lo; mergedRange[2 * i + 1] = hi;
+    }
+    dsb200_render_state rs; memset(&rs, 0, sizeof(rs));
+    rs.range_image = mergedRange; rs.raycast_result = out; rs.width = W; rs.height = H;
+    g_shardSet.n = n; g_shardSet.brickLog2 = brickLog2; g_shardSet.scenes = scenes;
+    genericRaycast(scenes[0], W, H, invM, intr, &rs);
+    g_shardSet.n = 0; g_shardSet.scenes = nullptr;
+}
+
+// nearest-hit composite of the shards' raycast results (definition in include/dsb200.h, dsb200_composite_nearest)
+void rst_composite_nearest(int n, const float *const *results, const float *invM, float voxelSize, int W, int H,
+                           int rowBegin, int rowEnd, float *out)
+{
+    (void)H;
+    const float k = 1.0f / voxelSize;
+    const float cx = invM[12] * k, cy = invM[13] * k, cz = invM[14] * k;
+    for (int i = rowBegin * W; i < rowEnd * W; i++) {
+        float best[4] = {0.0f, 0.0f, 0.0f, 0.0f}, bestD = 0.0f;
+        bool have = false;
+        for (int r = 0; r < n; r++) {
+            const float *q = results[r] + 4 * (size_t)i;
+            if (q[3] > 0.0f) {
+                float dx = q[0] - cx, dy = q[1] - cy, dz = q[2] - cz;
+                float d = dx * dx + dy * dy + dz * dz;
+                if (!have || d < bestD) { memcpy(best, q, 16); bestD = d; have = true; }
+            }
+        }
+        memcpy(out + 4 * (size_t)i, best, 16);
     }
 }
 

@@ -30,6 +30,16 @@ size_t rst_decayed_block_count(const rst_recon *e);
 void rst_history_sizes(const rst_recon *e, int *decay_q, int *slide_q, int *decay_defusion_q,
                        int *slide_defusion_q, int *snapshots);
 
+void rst_set_shard(rst_recon *e, const dsb200_shard *s);
+int rst_shard_owner(int bx, int by, int bz, int count, int brick_log2);
+int rst_shard_holds(int bx, int by, int bz, const dsb200_shard *s);
+void rst_raycast_sharded(int n, const dsb200_scene *const *scenes, const float *const *range_images, int brick_log2,
+                         const float *invM, const float *intr, int W, int H, float *merged_range, float *out);
+void rst_composite_nearest(int n, const float *const *results, const float *invM, float voxel_size, int W, int H,
+                           int row_begin, int row_end, float *out);
+void rst_icp_maps_from_raycast(const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *tracking,
+                               const float *raycast_result, uint8_t *out_rendering, int W, int H);
+
 void rst_reset_scene(rst_recon *e, dsb200_scene *scene);
 int rst_allocate_from_depth(rst_recon *e, dsb200_scene *scene, const dsb200_view *view,
                             const dsb200_tracking *tracking, dsb200_render_state *rs,

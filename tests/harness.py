@@ -298,3 +298,84 @@ def assert_images_equal(a, b, what=""):
             bad = np.nonzero(x.reshape(-1) != y.reshape(-1))[0]
             raise AssertionError("%s image '%s' differs at %d of %d elements; first %s: %s vs %s" % (
                 what, k, bad.size, x.size, bad[:4], a[k].reshape(-1)[bad[:4]], b[k].reshape(-1)[bad[:4]]))
+
+
+# ---------------------------------------------------------------- sharded scene
+class OracleShardedScene(object):
+    """CPU restatement of the sharded scene: `count` oracle shards with the ownership filter, each running the
+    unchanged serial pipeline on its own table; nearest-hit composite; ICP maps on the composite."""
+
+    def __init__(self, cfg, caps, count, brick_log2=2, ranks=None, halo=False, mode=None):
+        mode = mode or ("composite" if halo else "lookup")
+        halo = halo or mode == "composite"
+        self.cfg, self.count, self.mode, self.brick_log2 = cfg, count, mode, brick_log2
+        self.ranks = list(range(count)) if ranks is None else list(ranks)     # the shards THIS process restates
+        self.members = []
+        for r in self.ranks:
+            m = OracleBackend(cfg, caps)
+            sh = abi.Shard(r, count, brick_log2, 1 if halo else 0)
+            m.o.L.rst_set_shard(m.e, C.byref(sh))
+            self.members.append(m)
+        self.composite = np.zeros((cfg.H, cfg.W, 4), np.float32)
+        self.merged_range = np.zeros((cfg.H, cfg.W, 2), np.float32)
+
+    def fuse(self, f):
+        for m in self.members:
+            m.set_frame(f)
+            m.allocate(); m.integrate(); m.expected_depths()
+
+    def fuse_and_raycast(self, f):
+        self.fuse(f)
+        for m in self.members:
+            m.o.L.rst_find_surface(C.byref(m.scene.c), m.trk.invM_d, m.view.intr_d, C.byref(m.rs.c))
+
+    def raycast_lookup_and_icp(self, scenes=None, ranges=None):
+        """whole-scene raycast with owner-routed reads; scenes / ranges default to this process's members (all shards)"""
+        m0 = self.members[0]
+        scenes = [m.scene.c for m in self.members] if scenes is None else scenes
+        ranges = [m.rs.range_image for m in self.members] if ranges is None else ranges
+        sp = (C.c_void_p * len(scenes))(*[C.addressof(s) for s in scenes])
+        rp = (C.c_void_p * len(ranges))(*[po.ptr(r) for r in ranges])
+        m0.o.L.rst_raycast_sharded(len(scenes), sp, rp, self.brick_log2, m0.trk.invM_d, m0.view.intr_d, self.cfg.W, self.cfg.H,
+                                   po.ptr(self.merged_range), po.ptr(self.composite))
+        m0.o.L.rst_icp_maps_from_raycast(C.byref(m0.scene.c), C.byref(m0.view), C.byref(m0.trk), po.ptr(self.composite),
+                                         po.ptr(m0.rs.raycast_image), self.cfg.W, self.cfg.H)
+
+    def composite_and_icp(self, results=None):
+        """results: list of (H, W, 4) float32 raycast images in shard order (defaults to this process's members)"""
+        m0 = self.members[0]
+        results = [np.ascontiguousarray(m.rs.raycast_result) for m in self.members] if results is None else results
+        arr = (C.c_void_p * len(results))(*[po.ptr(r) for r in results])
+        m0.o.L.rst_composite_nearest(len(results), arr, m0.trk.invM_d, self.cfg.params().voxel_size, self.cfg.W, self.cfg.H,
+                                     0, self.cfg.H, po.ptr(self.composite))
+        m0.o.L.rst_icp_maps_from_raycast(C.byref(m0.scene.c), C.byref(m0.view), C.byref(m0.trk), po.ptr(self.composite),
+                                         po.ptr(m0.rs.raycast_image), self.cfg.W, self.cfg.H)
+
+    def process_frame(self, f):
+        if self.mode == "composite":
+            self.fuse_and_raycast(f)
+            self.composite_and_icp()
+        else:
+            self.fuse(f)
+            self.raycast_lookup_and_icp()
+
+    def images(self):
+        m0 = self.members[0]
+        return dict(composite=self.composite.copy(), points=m0.pts.copy(), normals=m0.nrm.copy(), rendering=m0.rs.raycast_image.copy())
+
+    def close(self):
+        for m in self.members:
+            m.close()
+
+
+def gpu_member_state(m):
+    """state dict of a sharded.ShardMember in the layout of GpuBackend.state()"""
+    return dict(hash=m.scene.hash(), visible=m.rs.visible(), visible_type=m.rs.visible_type(),
+                last_free=(m.scene.c.last_free_block, m.scene.c.last_free_excess), alloc_list=m.scene.alloc_list(),
+                excess_list=m.scene.excess_list(), voxels=m.scene.voxels())
+
+
+def allocated_blocks(hash_table):
+    """set of (x, y, z) of the live entries of a hash table download"""
+    live = hash_table[hash_table["ptr"] >= 0]
+    return set(map(tuple, live["pos"].tolist()))
