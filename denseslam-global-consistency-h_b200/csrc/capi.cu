@@ -109,6 +109,7 @@ struct dsb200_recon {
     Counters *hostCounters = nullptr; // pinned
     dsb200_weight_params weights{0, 10, 100};
     bool async = false, deviceCountersValid = false;
+    int lastKnownVisible = 0;         // visible count at the last host sync: sizes the snapshot reservations made while asynchronous
     const uint8_t *visBitsOwner = nullptr;   // the render state's visibility-flag array that fs.visBits currently describes
     cudaStream_t sideStream = nullptr; cudaEvent_t evFork = nullptr, evJoin = nullptr;   // fused frame: expected depths || integration
     dsb200_shard shard{0, 1, 2, 0};      // sharded scene: this engine's block ownership (count <= 1: everything)
@@ -244,6 +245,13 @@ static int sync_counters(dsb200_recon *e, dsb200_scene *scene, dsb200_render_sta
     CU(cudaStreamSynchronize(e->stream));
     if (scene) { scene->last_free_block = e->hostCounters->lastFreeBlock; scene->last_free_excess = e->hostCounters->lastFreeExcess; }
     if (rs) rs->no_visible = e->hostCounters->noVisible;
+    e->lastKnownVisible = e->hostCounters->noVisible;
+    if (e->hostCounters->snapshotOverflow) {
+        e->hostCounters->snapshotOverflow = 0;
+        CU(cudaMemcpyAsync(&e->fs.counters->snapshotOverflow, &e->hostCounters->snapshotOverflow, 4, cudaMemcpyHostToDevice, e->stream));
+        return fail(DSB200_ERR_INVALID, "a visible-list snapshot outgrew its asynchronous reservation (the visible set more than doubled "
+                                        "since the last dsb200_recon_sync): synchronise more often");
+    }
     if (e->prunePending) {
         e->totalDecayed += e->hostCounters->lastFreeBlock - e->lastFreeBeforePrune;
         e->prunePending = false;
@@ -349,7 +357,12 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     DSB_MARK_A(3);
     // snapshot reservation for decay / slide window / de-fusion (CUDA .cu:257-317)
     SnapPtr snap = std::make_shared<Snapshot>();
-    snap->regionInts = 64 + (((size_t)rs->visible_capacity + 63) & ~(size_t)63);
+    // Synchronous calls trim the reservation to the real count on return.  While asynchronous the count is unknown until
+    // the next sync, so reserve twice the last known visible count (+64 Ki) instead of the full capacity (8 MB per frame at
+    // the bench capacities); k_visible_list bounds its writes and flags an overflow, reported by the next sync.
+    size_t snapCap = (size_t)rs->visible_capacity;
+    if (e->async && e->deviceCountersValid && 2 * (size_t)e->lastKnownVisible + 65536 < snapCap) snapCap = 2 * (size_t)e->lastKnownVisible + 65536;
+    snap->regionInts = 64 + ((snapCap + 63) & ~(size_t)63);
     snap->chunk = e->arena.reserve(snap->regionInts, &snap->region);
     if (!snap->chunk) return fail(DSB200_ERR_CUDA, "out of device memory for the visible-list snapshot arena");
     snap->countDev = snap->region; snap->ids = snap->region + 64;
@@ -359,7 +372,7 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     launch_recheck_visibility(e->stream, VP, e->fs, scene->hash, rs->visible_ids, rs->visible_type);
     DSB_MARK_A(4);
     launch_visible_list(e->stream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, rs->visible_ids,
-                        rs->visible_capacity, snap->ids, snap->countDev, e->total);
+                        rs->visible_capacity, snap->ids, snap->countDev, (int)snapCap, e->total);
     DSB_MARK_A(5);
     if (e->profile) e->evAllocRecorded = true;
     e->unsynced.push_back(snap);

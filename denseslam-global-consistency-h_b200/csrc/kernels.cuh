@@ -72,7 +72,7 @@ void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs
                      unsigned *reqKey, int total, int doAllocate);
 void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &fs, dsb200_hash_entry *hash,
                          const int *allocList, uint8_t *visType, int *visibleIds, int visibleCapacity, int *snapshotIds,
-                         int *snapshotCount, int total);
+                         int *snapshotCount, int snapshotCapacity, int total);
 
 // recon_integrate.cu
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,

@@ -261,7 +261,7 @@ __device__ __forceinline__ unsigned flag_mask32(const uint8_t *visType, int w, i
 __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs, dsb200_hash_entry *hash,
                                                       const int *__restrict__ allocList, uint8_t *visType,
                                                       int *visibleIds, int visibleCapacity, int *snapshotIds,
-                                                      int *snapshotCount, int total)
+                                                      int *snapshotCount, int snapshotCapacity, int total)
 {
     __shared__ unsigned sScan[16];
     __shared__ int sTile;
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs
         DSB_FOR_EACH_BIT(keep, word0, h, j, bit) {
             if ((int)ra < visibleCapacity) {
                 visibleIds[ra] = h;
-                if (snapshotIds) snapshotIds[ra] = h;
+                if (snapshotIds && (int)ra < snapshotCapacity) snapshotIds[ra] = h;
             }
             ra++;
             if ((swapIn[j] >> bit) & 1u) {
@@ -359,7 +359,11 @@ __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs
     if (threadIdx.x == 0 && tile == gridDim.x - 1) {
         const int n = (int)(sEx[0] + totA);
         fs.counters->noVisible = n;
-        if (snapshotCount) *snapshotCount = n < visibleCapacity ? n : visibleCapacity;
+        if (snapshotCount) {
+            const int m = n < visibleCapacity ? n : visibleCapacity;
+            *snapshotCount = m < snapshotCapacity ? m : snapshotCapacity;
+            if (m > snapshotCapacity) fs.counters->snapshotOverflow = 1;
+        }
         // commit the frame's free-list tops (no tile of this kernel reads these two fields)
         fs.counters->lastFreeBlock = fs.counters->lastFreeBlockNew - (int)(sEx[1] + totB);
         fs.counters->lastFreeExcess = fs.counters->lastFreeExcessNew;
@@ -400,10 +404,10 @@ void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs
 
 void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &fs, dsb200_hash_entry *hash,
                          const int *allocList, uint8_t *visType, int *visibleIds, int visibleCapacity, int *snapshotIds,
-                         int *snapshotCount, int total)
+                         int *snapshotCount, int snapshotCapacity, int total)
 {
     DSB_LAUNCH(k_visible_list, fs.bitTiles, 256, 0, st, P, fs, hash, allocList, visType, visibleIds, visibleCapacity,
-               snapshotIds, snapshotCount, total);
+               snapshotIds, snapshotCount, snapshotCapacity, total);
 }
 
 // must run between launch_allocate and launch_visible_list: visibleIds still holds the PREVIOUS list at that point

@@ -11,6 +11,7 @@
 //    order == float order); the reference's rendering-block cap is honoured by an exact serial
 //    fallback that only runs when the cap would be hit;
 //  * nothing returns to the host between stages (counts stay on the device).
+#include <cstdlib>
 #include "kernels.cuh"
 #include "scan.cuh"
 #include "visibility.cuh"
@@ -345,12 +346,16 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 // pixels do not march at all, grazing road pixels cross hundreds of voxels), so a static pixel-tile -> CTA map leaves
 // most of the machine idle behind a few long tiles (41 % achieved occupancy in profiles/r01a).  Here every WARP pulls
 // the next 8x4 pixel tile from a device ticket; the last warp to run dry re-arms the ticket pair for the next launch.
+// `bottomUp` hands the tiles out from the last image row upwards (the long grazing rays of a forward-looking camera sit
+// at the bottom: they start first and the short ones fill the tail).
+// (A persistent lane-refilling variant -- idle lanes of a warp take new pixels while the others keep marching -- was
+// measured 1.6x SLOWER on B200: the march is bound by the two dependent L2 round trips per step, not by idle lanes.)
 // Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
 // root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
 template <class Tables>
 __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_constant__ Tables T,
                                                  const float2 *__restrict__ range, float4 *out, int *ticket, int tileFirst,
-                                                 int tileStride)
+                                                 int tileStride, int bottomUp)
 {
     const int lane = threadIdx.x & 31;
     const int tilesX = (P.W + 7) >> 3, tilesY = (P.H + 3) >> 2, nTiles = tilesX * tilesY;
@@ -359,6 +364,7 @@ __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_const
         if (lane == 0) tile = atomicAdd(&ticket[0], 1);
         tile = __shfl_sync(0xffffffffu, tile, 0) * tileStride + tileFirst;
         if (tile >= nTiles) break;
+        if (bottomUp) tile = nTiles - 1 - tile;
         const int ty = tile / tilesX, tx = tile - ty * tilesX;
         const int x = tx * 8 + (lane & 7), y = ty * 4 + (lane >> 3);
         if (x < P.W && y < P.H) {
@@ -605,15 +611,20 @@ void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_h
     DSB_LAUNCH(k_range_cap_fallback, 1, 1024, 0, st, P, hash, ids, count, rangeImage, counters);
 }
 
+// tuning knobs (defaults measured on B200, profiles/): tile hand-out order, CTAs launched per SM
+static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
+static int ray_bottom_up() { static int v = env_int("DSB200_RAY_BOTTOM_UP", 0); return v != 0; }
+static int ray_ctas_per_sm() { static int v = env_int("DSB200_RAY_CTAS", 12); return v < 1 ? 1 : v; }
+
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
                     const float *rangeImage, float *raycastResult, int *ticketPair)
 {
     const int nTiles = div_up(P.W, 8) * div_up(P.H, 4);
     int grid = div_up(nTiles, 4);
-    if (grid > kNumSMs * 12) grid = kNumSMs * 12;
+    if (grid > kNumSMs * ray_ctas_per_sm()) grid = kNumSMs * ray_ctas_per_sm();
     const SceneTables T = {voxels, hash};
     DSB_LAUNCH(k_raycast<SceneTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(rangeImage),
-               reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1);
+               reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1, ray_bottom_up());
 }
 
 // Expected-depth image of the whole sharded scene = element-wise (min of mins, max of maxes) of the shards' images: what
@@ -646,9 +657,9 @@ void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank
     for (int r = 0; r < kMaxShards; r++) { T.hash[r] = hash[r < n ? r : 0]; T.voxels[r] = voxels[r < n ? r : 0]; }
     const int nTiles = div_up(div_up(P.W, 8) * div_up(P.H, 4), n);
     int grid = div_up(nTiles, 4);
-    if (grid > kNumSMs * 12) grid = kNumSMs * 12;
+    if (grid > kNumSMs * ray_ctas_per_sm()) grid = kNumSMs * ray_ctas_per_sm();
     DSB_LAUNCH(k_raycast<ShardTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(mergedRange),
-               reinterpret_cast<float4 *>(raycastResult), ticketPair, rank, n);
+               reinterpret_cast<float4 *>(raycastResult), ticketPair, rank, n, ray_bottom_up());
 }
 
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,
