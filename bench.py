@@ -34,6 +34,16 @@ PKG = "denseslam-global-consistency-h_b200"
 
 WORKLOAD = "C2"
 CAPS = dict(num_blocks=1 << 21, bucket_num=1 << 22, excess_size=1 << 20)   # 8 GiB VBA: 1000 street frames fit
+# other BASELINE.json configs, selected with --workload (the driver's default run stays C2, the config the metric is quoted on)
+WORKLOADS = {
+    "C1": dict(caps=dict(num_blocks=1 << 20, bucket_num=1 << 21, excess_size=1 << 19), prune=None,
+               text="C1 ICL-NUIM-shaped 640x480 synthetic depth, 5 mm voxels, mu 2 cm, orbit in a furnished room"),
+    "C2": dict(caps=CAPS, prune=None,
+               text="C2 KITTI-stereo-shaped 1242x375 synthetic disparity depth, 2 cm voxels, mu 8 cm, depth weighting on"),
+    "C3": dict(caps=dict(num_blocks=1 << 20, bucket_num=1 << 21, excess_size=1 << 19), prune=dict(max_weight=3, min_age=40, max_age=80),
+               text="C3 TUM-RGBD-shaped 640x480 synthetic depth, 5 mm voxels, voxel decay (max weight 3, min age 40) + "
+                    "sliding-window block pruning (max age 80) after every frame"),
+}
 REF_SAMPLE_FRAMES = 12      # bounded CPU sample: the reference's capacities are compile-time (262144 blocks)
 METRIC = "frames/s alloc+integrate+raycast (1242x375, 2 cm voxels)"
 
@@ -180,9 +190,27 @@ def run_ours(args, rank, world, local_rank):
         v.depth, v.rgb, v.timestamp = d_depth[i].data_ptr(), d_rgb[i].data_ptr(), f.timestamp
         views.append(v)
 
-    def frame_async(i):
+    prune = WORKLOADS[WORKLOAD]["prune"]
+    prune_ev = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
+    prune_ms = [0.0]
+
+    def prune_pass(timed=False):
+        """DenseSlam::ProcessFrame's map maintenance (DS/DenseSlam.cpp:217-251): SlideWindow, then Decay"""
+        if not prune:
+            return
+        if timed:
+            prune_ev[0].record()
+        abi.check(lib.dsb200_slide_window(recon.h, C.byref(scene.c), C.byref(rs.c), prune["max_age"]))
+        abi.check(lib.dsb200_decay(recon.h, C.byref(scene.c), C.byref(rs.c), prune["max_weight"], prune["min_age"], 0))
+        if timed:
+            prune_ev[1].record()
+            prune_ev[1].synchronize()
+            prune_ms[0] += prune_ev[0].elapsed_time(prune_ev[1])
+
+    def frame_async(i, timed_prune=False):
         trk.set_pose(frames[i].M)
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views[i]), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
+        prune_pass(timed_prune)
 
     def reset_all():
         recon.ResetScene(scene)
@@ -214,7 +242,7 @@ def run_ours(args, rank, world, local_rank):
         for k in range(K):
             flush.zero_()                      # L2 flush between timed iterations (outside the event pair)
             evs[k][0].record()
-            frame_async(Wm + k)
+            frame_async(Wm + k, profile)
             evs[k][1].record()
             if profile:
                 abi.check(lib.dsb200_profile_read(recon.h, stage_buf))      # synchronises; device-side stage times
@@ -278,6 +306,7 @@ def run_ours(args, rank, world, local_rank):
         trk.set_pose(frames[i].M)
         rs.c.raycast_image = imgs_e[b]
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views_e[b].c), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
+        prune_pass()
         ev_free[b].record(main)
         ev_done[b].record(main)
         s_down.wait_event(ev_done[b])
@@ -332,8 +361,7 @@ def run_ours(args, rank, world, local_rank):
     out = {"metric": METRIC, "value": world * K / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic",
-           "config": {"workload": "C2 KITTI-stereo-shaped 1242x375 synthetic disparity depth, 2 cm voxels, mu 8 cm, depth weighting on; "
-                                  "one scene per GPU (replicas only)", "frames": K, "mean_visible_blocks": V,
+           "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only)", "frames": K, "mean_visible_blocks": V,
                       "blocks_allocated": int(blocks_used), "capacity_blocks": CAPS["num_blocks"], "l2": "flushed (256 MiB write) between timed steps"},
            "e2e": {"value": world * K / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": 8 * npx,
                    "d2h_bytes_per_step": 4 * npx, "ms_per_step": e2e_ms / K,
@@ -341,7 +369,8 @@ def run_ours(args, rank, world, local_rank):
            "gpu_launches": launches, "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"},
-           "stages": stages,
+           "stages": stages, "prune_ms_per_frame": (prune_ms[0] / K) if prune else None,
+           "decayed_blocks": recon.GetDecayedBlockCount() if prune else None,
            "allocate_kernels_ms": dict(zip(["begin_frame", "alloc_requests", "allocate", "recheck_visibility", "visible_list"],
                                            [float(x) / K for x in alloc_stage]))}
     if world == 1:
@@ -351,6 +380,92 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.destroy_process_group()
     return out
+
+
+# ------------------------------------------------------------------------------------------------ batched scenes
+def run_batched(args, rank, world, local_rank):
+    """BASELINE configs[4]: S independent sequences per GPU, one scene + one engine pair + one CUDA stream each, frames
+    submitted round-robin so the scenes' (latency-bound) kernels overlap.  value = total frames / max time over ranks."""
+    import torch
+    import torch.distributed as dist
+    abi = importlib.import_module(PKG + ".abi")
+    eng = importlib.import_module(PKG + ".engine")
+    lib = abi.load()
+    if lib.dsb200_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
+    abi.check(lib.dsb200_set_device(local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    K, Wm, S = args.steps, args.warmup, args.scenes
+    caps = dict(num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS, excess_size=abi.DEFAULT_EXCESS)   # the reference's capacities
+    lanes = []
+    for si in range(S):
+        cfg, frames = make_frames(K + Wm, seed=rank * S + si)
+        st = torch.cuda.Stream()
+        scene = eng.ITMScene(cfg.params(), **caps)
+        recon = eng.ITMSceneReconstructionEngine(stream=st.cuda_stream, **caps)
+        recon.SetFusionWeightParams(cfg.depth_weighting, 10, 100)
+        vis = eng.ITMVisualisationEngine(cfg.W, cfg.H, stream=st.cuda_stream)
+        rs = vis.CreateRenderState(scene, (cfg.W, cfg.H))
+        trk = eng.ITMTrackingState(cfg.W, cfg.H)
+        view = eng.ITMView(cfg.W, cfg.H, cfg.intr)
+        d_depth = torch.from_numpy(np.stack([f.depth for f in frames])).to(dev)
+        d_rgb = torch.from_numpy(np.stack([f.rgb for f in frames])).to(dev)
+        recon.ResetScene(scene)
+        recon.SetAsync(True)
+        lanes.append(dict(cfg=cfg, frames=frames, st=st, scene=scene, recon=recon, vis=vis, rs=rs, trk=trk, view=view, depth=d_depth, rgb=d_rgb))
+    torch.cuda.synchronize()
+
+    def submit(i):
+        for L in lanes:
+            L["view"].c.depth, L["view"].c.rgb = L["depth"][i].data_ptr(), L["rgb"][i].data_ptr()
+            L["view"].c.timestamp = L["frames"][i].timestamp
+            L["trk"].set_pose(L["frames"][i].M)
+            abi.check(lib.dsb200_process_frame(L["recon"].h, L["vis"].h, C.byref(L["scene"].c), C.byref(L["view"].c), C.byref(L["trk"].c),
+                                               C.byref(L["rs"].c), abi.FRAME_ALL))
+    for i in range(Wm):
+        submit(i)
+    for L in lanes:
+        L["recon"].Sync(L["scene"], L["rs"])
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    l0 = lib.dsb200_kernel_launch_count()
+    main = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank); sampler.start()
+    e0.record()
+    for L in lanes:
+        L["st"].wait_event(e0)
+    for k in range(K):
+        submit(Wm + k)
+    for L in lanes:
+        main.wait_stream(L["st"])
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    launches = int(lib.dsb200_kernel_launch_count() - l0)
+    ms = float(e0.elapsed_time(e1))
+    vis_mean = []
+    for L in lanes:
+        L["recon"].Sync(L["scene"], L["rs"])
+        vis_mean.append(L["rs"].c.no_visible)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    return {"metric": METRIC, "value": world * S * K / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic", "mode": "batched",
+            "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; %d independent sequences per GPU, one scene + one stream each "
+                                   "(a step = one frame of every sequence)" % S, "scenes_per_gpu": S, "frames_per_scene": K,
+                       "final_visible_blocks_mean": float(np.mean(vis_mean)), "l2": "not flushed: %d scenes x visible set exceed L2" % S},
+            "gpu_launches": launches, "clocks": clocks}
 
 
 # ------------------------------------------------------------------------------------------------ sharded scene
@@ -428,11 +543,18 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default="replicas", choices=["replicas", "sharded"],
+    ap.add_argument("--scenes", type=int, default=8, help="--mode batched: independent sequences per GPU")
+    ap.add_argument("--mode", default="replicas", choices=["replicas", "sharded", "batched"],
                     help="N > 1: independent scenes per GPU (default, weak scaling) or ONE scene sharded by block ownership")
     ap.add_argument("--shard-mode", default="lookup", choices=["lookup", "composite"])
     ap.add_argument("--brick-log2", type=int, default=2)
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS.keys()),
+                    help="BASELINE.json config to run (default C2: the configuration the metric is quoted on)")
     args = ap.parse_args()
+    global WORKLOAD, CAPS, METRIC
+    WORKLOAD, CAPS = args.workload, WORKLOADS[args.workload]["caps"]
+    if WORKLOAD != "C2":
+        METRIC = "frames/s alloc+integrate+raycast (640x480, 5 mm voxels%s)" % (", decay + slide window" if WORKLOAD == "C3" else "")
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -440,6 +562,8 @@ def main():
         out = run_reference(args, rank, world)
     elif args.mode == "sharded":
         out = run_sharded(args, rank, world, local_rank)
+    elif args.mode == "batched":
+        out = run_batched(args, rank, world, local_rank)
     else:
         out = run_ours(args, rank, world, local_rank)
     if out is not None:

@@ -134,6 +134,7 @@ def load():
         "dsb200_create_icp_maps": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
         "dsb200_render_image": (C.c_int, [vp, _P(Scene), _P(C.c_float), _P(C.c_float), _P(C.c_float), _P(RenderState), vp, vp, C.c_int]),
         "dsb200_forward_render": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
+        "dsb200_forward_projection": (C.c_int, [vp, _P(vp), _P(C.c_int)]),
         "dsb200_create_point_cloud": (C.c_int, [vp]),
         "dsb200_process_frame": (C.c_int, [vp, vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), C.c_int]),
         "dsb200_recon_set_shard": (C.c_int, [vp, _P(Shard)]),

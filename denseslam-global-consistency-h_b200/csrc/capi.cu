@@ -120,7 +120,6 @@ struct dsb200_recon {
     std::vector<SnapPtr> unsynced;         // snapshots whose host count is not known yet (async mode)
     size_t frameIdx = 0;
     long long totalDecayed = 0;
-    int lastFreeBeforePrune = 0; bool prunePending = false;
     Arena arena;
     cudaEvent_t evAlloc[DSB200_PROFILE_ALLOC_STAGES + 1] = {}; bool evAllocRecorded = false;
     bool profile = false; cudaEvent_t ev[DSB200_PROFILE_STAGES + 1] = {}; bool evRecorded[DSB200_PROFILE_STAGES + 1] = {};
@@ -252,10 +251,7 @@ static int sync_counters(dsb200_recon *e, dsb200_scene *scene, dsb200_render_sta
         return fail(DSB200_ERR_INVALID, "a visible-list snapshot outgrew its asynchronous reservation (the visible set more than doubled "
                                         "since the last dsb200_recon_sync): synchronise more often");
     }
-    if (e->prunePending) {
-        e->totalDecayed += e->hostCounters->lastFreeBlock - e->lastFreeBeforePrune;
-        e->prunePending = false;
-    }
+    e->totalDecayed = e->hostCounters->totalFreed;     // accumulated on the device: exact whatever ran between two syncs
     if (!e->unsynced.empty()) {
         // host counts of snapshots taken since the last sync
         std::vector<int> counts(e->unsynced.size());
@@ -479,7 +475,6 @@ static int prune_from_queue(dsb200_recon *e, dsb200_scene *scene, dsb200_render_
                 e->hostCounters->lastFreeBlock = scene->last_free_block;
                 CU(cudaMemcpyAsync(&e->fs.counters->lastFreeBlock, &e->hostCounters->lastFreeBlock, 4, cudaMemcpyHostToDevice, e->stream));
             }
-            if (!e->prunePending) { e->lastFreeBeforePrune = scene->last_free_block; e->prunePending = true; }
             int bound = snap->countHost >= 0 ? snap->countHost : (int)(snap->regionInts - 64);
             if (bound > e->pruneCap) return fail(DSB200_ERR_INVALID, "snapshot larger than the pruning scratch");
             launch_prune(e->stream, slide, scene->voxels, scene->hash, scene->bucket_num, snap->ids, snap->countDev, e->pruneCap,
@@ -696,10 +691,32 @@ int dsb200_ipc_open(const uint8_t handle[DSB200_IPC_HANDLE_BYTES], void **p)
 }
 int dsb200_ipc_close(void *p) { CU(cudaIpcCloseMemHandle(p)); return DSB200_OK; }
 
-int dsb200_forward_render(dsb200_vis *, const dsb200_scene *, const dsb200_view *, dsb200_tracking *, dsb200_render_state *)
+int dsb200_forward_render(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *trk, dsb200_render_state *rs)
 {
-    // only reachable with useApproximateRaycast, which DenseSLAM never sets
-    return fail(DSB200_ERR_UNSUPPORTED, "ForwardRender (approximate raycast) is not built yet");
+    // only reached with useApproximateRaycast, which DenseSLAM never sets; built for interface completeness
+    if (!v || !scene || !view || !trk || !rs || !view->depth) return fail(DSB200_ERR_INVALID, "forward_render: null argument");
+    const int px = rs->width * rs->height;
+    if (px > v->fwdPixels) {
+        if (v->fwdProjection) { CU(cudaFree(v->fwdProjection)); CU(cudaFree(v->fwdMissing)); }
+        CU(cudaMalloc(&v->fwdProjection, (size_t)px * 16));
+        CU(cudaMalloc(&v->fwdMissing, (size_t)px * 4));
+        v->fwdPixels = px;
+    }
+    RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
+    launch_forward_render(v->stream, P, view->intr_d, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, view->depth,
+                          v->fwdProjection, v->fwdMissing, v->countScratch + 2, rs->raycast_image);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(&v->hostInts[2], v->countScratch + 2, 4, cudaMemcpyDeviceToHost, v->stream));
+    CU(cudaStreamSynchronize(v->stream));
+    return DSB200_OK;
+}
+
+int dsb200_forward_projection(dsb200_vis *v, const float **fwd, int *no_missing)
+{
+    if (!v || !v->fwdProjection) return fail(DSB200_ERR_INVALID, "forward_projection: ForwardRender has not run");
+    if (fwd) *fwd = v->fwdProjection;
+    if (no_missing) *no_missing = v->hostInts[2];
+    return DSB200_OK;
 }
 
 int dsb200_create_point_cloud(dsb200_vis *)

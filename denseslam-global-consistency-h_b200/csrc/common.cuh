@@ -118,6 +118,7 @@ struct Counters {
     int freedBlocks;       // blocks released by the last pruning pass
     int lastFreeBlockNew;  // k_allocate result, committed by k_visible_list
     int lastFreeExcessNew;
+    int totalFreed;        // blocks released by all pruning passes since ResetScene (GetDecayedBlockCount)
     int snapshotOverflow;  // a visible-list snapshot did not fit its asynchronous reservation (sticky until the next sync)
 };
 

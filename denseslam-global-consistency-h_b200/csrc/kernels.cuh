@@ -110,6 +110,6 @@ void launch_shade(cudaStream_t st, const RayParams &P, int renderType, const dsb
                   const dsb200_hash_entry *hash, const float *raycastResult, uint8_t *outRGBA, float *outDepth);
 void launch_forward_render(cudaStream_t st, const RayParams &P, const float *proj, const dsb200_voxel *voxels,
                            const dsb200_hash_entry *hash, const float *rangeImage, const float *raycastResult,
-                           const float *depth, float *fwd, int *missing, int *noMissing, uint8_t *rendering);
+                           const float *depth, float *fwd, int *owner, int *noMissing, uint8_t *rendering);
 
 } // namespace dsb

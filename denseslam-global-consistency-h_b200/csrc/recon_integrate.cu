@@ -250,8 +250,8 @@ struct FuseWarpSmem {
     unsigned dirty[kFuseWarps][8];
 };
 
-template <bool DE, bool FAST>
-__global__ void __launch_bounds__(kFuseWarps * 32, 8) k_fuse_warp(FuseParams P, dsb200_voxel *voxels,
+template <bool DE, bool FAST, int MINB>
+__global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp(FuseParams P, dsb200_voxel *voxels,
                                                                    const dsb200_hash_entry *__restrict__ hash,
                                                                    const int *__restrict__ ids, const int *__restrict__ countPtr,
                                                                    const float *__restrict__ depth, const uchar4 *__restrict__ rgb)
@@ -358,11 +358,11 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
     if (variant == 1) {
         const int g = kNumSMs * 8;
         if (deintegrate) {
-            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<true, true>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
-            else DSB_LAUNCH((k_fuse_warp<true, false>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<true, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+            else DSB_LAUNCH((k_fuse_warp<true, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
         } else {
-            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<false, true>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
-            else DSB_LAUNCH((k_fuse_warp<false, false>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<false, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+            else DSB_LAUNCH((k_fuse_warp<false, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
         }
         return;
     }
@@ -456,7 +456,7 @@ __global__ void __launch_bounds__(256) k_reset_scene(uint4 *voxels2, size_t numV
     if (tid == 0) {
         counters->lastFreeBlock = numBlocks - 1; counters->lastFreeExcess = excessSize - 1;
         counters->lastFreeBlockNew = numBlocks - 1; counters->lastFreeExcessNew = excessSize - 1;
-        counters->noVisible = 0; counters->noVisiblePrev = 0; counters->renderBlocks = 0; counters->freedBlocks = 0; counters->snapshotOverflow = 0;
+        counters->noVisible = 0; counters->noVisiblePrev = 0; counters->renderBlocks = 0; counters->freedBlocks = 0; counters->snapshotOverflow = 0; counters->totalFreed = 0;
     }
 }
 

@@ -136,6 +136,7 @@ __global__ void __launch_bounds__(256) k_prune_rank(const dsb200_hash_entry *has
         }
         if (threadIdx.x == 0 && tile == nTiles - 1) {
             fs.counters->freedBlocks = (int)(sEx[0] + totA);
+            fs.counters->totalFreed += (int)(sEx[0] + totA);
             fs.counters->lastFreeBlockNew = lastFree0 + (int)(sEx[0] + totA);
         }
     }

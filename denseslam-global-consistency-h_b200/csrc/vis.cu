@@ -476,6 +476,73 @@ void launch_composite_nearest(cudaStream_t st, int n, const float *const *result
     DSB_LAUNCH(k_composite_nearest, grid, 256, 0, st, imgs, n, cx, cy, cz, begin, end, reinterpret_cast<float4 *>(out));
 }
 
+// ---------------------------------------------------------------- ForwardRender (approximate raycast)
+// CPU/ITMVisualisationEngine_CPU.cpp:464-540, CUDA .cu:486-547: re-project the previous raycast result into the new
+// pose, raycast only the holes, shade.  The reference scatters with plain stores (CPU: serial, last pixel in scan order
+// wins; CUDA: a race); here the winner is made explicit -- atomicMax of the source pixel index per target pixel, then
+// a gather -- which is the serial result.  Points that project to NaN (z == 0) are skipped (the reference indexes with
+// an undefined int there).
+__global__ void __launch_bounds__(256) k_fwd_project(RayParams P, float4 projParams, const float4 *__restrict__ pts, int *owner)
+{
+    const int loc = blockIdx.x * blockDim.x + threadIdx.x;
+    if (loc >= P.W * P.H) return;
+    const float4 px = __ldg(pts + loc);
+    Vec4 p = {px.x * P.voxelSize, px.y * P.voxelSize, px.z * P.voxelSize, 1.0f};   // forwardProjectPixel: pixel.w forced to 1
+    p = mul(P.M, p);
+    const float u = projParams.x * p.x / p.z + projParams.z, v = projParams.y * p.y / p.z + projParams.w;
+    if (!(u >= 0 && u <= (float)(P.W - 1) && v >= 0 && v <= (float)(P.H - 1))) return;
+    atomicMax(owner + (int)(u + 0.5f) + (int)(v + 0.5f) * P.W, loc + 1);
+}
+
+__global__ void __launch_bounds__(128) k_fwd_fill(RayParams P, const dsb200_voxel *__restrict__ voxels,
+                                                  const dsb200_hash_entry *__restrict__ hash, const float2 *__restrict__ range,
+                                                  const float4 *__restrict__ pts, const float *__restrict__ depth,
+                                                  const int *__restrict__ owner, float4 *fwd, int *noMissing)
+{
+    const int x = blockIdx.x * 16 + (threadIdx.x & 15), y = blockIdx.y * 8 + (threadIdx.x >> 4);
+    if (x >= P.W || y >= P.H) return;
+    const int loc = x + y * P.W;
+    const int o = owner[loc];
+    float4 f = (o > 0) ? __ldg(pts + (o - 1)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
+    const float2 mm = __ldg(range + loc2);
+    // findMissingPoints_device, CUDA .cu:873-905 / CPU .cpp:497-515
+    if ((f.w <= 0) && ((f.x == 0 && f.y == 0 && f.z == 0) || (__ldg(depth + loc) >= 0)) && (mm.x < mm.y)) {
+        atomicAdd(noMissing, 1);
+        const SceneTables T = {voxels, hash};
+        cast_ray(f, x, y, T, P, mm.x, mm.y);
+    }
+    fwd[loc] = f;
+}
+
+// processPixelForwardRender<true>, DeviceAgnostic/ITMVisualisationEngine.h:441-456
+__global__ void __launch_bounds__(256) k_fwd_shade(RayParams P, const float4 *__restrict__ fwd, uchar4 *rendering)
+{
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= P.W || y >= P.H) return;
+    const int loc = x + y * P.W;
+    bool found = __ldg(fwd + loc).w > 0.0f;
+    float n[3], angle = 0.0f;
+    normal_from_image(found, x, y, fwd, P, n, angle);
+    const unsigned char g = found ? (unsigned char)((0.8f * angle + 0.2f) * 255.0f) : 0;
+    rendering[loc] = make_uchar4(g, g, g, g);
+}
+
+void launch_forward_render(cudaStream_t st, const RayParams &P, const float *proj, const dsb200_voxel *voxels,
+                           const dsb200_hash_entry *hash, const float *rangeImage, const float *raycastResult,
+                           const float *depth, float *fwd, int *owner, int *noMissing, uint8_t *rendering)
+{
+    const int n = P.W * P.H;
+    cudaMemsetAsync(owner, 0, (size_t)n * sizeof(int), st);
+    cudaMemsetAsync(noMissing, 0, sizeof(int), st);
+    DSB_LAUNCH(k_fwd_project, div_up(n, 256), 256, 0, st, P, make_float4(proj[0], proj[1], proj[2], proj[3]),
+               reinterpret_cast<const float4 *>(raycastResult), owner);
+    DSB_LAUNCH(k_fwd_fill, dim3(div_up(P.W, 16), div_up(P.H, 8)), 128, 0, st, P, voxels, hash, reinterpret_cast<const float2 *>(rangeImage),
+               reinterpret_cast<const float4 *>(raycastResult), depth, owner, reinterpret_cast<float4 *>(fwd), noMissing);
+    DSB_LAUNCH(k_fwd_shade, dim3(div_up(P.W, 32), div_up(P.H, 8)), 256, 0, st, P, reinterpret_cast<const float4 *>(fwd),
+               reinterpret_cast<uchar4 *>(rendering));
+}
+
 // ---------------------------------------------------------------- free-view shading (RenderImage)
 #define DSB_RV(DX, DY, DZ) ((float)read_sdf(T, bucketNum, bucketMask, X + (DX), Y + (DY), Z + (DZ), f, cache))
 

@@ -268,5 +268,11 @@ class ITMVisualisationEngine(object):
     def ForwardRender(self, scene, view, trackingState, renderState):
         abi.check(_lib().dsb200_forward_render(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c), C.byref(renderState.c)))
 
+    def ForwardProjection(self, width, height):
+        """(forwardProjection image, noFwdProjMissingPoints) of the last ForwardRender"""
+        p, n = C.c_void_p(), C.c_int()
+        abi.check(_lib().dsb200_forward_projection(self.h, C.byref(p), C.byref(n)))
+        return _download(p.value, np.float32, width * height * 4).reshape(height, width, 4), n.value
+
     def CreatePointCloud(self):
         abi.check(_lib().dsb200_create_point_cloud(self.h))

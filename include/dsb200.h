@@ -180,6 +180,8 @@ int dsb200_render_image(dsb200_vis *v, const dsb200_scene *scene, const float *M
                         int render_type);
 int dsb200_forward_render(dsb200_vis *v, const dsb200_scene *scene, const dsb200_view *view,                  /* ForwardRender :122 */
                           dsb200_tracking *tracking, dsb200_render_state *rs);
+/* renderState->forwardProjection (Vector4f[W*H], device, engine-owned) and noFwdProjMissingPoints of the last ForwardRender */
+int dsb200_forward_projection(dsb200_vis *v, const float **forward_projection, int *no_missing_points);
 int dsb200_create_point_cloud(dsb200_vis *v);                                                                 /* CreatePointCloud :112 -> UNSUPPORTED */
 
 /* ---- fused frame: ITMDenseMapper::ProcessFrame + ITMTrackingController::Prepare in one submission

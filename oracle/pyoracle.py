@@ -170,6 +170,11 @@ class RefEngine(object):
         for name in ("itmref_destroy", "itmref_reset", "itmref_integrate", "itmref_create_expected_depths",
                      "itmref_create_icp_maps", "itmref_find_surface", "itmref_last_free_block", "itmref_last_free_excess"):
             getattr(L, name).argtypes = [vp]
+        if hasattr(L, "itmref_forward_render"):
+            L.itmref_forward_render.argtypes = [vp]
+            L.itmref_forward_projection.restype = vp
+            L.itmref_forward_projection.argtypes = [vp]
+            L.itmref_no_missing_points.argtypes = [vp]
         L.itmref_set_calib.argtypes = [vp, vp, vp, vp]
         L.itmref_set_view.argtypes = [vp, vp, vp, C.c_double]
         L.itmref_set_pose.argtypes = [vp, vp]
@@ -240,6 +245,12 @@ class RefEngine(object):
 
     def create_icp_maps(self):
         self.L.itmref_create_icp_maps(self.h)
+
+    def forward_render(self):
+        """ForwardRender at the current view/pose -> (forwardProjection copy, noFwdProjMissingPoints)"""
+        self.L.itmref_forward_render(self.h)
+        fwd = self._arr(self.L.itmref_forward_projection(self.h), np.float32, self.W * self.H * 4).reshape(self.H, self.W, 4).copy()
+        return fwd, int(self.L.itmref_no_missing_points(self.h))
 
     def render_free_view(self, M, intr, render_type=0):
         m = np.ascontiguousarray(M, np.float32)

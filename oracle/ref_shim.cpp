@@ -121,6 +121,11 @@ void itmref_find_surface(void *h)
     c->vis->FindSurface(c->scene, c->tracking->pose_d, &c->view->calib->intrinsics_d, c->rs);
 }
 
+// approximate raycast: ITMTrackingController::Prepare's ForwardRender branch (ITMTrackingController.cpp:40-47)
+void itmref_forward_render(void *h) { RefCtx *c = (RefCtx *)h; c->vis->ForwardRender(c->scene, c->view, c->tracking, c->rs); }
+void *itmref_forward_projection(void *h) { RefCtx *c = (RefCtx *)h; return c->rs->forwardProjection->GetData(MEMORYDEVICE_CPU); }
+int itmref_no_missing_points(void *h) { RefCtx *c = (RefCtx *)h; return c->rs->noFwdProjMissingPoints; }
+
 // free-view path: ITMMainEngine::GetImage (ITMLib/Engine/ITMMainEngine.cpp:272-277)
 void itmref_render_free_view(void *h, const float *M, const float *intr, int renderType)
 {

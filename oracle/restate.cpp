@@ -1142,7 +1142,7 @@ void rst_forward_render(const dsb200_scene *scene, const dsb200_view *view, dsb2
         V4 p = {px[0] * vs, px[1] * vs, px[2] * vs, 1.0f};      // forwardProjectPixel DA/...:202-215 (pixel.w = 1)
         p = mulM(M, p);
         float u = proj[0] * p.x / p.z + proj[2], v = proj[1] * p.y / p.z + proj[3];
-        if ((u < 0) || (u > W - 1) || (v < 0) || (v > H - 1)) continue;
+        if (!(u >= 0 && u <= W - 1 && v >= 0 && v <= H - 1)) continue;   // also skips NaN (reference: undefined index)
         int ln = (int)(u + 0.5f) + (int)(v + 0.5f) * W;
         memcpy(fwd + 4 * (size_t)ln, px, 16);
     }

@@ -117,6 +117,15 @@ class OracleBackend(object):
         self.icp_maps()
         return rc
 
+    def forward_render(self):
+        """ForwardRender at the current view/pose; returns (forwardProjection, noMissing, rendering)"""
+        fwd = np.zeros((self.cfg.H, self.cfg.W, 4), np.float32)
+        missing = np.zeros(self.cfg.H * self.cfg.W, np.int32)
+        n = C.c_int()
+        self.o.L.rst_forward_render(C.byref(self.scene.c), C.byref(self.view), C.byref(self.trk), C.byref(self.rs.c),
+                                    po.ptr(fwd), po.ptr(missing), C.byref(n))
+        return fwd, n.value, self.rs.raycast_image.copy()
+
     def free_view(self, M, intr, render_type=0):
         Mc, iM, ic = abi.f16(M), abi.f16(self.o.mat4_inverse(M)), abi.f4(intr)
         self.o.L.rst_find_visible_blocks(C.byref(self.scene.c), Mc, ic, C.byref(self.rs_free.c))
@@ -230,6 +239,11 @@ class GpuBackend(object):
 
     def process_frame(self):
         return self._rc(self.recon.ProcessFrame, self.vis, self.scene, self.view, self.trk, self.rs)
+
+    def forward_render(self):
+        self.vis.ForwardRender(self.scene, self.view, self.trk, self.rs)
+        fwd, n = self.vis.ForwardProjection(self.cfg.W, self.cfg.H)
+        return fwd, n, self.rs.raycast_image()
 
     def free_view(self, M, intr, render_type=0):
         lib = abi.load()

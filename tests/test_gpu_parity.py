@@ -95,3 +95,22 @@ def test_c2_kitti_shaped_frames():
     cfg, frames, gpu, ora = run_sequence("C2", 3, None, weights=(True, 10, 100))
     assert gpu.rs.c.no_visible > 5000
     gpu.close(); ora.close()
+
+
+def test_forward_render_approximate_raycast():
+    """ForwardRender: previous raycast re-projected into the next pose, holes raycast, shaded."""
+    for name in ("tiny", "tiny_street"):
+        cfg, frames = synth.make_sequence(name, 5)
+        gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+        for f in frames[:4]:
+            gpu.set_frame(f); ora.set_frame(f)
+            gpu.process_frame(); ora.process_frame()
+        f = frames[4]                      # new view + pose, nothing fused: ITMTrackingController::Prepare's approximate branch
+        gpu.set_frame(f); ora.set_frame(f)
+        gpu.expected_depths(); ora.expected_depths()
+        fg, ng, rg = gpu.forward_render()
+        fo, no, ro = ora.forward_render()
+        assert ng == no and 0 < no < cfg.W * cfg.H
+        hz.assert_images_equal(dict(fwd=fo, rendering=ro), dict(fwd=fg, rendering=rg), name + " forward render")
+        assert (fo[..., 3] > 0).mean() > 0.2
+        gpu.close(); ora.close()

@@ -60,3 +60,26 @@ def test_use_swapping_visibility_bit_exact():
     # app default useSwapping=true enlarges the visibility frustum
     cfg, frames, ref, ora = run_pair("tiny", 6, use_swapping=True)
     ref.close(); ora.close()
+
+
+def test_forward_render_matches_reference():
+    """ForwardRender (CPU/ITMVisualisationEngine_CPU.cpp:464-540): restatement == reference on forwardProjection,
+    the missing-point count and the shaded image."""
+    for name in ("tiny", "tiny_street"):
+        cfg, frames = synth.make_sequence(name, 4)
+        ref = po.RefEngine(cfg.W, cfg.H, cfg.params())
+        ref.set_calib(cfg.intr)
+        ora = hz.OracleBackend(cfg)
+        for f in frames[:3]:
+            ref.set_view(f.depth, f.rgb, f.timestamp); ref.set_pose(f.M)
+            ref.allocate(); ref.integrate(); ref.create_expected_depths(); ref.create_icp_maps()
+            ora.set_frame(f); ora.process_frame()
+        f = frames[3]
+        ref.set_view(f.depth, f.rgb, f.timestamp); ref.set_pose(f.M)
+        ref.create_expected_depths()
+        ora.set_frame(f); ora.expected_depths()
+        fr, nr = ref.forward_render()
+        fo, no, ro = ora.forward_render()
+        assert nr == no and no > 0
+        hz.assert_images_equal(dict(fwd=fr, rendering=ref.icp_rendering()), dict(fwd=fo, rendering=ro), name + " forward render")
+        ref.close(); ora.close()
