@@ -136,6 +136,7 @@ def load():
         "dsb200_forward_render": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState)]),
         "dsb200_forward_projection": (C.c_int, [vp, _P(vp), _P(C.c_int)]),
         "dsb200_create_point_cloud": (C.c_int, [vp]),
+        "dsb200_view_from_raw": (C.c_int, [vp, vp, C.c_float, C.c_float, _P(View), vp]),
         "dsb200_process_frame": (C.c_int, [vp, vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), C.c_int]),
         "dsb200_recon_set_shard": (C.c_int, [vp, _P(Shard)]),
         "dsb200_shard_owner": (C.c_int, [C.c_int] * 5),

@@ -724,6 +724,19 @@ int dsb200_create_point_cloud(dsb200_vis *)
     return fail(DSB200_ERR_UNSUPPORTED, "CreatePointCloud serves the colour tracker, which DenseSLAM never selects");
 }
 
+int dsb200_view_from_raw(const int16_t *raw_depth, const uint8_t *bgr, float scale, float offset, dsb200_view *view, void *stream)
+{
+    if (!raw_depth || !view || !view->depth || (bgr && !view->rgb)) return fail(DSB200_ERR_INVALID, "view_from_raw: null argument");
+    if (bgr && (view->depth_w != view->rgb_w || view->depth_h != view->rgb_h))
+        return fail(DSB200_ERR_INVALID, "view_from_raw: depth and colour images must have the same size");
+    if (((uintptr_t)raw_depth & 7) || ((uintptr_t)bgr & 3) || ((uintptr_t)view->depth & 15) || ((uintptr_t)view->rgb & 15))
+        return fail(DSB200_ERR_INVALID, "view_from_raw: buffers must be 16-byte aligned (raw depth 8, bgr 4)");
+    launch_view_from_raw((cudaStream_t)stream, raw_depth, bgr, scale, offset, const_cast<float *>(view->depth),
+                         const_cast<uint8_t *>(view->rgb), view->depth_w * view->depth_h);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
 // ---------------------------------------------------------------- fused frame
 int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *trk,
                          dsb200_render_state *rs, int stages)

@@ -106,6 +106,8 @@ void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastRe
                      uint8_t *rendering);
 void launch_composite_nearest(cudaStream_t st, int n, const float *const *resultsDev, float cx, float cy, float cz, int W,
                               int rowBegin, int rowEnd, float *out);
+void launch_view_from_raw(cudaStream_t st, const int16_t *raw, const uint8_t *bgr, float scale, float offset, float *depth,
+                          uint8_t *rgb, int n);
 void launch_shade(cudaStream_t st, const RayParams &P, int renderType, const dsb200_voxel *voxels,
                   const dsb200_hash_entry *hash, const float *raycastResult, uint8_t *outRGBA, float *outDepth);
 void launch_forward_render(cudaStream_t st, const RayParams &P, const float *proj, const dsb200_voxel *voxels,

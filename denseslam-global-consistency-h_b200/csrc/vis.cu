@@ -348,8 +348,10 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 // the next 8x4 pixel tile from a device ticket; the last warp to run dry re-arms the ticket pair for the next launch.
 // `bottomUp` hands the tiles out from the last image row upwards (the long grazing rays of a forward-looking camera sit
 // at the bottom: they start first and the short ones fill the tail).
-// (A persistent lane-refilling variant -- idle lanes of a warp take new pixels while the others keep marching -- was
-// measured 1.6x SLOWER on B200: the march is bound by the two dependent L2 round trips per step, not by idle lanes.)
+// Two variants were measured on B200 and dropped (profiles/README.md, r01d): a persistent lane-refilling march (idle lanes
+// take new pixels while the others keep marching) was 1.6x slower, and issuing the 8 interpolation loads speculatively
+// together with the nearest-voxel load (one round trip per step instead of two) was 1.14x slower.  ncu: long-scoreboard
+// stalls dominate at 21 of 40 possible resident warps per SM -- the kernel is bound by the tail of long grazing rays.
 // Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
 // root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
 template <class Tables>
@@ -653,6 +655,51 @@ __global__ void __launch_bounds__(128) k_shade(RayParams P, int type, const dsb2
         unsigned char g = (unsigned char)((0.8f * angle + 0.2f) * 255.0f);
         out[loc] = make_uchar4(g, g, g, g);
     }
+}
+
+// ---------------------------------------------------------------- view building
+// convertDepthAffineToFloat (DeviceAgnostic/ITMViewBuilder.h:22-28) + CvToItm's BGR -> RGBA (DS/InfiniTamDriver.cpp:84-104)
+// in one pass: 4 pixels per thread (one 8-byte depth load, three 4-byte colour loads, 16-byte stores).
+__global__ void __launch_bounds__(256) k_view_from_raw(const short *__restrict__ raw, const uint8_t *__restrict__ bgr, float scale,
+                                                       float offset, float *depth, uchar4 *rgb, int n)
+{
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q * 4 < n; q += gridDim.x * blockDim.x) {
+        const int i = q * 4;
+        if (i + 3 < n) {
+            const short4 d = *reinterpret_cast<const short4 *>(raw + i);
+            float4 o;
+            o.x = ((d.x <= 0) || (d.x > 32000)) ? -1.0f : (float)d.x * scale + offset;
+            o.y = ((d.y <= 0) || (d.y > 32000)) ? -1.0f : (float)d.y * scale + offset;
+            o.z = ((d.z <= 0) || (d.z > 32000)) ? -1.0f : (float)d.z * scale + offset;
+            o.w = ((d.w <= 0) || (d.w > 32000)) ? -1.0f : (float)d.w * scale + offset;
+            *reinterpret_cast<float4 *>(depth + i) = o;
+            if (bgr) {
+                const unsigned *c = reinterpret_cast<const unsigned *>(bgr + (size_t)i * 3);     // 12 bytes = 4 pixels, 4-byte aligned
+                const unsigned a = __ldg(c), b = __ldg(c + 1), e = __ldg(c + 2);
+                // bytes: a = B0 G0 R0 B1 | b = G1 R1 B2 G2 | e = R2 B3 G3 R3
+                uint4 px;
+                px.x = ((a >> 16) & 0xffu) | (a & 0xff00u) | ((a & 0xffu) << 16) | 0xff000000u;
+                px.y = ((b >> 8) & 0xffu) | ((b & 0xffu) << 8) | ((a >> 24) << 16) | 0xff000000u;
+                px.z = (e & 0xffu) | ((b >> 24) << 8) | (((b >> 16) & 0xffu) << 16) | 0xff000000u;
+                px.w = (e >> 24) | (((e >> 16) & 0xffu) << 8) | (((e >> 8) & 0xffu) << 16) | 0xff000000u;
+                *reinterpret_cast<uint4 *>(rgb + i) = px;
+            }
+        } else {
+            for (int k = i; k < n; k++) {
+                const short d = raw[k];
+                depth[k] = ((d <= 0) || (d > 32000)) ? -1.0f : (float)d * scale + offset;
+                if (bgr) rgb[k] = make_uchar4(bgr[3 * k + 2], bgr[3 * k + 1], bgr[3 * k], 255);
+            }
+        }
+    }
+}
+
+void launch_view_from_raw(cudaStream_t st, const int16_t *raw, const uint8_t *bgr, float scale, float offset, float *depth,
+                          uint8_t *rgb, int n)
+{
+    int grid = div_up(div_up(n, 4), 256);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    DSB_LAUNCH(k_view_from_raw, grid, 256, 0, st, raw, bgr, scale, offset, depth, reinterpret_cast<uchar4 *>(rgb), n);
 }
 
 // ---------------------------------------------------------------- host launchers

@@ -127,9 +127,24 @@ class ITMView(object):
         self.rgb.upload(np.asarray(rgb, np.uint8))
         self.c.timestamp = timestamp
 
+    def update_from_raw(self, depth_i16, bgr, timestamp=0.0, scale=0.001, offset=0.0, stream=None):
+        """ITMViewBuilder::UpdateView (affine calibration) + the driver's BGR -> RGBA conversion, on the device"""
+        d = np.ascontiguousarray(depth_i16, np.int16)
+        if not hasattr(self, "raw_depth"):
+            self.raw_depth, self.raw_bgr = DeviceBuffer(self.W * self.H * 2), DeviceBuffer(self.W * self.H * 3)
+        self.raw_depth.upload(d, stream)
+        if bgr is not None:
+            self.raw_bgr.upload(np.ascontiguousarray(bgr, np.uint8), stream)
+        abi.check(_lib().dsb200_view_from_raw(self.raw_depth.ptr, self.raw_bgr.ptr if bgr is not None else None, scale, offset,
+                                              C.byref(self.c), stream))
+        abi.check(_lib().dsb200_stream_synchronize(stream))
+        self.c.timestamp = timestamp
+
     def free(self):
         self.depth.free()
         self.rgb.free()
+        if hasattr(self, "raw_depth"):
+            self.raw_depth.free(); self.raw_bgr.free()
 
 
 class ITMTrackingState(object):

@@ -184,6 +184,15 @@ int dsb200_forward_render(dsb200_vis *v, const dsb200_scene *scene, const dsb200
 int dsb200_forward_projection(dsb200_vis *v, const float **forward_projection, int *no_missing_points);
 int dsb200_create_point_cloud(dsb200_vis *v);                                                                 /* CreatePointCloud :112 -> UNSUPPORTED */
 
+/* ---- view building: ITMViewBuilder::UpdateView for the TRAFO_AFFINE calibration DenseSLAM sets up
+ *      (DS/InfiniTamDriver.cpp:78-81, 280-287; convertDepthAffineToFloat, Engine/DeviceAgnostic/ITMViewBuilder.h:22-28),
+ *      fused with the driver's per-pixel BGR -> RGBA host loop (DS/InfiniTamDriver.cpp:84-104).
+ * raw_depth: int16[W*H] (millimetres for DenseSLAM), bgr: packed 8-bit B,G,R [W*H*3] or NULL (rgb left untouched); both are
+ * DEVICE staging buffers (5 bytes per pixel cross PCIe instead of 8).  Writes view->depth (float, <=0 or >32000 raw -> -1,
+ * else raw * scale + offset) and view->rgb (R,G,B,255).  Stream-ordered on cuda_stream, no host sync. ---- */
+int dsb200_view_from_raw(const int16_t *raw_depth, const uint8_t *bgr, float scale, float offset, dsb200_view *view,
+                         void *cuda_stream);
+
 /* ---- fused frame: ITMDenseMapper::ProcessFrame + ITMTrackingController::Prepare in one submission
  *      (ITMLib/Engine/ITMDenseMapper.cpp:56-81, ITMTrackingController.cpp:21-58) ---- */
 #define DSB200_FRAME_ALLOCATE 1

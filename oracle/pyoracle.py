@@ -170,6 +170,10 @@ class RefEngine(object):
         for name in ("itmref_destroy", "itmref_reset", "itmref_integrate", "itmref_create_expected_depths",
                      "itmref_create_icp_maps", "itmref_find_surface", "itmref_last_free_block", "itmref_last_free_excess"):
             getattr(L, name).argtypes = [vp]
+        if hasattr(L, "itmref_update_view_raw"):
+            L.itmref_update_view_raw.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double]
+            L.itmref_view_depth.restype = vp
+            L.itmref_view_depth.argtypes = [vp]
         if hasattr(L, "itmref_forward_render"):
             L.itmref_forward_render.argtypes = [vp]
             L.itmref_forward_projection.restype = vp
@@ -245,6 +249,13 @@ class RefEngine(object):
 
     def create_icp_maps(self):
         self.L.itmref_create_icp_maps(self.h)
+
+    def update_view_raw(self, raw_depth_i16, rgba, scale=0.001, offset=0.0, timestamp=0.0):
+        """ITMViewBuilder_CPU::UpdateView (TRAFO_AFFINE) -> copy of view->depth"""
+        d = np.ascontiguousarray(raw_depth_i16, np.int16)
+        r = np.ascontiguousarray(rgba, np.uint8)
+        self.L.itmref_update_view_raw(self.h, ptr(d), ptr(r), scale, offset, timestamp)
+        return self._arr(self.L.itmref_view_depth(self.h), np.float32, self.W * self.H).reshape(self.H, self.W).copy()
 
     def forward_render(self):
         """ForwardRender at the current view/pose -> (forwardProjection copy, noFwdProjMissingPoints)"""

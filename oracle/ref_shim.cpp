@@ -14,6 +14,7 @@
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.h"
 #include "ITMLib/Objects/ITMRenderState_VH.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMViewBuilder_CPU.h"
 
 #include <cstring>
 #include <cstdint>
@@ -92,6 +93,27 @@ void itmref_set_view(void *h, const float *depth, const uint8_t *rgba, double ti
     memcpy(c->view->rgb->GetData(MEMORYDEVICE_CPU), rgba, n * 4);
     c->view->mTimeStamp = timestamp;
 }
+
+// ITMViewBuilder_CPU::UpdateView with the affine depth calibration DenseSLAM configures (DS/InfiniTamDriver.cpp:78-81,286):
+// raw int16 depth + RGBA in, view->depth (float) out
+void itmref_update_view_raw(void *h, const short *rawDepth, const uint8_t *rgba, float scale, float offset, double timestamp)
+{
+    RefCtx *c = (RefCtx *)h;
+    c->calib.disparityCalib.SetFrom(scale, offset, ITMDisparityCalib::TRAFO_AFFINE);
+    ITMViewBuilder_CPU vb(&c->calib);
+    ITMUChar4Image rgb(c->imgSize, true, false);
+    ITMShortImage raw(c->imgSize, true, false);
+    size_t n = (size_t)c->imgSize.x * c->imgSize.y;
+    memcpy(rgb.GetData(MEMORYDEVICE_CPU), rgba, n * 4);
+    memcpy(raw.GetData(MEMORYDEVICE_CPU), rawDepth, n * sizeof(short));
+    ITMView *built = NULL;        // a fresh view makes the builder allocate its own staging images (UpdateView :12-27)
+    vb.UpdateView(&built, &rgb, &raw, timestamp, false);
+    memcpy(c->view->depth->GetData(MEMORYDEVICE_CPU), built->depth->GetData(MEMORYDEVICE_CPU), n * sizeof(float));
+    memcpy(c->view->rgb->GetData(MEMORYDEVICE_CPU), built->rgb->GetData(MEMORYDEVICE_CPU), n * 4);
+    c->view->mTimeStamp = timestamp;
+    delete built;
+}
+const float *itmref_view_depth(void *h) { return ((RefCtx *)h)->view->depth->GetData(MEMORYDEVICE_CPU); }
 
 void itmref_set_pose(void *h, const float *M) { ((RefCtx *)h)->tracking->pose_d->SetM(toM(M)); }
 void itmref_get_pose(void *h, float *M, float *invM)

@@ -393,3 +393,16 @@ def allocated_blocks(hash_table):
     """set of (x, y, z) of the live entries of a hash table download"""
     live = hash_table[hash_table["ptr"] >= 0]
     return set(map(tuple, live["pos"].tolist()))
+
+
+# ---------------------------------------------------------------- view building (SURVEY 8f rank 1)
+def view_from_raw_restated(depth_i16, bgr, scale=0.001, offset=0.0):
+    """numpy restatement of convertDepthAffineToFloat (Engine/DeviceAgnostic/ITMViewBuilder.h:22-28) and of the driver's
+    BGR -> RGBA loop (DS/InfiniTamDriver.cpp:84-104); float32 multiply then add, as the reference evaluates it"""
+    d = np.asarray(depth_i16, np.int16)
+    depth = np.where((d <= 0) | (d > 32000), np.float32(-1.0), d.astype(np.float32) * np.float32(scale) + np.float32(offset)).astype(np.float32)
+    rgba = None
+    if bgr is not None:
+        b = np.asarray(bgr, np.uint8)
+        rgba = np.concatenate([b[..., ::-1], np.full(b.shape[:-1] + (1,), 255, np.uint8)], axis=-1)
+    return depth, rgba

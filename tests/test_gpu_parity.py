@@ -114,3 +114,30 @@ def test_forward_render_approximate_raycast():
         hz.assert_images_equal(dict(fwd=fo, rendering=ro), dict(fwd=fg, rendering=rg), name + " forward render")
         assert (fo[..., 3] > 0).mean() > 0.2
         gpu.close(); ora.close()
+
+
+def test_view_from_raw_and_fusion_from_it():
+    """dsb200_view_from_raw: int16 depth + packed BGR on the device -> float depth + RGBA, bit-exact vs the restatement
+    (itself pinned to ITMViewBuilder_CPU), odd sizes included; fusing from the built view equals fusing from the floats."""
+    import importlib
+    eng = importlib.import_module(hz.PKG + ".engine")
+    rng = np.random.default_rng(9)
+    for W, H in ((160, 120), (313, 97), (5, 3)):
+        raw = rng.integers(-300, 33000, size=(H, W)).astype(np.int16)
+        bgr = rng.integers(0, 256, size=(H, W, 3)).astype(np.uint8)
+        v = eng.ITMView(W, H, (100.0, 100.0, W / 2.0, H / 2.0))
+        v.update_from_raw(raw, bgr, 0.5, scale=np.float32(1.0 / 1000.0))
+        want_d, want_c = hz.view_from_raw_restated(raw, bgr, np.float32(1.0 / 1000.0))
+        assert np.array_equal(hz.bits(v.depth.download(np.float32, W * H).reshape(H, W)), hz.bits(want_d))
+        assert np.array_equal(v.rgb.download(np.uint8, W * H * 4).reshape(H, W, 4), want_c)
+        v.free()
+    cfg, frames = synth.make_sequence("tiny", 3)
+    gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    for f in frames:
+        ora.set_frame(f); ora.process_frame()
+        gpu.view.update_from_raw(f.depth_mm, f.rgb[..., 2::-1], f.timestamp, scale=np.float32(1.0 / 1000.0))
+        gpu.trk.set_pose(f.M)
+        gpu.process_frame()
+    hz.assert_state_equal(ora.state(), gpu.state(), "fusion from raw view")
+    hz.assert_images_equal(ora.images(), gpu.images(), "fusion from raw view")
+    gpu.close(); ora.close()

@@ -83,3 +83,22 @@ def test_forward_render_matches_reference():
         assert nr == no and no > 0
         hz.assert_images_equal(dict(fwd=fr, rendering=ref.icp_rendering()), dict(fwd=fo, rendering=ro), name + " forward render")
         ref.close(); ora.close()
+
+
+def test_view_building_matches_reference():
+    """ITMViewBuilder_CPU::UpdateView (TRAFO_AFFINE, the calibration DenseSLAM sets): restatement == reference, and the synthetic
+    generator's float depth is exactly what the reference would have produced from its int16 millimetres."""
+    rng = np.random.default_rng(3)
+    for name in ("tiny", "tiny_street"):
+        cfg, frames = synth.make_sequence(name, 2)
+        ref = po.RefEngine(cfg.W, cfg.H, cfg.params())
+        ref.set_calib(cfg.intr)
+        for f in frames:
+            raw = f.depth_mm.copy()
+            raw.reshape(-1)[rng.integers(0, raw.size, 50)] = rng.integers(-32768, 32767, 50).astype(np.int16)   # negatives, > 32000
+            got = ref.update_view_raw(raw, f.rgb, np.float32(1.0 / 1000.0), 0.0, f.timestamp)
+            want, _ = hz.view_from_raw_restated(raw, None, np.float32(1.0 / 1000.0), 0.0)
+            assert np.array_equal(hz.bits(got), hz.bits(want))
+            same = raw == f.depth_mm
+            assert np.array_equal(hz.bits(got[same]), hz.bits(f.depth[same]))
+        ref.close()
