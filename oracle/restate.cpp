@@ -607,6 +607,10 @@ inline float sdfTrilinear(const dsb200_scene *s, V3 p, bool &found, BlockCache &
     return sdfToFloat((1.0f - cz) * res1 + cz * res2);
 }
 
+// analysis hook (profiles/): when set, castRay adds its loop-trip count per pixel here
+static int *g_rayStepCounts = nullptr; static int g_rayStepWidth = 0;
+extern "C" void rst_debug_ray_steps(int *counts, int width) { g_rayStepCounts = counts; g_rayStepWidth = width; }
+
 // castRay, DA/ITMVisualisationEngine.h:124-196
 inline bool castRay(float *out, int x, int y, const dsb200_scene *s, const float *invM, const float *invProj,
                     float oneOverVoxel, float mu, float zmin, float zmax)
@@ -634,6 +638,7 @@ inline bool castRay(float *out, int x, int y, const dsb200_scene *s, const float
     pr = ps;
     BlockCache cache;
     while (totalLength < totalLengthMax) {
+        if (g_rayStepCounts) g_rayStepCounts[x + y * g_rayStepWidth]++;
         sdf = sdfNearest(s, pr, hashFound, cache);
         if (!hashFound) stepLength = DSB200_BLOCK_SIZE;
         else {
