@@ -124,6 +124,8 @@ def load():
         "dsb200_slide_window_defusion": (C.c_int, [vp, _P(Scene), _P(RenderState), C.c_int, C.c_int]),
         "dsb200_decayed_block_count": (C.c_size_t, [vp]),
         "dsb200_set_fusion_weight_params": (C.c_int, [vp, _P(WeightParams)]),
+        "dsb200_recon_set_sdf_shadow": (C.c_int, [vp, C.c_int]),
+        "dsb200_recon_invalidate_sdf_shadow": (C.c_int, [vp]),
         "dsb200_history_sizes": (C.c_int, [vp] + [_P(C.c_int)] * 5),
         "dsb200_vis_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
         "dsb200_vis_destroy": (C.c_int, [vp]),

@@ -112,6 +112,9 @@ struct dsb200_recon {
     int lastKnownVisible = 0;         // visible count at the last host sync: sizes the snapshot reservations made while asynchronous
     const uint8_t *visBitsOwner = nullptr;   // the render state's visibility-flag array that fs.visBits currently describes
     cudaStream_t sideStream = nullptr; cudaEvent_t evFork = nullptr, evJoin = nullptr;   // fused frame: expected depths || integration
+    // SDF shadow: one short per voxel of the scene this engine maintains, kept in step by every kernel that writes voxels
+    // (reset, integrate, de-integrate, pruning) and read by the fused frame's raycast instead of the 8-byte voxel records.
+    short *sdfShadow = nullptr; const void *shadowFor = nullptr; bool shadowEnabled = true;
     dsb200_shard shard{0, 1, 2, 0};      // sharded scene: this engine's block ownership (count <= 1: everything)
     bool forceSlowDiv = false;        // debug: run the plain-division kernel variants (dsb200_debug_force_plain_division)
     // history (CUDA/ITMSceneReconstructionEngine_CUDA.h:41-48)
@@ -183,6 +186,8 @@ int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_n
     CU(cudaStreamCreateWithFlags(&e->sideStream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&e->evJoin, cudaEventDisableTiming));
+    // 2 bytes per voxel = +25 % of the voxel array; if it does not fit the engine simply runs without it
+    if (cudaMalloc(&e->sdfShadow, (size_t)num_blocks * DSB200_BLOCK_SIZE3 * sizeof(short)) != cudaSuccess) { cudaGetLastError(); e->sdfShadow = nullptr; }
     e->pruneCap = num_blocks;
     CU(cudaMalloc(&e->pruneScratch, (size_t)3 * e->pruneCap * 4));
     *out = e;
@@ -199,7 +204,7 @@ int dsb200_recon_destroy(dsb200_recon *e)
     e->arena.release_all();
     cudaFree(e->reqKey); cudaFree(e->slotMark); cudaFree(e->pruneScratch); cudaFree(e->fs.counters);
     cudaFree(e->fs.scanState); cudaFree(e->fs.tickets); cudaFreeHost(e->hostCounters);
-    cudaFree(e->fs.reqBits); cudaFree(e->fs.visBits);
+    cudaFree(e->fs.reqBits); cudaFree(e->fs.visBits); cudaFree(e->sdfShadow);
     delete e;
     return DSB200_OK;
 }
@@ -319,6 +324,18 @@ static void make_fuse_params(FuseParams &P, const dsb200_recon *e, const dsb200_
     P.fastDiv = (ok && !e->forceSlowDiv) ? 1 : 0;
 }
 
+// the shadow to hand to a kernel that writes / reads this scene's voxels (nullptr when disabled); brought up to date first if
+// the engine last maintained it for another scene (one engine serves all sub-maps in the reference, ITMMapGraphManager.h:60)
+static short *shadow_for(dsb200_recon *e, const dsb200_scene *scene)
+{
+    if (!e->sdfShadow || !e->shadowEnabled) return nullptr;
+    if (e->shadowFor != scene->voxels) {
+        launch_rebuild_shadow(e->stream, scene->voxels, (size_t)scene->num_blocks * DSB200_BLOCK_SIZE3, e->sdfShadow);
+        e->shadowFor = scene->voxels;
+    }
+    return e->sdfShadow;
+}
+
 static int check_scene(const dsb200_recon *e, const dsb200_scene *scene)
 {
     if (!e || !scene || !scene->voxels || !scene->hash || !scene->alloc_list || !scene->excess_list)
@@ -413,7 +430,8 @@ int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
     e->decayQ.clear(); e->slideQ.clear(); e->snapshots.clear();   // CUDA .cu:116-131
     launch_reset_scene(e->stream, scene->voxels, (size_t)scene->num_blocks * DSB200_BLOCK_SIZE3, scene->hash, e->total,
                        scene->alloc_list, scene->num_blocks, scene->excess_list, scene->excess_size, nullptr, e->reqKey,
-                       e->fs.counters);
+                       e->fs.counters, (e->sdfShadow && e->shadowEnabled) ? e->sdfShadow : nullptr);
+    if (e->sdfShadow && e->shadowEnabled) e->shadowFor = scene->voxels;
     CU(cudaMemsetAsync(e->fs.reqBits, 0, (size_t)e->fs.bitTiles * 8192, e->stream));   // the keys were cleared: so are their bits
     CU(cudaGetLastError());
     scene->last_free_block = scene->num_blocks - 1;
@@ -442,7 +460,7 @@ int dsb200_integrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *vi
         e->hostCounters->noVisible = rs->no_visible;
         CU(cudaMemcpyAsync(&e->fs.counters->noVisible, &e->hostCounters->noVisible, 4, cudaMemcpyHostToDevice, e->stream));
     }
-    launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb);
+    launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene));
     CU(cudaGetLastError());
     if (!e->async) CU(cudaStreamSynchronize(e->stream));
     return DSB200_OK;
@@ -455,7 +473,8 @@ int dsb200_deintegrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *
     if (it == e->snapshots.end()) return DSB200_OK;            // silent no-op, CUDA .cu:437-440
     if (it->second->countHost == 0) return DSB200_OK;
     FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
-    launch_fuse(e->stream, FP, true, scene->voxels, scene->hash, it->second->ids, it->second->countDev, view->depth, view->rgb);
+    launch_fuse(e->stream, FP, true, scene->voxels, scene->hash, it->second->ids, it->second->countDev, view->depth, view->rgb,
+                shadow_for(e, scene));
     CU(cudaGetLastError());
     if (!e->async) CU(cudaStreamSynchronize(e->stream));
     return DSB200_OK;
@@ -480,7 +499,7 @@ static int prune_from_queue(dsb200_recon *e, dsb200_scene *scene, dsb200_render_
             launch_prune(e->stream, slide, scene->voxels, scene->hash, scene->bucket_num, snap->ids, snap->countDev, e->pruneCap,
                          minAge, maxWeight, (int)e->frameIdx, scene->alloc_list, rs->visible_type,
                          rs->visible_type == e->visBitsOwner ? e->fs.visBits : nullptr, e->slotMark, e->pruneScratch,
-                         e->fs.counters, e->fs);
+                         e->fs.counters, e->fs, shadow_for(e, scene));
         }
     }
     return finish_call(e, scene, rs, false);
@@ -768,7 +787,7 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     }
     if (stages & DSB200_FRAME_INTEGRATE) {
         FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
-        launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb);
+        launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene));
     }
     DSB_MARK(2);
     if (fork) CU(cudaStreamWaitEvent(e->stream, e->evJoin, 0));
@@ -780,16 +799,30 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     if (stages & DSB200_FRAME_ICP_MAPS) {
         if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "process_frame: tracking state has no point cloud buffers");
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene));
         DSB_MARK(4);
         launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
     } else if (stages & DSB200_FRAME_RAYCAST) {
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene));
         DSB_MARK(4);
     } else DSB_MARK(4);
     DSB_MARK(5);
     return finish_call(e, scene, rs, (stages & DSB200_FRAME_ALLOCATE) != 0);
+}
+
+int dsb200_recon_set_sdf_shadow(dsb200_recon *e, int on)
+{
+    if (!e) return fail(DSB200_ERR_INVALID, "set_sdf_shadow: null engine");
+    e->shadowEnabled = on != 0;
+    e->shadowFor = nullptr;       // re-derived from the voxels at the next use
+    return DSB200_OK;
+}
+int dsb200_recon_invalidate_sdf_shadow(dsb200_recon *e)
+{
+    if (!e) return fail(DSB200_ERR_INVALID, "invalidate_sdf_shadow: null engine");
+    e->shadowFor = nullptr;
+    return DSB200_OK;
 }
 
 int dsb200_debug_force_plain_division(dsb200_recon *e, int on) { e->forceSlowDiv = on != 0; return DSB200_OK; }

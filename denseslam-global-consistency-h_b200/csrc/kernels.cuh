@@ -77,10 +77,11 @@ void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &
 // recon_integrate.cu
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,
                  const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth,
-                 const uint8_t *rgb);
+                 const uint8_t *rgb, short *sdfShadowOrNull);
 void launch_reset_scene(cudaStream_t st, dsb200_voxel *voxels, size_t numVoxels, dsb200_hash_entry *hash, int total,
                         int *allocList, int numBlocks, int *excessList, int excessSize, uint8_t *visTypeOrNull,
-                        unsigned *reqKey, Counters *counters);
+                        unsigned *reqKey, Counters *counters, short *sdfShadowOrNull);
+void launch_rebuild_shadow(cudaStream_t st, const dsb200_voxel *voxels, size_t numVoxels, short *sdfShadow);
 
 void launch_selftest_division(cudaStream_t st, unsigned long long n, unsigned long long seed, unsigned long long *mismatches);
 
@@ -88,7 +89,7 @@ void launch_selftest_division(cudaStream_t st, unsigned long long n, unsigned lo
 void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash_entry *hash, int bucketNum,
                   const int *ids, const int *count, int countUpperBound, int minAge, int maxWeight, int currentFrame,
                   int *allocList, uint8_t *visType, unsigned *visBitsOrNull, unsigned *slotMark, int *pendingList,
-                  Counters *counters, const FrameState &fs);
+                  Counters *counters, const FrameState &fs, short *sdfShadowOrNull);
 
 // vis.cu
 void launch_find_visible(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
@@ -98,7 +99,8 @@ void launch_count_visible(cudaStream_t st, const dsb200_hash_entry *hash, const 
 void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_hash_entry *hash, const int *ids,
                             const int *count, float *rangeImage, int *blockTileCounts, Counters *counters);
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
-                    const float *rangeImage, float *raycastResult, int *ticketPair /* two zeroed ints, re-armed by the kernel */);
+                    const float *rangeImage, float *raycastResult, int *ticketPair /* two zeroed ints, re-armed by the kernel */,
+                    const short *sdfShadowOrNull = nullptr);
 void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank, int brickLog2,
                             const dsb200_hash_entry *const *hash, const dsb200_voxel *const *voxels,
                             const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair);

@@ -159,7 +159,7 @@ template <bool DE, bool FAST>
 __global__ void __launch_bounds__(256) k_fuse(FuseParams P, dsb200_voxel *voxels,
                                               const dsb200_hash_entry *__restrict__ hash,
                                               const int *__restrict__ ids, const int *__restrict__ countPtr,
-                                              const float *__restrict__ depth, const uchar4 *__restrict__ rgb)
+                                              const float *__restrict__ depth, const uchar4 *__restrict__ rgb, unsigned *shadow2)
 {
     __shared__ FuseTables T;
     __shared__ uint4 sVox[256];
@@ -254,7 +254,8 @@ template <bool DE, bool FAST, int MINB>
 __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp(FuseParams P, dsb200_voxel *voxels,
                                                                    const dsb200_hash_entry *__restrict__ hash,
                                                                    const int *__restrict__ ids, const int *__restrict__ countPtr,
-                                                                   const float *__restrict__ depth, const uchar4 *__restrict__ rgb)
+                                                                   const float *__restrict__ depth, const uchar4 *__restrict__ rgb,
+                                                                   unsigned *shadow2)
 {
     __shared__ FuseWarpSmem S;
     const int n = *countPtr;
@@ -309,7 +310,11 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp(FuseParams 
                 }
                 uint4 out = raw;
                 pack(v0, out.x, out.y); pack(v1, out.z, out.w);
-                if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) dirty |= 1u << z;
+                if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) {
+                    dirty |= 1u << z;
+                    // sdf shadow (read by the raycast): the colour part never touches the sdf, so it is final here
+                    if (shadow2) shadow2[(size_t)e.ptr * 256 + z * 32 + lane] = (out.x & 0xffffu) | (out.z << 16);
+                }
                 sVox[z * 32 + lane] = out;
                 const unsigned m0 = __ballot_sync(0xffffffffu, c0), m1 = __ballot_sync(0xffffffffu, c1);
                 if (c0) sQueue[qn + __popc(m0 & lt)] = (unsigned short)(z * 64 + 2 * lane);
@@ -351,28 +356,30 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp(FuseParams 
 }
 
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,
-                 const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth, const uint8_t *rgb)
+                 const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth, const uint8_t *rgb,
+                 short *sdfShadow)
 {
+    unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
     static const int variant = getenv("DSB200_FUSE_KERNEL") ? atoi(getenv("DSB200_FUSE_KERNEL")) : 1;   // 0: CTA per block, 1: warp per block
     if (variant == 1) {
         const int g = kNumSMs * 8;
         if (deintegrate) {
-            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<true, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
-            else DSB_LAUNCH((k_fuse_warp<true, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<true, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
+            else DSB_LAUNCH((k_fuse_warp<true, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
         } else {
-            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<false, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
-            else DSB_LAUNCH((k_fuse_warp<false, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+            if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<false, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
+            else DSB_LAUNCH((k_fuse_warp<false, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
         }
         return;
     }
     const int grid = kNumSMs * 8;
     if (deintegrate) {
-        if (P.fastDiv) DSB_LAUNCH((k_fuse<true, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
-        else DSB_LAUNCH((k_fuse<true, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+        if (P.fastDiv) DSB_LAUNCH((k_fuse<true, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
+        else DSB_LAUNCH((k_fuse<true, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
     } else {
-        if (P.fastDiv) DSB_LAUNCH((k_fuse<false, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
-        else DSB_LAUNCH((k_fuse<false, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4);
+        if (P.fastDiv) DSB_LAUNCH((k_fuse<false, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
+        else DSB_LAUNCH((k_fuse<false, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
     }
 }
 
@@ -440,11 +447,12 @@ void launch_selftest_division(cudaStream_t st, unsigned long long n, unsigned lo
 // ResetScene (CPU .cpp:25-45; CUDA .cu:111-148): pure store bandwidth, 16-byte stores.
 __global__ void __launch_bounds__(256) k_reset_scene(uint4 *voxels2, size_t numVoxelPairs, int *hashWords, int total,
                                                      int *allocList, int numBlocks, int *excessList, int excessSize,
-                                                     uint8_t *visType, unsigned *reqKey, Counters *counters)
+                                                     uint8_t *visType, unsigned *reqKey, Counters *counters, uint4 *shadow8)
 {
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
     const uint4 blank = make_uint4(0x00007fffu, 0u, 0x00007fffu, 0u);   // {sdf 32767, w 0, clr 0, wc 0} x2
     for (size_t i = tid; i < numVoxelPairs; i += stride) voxels2[i] = blank;
+    if (shadow8) for (size_t i = tid; i < numVoxelPairs / 4; i += stride) shadow8[i] = make_uint4(0x7fff7fffu, 0x7fff7fffu, 0x7fff7fffu, 0x7fff7fffu);
     for (size_t i = tid; i < (size_t)total; i += stride) {
         int *p = hashWords + i * 5;
         p[0] = 0; p[1] = 0; p[2] = 0; p[3] = -2; p[4] = 0;
@@ -462,11 +470,25 @@ __global__ void __launch_bounds__(256) k_reset_scene(uint4 *voxels2, size_t numV
 
 void launch_reset_scene(cudaStream_t st, dsb200_voxel *voxels, size_t numVoxels, dsb200_hash_entry *hash, int total,
                         int *allocList, int numBlocks, int *excessList, int excessSize, uint8_t *visTypeOrNull,
-                        unsigned *reqKey, Counters *counters)
+                        unsigned *reqKey, Counters *counters, short *sdfShadow)
 {
     DSB_LAUNCH(k_reset_scene, kNumSMs * 16, 256, 0, st, reinterpret_cast<uint4 *>(voxels), numVoxels / 2,
                reinterpret_cast<int *>(hash), total, allocList, numBlocks, excessList, excessSize, visTypeOrNull, reqKey,
-               counters);
+               counters, reinterpret_cast<uint4 *>(sdfShadow));
+}
+
+// sdf shadow <- voxel array (a scene this engine has not been maintaining the shadow for)
+__global__ void __launch_bounds__(256) k_rebuild_shadow(const uint4 *__restrict__ voxels2, size_t numVoxelPairs, unsigned *shadow2)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < numVoxelPairs; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = voxels2[i];
+        shadow2[i] = (v.x & 0xffffu) | (v.z << 16);
+    }
+}
+void launch_rebuild_shadow(cudaStream_t st, const dsb200_voxel *voxels, size_t numVoxels, short *sdfShadow)
+{
+    DSB_LAUNCH(k_rebuild_shadow, kNumSMs * 16, 256, 0, st, reinterpret_cast<const uint4 *>(voxels), numVoxels / 2,
+               reinterpret_cast<unsigned *>(sdfShadow));
 }
 
 } // namespace dsb

@@ -40,7 +40,7 @@ template <bool SLIDE>
 __global__ void __launch_bounds__(256) k_prune_voxels(dsb200_voxel *voxels, const dsb200_hash_entry *hash, int bucketNum,
                                                       const int *__restrict__ ids, const int *__restrict__ countPtr,
                                                       int minAge, int maxWeight, int currentFrame, int *flags,
-                                                      FrameState fs, int pruneTiles)
+                                                      FrameState fs, int pruneTiles, unsigned *shadow2)
 {
     const int n = *countPtr;
     const int t = threadIdx.x;
@@ -74,14 +74,20 @@ __global__ void __launch_bounds__(256) k_prune_voxels(dsb200_voxel *voxels, cons
                 // deleteVoxel: every voxel is reset (pad byte preserved); the block always empties
                 uint4 raw = *p;
                 uint4 out = make_uint4(blankLo, raw.y & 0xff000000u, blankLo, raw.w & 0xff000000u);
-                if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) *p = out;
+                if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) {
+                    *p = out;
+                    if (shadow2) shadow2[(size_t)ptr * 256 + t] = 0x7fff7fffu;
+                }
                 allEmpty = 1;
             } else {
                 uint4 raw = *p, out = raw;
                 unsigned w0 = (raw.x >> 16) & 0xff, w1 = (raw.z >> 16) & 0xff;
                 if (w0 > 0 && (int)w0 <= maxWeight) { out.x = blankLo; out.y = raw.y & 0xff000000u; w0 = 0; }
                 if (w1 > 0 && (int)w1 <= maxWeight) { out.z = blankLo; out.w = raw.w & 0xff000000u; w1 = 0; }
-                if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) *p = out;
+                if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) {
+                    *p = out;
+                    if (shadow2) shadow2[(size_t)ptr * 256 + t] = (out.x & 0xffffu) | (out.z << 16);
+                }
                 allEmpty = (w0 == 0 && w1 == 0);
             }
         }
@@ -203,8 +209,9 @@ __global__ void k_prune_cleanup(const int *compactSlot, unsigned *slotMark, Fram
 void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash_entry *hash, int bucketNum,
                   const int *ids, const int *count, int countUpperBound, int minAge, int maxWeight, int currentFrame,
                   int *allocList, uint8_t *visType, unsigned *visBits, unsigned *slotMark, int *scratch, Counters *counters,
-                  const FrameState &fs)
+                  const FrameState &fs, short *sdfShadow)
 {
+    unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     (void)counters;
     const int cap = countUpperBound;
     int *flags = scratch, *compactSlot = scratch + cap, *compactBucket = scratch + 2 * cap;
@@ -213,10 +220,10 @@ void launch_prune(cudaStream_t st, bool slide, dsb200_voxel *voxels, dsb200_hash
     const int grid = kNumSMs * 8;
     if (slide)
         DSB_LAUNCH(k_prune_voxels<true>, grid, 256, 0, st, voxels, hash, bucketNum, ids, count, minAge, maxWeight,
-                   currentFrame, flags, fs, pruneTiles);
+                   currentFrame, flags, fs, pruneTiles, shadow2);
     else
         DSB_LAUNCH(k_prune_voxels<false>, grid, 256, 0, st, voxels, hash, bucketNum, ids, count, minAge, maxWeight,
-                   currentFrame, flags, fs, pruneTiles);
+                   currentFrame, flags, fs, pruneTiles, shadow2);
     int rankGrid = pruneTiles < kNumSMs * 4 ? pruneTiles : kNumSMs * 4;
     if (rankGrid < 1) rankGrid = 1;
     DSB_LAUNCH(k_prune_rank, rankGrid, 256, 0, st, hash, bucketNum, ids, count, flags, compactSlot, compactBucket,

@@ -222,23 +222,35 @@ __global__ void __launch_bounds__(1024) k_range_cap_fallback(ProjParams P, const
 }
 
 // ---------------------------------------------------------------- raycast
-struct BlockCache { int bx, by, bz; const dsb200_voxel *blk; };
+struct BlockCache { int bx, by, bz; const short *blk; };     // blk: first sdf of the block (element stride Tables::kStride shorts)
 
 // Where a block's hash table and voxel array live.  One scene: the two pointers.  Sharded scene (dsb200_raycast_sharded):
 // the tables of the shard that OWNS the block, which may be peer-GPU memory mapped with CUDA IPC -- the probe and the
 // voxel read then travel over NVLink, and the march is the single-scene march probe for probe.
-struct SceneTables {
-    const dsb200_voxel *voxels; const dsb200_hash_entry *hash;
-    __device__ __forceinline__ void resolve(int, int, int, const dsb200_hash_entry *&h, const dsb200_voxel *&v) const { h = hash; v = voxels; }
+// The sdf samples come either from the voxel array itself (8-byte ITMVoxel records: stride 4 shorts) or from the
+// reconstruction engine's SDF SHADOW (one short per voxel, stride 1; capi.cu): a quarter of the bytes, so the visible set
+// (36 MB at the bench workload instead of 143 MB) stays L2-resident between integration and raycast.
+template <int STRIDE>
+struct SceneTablesT {
+    static constexpr int kStride = STRIDE;
+    const short *sdf; const dsb200_hash_entry *hash;
+    __device__ __forceinline__ void resolve(int, int, int, const dsb200_hash_entry *&h, const short *&v) const { h = hash; v = sdf; }
 };
+typedef SceneTablesT<4> SceneTables;      // straight from the voxel array
+typedef SceneTablesT<1> ShadowTables;     // from the sdf shadow
+__device__ __host__ __forceinline__ SceneTables scene_tables(const dsb200_voxel *voxels, const dsb200_hash_entry *hash)
+{
+    SceneTables T; T.sdf = reinterpret_cast<const short *>(voxels); T.hash = hash; return T;
+}
 struct ShardTables {
+    static constexpr int kStride = 4;
     int n, brickLog2;
     const dsb200_hash_entry *hash[kMaxShards];
     const dsb200_voxel *voxels[kMaxShards];
-    __device__ __forceinline__ void resolve(int bx, int by, int bz, const dsb200_hash_entry *&h, const dsb200_voxel *&v) const
+    __device__ __forceinline__ void resolve(int bx, int by, int bz, const dsb200_hash_entry *&h, const short *&v) const
     {
         const int o = shard_owner(bx, by, bz, n, brickLog2);
-        h = hash[o]; v = voxels[o];
+        h = hash[o]; v = reinterpret_cast<const short *>(voxels[o]);
     }
 };
 
@@ -250,15 +262,15 @@ __device__ __forceinline__ short read_sdf(const Tables &T, int bucketNum, int bu
     // floor division by 8 (arithmetic shift == the reference's ((p<0)?p-7:p)/8)
     const int bx = px >> 3, by = py >> 3, bz = pz >> 3;
     const int lin = (px & 7) + ((py & 7) << 3) + ((pz & 7) << 6);
-    if (bx == c.bx && by == c.by && bz == c.bz) { found = true; return __ldg(reinterpret_cast<const short *>(c.blk + lin)); }
-    const dsb200_hash_entry *hash; const dsb200_voxel *voxels;
+    if (bx == c.bx && by == c.by && bz == c.bz) { found = true; return __ldg(c.blk + lin * Tables::kStride); }
+    const dsb200_hash_entry *hash; const short *voxels;
     T.resolve(bx, by, bz, hash, voxels);
     int h = hash_index(bx, by, bz, bucketMask);
     while (true) {
         HashEntry e = load_entry(hash, h);
         if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= 0) {
-            found = true; c.bx = bx; c.by = by; c.bz = bz; c.blk = voxels + (size_t)e.ptr * kBlock3;
-            return __ldg(reinterpret_cast<const short *>(c.blk + lin));
+            found = true; c.bx = bx; c.by = by; c.bz = bz; c.blk = voxels + (size_t)e.ptr * (kBlock3 * Tables::kStride);
+            return __ldg(c.blk + lin * Tables::kStride);
         }
         if (e.offset < 1) break;
         h = bucketNum + e.offset - 1;
@@ -271,14 +283,14 @@ __device__ __forceinline__ float round_half_away(float x) { return (x < 0) ? (x 
 
 // findVoxel's block part: hash probe -> first voxel of the block, or nullptr (ITMRepresentationAccess.h:176-210)
 template <class Tables>
-__device__ __forceinline__ const dsb200_voxel *resolve_block(const Tables &T, int bucketNum, int bucketMask, int bx, int by, int bz)
+__device__ __forceinline__ const short *resolve_block(const Tables &T, int bucketNum, int bucketMask, int bx, int by, int bz)
 {
-    const dsb200_hash_entry *hash; const dsb200_voxel *voxels;
+    const dsb200_hash_entry *hash; const short *voxels;
     T.resolve(bx, by, bz, hash, voxels);
     int h = hash_index(bx, by, bz, bucketMask);
     while (true) {
         HashEntry e = load_entry(hash, h);
-        if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= 0) return voxels + (size_t)e.ptr * kBlock3;
+        if (e.px == bx && e.py == by && e.pz == bz && e.ptr >= 0) return voxels + (size_t)e.ptr * (kBlock3 * Tables::kStride);
         if (e.offset < 1) return nullptr;
         h = bucketNum + e.offset - 1;
     }
@@ -300,22 +312,22 @@ __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, i
     const int bx = ix >> 3, by = iy >> 3, bz = iz >> 3;
     const int lx = ix & 7, ly = iy & 7, lz = iz & 7;
     const bool ex = lx == 7, ey = ly == 7, ez = lz == 7;        // the +1 corner leaves the block along this axis
-    const dsb200_voxel *p000;
+    const short *p000;
     if (bx == cache.bx && by == cache.by && bz == cache.bz) p000 = cache.blk;
     else {
         p000 = resolve_block(T, bucketNum, bucketMask, bx, by, bz);
         if (p000) { cache.bx = bx; cache.by = by; cache.bz = bz; cache.blk = p000; }
     }
-    const dsb200_voxel *p100 = ex ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz) : p000;
-    const dsb200_voxel *p010 = ey ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz) : p000;
-    const dsb200_voxel *p001 = ez ? resolve_block(T, bucketNum, bucketMask, bx, by, bz + 1) : p000;
-    const dsb200_voxel *p110 = (ex && ey) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by + 1, bz) : (ex ? p100 : p010);
-    const dsb200_voxel *p101 = (ex && ez) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz + 1) : (ex ? p100 : p001);
-    const dsb200_voxel *p011 = (ey && ez) ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz + 1) : (ey ? p010 : p001);
-    const dsb200_voxel *p111 = (ex && ey && ez) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by + 1, bz + 1)
+    const short *p100 = ex ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz) : p000;
+    const short *p010 = ey ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz) : p000;
+    const short *p001 = ez ? resolve_block(T, bucketNum, bucketMask, bx, by, bz + 1) : p000;
+    const short *p110 = (ex && ey) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by + 1, bz) : (ex ? p100 : p010);
+    const short *p101 = (ex && ez) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz + 1) : (ex ? p100 : p001);
+    const short *p011 = (ey && ez) ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz + 1) : (ey ? p010 : p001);
+    const short *p111 = (ex && ey && ez) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by + 1, bz + 1)
                                                 : ((ex && ey) ? p110 : ((ex && ez) ? p101 : ((ey && ez) ? p011 : (ex ? p100 : (ey ? p010 : p001)))));
     const int x1 = (lx + 1) & 7, y1 = ((ly + 1) & 7) << 3, z1 = ((lz + 1) & 7) << 6, y0 = ly << 3, z0 = lz << 6;
-#define DSB_CORNER(P, L) ((P) ? (float)__ldg(reinterpret_cast<const short *>((P) + (L))) : 32767.0f)
+#define DSB_CORNER(P, L) ((P) ? (float)__ldg((P) + (L) * Tables::kStride) : 32767.0f)
     const float v000 = DSB_CORNER(p000, lx + y0 + z0), v100 = DSB_CORNER(p100, x1 + y0 + z0);
     const float v010 = DSB_CORNER(p010, lx + y1 + z0), v110 = DSB_CORNER(p110, x1 + y1 + z0);
     const float v001 = DSB_CORNER(p001, lx + y0 + z1), v101 = DSB_CORNER(p101, x1 + y0 + z1);
@@ -548,7 +560,7 @@ __global__ void __launch_bounds__(128) k_fwd_fill(RayParams P, const dsb200_voxe
     // findMissingPoints_device, CUDA .cu:873-905 / CPU .cpp:497-515
     if ((f.w <= 0) && ((f.x == 0 && f.y == 0 && f.z == 0) || (__ldg(depth + loc) >= 0)) && (mm.x < mm.y)) {
         atomicAdd(noMissing, 1);
-        const SceneTables T = {voxels, hash};
+        const SceneTables T = scene_tables(voxels, hash);
         cast_ray(f, x, y, T, P, mm.x, mm.y);
     }
     fwd[loc] = f;
@@ -589,7 +601,7 @@ void launch_forward_render(cudaStream_t st, const RayParams &P, const float *pro
 __device__ void normal_from_sdf(const dsb200_voxel *__restrict__ voxels, const dsb200_hash_entry *__restrict__ hash,
                                 int bucketNum, int bucketMask, float px, float py, float pz, float ret[3])
 {
-    const SceneTables T = {voxels, hash};
+    const SceneTables T = scene_tables(voxels, hash);
     bool f; BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
     float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
     float cx = px - flx, cy = py - fly, cz = pz - flz;
@@ -629,11 +641,11 @@ __device__ __forceinline__ uchar4 read_clr(const dsb200_voxel *__restrict__ voxe
                                            int bucketNum, int bucketMask, int px, int py, int pz, BlockCache &c)
 {
     bool found;
-    const SceneTables T = {voxels, hash};
+    const SceneTables T = scene_tables(voxels, hash);
     read_sdf(T, bucketNum, bucketMask, px, py, pz, found, c);   // positions the cache
     if (!found) return make_uchar4(0, 0, 0, 0);
     const int lin = (px & 7) + ((py & 7) << 3) + ((pz & 7) << 6);
-    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(c.blk + lin));
+    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(c.blk) + lin);
     return make_uchar4(raw.x >> 24, raw.y & 0xff, (raw.y >> 8) & 0xff, 0);
 }
 
@@ -768,12 +780,18 @@ static int ray_bottom_up() { static int v = env_int("DSB200_RAY_BOTTOM_UP", 0); 
 static int ray_ctas_per_sm() { static int v = env_int("DSB200_RAY_CTAS", 12); return v < 1 ? 1 : v; }
 
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
-                    const float *rangeImage, float *raycastResult, int *ticketPair)
+                    const float *rangeImage, float *raycastResult, int *ticketPair, const short *sdfShadow)
 {
     const int nTiles = div_up(P.W, 8) * div_up(P.H, 4);
     int grid = div_up(nTiles, 4);
     if (grid > kNumSMs * ray_ctas_per_sm()) grid = kNumSMs * ray_ctas_per_sm();
-    const SceneTables T = {voxels, hash};
+    if (sdfShadow) {
+        ShadowTables T; T.sdf = sdfShadow; T.hash = hash;
+        DSB_LAUNCH(k_raycast<ShadowTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(rangeImage),
+                   reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1, ray_bottom_up());
+        return;
+    }
+    const SceneTables T = scene_tables(voxels, hash);
     DSB_LAUNCH(k_raycast<SceneTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(rangeImage),
                reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1, ray_bottom_up());
 }

@@ -141,3 +141,23 @@ def test_view_from_raw_and_fusion_from_it():
     hz.assert_state_equal(ora.state(), gpu.state(), "fusion from raw view")
     hz.assert_images_equal(ora.images(), gpu.images(), "fusion from raw view")
     gpu.close(); ora.close()
+
+
+def test_sdf_shadow_on_off_and_rebuild():
+    """The fused frame raycasts from the engine's sdf shadow; turning it off (voxel-array reads) and on again (rebuilt from the
+    voxels) mid-sequence must not change a bit, nor must handing the engine a scene it did not maintain the shadow for."""
+    lib = abi.load()
+    cfg, frames = synth.make_sequence("tiny", 8)
+    gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    for i, f in enumerate(frames):
+        if i == 2:
+            abi.check(lib.dsb200_recon_set_sdf_shadow(gpu.recon.h, 0))
+        if i == 4:
+            abi.check(lib.dsb200_recon_set_sdf_shadow(gpu.recon.h, 1))
+        if i == 6:
+            abi.check(lib.dsb200_recon_invalidate_sdf_shadow(gpu.recon.h))
+        gpu.set_frame(f); ora.set_frame(f)
+        gpu.process_frame(); ora.process_frame()
+        hz.assert_images_equal(ora.images(), gpu.images(), "shadow frame %d" % i)
+    hz.assert_state_equal(ora.state(), gpu.state(), "shadow sequence")
+    gpu.close(); ora.close()
