@@ -399,8 +399,11 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 // at the bottom: they start first and the short ones fill the tail).
 // Two variants were measured on B200 and dropped (profiles/README.md, r01d): a persistent lane-refilling march (idle lanes
 // take new pixels while the others keep marching) was 1.6x slower, and issuing the 8 interpolation loads speculatively
-// together with the nearest-voxel load (one round trip per step instead of two) was 1.14x slower.  ncu: long-scoreboard
-// stalls dominate at 21 of 40 possible resident warps per SM -- the kernel is bound by the tail of long grazing rays.
+// together with the nearest-voxel load (one round trip per step instead of two) was 1.14x slower; a unit-step look-ahead
+// (samples of the next 3 one-voxel steps loaded together, committed one by one) was 2x slower at 80 registers.
+// A per-tile globaltimer trace (profiles/README.md, r01f) shows why the kernel is hard to shorten: the tickets run out after
+// a third of the kernel's duration and the rest is the tail of ~20 tiles of grazing rays that START in the first 12 us and
+// run for 100-130 us each (>100 dependent one-voxel steps).
 // Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
 // root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
 template <class Tables>
