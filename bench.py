@@ -89,6 +89,26 @@ class ClockSampler(object):
                 "samples": len(sm)}
 
 
+def ncu_traffic(stage):
+    """DRAM bytes per launch (read + write) of the stage's dominant kernel from the newest committed `ncu --set full`
+    extract under profiles/ (captured on the same bench command; see profiles/README.md).  None if no capture exists."""
+    import csv
+    import glob
+    kernel = {"integrate": "k_fuse", "raycast": "k_raycast", "allocate+visible_list": "k_alloc_requests"}.get(stage)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_summary.csv")))
+    if not kernel or not files or WORKLOAD != "C2":
+        return None, None
+    try:
+        rows = list(csv.reader(open(files[-1])))
+        hdr, units = rows[0], rows[1]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        vals = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]] for r in rows[2:] if kernel in r[0]]
+        return (sum(vals) / len(vals), os.path.basename(files[-1])) if vals else (None, None)
+    except Exception:
+        return None, None
+
+
 def make_frames(n, seed):
     synth = importlib.import_module(PKG + ".synth")
     return synth.make_sequence(WORKLOAD, n, seed=seed)
@@ -362,6 +382,7 @@ def run_ours(args, rank, world, local_rank):
            4116.0 * V + 16.0 * npx, 52.0 * npx]
     dom = int(np.argmax(per_stage))
     achieved = alg[dom] / (per_stage[dom] * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(stage_names[dom])
     stages = {stage_names[i]: {"ms": float(per_stage[i]), "alg_MB": alg[i] / 1e6,
                                "GBps": alg[i] / (per_stage[i] * 1e-3) / 1e9 if per_stage[i] > 0 else None} for i in range(5)}
     out = {"metric": METRIC, "value": world * K / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
@@ -375,7 +396,8 @@ def run_ours(args, rank, world, local_rank):
                    "pipeline": "double-buffered: upload of frame k+1 and read-back of frame k-1 overlap the fusion of frame k; one host sync at the end"},
            "gpu_launches": launches, "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                        "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"},
+                        "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
+                        "algorithmic_bytes_per_launch": alg[dom], "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"},
            "stages": stages, "prune_ms_per_frame": (prune_ms[0] / K) if prune else None,
            "decayed_blocks": recon.GetDecayedBlockCount() if prune else None,
            "allocate_kernels_ms": dict(zip(["begin_frame", "alloc_requests", "allocate", "recheck_visibility", "visible_list"],
