@@ -24,6 +24,9 @@ RENDER_SHADED_GREYSCALE, RENDER_COLOUR_FROM_VOLUME, RENDER_COLOUR_FROM_NORMAL, R
 PROFILE_STAGES = 5
 FRAME_ALLOCATE, FRAME_INTEGRATE, FRAME_EXPECTED_DEPTHS, FRAME_ICP_MAPS, FRAME_ALL = 1, 2, 4, 8, 15
 FRAME_RAYCAST = 16
+# TrackerIterationType, ITMLib/Utils/ITMLibDefines.h:289-295
+TRACKER_ITERATION_ROTATION, TRACKER_ITERATION_TRANSLATION, TRACKER_ITERATION_BOTH, TRACKER_ITERATION_NONE = 1, 2, 3, 4
+TRACKER_MAX_LEVELS = 8
 IPC_HANDLE_BYTES = 64
 MAX_SHARDS = 16
 
@@ -78,6 +81,15 @@ class Shard(C.Structure):
 class ShardTables(C.Structure):
     _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("brick_log2", C.c_int32), ("pad_", C.c_int32),
                 ("hash", C.c_void_p * 16), ("voxels", C.c_void_p * 16), ("range_image", C.c_void_p * 16)]
+
+
+class TrackerConfig(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("regime", C.c_int32 * 8), ("no_icp_run_till_level", C.c_int32),
+                ("dist_thresh", C.c_float), ("termination_threshold", C.c_float)]
+
+
+class TrackerReport(C.Structure):
+    _fields_ = [("evaluations", C.c_int32), ("steps", C.c_int32), ("last_valid_points", C.c_int32), ("last_f", C.c_float)]
 
 
 def f16(a):
@@ -162,6 +174,18 @@ def load():
         "dsb200_stream_synchronize": (C.c_int, [vp]),
         "dsb200_mat4_inverse": (C.c_int, [_P(C.c_float), _P(C.c_float)]),
         "dsb200_mat4_multiply": (None, [_P(C.c_float), _P(C.c_float), _P(C.c_float)]),
+        "dsb200_tracker_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
+        "dsb200_tracker_destroy": (C.c_int, [vp]),
+        "dsb200_tracker_set_evaluation_data": (C.c_int, [vp, vp, _P(C.c_float), vp, vp, i32, i32, _P(C.c_float), _P(C.c_float)]),
+        "dsb200_tracker_compute_g_and_h": (C.c_int, [vp, i32, i32, C.c_float, _P(C.c_float), _P(C.c_float), _P(C.c_float),
+                                                     _P(C.c_float), _P(i32)]),
+        "dsb200_tracker_last_sums": (C.c_int, [vp, _P(C.c_double)]),
+        "dsb200_tracker_level": (C.c_int, [vp, i32, _P(vp), _P(i32), _P(i32), _P(C.c_float)]),
+        "dsb200_filter_subsample_with_holes": (C.c_int, [vp, i32, i32, vp, vp]),
+        "dsb200_tracker_track_camera": (C.c_int, [vp, _P(TrackerConfig), _P(View), _P(Tracking), _P(C.c_float), i32, i32,
+                                                  _P(TrackerReport)]),
+        "dsb200_pose_coerce": (C.c_int, [_P(C.c_float), _P(C.c_float)]),
+        "dsb200_pose_from_params": (C.c_int, [_P(C.c_float), _P(C.c_float)]),
         "dsb200_profile_enable": (C.c_int, [vp, C.c_int]),
         "dsb200_profile_read": (C.c_int, [vp, _P(C.c_float)]),
         "dsb200_profile_read_allocate": (C.c_int, [vp, _P(C.c_float)]),

@@ -28,6 +28,7 @@ using namespace dsb;
 static thread_local std::string g_error;
 
 static int fail(int code, const std::string &msg) { g_error = msg; return code; }
+namespace dsb { int fail_with(int code, const char *msg) { return fail(code, msg); } }   // for tracker_host.cpp
 static int cuda_fail(cudaError_t e, const char *what)
 {
     return fail(e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? DSB200_ERR_NO_DEVICE : DSB200_ERR_CUDA,
@@ -752,6 +753,132 @@ int dsb200_view_from_raw(const int16_t *raw_depth, const uint8_t *bgr, float sca
         return fail(DSB200_ERR_INVALID, "view_from_raw: buffers must be 16-byte aligned (raw depth 8, bgr 4)");
     launch_view_from_raw((cudaStream_t)stream, raw_depth, bgr, scale, offset, const_cast<float *>(view->depth),
                          const_cast<uint8_t *>(view->rgb), view->depth_w * view->depth_h);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
+// ---------------------------------------------------------------- ICP depth tracker (device half)
+struct dsb200_tracker {
+    cudaStream_t stream = nullptr;
+    int levels = 0, width = 0, height = 0;
+    float *owned[DSB200_TRACKER_MAX_LEVELS] = {};        // levels 1.. (level 0 is the caller's image)
+    const float *depth[DSB200_TRACKER_MAX_LEVELS] = {};
+    int w[DSB200_TRACKER_MAX_LEVELS] = {}, h[DSB200_TRACKER_MAX_LEVELS] = {};
+    float intr[DSB200_TRACKER_MAX_LEVELS][4] = {};
+    const float *points = nullptr, *normals = nullptr;
+    int sceneW = 0, sceneH = 0;
+    float sceneIntr[4] = {}, scenePose[16] = {};
+    double *partials = nullptr, *result = nullptr, *hostResult = nullptr;
+    unsigned *ticket = nullptr;
+    int lastPara = 0;
+};
+
+int dsb200_tracker_create(dsb200_tracker **out, int32_t width, int32_t height, int32_t levels, void *stream)
+{
+    if (!out || width <= 0 || height <= 0 || levels < 1 || levels > DSB200_TRACKER_MAX_LEVELS)
+        return fail(DSB200_ERR_INVALID, "tracker_create: bad size or level count");
+    std::unique_ptr<dsb200_tracker> t(new dsb200_tracker);
+    t->stream = (cudaStream_t)stream; t->levels = levels; t->width = width; t->height = height;
+    t->w[0] = width; t->h[0] = height;
+    for (int i = 1; i < levels; i++) {
+        t->w[i] = t->w[i - 1] / 2; t->h[i] = t->h[i - 1] / 2;
+        if (t->w[i] <= 0 || t->h[i] <= 0) return fail(DSB200_ERR_INVALID, "tracker_create: too many levels for this image size");
+        CU(cudaMalloc(&t->owned[i], sizeof(float) * (size_t)t->w[i] * t->h[i]));
+        t->depth[i] = t->owned[i];
+    }
+    CU(cudaMalloc(&t->partials, sizeof(double) * (size_t)tracker_gh_max_ctas() * tracker_gh_slots()));
+    CU(cudaMalloc(&t->result, sizeof(double) * tracker_gh_slots()));
+    CU(cudaMalloc(&t->ticket, sizeof(unsigned)));
+    CU(cudaMemset(t->ticket, 0, sizeof(unsigned)));
+    CU(cudaMallocHost(&t->hostResult, sizeof(double) * tracker_gh_slots()));
+    *out = t.release();
+    return DSB200_OK;
+}
+
+int dsb200_tracker_destroy(dsb200_tracker *t)
+{
+    if (!t) return DSB200_OK;
+    for (int i = 1; i < t->levels; i++) cudaFree(t->owned[i]);
+    cudaFree(t->partials); cudaFree(t->result); cudaFree(t->ticket); cudaFreeHost(t->hostResult);
+    delete t;
+    return DSB200_OK;
+}
+
+int dsb200_tracker_set_evaluation_data(dsb200_tracker *t, const float *depth, const float *viewIntr, const float *points,
+                                       const float *normals, int32_t sceneW, int32_t sceneH, const float *sceneIntr,
+                                       const float *scenePose)
+{
+    if (!t || !depth || !viewIntr || !points || !normals || !sceneIntr || !scenePose || sceneW < 2 || sceneH < 2)
+        return fail(DSB200_ERR_INVALID, "tracker_set_evaluation_data: null argument or empty scene maps");
+    if (((uintptr_t)points & 15) || ((uintptr_t)normals & 15))
+        return fail(DSB200_ERR_INVALID, "tracker_set_evaluation_data: the point and normal maps must be 16-byte aligned");
+    if (sceneW > 32767 || sceneH > 32767)
+        return fail(DSB200_ERR_INVALID, "tracker_set_evaluation_data: scene maps beyond 32767 pixels a side (the reference indexes them with shorts)");
+    t->depth[0] = depth;
+    for (int k = 0; k < 4; k++) t->intr[0][k] = viewIntr[k];
+    for (int i = 1; i < t->levels; i++) {
+        launch_filter_subsample_holes(t->stream, t->depth[i - 1], t->w[i - 1], t->h[i - 1], t->owned[i]);
+        for (int k = 0; k < 4; k++) t->intr[i][k] = t->intr[i - 1][k] * 0.5f;
+    }
+    CU(cudaGetLastError());
+    t->points = points; t->normals = normals; t->sceneW = sceneW; t->sceneH = sceneH;
+    memcpy(t->sceneIntr, sceneIntr, sizeof(t->sceneIntr));
+    memcpy(t->scenePose, scenePose, sizeof(t->scenePose));
+    return DSB200_OK;
+}
+
+int dsb200_tracker_compute_g_and_h(dsb200_tracker *t, int32_t level, int32_t iterationType, float distThresh,
+                                   const float *approxInvPose, float *f, float *nabla, float *hessian, int32_t *noValid)
+{
+    if (!t || !approxInvPose || !f || !nabla || !hessian || !noValid) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: null argument");
+    if (level < 0 || level >= t->levels) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: no such pyramid level");
+    if (!t->depth[0] || !t->points) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: set_evaluation_data has not been called");
+    if (iterationType == DSB200_TRACKER_ITERATION_NONE) { *noValid = 0; return DSB200_OK; }   // ITMDepthTracker_CPU.cpp:25
+    if (iterationType != DSB200_TRACKER_ITERATION_ROTATION && iterationType != DSB200_TRACKER_ITERATION_TRANSLATION &&
+        iterationType != DSB200_TRACKER_ITERATION_BOTH)
+        return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: unknown iteration type");
+    launch_tracker_gh(t->stream, iterationType, approxInvPose, t->scenePose, t->intr[level], t->sceneIntr, distThresh,
+                      t->depth[level], t->w[level], t->h[level], t->points, t->normals, t->sceneW, t->sceneH, t->partials,
+                      t->ticket, t->result);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(t->hostResult, t->result, sizeof(double) * tracker_gh_slots(), cudaMemcpyDeviceToHost, t->stream));
+    CU(cudaStreamSynchronize(t->stream));
+    const bool shortIt = iterationType != DSB200_TRACKER_ITERATION_BOTH;
+    const int noPara = shortIt ? 3 : 6, noParaSQ = shortIt ? 6 : 21;
+    t->lastPara = noPara;
+    const double *S = t->hostResult;
+    // ITMDepthTracker_CPU.cpp:71-77
+    for (int r = 0, counter = 0; r < noPara; r++) for (int c = 0; c <= r; c++, counter++) hessian[r + c * 6] = (float)S[counter];
+    for (int r = 0; r < noPara; ++r) for (int c = r + 1; c < noPara; c++) hessian[r + c * 6] = hessian[c + r * 6];
+    for (int r = 0; r < noPara; r++) nabla[r] = (float)S[noParaSQ + r];
+    const int n = (int)S[noParaSQ + noPara + 1];
+    const float sumF = (float)S[noParaSQ + noPara];
+    *f = (n > 100) ? sqrtf(sumF) / (float)n : 1e5f;
+    *noValid = n;
+    return DSB200_OK;
+}
+
+int dsb200_tracker_last_sums(const dsb200_tracker *t, double *sums)
+{
+    if (!t || !sums) return fail(DSB200_ERR_INVALID, "tracker_last_sums: null argument");
+    memcpy(sums, t->hostResult, sizeof(double) * 32);
+    return DSB200_OK;
+}
+
+int dsb200_tracker_level(const dsb200_tracker *t, int32_t level, const float **depth, int32_t *w, int32_t *h, float *intr)
+{
+    if (!t || level < 0 || level >= t->levels) return fail(DSB200_ERR_INVALID, "tracker_level: no such pyramid level");
+    if (depth) *depth = t->depth[level];
+    if (w) *w = t->w[level];
+    if (h) *h = t->h[level];
+    if (intr) memcpy(intr, t->intr[level], sizeof(float) * 4);
+    return DSB200_OK;
+}
+
+int dsb200_filter_subsample_with_holes(const float *in, int32_t w, int32_t h, float *out, void *stream)
+{
+    if (!in || !out || w < 2 || h < 2) return fail(DSB200_ERR_INVALID, "filter_subsample_with_holes: null argument or image smaller than 2x2");
+    launch_filter_subsample_holes((cudaStream_t)stream, in, w, h, out);
     CU(cudaGetLastError());
     return DSB200_OK;
 }

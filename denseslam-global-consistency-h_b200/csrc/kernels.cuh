@@ -116,4 +116,13 @@ void launch_forward_render(cudaStream_t st, const RayParams &P, const float *pro
                            const dsb200_hash_entry *hash, const float *rangeImage, const float *raycastResult,
                            const float *depth, float *fwd, int *owner, int *noMissing, uint8_t *rendering);
 
+// tracker.cu
+void launch_filter_subsample_holes(cudaStream_t st, const float *in, int oldW, int oldH, float *out);
+int tracker_gh_max_ctas();
+int tracker_gh_slots();
+void launch_tracker_gh(cudaStream_t st, int iterationType, const float *approxInvPose, const float *scenePose,
+                       const float *viewIntr, const float *sceneIntr, float distThresh, const float *depth, int viewW, int viewH,
+                       const float *points, const float *normals, int sceneW, int sceneH, double *partials, unsigned *ticket,
+                       double *result);
+
 } // namespace dsb

@@ -3,6 +3,7 @@
 Class / method names follow the reference so call sites read the same:
   ITMSceneReconstructionEngine  (ITMLib/Engine/ITMSceneReconstructionEngine.h:45-96)
   ITMVisualisationEngine        (ITMLib/Engine/ITMVisualisationEngine.h:71-124)
+  ITMDepthTracker               (ITMLib/Engine/ITMDepthTracker.h:26-70)
   ITMScene / ITMRenderState_VH / ITMView / ITMTrackingState  (ITMLib/Objects/*.h)
 All heavy state lives in device memory owned through the C ABI helpers; numpy is used only to
 move data in and out.  Errors surface as abi.Dsb200Error carrying the reference's messages.
@@ -156,6 +157,12 @@ class ITMTrackingState(object):
         self.c.icp_points, self.c.icp_normals = self.points.ptr, self.normals.ptr
         self.c.requires_full_rendering = 1
         self.set_pose(abi.IDENTITY16)
+        # pose_pointCloud->GetM(): pose the ICP maps were raycast from (set by CreateICPMaps, ITMVisualisationEngine_CPU.cpp:430)
+        self.pose_pointCloud = np.array(abi.IDENTITY16, np.float32)
+
+    def pose(self):
+        """(M_d, invM_d) as float32[16] column-major"""
+        return np.array(self.c.M_d[:], np.float32), np.array(self.c.invM_d[:], np.float32)
 
     def set_pose(self, M, invM=None):
         """pose_d->SetM: M is world->camera, column-major. invM defaults to the cofactor inverse."""
@@ -242,6 +249,8 @@ class ITMSceneReconstructionEngine(object):
         """ITMDenseMapper::ProcessFrame + ITMTrackingController::Prepare as one submission."""
         abi.check(_lib().dsb200_process_frame(self.h, vis.h if vis is not None else None, C.byref(scene.c), C.byref(view.c),
                                               C.byref(trackingState.c), C.byref(renderState.c), stages))
+        if stages & abi.FRAME_ICP_MAPS:
+            trackingState.pose_pointCloud = np.array(trackingState.c.M_d[:], np.float32)
 
 
 class ITMVisualisationEngine(object):
@@ -274,6 +283,7 @@ class ITMVisualisationEngine(object):
 
     def CreateICPMaps(self, scene, view, trackingState, renderState):
         abi.check(_lib().dsb200_create_icp_maps(self.h, C.byref(scene.c), C.byref(view.c), C.byref(trackingState.c), C.byref(renderState.c)))
+        trackingState.pose_pointCloud = np.array(trackingState.c.M_d[:], np.float32)
 
     def RenderImage(self, scene, M, invM, intrinsics, renderState, outImage, outFloat, renderType=abi.RENDER_SHADED_GREYSCALE):
         abi.check(_lib().dsb200_render_image(self.h, C.byref(scene.c), abi.f16(M), abi.f16(invM), abi.f4(intrinsics),
@@ -291,3 +301,75 @@ class ITMVisualisationEngine(object):
 
     def CreatePointCloud(self):
         abi.check(_lib().dsb200_create_point_cloud(self.h))
+
+
+class ITMDepthTracker(object):
+    """ICP depth tracker (ITMLib/Engine/ITMDepthTracker.h:26-70): constructor arguments and TrackCamera as in the
+    reference; ComputeGandH / FilterSubsampleWithHoles run on the GPU, the Levenberg-Marquardt loop on the host
+    (csrc/tracker_host.cpp).  Defaults are ITMLibSettings.cpp:13-16,62-73."""
+
+    DEFAULT_REGIME = (abi.TRACKER_ITERATION_BOTH, abi.TRACKER_ITERATION_BOTH, abi.TRACKER_ITERATION_ROTATION,
+                      abi.TRACKER_ITERATION_ROTATION, abi.TRACKER_ITERATION_ROTATION)
+
+    def __init__(self, imgSize, trackingRegime=DEFAULT_REGIME, noHierarchyLevels=None, noICPRunTillLevel=0,
+                 distThresh=0.1 * 0.1, terminationThreshold=1e-3, stream=None):
+        levels = len(trackingRegime) if noHierarchyLevels is None else noHierarchyLevels
+        if not 1 <= levels <= abi.TRACKER_MAX_LEVELS or levels > len(trackingRegime):
+            raise ValueError("noHierarchyLevels must be 1..%d and covered by trackingRegime" % abi.TRACKER_MAX_LEVELS)
+        self.W, self.H = int(imgSize[0]), int(imgSize[1])
+        self.cfg = abi.TrackerConfig()
+        self.cfg.levels = levels
+        for i in range(levels):
+            self.cfg.regime[i] = int(trackingRegime[i])
+        self.cfg.no_icp_run_till_level = noICPRunTillLevel
+        self.cfg.dist_thresh = distThresh
+        self.cfg.termination_threshold = terminationThreshold
+        self.report = abi.TrackerReport()
+        self.h = C.c_void_p()
+        abi.check(_lib().dsb200_tracker_create(C.byref(self.h), self.W, self.H, levels, stream))
+
+    def close(self):
+        if self.h:
+            _lib().dsb200_tracker_destroy(self.h)
+            self.h = None
+
+    def TrackCamera(self, trackingState, view):
+        """Refines trackingState's pose_d against its point cloud (the last CreateICPMaps) using view.depth."""
+        abi.check(_lib().dsb200_tracker_track_camera(self.h, C.byref(self.cfg), C.byref(view.c), C.byref(trackingState.c),
+                                                     abi.f16(trackingState.pose_pointCloud), trackingState.W, trackingState.H,
+                                                     C.byref(self.report)))
+
+    # ---- the device half on its own (what a C++ subclass of the reference's ITMDepthTracker forwards to) ----
+    def SetEvaluationData(self, trackingState, view):
+        abi.check(_lib().dsb200_tracker_set_evaluation_data(self.h, view.c.depth, view.c.intr_d, trackingState.c.icp_points,
+                                                            trackingState.c.icp_normals, trackingState.W, trackingState.H,
+                                                            view.c.intr_d, abi.f16(trackingState.pose_pointCloud)))
+
+    def ComputeGandH(self, levelId, iterationType, distThresh, approxInvPose):
+        """-> (noValidPoints, f, nabla[6], hessian[36], sums[32] float64)"""
+        f, n = C.c_float(), C.c_int32()
+        nabla, hessian, sums = (C.c_float * 6)(), (C.c_float * 36)(), (C.c_double * 32)()
+        abi.check(_lib().dsb200_tracker_compute_g_and_h(self.h, levelId, iterationType, distThresh, abi.f16(approxInvPose),
+                                                        C.byref(f), nabla, hessian, C.byref(n)))
+        abi.check(_lib().dsb200_tracker_last_sums(self.h, sums))
+        return n.value, f.value, np.array(nabla[:], np.float32), np.array(hessian[:], np.float32), np.array(sums[:], np.float64)
+
+    def Level(self, levelId):
+        """(depth image copy, intrinsics) of a pyramid level after SetEvaluationData / TrackCamera"""
+        p, w, h = C.c_void_p(), C.c_int32(), C.c_int32()
+        intr = (C.c_float * 4)()
+        abi.check(_lib().dsb200_tracker_level(self.h, levelId, C.byref(p), C.byref(w), C.byref(h), intr))
+        return _download(p.value, np.float32, w.value * h.value).reshape(h.value, w.value), np.array(intr[:], np.float32)
+
+
+def pose_coerce(M):
+    """ITMPose::SetM + Coerce -> (M float32[16], params (tx, ty, tz, rx, ry, rz))"""
+    m, p = abi.f16(M), (C.c_float * 6)()
+    abi.check(_lib().dsb200_pose_coerce(m, p))
+    return np.array(m[:], np.float32), np.array(p[:], np.float32)
+
+
+def pose_from_params(params):
+    m = (C.c_float * 16)()
+    abi.check(_lib().dsb200_pose_from_params((C.c_float * 6)(*[float(x) for x in params]), m))
+    return np.array(m[:], np.float32)

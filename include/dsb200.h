@@ -282,6 +282,70 @@ int dsb200_stream_synchronize(void *cuda_stream);
 int dsb200_mat4_inverse(const float *M, float *out);
 void dsb200_mat4_multiply(const float *A, const float *B, float *out);
 
+/* ---- ICP depth tracker: the device-specific half ----
+ * The reference's tracker is a host Levenberg-Marquardt loop (ITMLib/Engine/ITMDepthTracker.cpp:153-211, shared by
+ * its CPU and CUDA builds) around ONE device virtual, ComputeGandH (ITMDepthTracker.h:59;
+ * DeviceSpecific/CPU/ITMDepthTracker_CPU.cpp:13-79, DeviceSpecific/CUDA/ITMDepthTracker_CUDA.cu), plus the low-level
+ * engine's FilterSubsampleWithHoles for the depth pyramid (ITMDepthTracker.cpp:66-76).  The adapter in INTEGRATION.md
+ * subclasses ITMDepthTracker and forwards exactly these; the host loop stays the reference's. */
+#define DSB200_TRACKER_ITERATION_ROTATION 1      /* TrackerIterationType, ITMLib/Utils/ITMLibDefines.h:289-295 */
+#define DSB200_TRACKER_ITERATION_TRANSLATION 2
+#define DSB200_TRACKER_ITERATION_BOTH 3
+#define DSB200_TRACKER_ITERATION_NONE 4
+#define DSB200_TRACKER_MAX_LEVELS 8
+typedef struct dsb200_tracker dsb200_tracker;
+/* ITMDepthTracker ctor (ITMDepthTracker.cpp:12-40): owns levels 1.. of the view-depth pyramid and the reduction scratch */
+int dsb200_tracker_create(dsb200_tracker **out, int32_t width, int32_t height, int32_t levels, void *cuda_stream);
+int dsb200_tracker_destroy(dsb200_tracker *t);
+/* SetEvaluationData + PrepareForEvaluation (ITMDepthTracker.cpp:43-76).  depth: DEVICE float image of the tracker's
+ * size, used in place as level 0; levels 1.. are rebuilt (FilterSubsampleWithHoles), intrinsics halve per level.
+ * points / normals: DEVICE float4 maps of the last raycast (trackingState->pointCloud locations / colours), NOT
+ * subsampled (SetEvaluationParams always selects scene level 0, :78-84); scene_pose = pose_pointCloud->GetM(). */
+int dsb200_tracker_set_evaluation_data(dsb200_tracker *t, const float *depth, const float *view_intrinsics,
+                                       const float *points, const float *normals, int32_t scene_w, int32_t scene_h,
+                                       const float *scene_intrinsics, const float *scene_pose);
+/* ComputeGandH at pyramid level `level`.  hessian: 36 floats, filled like the reference (hessian[r + c*6] for the
+ * noPara x noPara block, symmetric; other entries untouched); nabla: 6 floats (first noPara written);
+ * *f = sqrt(sum b^2) / valid if valid > 100 else 1e5; *no_valid_points = the return value of the reference.
+ * Sums are accumulated in double along a fixed tree (deterministic).  Synchronous. */
+int dsb200_tracker_compute_g_and_h(dsb200_tracker *t, int32_t level, int32_t iteration_type, float dist_thresh,
+                                   const float *approx_inv_pose, float *f, float *nabla, float *hessian,
+                                   int32_t *no_valid_points);
+/* raw double sums of the last compute_g_and_h: [0,NH) hessian lower triangle by rows, [NH,NH+NP) nabla, sum b^2, count */
+int dsb200_tracker_last_sums(const dsb200_tracker *t, double *sums /* [32] */);
+/* pyramid level access (device pointer owned by the tracker; level 0 is the caller's image) */
+int dsb200_tracker_level(const dsb200_tracker *t, int32_t level, const float **depth, int32_t *w, int32_t *h,
+                         float *intrinsics);
+/* ITMLowLevelEngine::FilterSubsampleWithHoles(ITMFloatImage) (DeviceAgnostic/ITMLowLevelEngine.h:26-47):
+ * out is (w/2) x (h/2), device pointers */
+int dsb200_filter_subsample_with_holes(const float *in, int32_t w, int32_t h, float *out, void *cuda_stream);
+
+/* ITMDepthTracker::TrackCamera (ITMDepthTracker.cpp:153-211) as one call, for callers without the reference's
+ * host loop: pyramid, Levenberg-Marquardt iterations per level (2, 4, 6, ... from the finest; distance thresholds
+ * dist_thresh * (level + 1) / levels, :20-30), Cholesky step (ORUtils/Cholesky.h), pose re-orthogonalised through its
+ * six parameters after every step (ITMPose::Coerce, Objects/ITMPose.cpp:82-262).  Host arithmetic is float without
+ * contraction, like the reference.  In: tracking->M_d = start pose, tracking->icp_points / icp_normals = the maps of
+ * the last raycast (scene_w x scene_h), scene_pose = pose_pointCloud->GetM().  Out: tracking->M_d / invM_d.
+ * Where the reference would step along an uninitialised Hessian (no valid evaluation yet), the pose is left alone. */
+typedef struct dsb200_tracker_config {
+    int32_t levels;                                  /* noHierarchyLevels (ITMLibSettings.cpp:62-69: 5) */
+    int32_t regime[DSB200_TRACKER_MAX_LEVELS];       /* trackingRegime, level 0 = finest */
+    int32_t no_icp_run_till_level;                   /* ITMLibSettings.cpp:72-73: 0 */
+    float dist_thresh;                               /* depthTrackerICPThreshold, :13: 0.1^2 */
+    float termination_threshold;                     /* depthTrackerTerminationThreshold, :16: 1e-3 */
+} dsb200_tracker_config;
+typedef struct dsb200_tracker_report {
+    int32_t evaluations, steps, last_valid_points;
+    float last_f;
+} dsb200_tracker_report;
+int dsb200_tracker_track_camera(dsb200_tracker *t, const dsb200_tracker_config *cfg, const dsb200_view *view,
+                                dsb200_tracking *tracking, const float *scene_pose, int32_t scene_w, int32_t scene_h,
+                                dsb200_tracker_report *report /* may be NULL */);
+/* ITMPose::Coerce on a column-major 4x4 (in place); params (optional) receives (tx, ty, tz, rx, ry, rz) */
+int dsb200_pose_coerce(float *M, float *params);
+/* ITMPose::SetFrom(tx..rz) -> GetM() (SetModelViewFromParams, Objects/ITMPose.cpp:82-180) */
+int dsb200_pose_from_params(const float *params, float *M);
+
 /* per-stage device timing of dsb200_process_frame (CUDA events on the engine's stream).  Stage order:
  * 0 allocate(+visible list) 1 integrate 2 expected depths 3 raycast 4 ICP maps.  read() synchronises. */
 #define DSB200_PROFILE_STAGES 5

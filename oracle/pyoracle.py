@@ -123,7 +123,48 @@ class Oracle(object):
         L.rst_mat4_inverse.restype = C.c_int
         L.rst_mat4_inverse.argtypes = [fp, fp]
         L.rst_mat4_multiply.argtypes = [fp, fp, fp]
+        L.rst_filter_subsample_with_holes.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.rst_tracker_compute_g_and_h.restype = C.c_int
+        L.rst_tracker_compute_g_and_h.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_int, vp, vp, vp, C.c_float,
+                                                  C.c_int, C.c_int, vp, vp, vp, vp]
+        L.rst_pose_coerce.argtypes = [vp, vp]
+        L.rst_pose_from_params.argtypes = [vp, vp]
+        L.rst_track_camera.argtypes = [P(abi.TrackerConfig), P(abi.View), P(abi.Tracking), vp, C.c_int, C.c_int, C.c_int,
+                                       P(abi.TrackerReport)]
         self.L = L
+
+    def pose_coerce(self, M):
+        m = np.array(M, np.float32).copy()
+        p = np.zeros(6, np.float32)
+        self.L.rst_pose_coerce(ptr(m), ptr(p))
+        return m, p
+
+    def pose_from_params(self, params):
+        p = np.ascontiguousarray(params, np.float32)
+        m = np.zeros(16, np.float32)
+        self.L.rst_pose_from_params(ptr(p), ptr(m))
+        return m
+
+    def track_camera(self, cfg, view, tracking, scene_pose, scene_w, scene_h, double_sums=False):
+        """rst_track_camera: tracking (abi.Tracking with HOST maps) is updated in place; returns the report"""
+        sp = np.ascontiguousarray(scene_pose, np.float32)
+        rep = abi.TrackerReport()
+        self.L.rst_track_camera(C.byref(cfg), C.byref(view), C.byref(tracking), ptr(sp), scene_w, scene_h,
+                                1 if double_sums else 0, C.byref(rep))
+        return rep
+
+    def filter_subsample_with_holes(self, image):
+        src = np.ascontiguousarray(image, np.float32)
+        h, w = src.shape
+        out = np.zeros((h // 2, w // 2), np.float32)
+        self.L.rst_filter_subsample_with_holes(ptr(src), w, h, ptr(out))
+        return out
+
+    def tracker_compute_g_and_h(self, depth, view_intr, points, normals, scene_intr, scene_pose, approx_inv_pose,
+                                dist_thresh, iteration_type, double_sums=False):
+        """ComputeGandH restated -> (noValidPoints, f, nabla[6], hessian[36], sums[32])"""
+        return _gh_call(self.L.rst_tracker_compute_g_and_h, depth, view_intr, points, normals, scene_intr, scene_pose,
+                        approx_inv_pose, dist_thresh, iteration_type, 1 if double_sums else 0)
 
     def mat4_inverse(self, M):
         out = (C.c_float * 16)()
@@ -135,6 +176,29 @@ class Oracle(object):
         out = (C.c_float * 16)()
         self.L.rst_mat4_multiply(abi.f16(A), abi.f16(B), out)
         return np.array(out[:], dtype=np.float32)
+
+
+def _gh_call(fn, depth, view_intr, points, normals, scene_intr, scene_pose, approx_inv_pose, dist_thresh, iteration_type,
+             double_sums=None):
+    d = np.ascontiguousarray(depth, np.float32)
+    pts = np.ascontiguousarray(points, np.float32)
+    nrm = np.ascontiguousarray(normals, np.float32)
+    vh, vw = d.shape
+    sh, sw = pts.shape[:2]
+    vi = np.ascontiguousarray(view_intr, np.float32)
+    si = np.ascontiguousarray(scene_intr, np.float32)
+    sp = np.ascontiguousarray(scene_pose, np.float32)
+    ap = np.ascontiguousarray(approx_inv_pose, np.float32)
+    f = np.zeros(1, np.float32)
+    nabla = np.zeros(6, np.float32)
+    hessian = np.zeros(36, np.float32)
+    sums = np.zeros(32, np.float64)
+    args = [ptr(d), vw, vh, ptr(vi), ptr(pts), ptr(nrm), sw, sh, ptr(si), ptr(sp), ptr(ap), dist_thresh, iteration_type]
+    if double_sums is not None:
+        n = fn(*(args + [double_sums, ptr(f), ptr(nabla), ptr(hessian), ptr(sums)]))
+    else:
+        n = fn(*(args + [ptr(f), ptr(nabla), ptr(hessian)]))
+    return int(n), float(f[0]), nabla, hessian, sums
 
 
 def make_tracking(M, invM, icp_points=None, icp_normals=None, requires_full_rendering=True,
@@ -188,6 +252,14 @@ class RefEngine(object):
         L.itmref_count_visible_blocks.argtypes = [vp, C.c_int, C.c_int]
         L.itmref_mat4_inv.argtypes = [vp, vp]
         L.itmref_mat4_mul.argtypes = [vp, vp, vp]
+        if hasattr(L, "itmref_track_camera"):
+            L.itmref_tracker_compute_g_and_h.restype = C.c_int
+            L.itmref_tracker_compute_g_and_h.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_int, vp, vp, vp,
+                                                         C.c_float, C.c_int, vp, vp, vp]
+            L.itmref_filter_subsample_with_holes.argtypes = [vp, C.c_int, C.c_int, vp]
+            L.itmref_track_camera.argtypes = [vp, C.c_int, vp, C.c_int, C.c_float, C.c_float]
+            L.itmref_pose_coerce.argtypes = [vp, vp, vp]
+            L.itmref_pose_from_params.argtypes = [vp, vp]
         self.L, self.W, self.H = L, W, H
         self.h = L.itmref_create(W, H, params.voxel_size, params.mu, params.max_w, params.vf_min, params.vf_max,
                                  params.stop_integrating_at_max_w, 1 if use_swapping else 0)
@@ -256,6 +328,38 @@ class RefEngine(object):
         r = np.ascontiguousarray(rgba, np.uint8)
         self.L.itmref_update_view_raw(self.h, ptr(d), ptr(r), scale, offset, timestamp)
         return self._arr(self.L.itmref_view_depth(self.h), np.float32, self.W * self.H).reshape(self.H, self.W).copy()
+
+    def tracker_compute_g_and_h(self, depth, view_intr, points, normals, scene_intr, scene_pose, approx_inv_pose,
+                                dist_thresh, iteration_type):
+        """ITMDepthTracker_CPU::ComputeGandH on raw arrays -> (noValidPoints, f, nabla[6], hessian[36], unused)"""
+        return _gh_call(self.L.itmref_tracker_compute_g_and_h, depth, view_intr, points, normals, scene_intr, scene_pose,
+                        approx_inv_pose, dist_thresh, iteration_type)
+
+    def filter_subsample_with_holes(self, image):
+        src = np.ascontiguousarray(image, np.float32)
+        h, w = src.shape
+        out = np.zeros((h // 2, w // 2), np.float32)
+        self.L.itmref_filter_subsample_with_holes(ptr(src), w, h, ptr(out))
+        return out
+
+    def pose_coerce(self, M):
+        m = np.ascontiguousarray(M, np.float32)
+        o = np.zeros(16, np.float32)
+        p = np.zeros(6, np.float32)
+        self.L.itmref_pose_coerce(ptr(m), ptr(o), ptr(p))
+        return o, p
+
+    def pose_from_params(self, params):
+        p = np.ascontiguousarray(params, np.float32)
+        o = np.zeros(16, np.float32)
+        self.L.itmref_pose_from_params(ptr(p), ptr(o))
+        return o
+
+    def track_camera(self, regime, no_icp_run_till_level=0, dist_thresh=0.01, termination_threshold=1e-3):
+        """ITMDepthTracker::TrackCamera on the current view / point cloud; pose_d is the start and receives the result"""
+        r = np.ascontiguousarray(regime, np.int32)
+        self.L.itmref_track_camera(self.h, len(r), ptr(r), no_icp_run_till_level, dist_thresh, termination_threshold)
+        return self.get_pose()
 
     def forward_render(self):
         """ForwardRender at the current view/pose -> (forwardProjection copy, noFwdProjMissingPoints)"""

@@ -11,10 +11,14 @@
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.cpp:25-342
 //   ITMVisualisationEngine_CPU<ITMVoxel,ITMVoxelBlockHash>
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.cpp:27-180,296-459
+//   ITMDepthTracker_CPU (+ the shared host loop ITMLib/Engine/ITMDepthTracker.cpp) and ITMLowLevelEngine_CPU
+//       ITMLib/Engine/DeviceSpecific/CPU/ITMDepthTracker_CPU.cpp:13-79, CPU/ITMLowLevelEngine_CPU.cpp:50-62
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.h"
 #include "ITMLib/Objects/ITMRenderState_VH.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMViewBuilder_CPU.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMDepthTracker_CPU.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
 
 #include <cstring>
 #include <cstdint>
@@ -186,5 +190,82 @@ float *itmref_icp_points(void *h) { return (float *)((RefCtx *)h)->tracking->poi
 float *itmref_icp_normals(void *h) { return (float *)((RefCtx *)h)->tracking->pointCloud->colours->GetData(MEMORYDEVICE_CPU); }
 uint8_t *itmref_icp_rendering(void *h) { return (uint8_t *)((RefCtx *)h)->rs->raycastImage->GetData(MEMORYDEVICE_CPU); }
 uint8_t *itmref_out_image(void *h) { return (uint8_t *)((RefCtx *)h)->outImg->GetData(MEMORYDEVICE_CPU); }
+
+} // extern "C"
+
+// ---- ICP depth tracker ----
+namespace {
+// ComputeGandH is protected: a subclass that fills the protected evaluation state from raw arrays and calls it
+struct TrackerProbe : public ITMDepthTracker_CPU {
+    TrackerProbe(Vector2i size, TrackerIterationType *regime, const ITMLowLevelEngine *ll)
+        : ITMDepthTracker_CPU(size, regime, 1, 0, 0.01f, 1e-3f, ll) {}
+    int probe(const float *depth, int vW, int vH, const float *vIntr, const float *points, const float *normals, int sW, int sH,
+              const float *sIntr, const float *scenePoseM, const float *approxInvPose, float dt, int type, float *f, float *nabla,
+              float *hessian)
+    {
+        ITMTemplatedHierarchyLevel<ITMFloatImage> vl(Vector2i(vW, vH), 0, (TrackerIterationType)type, MEMORYDEVICE_CPU);
+        ITMSceneHierarchyLevel sl(Vector2i(sW, sH), 0, (TrackerIterationType)type, MEMORYDEVICE_CPU);
+        memcpy(vl.depth->GetData(MEMORYDEVICE_CPU), depth, sizeof(float) * (size_t)vW * vH);
+        memcpy(sl.pointsMap->GetData(MEMORYDEVICE_CPU), points, sizeof(float) * 4 * (size_t)sW * sH);
+        memcpy(sl.normalsMap->GetData(MEMORYDEVICE_CPU), normals, sizeof(float) * 4 * (size_t)sW * sH);
+        vl.intrinsics = Vector4f(vIntr[0], vIntr[1], vIntr[2], vIntr[3]);
+        sl.intrinsics = Vector4f(sIntr[0], sIntr[1], sIntr[2], sIntr[3]);
+        this->levelId = 0; this->distThresh[0] = dt; this->iterationType = (TrackerIterationType)type;
+        this->scenePose = toM(scenePoseM); this->sceneHierarchyLevel = &sl; this->viewHierarchyLevel = &vl;
+        return this->ComputeGandH(*f, nabla, hessian, toM(approxInvPose));
+    }
+};
+}
+
+extern "C" {
+
+int itmref_tracker_compute_g_and_h(const float *depth, int vW, int vH, const float *vIntr, const float *points,
+                                   const float *normals, int sW, int sH, const float *sIntr, const float *scenePose,
+                                   const float *approxInvPose, float distThresh, int iterationType, float *f, float *nabla,
+                                   float *hessian)
+{
+    ITMLowLevelEngine_CPU ll;
+    TrackerIterationType regime[1] = {(TrackerIterationType)iterationType};
+    TrackerProbe t(Vector2i(vW, vH), regime, &ll);
+    return t.probe(depth, vW, vH, vIntr, points, normals, sW, sH, sIntr, scenePose, approxInvPose, distThresh, iterationType, f,
+                   nabla, hessian);
+}
+
+void itmref_filter_subsample_with_holes(const float *in, int w, int h, float *out)
+{
+    ITMLowLevelEngine_CPU ll;
+    ITMFloatImage src(Vector2i(w, h), true, false), dst(Vector2i(w / 2, h / 2), true, false);
+    memcpy(src.GetData(MEMORYDEVICE_CPU), in, sizeof(float) * (size_t)w * h);
+    ll.FilterSubsampleWithHoles(&dst, &src);
+    memcpy(out, dst.GetData(MEMORYDEVICE_CPU), sizeof(float) * (size_t)(w / 2) * (h / 2));
+}
+
+// ITMPose::SetM + Coerce; params = (tx, ty, tz, rx, ry, rz)
+void itmref_pose_coerce(const float *Min, float *Mout, float *params)
+{
+    ITMPose p; p.SetM(toM(Min)); p.Coerce();
+    Matrix4f m = p.GetM(); memcpy(Mout, m.m, 64);
+    for (int i = 0; i < 6; i++) params[i] = p.GetParams()[i];
+}
+void itmref_pose_from_params(const float *params, float *Mout)
+{
+    ITMPose p(params[0], params[1], params[2], params[3], params[4], params[5]);
+    Matrix4f m = p.GetM(); memcpy(Mout, m.m, 64);
+}
+
+// pose_pointCloud (normally written by CreateICPMaps, ITMVisualisationEngine_CPU.cpp) for maps loaded from a fixture
+void itmref_set_scene_pose(void *h, const float *M) { ((RefCtx *)h)->tracking->pose_pointCloud->SetM(toM(M)); }
+
+// The whole tracker: ITMDepthTracker::TrackCamera (ITMDepthTracker.cpp:153-211) on the context's view and tracking state
+// (point cloud + pose_pointCloud from the last CreateICPMaps; pose_d is the initial guess and receives the result).
+void itmref_track_camera(void *h, int levels, const int *regime, int noICPRunTillLevel, float distThresh, float terminationThreshold)
+{
+    RefCtx *c = (RefCtx *)h;
+    ITMLowLevelEngine_CPU ll;
+    TrackerIterationType r[16];
+    for (int i = 0; i < levels && i < 16; i++) r[i] = (TrackerIterationType)regime[i];
+    ITMDepthTracker_CPU t(c->imgSize, r, levels, noICPRunTillLevel, distThresh, terminationThreshold, &ll);
+    t.TrackCamera(c->tracking, c->view);
+}
 
 } // extern "C"

@@ -1178,3 +1178,342 @@ void rst_forward_render(const dsb200_scene *scene, const dsb200_view *view, dsb2
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------- ICP depth tracker (device half)
+namespace {
+
+// interpolateBilinear_withHoles, DA/ITMPixelUtils.h:41-71 (Vector4f source)
+inline V4 bilinearHoles(const V4 *src, float px, float py, int W)
+{
+    short ix = (short)floorf(px), iy = (short)floorf(py);
+    float dx = px - (float)ix, dy = py - (float)iy;
+    V4 a = src[ix + iy * W], b = src[(ix + 1) + iy * W], c = src[ix + (iy + 1) * W], d = src[(ix + 1) + (iy + 1) * W];
+    V4 r;
+    if (a.w < 0 || b.w < 0 || c.w < 0 || d.w < 0) { r.x = 0; r.y = 0; r.z = 0; r.w = -1.0f; return r; }
+    r.x = a.x * (1.0f - dx) * (1.0f - dy) + b.x * dx * (1.0f - dy) + c.x * (1.0f - dx) * dy + d.x * dx * dy;
+    r.y = a.y * (1.0f - dx) * (1.0f - dy) + b.y * dx * (1.0f - dy) + c.y * (1.0f - dx) * dy + d.y * dx * dy;
+    r.z = a.z * (1.0f - dx) * (1.0f - dy) + b.z * dx * (1.0f - dy) + c.z * (1.0f - dx) * dy + d.z * dx * dy;
+    r.w = a.w * (1.0f - dx) * (1.0f - dy) + b.w * dx * (1.0f - dy) + c.w * (1.0f - dx) * dy + d.w * dx * dy;
+    return r;
+}
+
+// computePerPointGH_Depth_Ab, DA/ITMDepthTracker.h:9-74.  mode: 0 both (6 parameters), 1 rotation only, 2 translation only
+inline bool perPointAb(int mode, float *A, float &b, int x, int y, float depth, const float *vIntr, int sW, int sH,
+                       const float *sIntr, const float *approxInvPose, const float *scenePose, const V4 *points,
+                       const V4 *normals, float distThresh)
+{
+    if (depth <= 1e-8f) return false;
+    V4 p;
+    p.x = depth * (((float)x - vIntr[2]) / vIntr[0]);
+    p.y = depth * (((float)y - vIntr[3]) / vIntr[1]);
+    p.z = depth; p.w = 1.0f;
+    p = mulM(approxInvPose, p);
+    p.w = 1.0f;
+    V4 q = mulM(scenePose, p);
+    if (q.z <= 0.0f) return false;
+    float u = sIntr[0] * q.x / q.z + sIntr[2];
+    float v = sIntr[1] * q.y / q.z + sIntr[3];
+    if (!((u >= 0.0f) && (u <= sW - 2) && (v >= 0.0f) && (v <= sH - 2))) return false;
+    V4 c = bilinearHoles(points, u, v, sW);
+    if (c.w < 0.0f) return false;
+    float dx = c.x - p.x, dy = c.y - p.y, dz = c.z - p.z;
+    float dist = dx * dx + dy * dy + dz * dz;
+    if (dist > distThresh) return false;
+    V4 n = bilinearHoles(normals, u, v, sW);
+    b = n.x * dx + n.y * dy + n.z * dz;
+    if (mode == 2) { A[0] = n.x; A[1] = n.y; A[2] = n.z; }
+    else {
+        A[0] = +p.z * n.y - p.y * n.z;
+        A[1] = -p.z * n.x + p.x * n.z;
+        A[2] = +p.y * n.x - p.x * n.y;
+        if (mode == 0) { A[3] = n.x; A[4] = n.y; A[5] = n.z; }
+    }
+    return true;
+}
+
+template <typename Acc>
+int trackerSums(int mode, const float *depth, int vW, int vH, const float *vIntr, const V4 *points, const V4 *normals, int sW,
+                int sH, const float *sIntr, const float *scenePose, const float *approxInvPose, float distThresh, Acc *sumH,
+                Acc *sumN, Acc &sumF)
+{
+    const int noPara = mode == 0 ? 6 : 3, noParaSQ = mode == 0 ? 21 : 6;
+    int valid = 0; sumF = 0;
+    for (int i = 0; i < noParaSQ; i++) sumH[i] = 0;
+    for (int i = 0; i < noPara; i++) sumN[i] = 0;
+    // serial, row-major pixel order: DeviceSpecific/CPU/ITMDepthTracker_CPU.cpp:35-69
+    for (int y = 0; y < vH; y++) for (int x = 0; x < vW; x++) {
+        float A[6], b;
+        if (!perPointAb(mode, A, b, x, y, depth[x + y * vW], vIntr, sW, sH, sIntr, approxInvPose, scenePose, points, normals, distThresh))
+            continue;
+        // computePerPointGH_Depth, DA/ITMDepthTracker.h:76-104
+        valid++; sumF += (Acc)(b * b);
+        for (int r = 0, counter = 0; r < noPara; r++) {
+            sumN[r] += (Acc)(b * A[r]);
+            for (int c = 0; c <= r; c++, counter++) sumH[counter] += (Acc)(A[r] * A[c]);
+        }
+    }
+    return valid;
+}
+
+} // namespace
+
+extern "C" {
+
+// ITMLowLevelEngine_CPU::FilterSubsampleWithHoles(ITMFloatImage), CPU/ITMLowLevelEngine_CPU.cpp:50-62 with
+// filterSubsampleWithHoles, DA/ITMLowLevelEngine.h:26-47
+void rst_filter_subsample_with_holes(const float *in, int w, int h, float *out)
+{
+    const int nw = w / 2, nh = h / 2;
+    for (int y = 0; y < nh; y++) for (int x = 0; x < nw; x++) {
+        float acc = 0.0f, good = 0.0f, v;
+        v = in[(2 * x + 0) + (2 * y + 0) * w]; if (v > 0.0f) { acc += v; good++; }
+        v = in[(2 * x + 1) + (2 * y + 0) * w]; if (v > 0.0f) { acc += v; good++; }
+        v = in[(2 * x + 0) + (2 * y + 1) * w]; if (v > 0.0f) { acc += v; good++; }
+        v = in[(2 * x + 1) + (2 * y + 1) * w]; if (v > 0.0f) { acc += v; good++; }
+        if (good > 0) acc /= good;
+        out[x + y * nw] = acc;
+    }
+}
+
+// ITMDepthTracker_CPU::ComputeGandH, CPU/ITMDepthTracker_CPU.cpp:13-79.  double_sums = 0 follows the reference's float
+// accumulators (bit-exact with it); double_sums = 1 accumulates the same float terms in double (the libdsb200 contract).
+// sums (optional, 32 doubles): hessian lower triangle by rows, nabla, sum b^2, valid count.
+int rst_tracker_compute_g_and_h(const float *depth, int vW, int vH, const float *vIntr, const float *points,
+                                const float *normals, int sW, int sH, const float *sIntr, const float *scenePose,
+                                const float *approxInvPose, float distThresh, int iterationType, int doubleSums, float *f,
+                                float *nabla, float *hessian, double *sums)
+{
+    if (iterationType == DSB200_TRACKER_ITERATION_NONE) return 0;
+    const int mode = iterationType == DSB200_TRACKER_ITERATION_ROTATION ? 1 : iterationType == DSB200_TRACKER_ITERATION_TRANSLATION ? 2 : 0;
+    const int noPara = mode == 0 ? 6 : 3, noParaSQ = mode == 0 ? 21 : 6;
+    const V4 *P = reinterpret_cast<const V4 *>(points), *N = reinterpret_cast<const V4 *>(normals);
+    float sumH[21], sumN[6], sumF; int valid;
+    double dH[21] = {0}, dN[6] = {0}, dF = 0;
+    if (doubleSums) {
+        valid = trackerSums<double>(mode, depth, vW, vH, vIntr, P, N, sW, sH, sIntr, scenePose, approxInvPose, distThresh, dH, dN, dF);
+        for (int i = 0; i < noParaSQ; i++) sumH[i] = (float)dH[i];
+        for (int i = 0; i < noPara; i++) sumN[i] = (float)dN[i];
+        sumF = (float)dF;
+    } else {
+        valid = trackerSums<float>(mode, depth, vW, vH, vIntr, P, N, sW, sH, sIntr, scenePose, approxInvPose, distThresh, sumH, sumN, sumF);
+        for (int i = 0; i < noParaSQ; i++) dH[i] = sumH[i];
+        for (int i = 0; i < noPara; i++) dN[i] = sumN[i];
+        dF = sumF;
+    }
+    for (int r = 0, counter = 0; r < noPara; r++) for (int c = 0; c <= r; c++, counter++) hessian[r + c * 6] = sumH[counter];
+    for (int r = 0; r < noPara; ++r) for (int c = r + 1; c < noPara; c++) hessian[r + c * 6] = hessian[c + r * 6];
+    memcpy(nabla, sumN, noPara * sizeof(float));
+    *f = (valid > 100) ? sqrtf(sumF) / valid : 1e5f;
+    if (sums) {
+        for (int i = 0; i < 32; i++) sums[i] = 0;
+        for (int i = 0; i < noParaSQ; i++) sums[i] = dH[i];
+        for (int i = 0; i < noPara; i++) sums[noParaSQ + i] = dN[i];
+        sums[noParaSQ + noPara] = dF; sums[noParaSQ + noPara + 1] = valid;
+    }
+    return valid;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------- ICP depth tracker (host loop)
+namespace {
+
+struct P3 { float x, y, z; };
+inline float dotP(P3 a, P3 b) { float r = 0; r += a.x * b.x; r += a.y * b.y; r += a.z * b.z; return r; }   // ORUtils/Vector.h:811-816
+inline P3 crossP(P3 a, P3 b) { P3 r = {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; return r; }
+
+// ITMPose::SetModelViewFromParams, Objects/ITMPose.cpp:82-180
+void poseToMatrix(P3 t, P3 w, float *M)
+{
+    float one_6th = 1.0f / 6.0f, one_20th = 1.0f / 20.0f;
+    float theta_sq = dotP(w, w), theta = sqrtf(theta_sq), A, B;
+    P3 T, cv = crossP(w, t);
+    if (theta_sq < 1e-8f) {
+        A = 1.0f - one_6th * theta_sq; B = 0.5f;
+        T.x = t.x + 0.5f * cv.x; T.y = t.y + 0.5f * cv.y; T.z = t.z + 0.5f * cv.z;
+    } else {
+        float Cc;
+        if (theta_sq < 1e-6f) {
+            Cc = one_6th * (1.0f - one_20th * theta_sq); A = 1.0f - theta_sq * Cc; B = 0.5f - 0.25f * one_6th * theta_sq;
+        } else {
+            float inv_theta = 1.0f / theta;
+            A = sinf(theta) * inv_theta; B = (1.0f - cosf(theta)) * (inv_theta * inv_theta); Cc = (1.0f - A) * (inv_theta * inv_theta);
+        }
+        P3 c2 = crossP(w, cv);
+        T.x = t.x + B * cv.x + Cc * c2.x; T.y = t.y + B * cv.y + Cc * c2.y; T.z = t.z + B * cv.z + Cc * c2.z;
+    }
+    float wx2 = w.x * w.x, wy2 = w.y * w.y, wz2 = w.z * w.z, a, b;
+    M[0] = 1.0f - B * (wy2 + wz2); M[5] = 1.0f - B * (wx2 + wz2); M[10] = 1.0f - B * (wx2 + wy2);
+    a = A * w.z; b = B * (w.x * w.y); M[4] = b - a; M[1] = b + a;
+    a = A * w.y; b = B * (w.x * w.z); M[8] = b + a; M[2] = b - a;
+    a = A * w.x; b = B * (w.y * w.z); M[9] = b - a; M[6] = b + a;
+    M[12] = T.x; M[13] = T.y; M[14] = T.z;
+    M[3] = 0.0f; M[7] = 0.0f; M[11] = 0.0f; M[15] = 1.0f;
+}
+
+// ITMPose::SetParamsFromModelView, Objects/ITMPose.cpp:183-262
+void matrixToPose(const float *M, P3 &tOut, P3 &wOut)
+{
+#define RM(r, c) M[(r) + 4 * (c)]
+    P3 T = {M[12], M[13], M[14]}, rot;
+    float cos_angle = (RM(0, 0) + RM(1, 1) + RM(2, 2) - 1.0f) * 0.5f;
+    rot.x = (RM(2, 1) - RM(1, 2)) * 0.5f; rot.y = (RM(0, 2) - RM(2, 0)) * 0.5f; rot.z = (RM(1, 0) - RM(0, 1)) * 0.5f;
+    float sin_angle_abs = sqrtf(dotP(rot, rot));
+    if (cos_angle > M_SQRT1_2) {
+        if (sin_angle_abs) { float p = asinf(sin_angle_abs) / sin_angle_abs; rot.x *= p; rot.y *= p; rot.z *= p; }
+    } else if (cos_angle > -M_SQRT1_2) {
+        float p = acosf(cos_angle) / sin_angle_abs; rot.x *= p; rot.y *= p; rot.z *= p;
+    } else {
+        float angle = (float)M_PI - asinf(sin_angle_abs);
+        float d0 = RM(0, 0) - cos_angle, d1 = RM(1, 1) - cos_angle, d2 = RM(2, 2) - cos_angle;
+        P3 r2;
+        if (fabsf(d0) > fabsf(d1) && fabsf(d0) > fabsf(d2)) { r2.x = d0; r2.y = (RM(1, 0) + RM(0, 1)) * 0.5f; r2.z = (RM(0, 2) + RM(2, 0)) * 0.5f; }
+        else if (fabsf(d1) > fabsf(d2)) { r2.x = (RM(1, 0) + RM(0, 1)) * 0.5f; r2.y = d1; r2.z = (RM(2, 1) + RM(1, 2)) * 0.5f; }
+        else { r2.x = (RM(0, 2) + RM(2, 0)) * 0.5f; r2.y = (RM(2, 1) + RM(1, 2)) * 0.5f; r2.z = d2; }
+        if (dotP(r2, rot) < 0.0f) { r2.x *= -1.0f; r2.y *= -1.0f; r2.z *= -1.0f; }
+        float len = sqrtf(dotP(r2, r2));
+        if (len == 0) { r2.x = r2.y = r2.z = 0; } else { r2.x /= len; r2.y /= len; r2.z /= len; }
+        rot.x = angle * r2.x; rot.y = angle * r2.y; rot.z = angle * r2.z;
+    }
+#undef RM
+    float shtot = 0.5f, theta = sqrtf(dotP(rot, rot));
+    if (theta > 0.00001f) shtot = sinf(theta * 0.5f) / theta;
+    float H[16];
+    P3 zero = {0.0f, 0.0f, 0.0f}, hw = {rot.x * -0.5f, rot.y * -0.5f, rot.z * -0.5f};
+    poseToMatrix(zero, hw, H);
+    P3 rt;   // Matrix3 * Vector3, ORUtils/Matrix.h:310-316
+    rt.x = H[0] * T.x + H[4] * T.y + H[8] * T.z;
+    rt.y = H[1] * T.x + H[5] * T.y + H[9] * T.z;
+    rt.z = H[2] * T.x + H[6] * T.y + H[10] * T.z;
+    if (theta > 0.001f) {
+        float denom = dotP(rot, rot);
+        float param = dotP(T, rot) * (1 - 2 * shtot) / denom;
+        rt.x -= rot.x * param; rt.y -= rot.y * param; rt.z -= rot.z * param;
+    } else {
+        float param = dotP(T, rot) / 24;
+        rt.x -= rot.x * param; rt.y -= rot.y * param; rt.z -= rot.z * param;
+    }
+    rt.x /= 2 * shtot; rt.y /= 2 * shtot; rt.z /= 2 * shtot;
+    tOut = rt; wOut = rot;
+}
+
+// ORUtils::Cholesky<float>, ORUtils/Cholesky.h:11-72
+struct Chol {
+    std::vector<float> a; int n;
+    Chol(const float *mat, int size) : a(mat, mat + size * size), n(size)
+    {
+        for (int c = 0; c < n; c++) {
+            float inv_diag = 1;
+            for (int r = c; r < n; r++) {
+                float val = a[c + r * n];
+                for (int c2 = 0; c2 < c; c2++) val -= a[c + c2 * n] * a[c2 + r * n];
+                if (r == c) { a[c + r * n] = val; inv_diag = 1.0f / val; }
+                else { a[r + c * n] = val; a[c + r * n] = val * inv_diag; }
+            }
+        }
+    }
+    void backsub(float *result, const float *v) const
+    {
+        std::vector<float> y(n);
+        for (int i = 0; i < n; i++) { float val = v[i]; for (int j = 0; j < i; j++) val -= a[j + i * n] * y[j]; y[i] = val; }
+        for (int i = 0; i < n; i++) y[i] /= a[i + i * n];
+        for (int i = n - 1; i >= 0; i--) { float val = y[i]; for (int j = i + 1; j < n; j++) val -= a[i + j * n] * result[j]; result[i] = val; }
+    }
+};
+
+} // namespace
+
+extern "C" {
+
+// ITMPose::Coerce (Objects/ITMPose.cpp:345-349) on a raw matrix; params = (tx, ty, tz, rx, ry, rz)
+void rst_pose_coerce(float *M, float *params)
+{
+    P3 t, w; matrixToPose(M, t, w); poseToMatrix(t, w, M);
+    if (params) { params[0] = t.x; params[1] = t.y; params[2] = t.z; params[3] = w.x; params[4] = w.y; params[5] = w.z; }
+}
+void rst_pose_from_params(const float *p, float *M)
+{
+    P3 t = {p[0], p[1], p[2]}, w = {p[3], p[4], p[5]}; poseToMatrix(t, w, M);
+}
+
+// ITMDepthTracker::TrackCamera, Engine/ITMDepthTracker.cpp:153-211 with the ctor's schedules (:12-40).
+// double_sums selects the accumulation of the G&H sums (0 = the reference CPU engine's float accumulators).
+// hessian_good / nabla_good start zeroed here (uninitialised in the reference) and, like libdsb200, a level whose first
+// evaluation fails before any good evaluation exists is left without a step.
+void rst_track_camera(const dsb200_tracker_config *cfg, const dsb200_view *view, dsb200_tracking *trk, const float *scenePose,
+                      int sceneW, int sceneH, int doubleSums, dsb200_tracker_report *report)
+{
+    const int L = cfg->levels;
+    std::vector<std::vector<float> > pyr(L);
+    std::vector<const float *> depth(L); std::vector<int> w(L), h(L); float intr[DSB200_TRACKER_MAX_LEVELS][4];
+    depth[0] = view->depth; w[0] = view->depth_w; h[0] = view->depth_h;
+    for (int k = 0; k < 4; k++) intr[0][k] = view->intr_d[k];
+    for (int i = 1; i < L; i++) {   // PrepareForEvaluation :66-76
+        w[i] = w[i - 1] / 2; h[i] = h[i - 1] / 2; pyr[i].resize((size_t)w[i] * h[i]);
+        rst_filter_subsample_with_holes(depth[i - 1], w[i - 1], h[i - 1], pyr[i].data()); depth[i] = pyr[i].data();
+        for (int k = 0; k < 4; k++) intr[i][k] = intr[i - 1][k] * 0.5f;
+    }
+    float distThresh[DSB200_TRACKER_MAX_LEVELS]; int noIter[DSB200_TRACKER_MAX_LEVELS];
+    noIter[0] = 2; for (int i = 1; i < L; i++) noIter[i] = noIter[i - 1] + 2;
+    float distThreshStep = cfg->dist_thresh / L;
+    distThresh[L - 1] = cfg->dist_thresh;
+    for (int i = L - 2; i >= 0; i--) distThresh[i] = distThresh[i + 1] - distThreshStep;
+
+    float M[16]; memcpy(M, trk->M_d, sizeof(M));
+    float f_old = 1e10, f_new = 0;
+    float hessian_good[36] = {0}, hessian_new[36] = {0}, A[36], nabla_good[6] = {0}, nabla_new[6] = {0}, step[6];
+    bool haveGood = false;
+    if (report) memset(report, 0, sizeof(*report));
+    (void)f_old;
+    for (int levelId = L - 1; levelId >= cfg->no_icp_run_till_level; levelId--) {
+        int iterationType = cfg->regime[levelId];
+        if (iterationType == DSB200_TRACKER_ITERATION_NONE) continue;
+        float approxInvPose[16], lastGood[16];
+        rst_mat4_inverse(M, approxInvPose); memcpy(lastGood, M, sizeof(M));
+        f_old = 1e20f; float lambda = 1.0;
+        for (int iterNo = 0; iterNo < noIter[levelId]; iterNo++) {
+            int n = rst_tracker_compute_g_and_h(depth[levelId], w[levelId], h[levelId], intr[levelId], trk->icp_points,
+                                                trk->icp_normals, sceneW, sceneH, view->intr_d, scenePose, approxInvPose,
+                                                distThresh[levelId], iterationType, doubleSums, &f_new, nabla_new, hessian_new, nullptr);
+            if (report) { report->evaluations++; report->last_valid_points = n; report->last_f = f_new; }
+            if (n <= 0 || f_new > f_old) {
+                memcpy(M, lastGood, sizeof(M)); rst_mat4_inverse(M, approxInvPose); lambda *= 10.0f;
+            } else {
+                memcpy(lastGood, M, sizeof(M)); f_old = f_new;
+                for (int i = 0; i < 36; ++i) hessian_good[i] = hessian_new[i] / n;
+                for (int i = 0; i < 6; ++i) nabla_good[i] = nabla_new[i] / n;
+                lambda /= 10.0f; haveGood = true;
+            }
+            if (!haveGood) break;
+            for (int i = 0; i < 36; ++i) A[i] = hessian_good[i];
+            for (int i = 0; i < 6; ++i) A[i + i * 6] *= 1.0f + lambda;
+            // ComputeDelta :86-109
+            for (int i = 0; i < 6; i++) step[i] = 0;
+            if (iterationType != DSB200_TRACKER_ITERATION_BOTH) {
+                float sm[9]; for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) sm[r + c * 3] = A[r + c * 6];
+                Chol ch(sm, 3); ch.backsub(step, nabla_good);
+            } else { Chol ch(A, 6); ch.backsub(step, nabla_good); }
+            // ApplyDelta :122-151
+            float s[6] = {0, 0, 0, 0, 0, 0};
+            if (iterationType == DSB200_TRACKER_ITERATION_ROTATION) { s[0] = step[0]; s[1] = step[1]; s[2] = step[2]; }
+            else if (iterationType == DSB200_TRACKER_ITERATION_TRANSLATION) { s[3] = step[0]; s[4] = step[1]; s[5] = step[2]; }
+            else for (int i = 0; i < 6; i++) s[i] = step[i];
+            float Tinc[16];
+            Tinc[0] = 1.0f; Tinc[4] = s[2]; Tinc[8] = -s[1]; Tinc[12] = s[3];
+            Tinc[1] = -s[2]; Tinc[5] = 1.0f; Tinc[9] = s[0]; Tinc[13] = s[4];
+            Tinc[2] = s[1]; Tinc[6] = -s[0]; Tinc[10] = 1.0f; Tinc[14] = s[5];
+            Tinc[3] = 0.0f; Tinc[7] = 0.0f; Tinc[11] = 0.0f; Tinc[15] = 1.0f;
+            float next[16]; rst_mat4_multiply(Tinc, approxInvPose, next);
+            rst_mat4_inverse(next, M);          // pose_d->SetInvM
+            rst_pose_coerce(M, nullptr);        // pose_d->Coerce
+            rst_mat4_inverse(M, approxInvPose); // pose_d->GetInvM
+            if (report) report->steps++;
+            float stepLength = 0.0f;            // HasConverged :111-120
+            for (int i = 0; i < 6; i++) stepLength += step[i] * step[i];
+            if (sqrtf(stepLength) / 6 < cfg->termination_threshold) break;
+        }
+    }
+    memcpy(trk->M_d, M, sizeof(M)); rst_mat4_inverse(M, trk->invM_d);
+}
+
+} // extern "C"

@@ -71,6 +71,19 @@ void rst_forward_render(const dsb200_scene *scene, const dsb200_view *view, dsb2
                         dsb200_render_state *rs, float *forward_projection, int *missing_points,
                         int *no_missing);
 
+/* ICP depth tracker, device half (CPU/ITMDepthTracker_CPU.cpp:13-79, CPU/ITMLowLevelEngine_CPU.cpp:50-62) */
+void rst_filter_subsample_with_holes(const float *in, int w, int h, float *out);
+int rst_tracker_compute_g_and_h(const float *depth, int view_w, int view_h, const float *view_intrinsics,
+                                const float *points, const float *normals, int scene_w, int scene_h,
+                                const float *scene_intrinsics, const float *scene_pose, const float *approx_inv_pose,
+                                float dist_thresh, int iteration_type, int double_sums, float *f, float *nabla,
+                                float *hessian, double *sums);
+
+void rst_pose_coerce(float *M, float *params);
+void rst_pose_from_params(const float *params, float *M);
+void rst_track_camera(const dsb200_tracker_config *cfg, const dsb200_view *view, dsb200_tracking *tracking,
+                      const float *scene_pose, int scene_w, int scene_h, int double_sums, dsb200_tracker_report *report);
+
 int rst_mat4_inverse(const float *M, float *out);
 void rst_mat4_multiply(const float *A, const float *B, float *out);
 
