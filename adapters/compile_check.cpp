@@ -3,6 +3,8 @@
 // two interfaces with matching signatures, and that the reference's struct layouts match include/dsb200.h.
 #include "ITMSceneReconstructionEngine_B200.h"
 #include "ITMVisualisationEngine_B200.h"
+#include "ITMDepthTracker_B200.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
 
 using namespace ITMLib::Engine;
 
@@ -21,3 +23,10 @@ static_assert((int)IITMVisualisationEngine::RENDER_SHADED_GREYSCALE == DSB200_RE
 // what ITMDenseMapper / ITMMainEngine would do with deviceType == DEVICE_B200 (never executed here: no GPU)
 ITMSceneReconstructionEngine<ITMVoxel, ITMVoxelIndex> *make_recon() { return new ITMSceneReconstructionEngine_B200<ITMVoxel, ITMVoxelIndex>(); }
 IITMVisualisationEngine *make_vis(Vector2i imgSize) { return new ITMVisualisationEngine_B200<ITMVoxel, ITMVoxelIndex>(imgSize); }
+// ITMTrackerFactory.h:147 with deviceType == DEVICE_B200 (the low-level engine would be ITMLowLevelEngine_CUDA there)
+ITMTracker *make_tracker(Vector2i imgSize, TrackerIterationType *regime, const ITMLowLevelEngine *lowLevelEngine)
+{
+	return new ITMDepthTracker_B200(imgSize, regime, 5, 0, 0.01f, 1e-3f, lowLevelEngine);
+}
+static_assert((int)TRACKER_ITERATION_ROTATION == DSB200_TRACKER_ITERATION_ROTATION && (int)TRACKER_ITERATION_TRANSLATION == DSB200_TRACKER_ITERATION_TRANSLATION &&
+              (int)TRACKER_ITERATION_BOTH == DSB200_TRACKER_ITERATION_BOTH && (int)TRACKER_ITERATION_NONE == DSB200_TRACKER_ITERATION_NONE, "TrackerIterationType values");

@@ -497,6 +497,93 @@ def run_batched(args, rank, world, local_rank):
             "gpu_launches": launches, "clocks": clocks}
 
 
+# ------------------------------------------------------------------------------------------------ tracking in the loop
+def run_tracked(args, rank, world, local_rank):
+    """SURVEY 8(f) rank 2: the whole InfiniTAM frame (ITMMainEngine::ProcessFrame) with NO external poses -- ICP depth
+    tracking of frame k against the raycast of frame k-1 (dsb200_tracker_track_camera), then allocate + integrate +
+    expected depths + raycast + ICP maps at the tracked pose.  Not the headline metric (DenseSLAM takes its poses from
+    ORB-SLAM2); reported as frames/s of the closed loop plus the drift against the synthetic ground truth."""
+    import torch
+    import torch.distributed as dist
+    abi = importlib.import_module(PKG + ".abi")
+    eng = importlib.import_module(PKG + ".engine")
+    lib = abi.load()
+    if lib.dsb200_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
+    abi.check(lib.dsb200_set_device(local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    K, Wm = args.steps, args.warmup
+    cfg, frames = make_frames(K + Wm, seed=rank)
+    W, H = cfg.W, cfg.H
+    scene = eng.ITMScene(cfg.params(), CAPS["num_blocks"], CAPS["bucket_num"], CAPS["excess_size"])
+    recon = eng.ITMSceneReconstructionEngine(CAPS["num_blocks"], CAPS["bucket_num"], CAPS["excess_size"])
+    recon.SetFusionWeightParams(cfg.depth_weighting, 10, 100)
+    vis = eng.ITMVisualisationEngine(W, H)
+    rs = vis.CreateRenderState(scene, (W, H))
+    trk = eng.ITMTrackingState(W, H)
+    view = eng.ITMView(W, H, cfg.intr)
+    tracker = eng.ITMDepthTracker((W, H))          # ITMLibSettings defaults: 5 levels, b b r r r, 0.1^2, 1e-3
+    d_depth = torch.from_numpy(np.stack([f.depth for f in frames])).to(dev)
+    d_rgb = torch.from_numpy(np.stack([f.rgb for f in frames])).to(dev)
+    recon.ResetScene(scene)
+    recon.SetAsync(True)
+    err, evals, track_ms = [], [], []
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def frame(i, timed):
+        view.c.depth, view.c.rgb, view.c.timestamp = d_depth[i].data_ptr(), d_rgb[i].data_ptr(), frames[i].timestamp
+        if i == 0:
+            trk.set_pose(frames[0].M)               # the first pose anchors the map, like ITMMainEngine's identity start
+        else:
+            if timed:
+                t0.record()
+            tracker.TrackCamera(trk, view)          # starts from the previous frame's estimate
+            if timed:
+                t1.record(); t1.synchronize()
+                track_ms.append(t0.elapsed_time(t1)); evals.append(tracker.report.evaluations)
+                err.append(float(np.abs(trk.pose()[0] - frames[i].M).max()))
+        recon.ProcessFrame(vis, scene, view, trk, rs, abi.FRAME_ALL)
+
+    for i in range(Wm):
+        frame(i, False)
+    recon.Sync(scene, rs)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    l0 = lib.dsb200_kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank); sampler.start()
+    e0.record()
+    for k in range(K):
+        frame(Wm + k, True)
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    recon.Sync(scene, rs)
+    launches = int(lib.dsb200_kernel_launch_count() - l0)
+    ms = float(e0.elapsed_time(e1))
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        dist.destroy_process_group()
+    if rank != 0:
+        return None
+    return {"metric": "frames/s track+alloc+integrate+raycast (closed loop, no external poses)", "value": world * K / (ms * 1e-3),
+            "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 math (f64 tracker sums) -> i16 sdf / u8 weights", "data": "synthetic",
+            "mode": "tracked",
+            "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; poses from the ICP depth tracker (5 levels, ITMLibSettings defaults)",
+                       "l2": "not flushed (closed loop: each frame depends on the previous one)"},
+            "tracker": {"ms_per_frame": float(np.mean(track_ms)), "evaluations_per_frame": float(np.mean(evals)),
+                        "pose_error_max_abs_entry": {"mean": float(np.mean(err)), "last": err[-1], "max": float(np.max(err))},
+                        "final_visible_blocks": int(rs.c.no_visible)},
+            "gpu_launches": launches, "clocks": clocks}
+
+
 # ------------------------------------------------------------------------------------------------ sharded scene
 def run_sharded(args, rank, world, local_rank):
     """BASELINE configs[3]: ONE scene partitioned by block ownership across the N GPUs (sharded.py).  Rank 0 owns the camera
@@ -573,7 +660,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scenes", type=int, default=8, help="--mode batched: independent sequences per GPU")
-    ap.add_argument("--mode", default="replicas", choices=["replicas", "sharded", "batched"],
+    ap.add_argument("--mode", default="replicas", choices=["replicas", "sharded", "batched", "tracked"],
                     help="N > 1: independent scenes per GPU (default, weak scaling) or ONE scene sharded by block ownership")
     ap.add_argument("--shard-mode", default="lookup", choices=["lookup", "composite"])
     ap.add_argument("--brick-log2", type=int, default=2)
@@ -593,6 +680,8 @@ def main():
         out = run_sharded(args, rank, world, local_rank)
     elif args.mode == "batched":
         out = run_batched(args, rank, world, local_rank)
+    elif args.mode == "tracked":
+        out = run_tracked(args, rank, world, local_rank)
     else:
         out = run_ours(args, rank, world, local_rank)
     if out is not None:

@@ -179,6 +179,8 @@ def load():
         "dsb200_tracker_set_evaluation_data": (C.c_int, [vp, vp, _P(C.c_float), vp, vp, i32, i32, _P(C.c_float), _P(C.c_float)]),
         "dsb200_tracker_compute_g_and_h": (C.c_int, [vp, i32, i32, C.c_float, _P(C.c_float), _P(C.c_float), _P(C.c_float),
                                                      _P(C.c_float), _P(i32)]),
+        "dsb200_tracker_compute_g_and_h_on": (C.c_int, [vp, vp, i32, i32, _P(C.c_float), vp, vp, i32, i32, _P(C.c_float), _P(C.c_float),
+                                                        i32, C.c_float, _P(C.c_float), _P(C.c_float), _P(C.c_float), _P(C.c_float), _P(i32)]),
         "dsb200_tracker_last_sums": (C.c_int, [vp, _P(C.c_double)]),
         "dsb200_tracker_level": (C.c_int, [vp, i32, _P(vp), _P(i32), _P(i32), _P(C.c_float)]),
         "dsb200_filter_subsample_with_holes": (C.c_int, [vp, i32, i32, vp, vp]),

@@ -827,19 +827,16 @@ int dsb200_tracker_set_evaluation_data(dsb200_tracker *t, const float *depth, co
     return DSB200_OK;
 }
 
-int dsb200_tracker_compute_g_and_h(dsb200_tracker *t, int32_t level, int32_t iterationType, float distThresh,
-                                   const float *approxInvPose, float *f, float *nabla, float *hessian, int32_t *noValid)
+static int tracker_gh(dsb200_tracker *t, const float *depth, int vW, int vH, const float *vIntr, const float *points,
+                      const float *normals, int sW, int sH, const float *sIntr, const float *scenePose, int iterationType,
+                      float distThresh, const float *approxInvPose, float *f, float *nabla, float *hessian, int32_t *noValid)
 {
-    if (!t || !approxInvPose || !f || !nabla || !hessian || !noValid) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: null argument");
-    if (level < 0 || level >= t->levels) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: no such pyramid level");
-    if (!t->depth[0] || !t->points) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: set_evaluation_data has not been called");
     if (iterationType == DSB200_TRACKER_ITERATION_NONE) { *noValid = 0; return DSB200_OK; }   // ITMDepthTracker_CPU.cpp:25
     if (iterationType != DSB200_TRACKER_ITERATION_ROTATION && iterationType != DSB200_TRACKER_ITERATION_TRANSLATION &&
         iterationType != DSB200_TRACKER_ITERATION_BOTH)
         return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: unknown iteration type");
-    launch_tracker_gh(t->stream, iterationType, approxInvPose, t->scenePose, t->intr[level], t->sceneIntr, distThresh,
-                      t->depth[level], t->w[level], t->h[level], t->points, t->normals, t->sceneW, t->sceneH, t->partials,
-                      t->ticket, t->result);
+    launch_tracker_gh(t->stream, iterationType, approxInvPose, scenePose, vIntr, sIntr, distThresh, depth, vW, vH, points, normals,
+                      sW, sH, t->partials, t->ticket, t->result);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(t->hostResult, t->result, sizeof(double) * tracker_gh_slots(), cudaMemcpyDeviceToHost, t->stream));
     CU(cudaStreamSynchronize(t->stream));
@@ -856,6 +853,29 @@ int dsb200_tracker_compute_g_and_h(dsb200_tracker *t, int32_t level, int32_t ite
     *f = (n > 100) ? sqrtf(sumF) / (float)n : 1e5f;
     *noValid = n;
     return DSB200_OK;
+}
+
+int dsb200_tracker_compute_g_and_h(dsb200_tracker *t, int32_t level, int32_t iterationType, float distThresh,
+                                   const float *approxInvPose, float *f, float *nabla, float *hessian, int32_t *noValid)
+{
+    if (!t || !approxInvPose || !f || !nabla || !hessian || !noValid) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: null argument");
+    if (level < 0 || level >= t->levels) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: no such pyramid level");
+    if (!t->depth[0] || !t->points) return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: set_evaluation_data has not been called");
+    return tracker_gh(t, t->depth[level], t->w[level], t->h[level], t->intr[level], t->points, t->normals, t->sceneW, t->sceneH,
+                      t->sceneIntr, t->scenePose, iterationType, distThresh, approxInvPose, f, nabla, hessian, noValid);
+}
+
+int dsb200_tracker_compute_g_and_h_on(dsb200_tracker *t, const float *depth, int32_t vW, int32_t vH, const float *vIntr,
+                                      const float *points, const float *normals, int32_t sW, int32_t sH, const float *sIntr,
+                                      const float *scenePose, int32_t iterationType, float distThresh, const float *approxInvPose,
+                                      float *f, float *nabla, float *hessian, int32_t *noValid)
+{
+    if (!t || !depth || !vIntr || !points || !normals || !sIntr || !scenePose || !approxInvPose || !f || !nabla || !hessian || !noValid)
+        return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h_on: null argument");
+    if (vW <= 0 || vH <= 0 || sW < 2 || sH < 2 || sW > 32767 || sH > 32767 || ((uintptr_t)points & 15) || ((uintptr_t)normals & 15))
+        return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h_on: bad image size or unaligned maps");
+    return tracker_gh(t, depth, vW, vH, vIntr, points, normals, sW, sH, sIntr, scenePose, iterationType, distThresh, approxInvPose, f,
+                      nabla, hessian, noValid);
 }
 
 int dsb200_tracker_last_sums(const dsb200_tracker *t, double *sums)

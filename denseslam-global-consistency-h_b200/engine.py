@@ -354,6 +354,17 @@ class ITMDepthTracker(object):
         abi.check(_lib().dsb200_tracker_last_sums(self.h, sums))
         return n.value, f.value, np.array(nabla[:], np.float32), np.array(hessian[:], np.float32), np.array(sums[:], np.float64)
 
+    def ComputeGandHOn(self, view, trackingState, iterationType, distThresh, approxInvPose):
+        """the same evaluation on caller-owned images (dsb200_tracker_compute_g_and_h_on), here the view's full-size depth"""
+        f, n = C.c_float(), C.c_int32()
+        nabla, hessian, sums = (C.c_float * 6)(), (C.c_float * 36)(), (C.c_double * 32)()
+        abi.check(_lib().dsb200_tracker_compute_g_and_h_on(
+            self.h, view.c.depth, view.c.depth_w, view.c.depth_h, view.c.intr_d, trackingState.c.icp_points,
+            trackingState.c.icp_normals, trackingState.W, trackingState.H, view.c.intr_d, abi.f16(trackingState.pose_pointCloud),
+            iterationType, distThresh, abi.f16(approxInvPose), C.byref(f), nabla, hessian, C.byref(n)))
+        abi.check(_lib().dsb200_tracker_last_sums(self.h, sums))
+        return n.value, f.value, np.array(nabla[:], np.float32), np.array(hessian[:], np.float32), np.array(sums[:], np.float64)
+
     def Level(self, levelId):
         """(depth image copy, intrinsics) of a pyramid level after SetEvaluationData / TrackCamera"""
         p, w, h = C.c_void_p(), C.c_int32(), C.c_int32()

@@ -311,6 +311,15 @@ int dsb200_tracker_set_evaluation_data(dsb200_tracker *t, const float *depth, co
 int dsb200_tracker_compute_g_and_h(dsb200_tracker *t, int32_t level, int32_t iteration_type, float dist_thresh,
                                    const float *approx_inv_pose, float *f, float *nabla, float *hessian,
                                    int32_t *no_valid_points);
+/* The same evaluation on caller-owned images (what a subclass of the reference's ITMDepthTracker forwards its protected
+ * evaluation state to: viewHierarchyLevel->depth / intrinsics, sceneHierarchyLevel->pointsMap / normalsMap / intrinsics,
+ * scenePose, distThresh[levelId], iterationType); the tracker handle only lends its reduction scratch and stream. */
+int dsb200_tracker_compute_g_and_h_on(dsb200_tracker *t, const float *depth, int32_t view_w, int32_t view_h,
+                                      const float *view_intrinsics, const float *points, const float *normals,
+                                      int32_t scene_w, int32_t scene_h, const float *scene_intrinsics,
+                                      const float *scene_pose, int32_t iteration_type, float dist_thresh,
+                                      const float *approx_inv_pose, float *f, float *nabla, float *hessian,
+                                      int32_t *no_valid_points);
 /* raw double sums of the last compute_g_and_h: [0,NH) hessian lower triangle by rows, [NH,NH+NP) nabla, sum b^2, count */
 int dsb200_tracker_last_sums(const dsb200_tracker *t, double *sums /* [32] */);
 /* pyramid level access (device pointer owned by the tracker; level 0 is the caller's image) */
