@@ -60,12 +60,17 @@ class ClockSampler(object):
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
-        self.rows, self.proc, self.gpu = [], None, gpu_index
+    def __init__(self, gpu_index, rank=0, world=1):
+        # N > 1: rank 0 alone samples, all N GPUs with one nvidia-smi process (N concurrent NVML pollers perturb submission)
+        self.rows, self.proc = [], None
+        self.gpu = ",".join(str(i) for i in range(world)) if world > 1 else str(gpu_index)
+        self.enabled = rank == 0
 
     def start(self):
+        if not self.enabled:
+            return
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", self.gpu, "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -77,6 +82,8 @@ class ClockSampler(object):
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
+        if not self.enabled:
+            return None
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -187,7 +194,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     K, Wm = args.steps, args.warmup
-    cfg, frames = make_frames(K + Wm, seed=rank)
+    cfg, frames = make_frames(K + Wm, seed=0)      # replicas: every GPU runs the same sequence (weak scaling, equal work per GPU)
     W, H = cfg.W, cfg.H
     npx = W * H
 
@@ -280,7 +287,7 @@ def run_ours(args, rank, world, local_rank):
         recon.SetAsync(False)
         return ms, stage, counts, n_launch
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, rank, world)
     sampler.start()
     dev_ms, _, vis_counts, launches = resident_pass(False)
     clocks = sampler.stop()
@@ -388,7 +395,7 @@ def run_ours(args, rank, world, local_rank):
     out = {"metric": METRIC, "value": world * K / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic",
-           "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only)", "frames": K, "mean_visible_blocks": V,
+           "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only; every GPU runs the same synthetic sequence)", "frames": K, "mean_visible_blocks": V,
                       "blocks_allocated": int(blocks_used), "capacity_blocks": CAPS["num_blocks"], "l2": "flushed (256 MiB write) between timed steps"},
            "e2e": {"value": world * K / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": 5 * npx,
                    "d2h_bytes_per_step": 4 * npx, "ms_per_step": e2e_ms / K,
@@ -431,7 +438,7 @@ def run_batched(args, rank, world, local_rank):
     caps = dict(num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS, excess_size=abi.DEFAULT_EXCESS)   # the reference's capacities
     lanes = []
     for si in range(S):
-        cfg, frames = make_frames(K + Wm, seed=rank * S + si)
+        cfg, frames = make_frames(K + Wm, seed=si)
         st = torch.cuda.Stream()
         scene = eng.ITMScene(cfg.params(), **caps)
         recon = eng.ITMSceneReconstructionEngine(stream=st.cuda_stream, **caps)
@@ -464,7 +471,7 @@ def run_batched(args, rank, world, local_rank):
     l0 = lib.dsb200_kernel_launch_count()
     main = torch.cuda.current_stream()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank); sampler.start()
+    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     e0.record()
     for L in lanes:
         L["st"].wait_event(e0)
@@ -516,7 +523,7 @@ def run_tracked(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     K, Wm = args.steps, args.warmup
-    cfg, frames = make_frames(K + Wm, seed=rank)
+    cfg, frames = make_frames(K + Wm, seed=0)
     W, H = cfg.W, cfg.H
     scene = eng.ITMScene(cfg.params(), CAPS["num_blocks"], CAPS["bucket_num"], CAPS["excess_size"])
     recon = eng.ITMSceneReconstructionEngine(CAPS["num_blocks"], CAPS["bucket_num"], CAPS["excess_size"])
@@ -555,7 +562,7 @@ def run_tracked(args, rank, world, local_rank):
         dist.barrier()
     l0 = lib.dsb200_kernel_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank); sampler.start()
+    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     e0.record()
     for k in range(K):
         frame(Wm + k, True)
@@ -616,7 +623,7 @@ def run_sharded(args, rank, world, local_rank):
     torch.cuda.synchronize(); dist.barrier()
     l0 = lib.dsb200_kernel_launch_count()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    sampler = ClockSampler(local_rank); sampler.start()
+    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     vis_counts = []
     for k in range(K):
         flush.zero_()

@@ -787,10 +787,12 @@ int dsb200_tracker_create(dsb200_tracker **out, int32_t width, int32_t height, i
         t->depth[i] = t->owned[i];
     }
     CU(cudaMalloc(&t->partials, sizeof(double) * (size_t)tracker_gh_max_ctas() * tracker_gh_slots()));
-    CU(cudaMalloc(&t->result, sizeof(double) * tracker_gh_slots()));
     CU(cudaMalloc(&t->ticket, sizeof(unsigned)));
     CU(cudaMemset(t->ticket, 0, sizeof(unsigned)));
-    CU(cudaMallocHost(&t->hostResult, sizeof(double) * tracker_gh_slots()));
+    // the last CTA writes the 30 sums straight into mapped pinned memory: no copy call between the kernel and the host's read
+    CU(cudaHostAlloc(&t->hostResult, sizeof(double) * tracker_gh_slots(), cudaHostAllocMapped));
+    CU(cudaHostGetDevicePointer(&t->result, t->hostResult, 0));
+    memset(t->hostResult, 0, sizeof(double) * tracker_gh_slots());
     *out = t.release();
     return DSB200_OK;
 }
@@ -799,7 +801,7 @@ int dsb200_tracker_destroy(dsb200_tracker *t)
 {
     if (!t) return DSB200_OK;
     for (int i = 1; i < t->levels; i++) cudaFree(t->owned[i]);
-    cudaFree(t->partials); cudaFree(t->result); cudaFree(t->ticket); cudaFreeHost(t->hostResult);
+    cudaFree(t->partials); cudaFree(t->ticket); cudaFreeHost(t->hostResult);
     delete t;
     return DSB200_OK;
 }
@@ -838,8 +840,7 @@ static int tracker_gh(dsb200_tracker *t, const float *depth, int vW, int vH, con
     launch_tracker_gh(t->stream, iterationType, approxInvPose, scenePose, vIntr, sIntr, distThresh, depth, vW, vH, points, normals,
                       sW, sH, t->partials, t->ticket, t->result);
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(t->hostResult, t->result, sizeof(double) * tracker_gh_slots(), cudaMemcpyDeviceToHost, t->stream));
-    CU(cudaStreamSynchronize(t->stream));
+    CU(cudaStreamSynchronize(t->stream));      // t->result aliases t->hostResult (mapped)
     const bool shortIt = iterationType != DSB200_TRACKER_ITERATION_BOTH;
     const int noPara = shortIt ? 3 : 6, noParaSQ = shortIt ? 6 : 21;
     t->lastPara = noPara;

@@ -178,7 +178,8 @@ __global__ void __launch_bounds__(kGhThreads) k_tracker_gh(TrackerParams P, cons
     if (threadIdx.x <= NV) {
         double s = 0.0;
         for (unsigned cta = 0; cta < gridDim.x; cta++) s += __ldcg(partials + (size_t)cta * kGhSlots + threadIdx.x);
-        result[threadIdx.x] = s;
+        result[threadIdx.x] = s;           // mapped host memory
+        __threadfence_system();
     }
     if (threadIdx.x == 0) *ticket = 0;   // re-armed for the next launch on this stream
 }
