@@ -194,7 +194,9 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     K, Wm = args.steps, args.warmup
-    cfg, frames = make_frames(K + Wm, seed=0)      # replicas: every GPU runs the same sequence (weak scaling, equal work per GPU)
+    cfg, frames = make_frames(K + Wm + 1, seed=0)  # replicas: every GPU runs the same sequence (weak scaling, equal work per GPU);
+    # one extra frame: the look-ahead issued during the last timed frame has a real successor, so every timed frame carries
+    # exactly one request pass (its successor's) and none is left outside the timed region
     W, H = cfg.W, cfg.H
     npx = W * H
 
@@ -234,10 +236,17 @@ def run_ours(args, rank, world, local_rank):
             prune_ev[1].synchronize()
             prune_ms[0] += prune_ev[0].elapsed_time(prune_ev[1])
 
-    def frame_async(i, timed_prune=False):
+    lookahead = not args.no_lookahead
+
+    def frame_async(i, timed_prune=False, profile=False):
         trk.set_pose(frames[i].M)
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views[i]), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
         prune_pass(timed_prune)
+        if lookahead and not profile and i + 1 < len(views):
+            # streaming look-ahead: the request pass of frame i+1 overlaps the raycast of frame i
+            trk.set_pose(frames[i + 1].M)
+            abi.check(lib.dsb200_recon_prefetch_allocation(recon.h, C.byref(scene.c), C.byref(views[i + 1]), C.byref(trk.c), C.byref(rs.c), None))
+            abi.check(lib.dsb200_recon_join_prefetch(recon.h))     # the frame's closing event (and the L2 flush) come after the look-ahead
 
     def reset_all():
         recon.ResetScene(scene)
@@ -258,7 +267,7 @@ def run_ours(args, rank, world, local_rank):
         stage = np.zeros(abi.PROFILE_STAGES)
         counts = []
         for i in range(Wm):
-            frame_async(i)
+            frame_async(i, False, profile)
         recon.Sync(scene, rs)
         torch.cuda.synchronize()
         if world > 1:
@@ -269,7 +278,7 @@ def run_ours(args, rank, world, local_rank):
         for k in range(K):
             flush.zero_()                      # L2 flush between timed iterations (outside the event pair)
             evs[k][0].record()
-            frame_async(Wm + k, profile)
+            frame_async(Wm + k, profile, profile)
             evs[k][1].record()
             if profile:
                 abi.check(lib.dsb200_profile_read(recon.h, stage_buf))      # synchronises; device-side stage times
@@ -340,6 +349,11 @@ def run_ours(args, rank, world, local_rank):
         rs.c.raycast_image = imgs_e[b]
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views_e[b].c), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
         prune_pass()
+        if lookahead and i + 1 < last:
+            nb = (i + 1) & 1                                 # request pass of frame i+1 as soon as its upload has landed
+            trk.set_pose(frames[i + 1].M)
+            abi.check(lib.dsb200_recon_prefetch_allocation(recon.h, C.byref(scene.c), C.byref(views_e[nb].c), C.byref(trk.c), C.byref(rs.c),
+                                                           ev_ready[nb].cuda_event))
         ev_free[b].record(main)
         ev_done[b].record(main)
         s_down.wait_event(ev_done[b])
@@ -351,7 +365,7 @@ def run_ours(args, rank, world, local_rank):
         ev_free[b].record(main); ev_read[b].record(main)
     upload(0)
     for i in range(Wm):
-        frame_e2e(i, Wm + K)
+        frame_e2e(i, Wm + K + 1)
     recon.Sync(scene, rs)
     torch.cuda.synchronize()
     if world > 1:
@@ -360,7 +374,8 @@ def run_ours(args, rank, world, local_rank):
     t0 = time.perf_counter()
     e0.record()
     for k in range(K):
-        frame_e2e(Wm + k, Wm + K)
+        frame_e2e(Wm + k, Wm + K + 1)       # the last timed frame still uploads and looks ahead to a successor
+    abi.check(lib.dsb200_recon_join_prefetch(recon.h))
     main.wait_stream(s_down)
     e1.record()
     torch.cuda.synchronize()
@@ -395,12 +410,15 @@ def run_ours(args, rank, world, local_rank):
     out = {"metric": METRIC, "value": world * K / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic",
-           "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only; every GPU runs the same synthetic sequence)", "frames": K, "mean_visible_blocks": V,
+           "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only; every GPU runs the same synthetic sequence)",
+                      "lookahead": ("request pass of frame k+1 submitted with frame k and joined before frame k's closing event (results bit-identical)"
+                                    if lookahead else "off"), "frames": K, "mean_visible_blocks": V,
                       "blocks_allocated": int(blocks_used), "capacity_blocks": CAPS["num_blocks"], "l2": "flushed (256 MiB write) between timed steps"},
            "e2e": {"value": world * K / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": 5 * npx,
                    "d2h_bytes_per_step": 4 * npx, "ms_per_step": e2e_ms / K,
                    "input": "int16 mm depth + packed BGR from pinned host memory, view built on the device (dsb200_view_from_raw)",
-                   "pipeline": "double-buffered: upload of frame k+1 and read-back of frame k-1 overlap the fusion of frame k; one host sync at the end"},
+                   "pipeline": "double-buffered: upload of frame k+1 and read-back of frame k-1 overlap the fusion of frame k; one host sync at the end"
+                               + ("; allocation request pass of frame k+1 overlaps the raycast of frame k (dsb200_recon_prefetch_allocation)" if lookahead else "")},
            "gpu_launches": launches, "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
@@ -671,6 +689,8 @@ def main():
                     help="N > 1: independent scenes per GPU (default, weak scaling) or ONE scene sharded by block ownership")
     ap.add_argument("--shard-mode", default="lookup", choices=["lookup", "composite"])
     ap.add_argument("--brick-log2", type=int, default=2)
+    ap.add_argument("--no-lookahead", action="store_true",
+                    help="do not overlap the next frame's allocation request pass with the current frame's raycast")
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS.keys()),
                     help="BASELINE.json config to run (default C2: the configuration the metric is quoted on)")
     args = ap.parse_args()

@@ -113,6 +113,11 @@ struct dsb200_recon {
     int lastKnownVisible = 0;         // visible count at the last host sync: sizes the snapshot reservations made while asynchronous
     const uint8_t *visBitsOwner = nullptr;   // the render state's visibility-flag array that fs.visBits currently describes
     cudaStream_t sideStream = nullptr; cudaEvent_t evFork = nullptr, evJoin = nullptr;   // fused frame: expected depths || integration
+    // look-ahead (dsb200_recon_prefetch_allocation): first half of the next frame's allocation on its own stream
+    cudaStream_t prefetchStream = nullptr; cudaEvent_t evSceneWritten = nullptr, evPrefetchDone = nullptr;
+    unsigned long long modEpoch = 0, epochSceneWritten = ~0ull;   // scene-modifying calls so far / value when evSceneWritten was recorded
+    bool prefetchPending = false;
+    struct PrefetchKey { const float *depth; int w, h; float M[16], invM[16], intr[4]; const uint8_t *visType; } prefetchKey{};
     // SDF shadow: one short per voxel of the scene this engine maintains, kept in step by every kernel that writes voxels
     // (reset, integrate, de-integrate, pruning) and read by the fused frame's raycast instead of the 8-byte voxel records.
     short *sdfShadow = nullptr; const void *shadowFor = nullptr; bool shadowEnabled = true;
@@ -187,6 +192,9 @@ int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_n
     CU(cudaStreamCreateWithFlags(&e->sideStream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&e->evJoin, cudaEventDisableTiming));
+    CU(cudaStreamCreateWithFlags(&e->prefetchStream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&e->evSceneWritten, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e->evPrefetchDone, cudaEventDisableTiming));
     // 2 bytes per voxel = +25 % of the voxel array; if it does not fit the engine simply runs without it
     if (cudaMalloc(&e->sdfShadow, (size_t)num_blocks * DSB200_BLOCK_SIZE3 * sizeof(short)) != cudaSuccess) { cudaGetLastError(); e->sdfShadow = nullptr; }
     e->pruneCap = num_blocks;
@@ -200,6 +208,7 @@ int dsb200_recon_destroy(dsb200_recon *e)
     if (!e) return DSB200_OK;
     cudaStreamSynchronize(e->stream);
     if (e->sideStream) { cudaStreamSynchronize(e->sideStream); cudaStreamDestroy(e->sideStream); cudaEventDestroy(e->evFork); cudaEventDestroy(e->evJoin); }
+    if (e->prefetchStream) { cudaStreamSynchronize(e->prefetchStream); cudaStreamDestroy(e->prefetchStream); cudaEventDestroy(e->evSceneWritten); cudaEventDestroy(e->evPrefetchDone); }
     e->decayQ.clear(); e->slideQ.clear(); e->decayDefusionQ.clear(); e->slideDefusionQ.clear();
     e->snapshots.clear(); e->unsynced.clear();
     e->arena.release_all();
@@ -337,12 +346,17 @@ static short *shadow_for(dsb200_recon *e, const dsb200_scene *scene)
     return e->sdfShadow;
 }
 
-static int check_scene(const dsb200_recon *e, const dsb200_scene *scene)
+// Every scene-modifying entry point passes through here.  consumesPrefetch: the call is an allocation that may pick up a
+// pending look-ahead; any other call while one is pending would invalidate what the look-ahead already wrote.
+static int check_scene(dsb200_recon *e, const dsb200_scene *scene, bool consumesPrefetch = false)
 {
     if (!e || !scene || !scene->voxels || !scene->hash || !scene->alloc_list || !scene->excess_list)
         return fail(DSB200_ERR_INVALID, "null engine/scene pointer");
     if (scene->num_blocks != e->numBlocks || scene->bucket_num != e->bucketNum || scene->excess_size != e->excessSize)
         return fail(DSB200_ERR_INVALID, "scene capacities differ from the capacities the engine was created with");
+    if (e->prefetchPending && !consumesPrefetch)
+        return fail(DSB200_ERR_INVALID, "a prefetched allocation is pending: the next scene call must be the allocation of that frame");
+    e->modEpoch++;
     return DSB200_OK;
 }
 
@@ -361,10 +375,23 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     }
 #define DSB_MARK_A(i) do { if (e->profile) cudaEventRecord(e->evAlloc[i], e->stream); } while (0)
     DSB_MARK_A(0);
-    launch_begin_frame(e->stream, e->fs, scene->last_free_block, scene->last_free_excess, rs->no_visible, useHost ? 1 : 0,
-                       rs->visible_ids, rs->visible_type, useHost ? rs->no_visible : rs->visible_capacity);
-    DSB_MARK_A(1);
-    launch_alloc_requests(e->stream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    if (e->prefetchPending) {
+        const dsb200_recon::PrefetchKey &k = e->prefetchKey;
+        e->prefetchPending = false;
+        if (k.depth != view->depth || k.w != AP.W || k.h != AP.H || k.visType != rs->visible_type || memcmp(k.M, trk->M_d, 64) ||
+            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost)
+            return fail(DSB200_ERR_INVALID, "the pending prefetched allocation was made for a different view / pose / render state");
+        CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));     // setToType3 + requests already ran on the look-ahead stream
+        DSB_MARK_A(1);
+    } else {
+        launch_begin_frame(e->stream, e->fs, scene->last_free_block, scene->last_free_excess, rs->no_visible, useHost ? 1 : 0,
+                           rs->visible_ids, rs->visible_type, useHost ? rs->no_visible : rs->visible_capacity);
+        DSB_MARK_A(1);
+        launch_alloc_requests(e->stream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    }
+    // The host mirrors seeded the device counters above (first asynchronous frame of an engine that has never synchronised);
+    // from here on the device copies are the authoritative ones until the next dsb200_recon_sync.
+    if (e->async) e->deviceCountersValid = true;
     DSB_MARK_A(2);
     launch_allocate(e->stream, AP, e->fs, view->depth, scene->hash, scene->alloc_list, scene->excess_list, rs->visible_type,
                     e->reqKey, e->total, onlyVisible ? 0 : 1);
@@ -426,6 +453,10 @@ extern "C" {
 
 int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
 {
+    if (e && e->prefetchPending) {       // a reset abandons a pending look-ahead: let its kernels finish, then wipe what they wrote
+        CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));
+        e->prefetchPending = false;
+    }
     int rc = check_scene(e, scene); if (rc) return rc;
     e->totalDecayed = 0;
     e->decayQ.clear(); e->slideQ.clear(); e->snapshots.clear();   // CUDA .cu:116-131
@@ -437,6 +468,8 @@ int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
     CU(cudaGetLastError());
     scene->last_free_block = scene->num_blocks - 1;
     scene->last_free_excess = scene->excess_size - 1;
+    e->deviceCountersValid = true;       // k_reset_scene initialised every device counter
+    e->lastKnownVisible = 0;
     if (!e->async) CU(cudaStreamSynchronize(e->stream));
     return DSB200_OK;
 }
@@ -444,7 +477,7 @@ int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
 int dsb200_allocate_from_depth(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
                                dsb200_render_state *rs, int onlyVisible, int isDefusion)
 {
-    int rc = check_scene(e, scene); if (rc) return rc;
+    int rc = check_scene(e, scene, true); if (rc) return rc;
     if (!view || !trk || !rs || !view->depth) return fail(DSB200_ERR_INVALID, "allocate: null view/tracking/render state");
     rc = enqueue_allocate(e, scene, view, trk, rs, onlyVisible, isDefusion); if (rc) return rc;
     return finish_call(e, scene, rs, true);
@@ -904,11 +937,49 @@ int dsb200_filter_subsample_with_holes(const float *in, int32_t w, int32_t h, fl
     return DSB200_OK;
 }
 
+// ---------------------------------------------------------------- look-ahead
+int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
+                                     dsb200_render_state *rs, void *waitEvent)
+{
+    if (!e || !scene || !view || !trk || !rs || !view->depth) return fail(DSB200_ERR_INVALID, "prefetch_allocation: null argument");
+    if (scene->num_blocks != e->numBlocks || scene->bucket_num != e->bucketNum || scene->excess_size != e->excessSize)
+        return fail(DSB200_ERR_INVALID, "scene capacities differ from the capacities the engine was created with");
+    if (e->prefetchPending) return fail(DSB200_ERR_INVALID, "prefetch_allocation: a prefetched allocation is already pending");
+    if (!(e->async && e->deviceCountersValid))
+        return fail(DSB200_ERR_INVALID, "prefetch_allocation: asynchronous mode with at least one frame submitted is required");
+    if (e->profile) return DSB200_OK;                               // per-stage timing keeps every kernel on the main stream
+    if (rs->visible_type != e->visBitsOwner) return fail(DSB200_ERR_INVALID, "prefetch_allocation: render state differs from the previous frame's");
+    AllocParams AP; make_alloc_params(AP, e, scene, view, trk);
+    if ((long long)AP.W * AP.H >= (1ll << 24)) return fail(DSB200_ERR_INVALID, "depth image too large for the 24-bit pixel order key");
+    if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
+    // Wait only for the last kernel that wrote the scene when that was the integration of the frame just submitted (its
+    // raycast then overlaps the look-ahead); after any other scene call, wait for everything submitted so far.
+    if (e->epochSceneWritten != e->modEpoch) CU(cudaEventRecord(e->evSceneWritten, e->stream));
+    CU(cudaStreamWaitEvent(e->prefetchStream, e->evSceneWritten, 0));
+    if (waitEvent) CU(cudaStreamWaitEvent(e->prefetchStream, (cudaEvent_t)waitEvent, 0));
+    launch_begin_frame(e->prefetchStream, e->fs, 0, 0, 0, 0, rs->visible_ids, rs->visible_type, rs->visible_capacity);
+    launch_alloc_requests(e->prefetchStream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(e->evPrefetchDone, e->prefetchStream));
+    dsb200_recon::PrefetchKey &k = e->prefetchKey;
+    k.depth = view->depth; k.w = AP.W; k.h = AP.H; k.visType = rs->visible_type;
+    memcpy(k.M, trk->M_d, 64); memcpy(k.invM, trk->invM_d, 64); memcpy(k.intr, view->intr_d, 16);
+    e->prefetchPending = true;
+    return DSB200_OK;
+}
+
+int dsb200_recon_join_prefetch(dsb200_recon *e)
+{
+    if (!e) return fail(DSB200_ERR_INVALID, "join_prefetch: null engine");
+    if (e->prefetchPending) CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));
+    return DSB200_OK;
+}
+
 // ---------------------------------------------------------------- fused frame
 int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, const dsb200_view *view, dsb200_tracking *trk,
                          dsb200_render_state *rs, int stages)
 {
-    int rc = check_scene(e, scene); if (rc) return rc;
+    int rc = check_scene(e, scene, (stages & DSB200_FRAME_ALLOCATE) != 0); if (rc) return rc;
     if ((stages & (DSB200_FRAME_EXPECTED_DEPTHS | DSB200_FRAME_ICP_MAPS | DSB200_FRAME_RAYCAST)) && (!v || v->stream != e->stream))
         return fail(DSB200_ERR_INVALID, "process_frame: the two engines must share one stream");
     const int *countPtr = &e->fs.counters->noVisible;
@@ -936,6 +1007,10 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     if (stages & DSB200_FRAME_INTEGRATE) {
         FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
         launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene));
+    }
+    if (e->async && !e->profile) {     // nothing after this point writes the scene: a look-ahead may start here
+        CU(cudaEventRecord(e->evSceneWritten, e->stream));
+        e->epochSceneWritten = e->modEpoch;
     }
     DSB_MARK(2);
     if (fork) CU(cudaStreamWaitEvent(e->stream, e->evJoin, 0));

@@ -245,6 +245,13 @@ class ITMSceneReconstructionEngine(object):
         _lib().dsb200_history_sizes(self.h, *[C.byref(x) for x in v])
         return tuple(x.value for x in v)
 
+    def PrefetchAllocation(self, scene, nextView, nextTrackingState, renderState, waitEvent=None):
+        """Look-ahead (asynchronous mode): the request pass of the NEXT frame's allocation, overlapping this frame's raycast.
+        nextView / nextTrackingState may be engine objects or raw abi.View / abi.Tracking structs."""
+        v = nextView.c if hasattr(nextView, "c") else nextView
+        t = nextTrackingState.c if hasattr(nextTrackingState, "c") else nextTrackingState
+        abi.check(_lib().dsb200_recon_prefetch_allocation(self.h, C.byref(scene.c), C.byref(v), C.byref(t), C.byref(renderState.c), waitEvent))
+
     def ProcessFrame(self, vis, scene, view, trackingState, renderState, stages=abi.FRAME_ALL):
         """ITMDenseMapper::ProcessFrame + ITMTrackingController::Prepare as one submission."""
         abi.check(_lib().dsb200_process_frame(self.h, vis.h if vis is not None else None, C.byref(scene.c), C.byref(view.c),

@@ -282,6 +282,21 @@ int dsb200_stream_synchronize(void *cuda_stream);
 int dsb200_mat4_inverse(const float *M, float *out);
 void dsb200_mat4_multiply(const float *A, const float *B, float *out);
 
+/* Look-ahead for streaming callers (asynchronous mode only; no counterpart in the reference).  Enqueues the first half
+ * of the NEXT frame's AllocateSceneFromDepth -- setToType3 over the current visible list and the per-pixel request pass
+ * (ITMSceneReconstructionEngine_CPU.cpp:185-201), which only READ the hash table -- on an internal stream that waits for
+ * the last scene write of the frame just submitted with dsb200_process_frame, not for its raycast: the two overlap.
+ * The next scene call must be dsb200_process_frame (with DSB200_FRAME_ALLOCATE) or dsb200_allocate_from_depth for exactly
+ * this view (same depth pointer, size, intrinsics), pose and render state; it picks the work up and continues with the
+ * ordered allocation.  Any other scene call in between, or a mismatch, returns DSB200_ERR_INVALID.  Results are bit-identical
+ * to the un-prefetched call sequence.  wait_cuda_event (optional): a cudaEvent_t after which next_view->depth is valid
+ * (e.g. recorded after its upload).  A no-op while per-stage profiling is enabled. */
+int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *next_view,
+                                     const dsb200_tracking *next_tracking, dsb200_render_state *rs, void *wait_cuda_event);
+/* Orders whatever is submitted next on the engine's stream after the pending look-ahead, without consuming it (for callers
+ * that record timing events or flush caches between frames: bench.py).  dsb200_reset_scene abandons a pending look-ahead. */
+int dsb200_recon_join_prefetch(dsb200_recon *e);
+
 /* ---- ICP depth tracker: the device-specific half ----
  * The reference's tracker is a host Levenberg-Marquardt loop (ITMLib/Engine/ITMDepthTracker.cpp:153-211, shared by
  * its CPU and CUDA builds) around ONE device virtual, ComputeGandH (ITMDepthTracker.h:59;

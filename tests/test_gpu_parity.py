@@ -161,3 +161,50 @@ def test_sdf_shadow_on_off_and_rebuild():
         hz.assert_images_equal(ora.images(), gpu.images(), "shadow frame %d" % i)
     hz.assert_state_equal(ora.state(), gpu.state(), "shadow sequence")
     gpu.close(); ora.close()
+
+
+def test_prefetched_allocation_matches_plain_sequence():
+    """dsb200_recon_prefetch_allocation: the request pass of frame k+1 submitted right after frame k (asynchronous mode,
+    views alternating between two device buffers) must leave every frame bit-identical to the oracle's plain sequence;
+    calls that would invalidate a pending look-ahead are refused."""
+    cfg, frames = synth.make_sequence("tiny", 10)
+    gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    eng = gpu.eng
+    views = [gpu.view, eng.ITMView(cfg.W, cfg.H, cfg.intr)]
+    nxt = eng.ITMTrackingState(cfg.W, cfg.H)
+    gpu.recon.SetAsync(True)
+    views[0].update(frames[0].depth, frames[0].rgb, frames[0].timestamp)
+    nxt.set_pose(frames[0].M)
+    gpu.recon.PrefetchAllocation(gpu.scene, views[0], nxt, gpu.rs)      # right after ResetScene is fine too
+    for i, f in enumerate(frames):
+        v = views[i % 2]
+        gpu.trk.set_pose(f.M)
+        gpu.recon.ProcessFrame(gpu.vis, gpu.scene, v, gpu.trk, gpu.rs)
+        if i + 1 < len(frames):
+            g = frames[i + 1]
+            views[(i + 1) % 2].update(g.depth, g.rgb, g.timestamp)
+            nxt.set_pose(g.M)
+            gpu.recon.PrefetchAllocation(gpu.scene, views[(i + 1) % 2], nxt, gpu.rs)
+            if i == 3:
+                with pytest.raises(abi.Dsb200Error):    # a second look-ahead
+                    gpu.recon.PrefetchAllocation(gpu.scene, views[(i + 1) % 2], nxt, gpu.rs)
+                with pytest.raises(abi.Dsb200Error):    # another scene call in between
+                    gpu.recon.IntegrateIntoScene(gpu.scene, v, gpu.trk, gpu.rs)
+        ora.set_frame(f); ora.process_frame()
+        if i in (4, 7) or i + 1 == len(frames):     # frames 0..4 run without any host synchronisation
+            # sync() only reads counters back; the pending look-ahead stays valid
+            gpu.recon.Sync(gpu.scene, gpu.rs)
+            s, so = gpu.state(), ora.state()
+            if i + 1 < len(frames):
+                s["visible_type"] = so["visible_type"]   # the look-ahead has already re-flagged the visibility types for frame i+1
+            hz.assert_state_equal(so, s, "prefetched sequence, frame %d" % i)
+            hz.assert_images_equal(ora.images(), gpu.images(), "prefetched sequence frame %d" % i)
+    # a look-ahead consumed by the wrong frame is refused
+    gpu.recon.PrefetchAllocation(gpu.scene, views[0], nxt, gpu.rs)
+    nxt2 = eng.ITMTrackingState(cfg.W, cfg.H)
+    nxt2.set_pose(frames[2].M)
+    with pytest.raises(abi.Dsb200Error):
+        gpu.recon.ProcessFrame(gpu.vis, gpu.scene, views[0], nxt2, gpu.rs)
+    gpu.recon.SetAsync(False)
+    views[1].free(); nxt.free(); nxt2.free()
+    gpu.close(); ora.close()
