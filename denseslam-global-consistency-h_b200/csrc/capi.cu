@@ -948,7 +948,6 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
     if (!(e->async && e->deviceCountersValid))
         return fail(DSB200_ERR_INVALID, "prefetch_allocation: asynchronous mode with at least one frame submitted is required");
     if (e->profile) return DSB200_OK;                               // per-stage timing keeps every kernel on the main stream
-    if (rs->visible_type != e->visBitsOwner) return fail(DSB200_ERR_INVALID, "prefetch_allocation: render state differs from the previous frame's");
     AllocParams AP; make_alloc_params(AP, e, scene, view, trk);
     if ((long long)AP.W * AP.H >= (1ll << 24)) return fail(DSB200_ERR_INVALID, "depth image too large for the 24-bit pixel order key");
     if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
@@ -957,6 +956,10 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
     if (e->epochSceneWritten != e->modEpoch) CU(cudaEventRecord(e->evSceneWritten, e->stream));
     CU(cudaStreamWaitEvent(e->prefetchStream, e->evSceneWritten, 0));
     if (waitEvent) CU(cudaStreamWaitEvent(e->prefetchStream, (cudaEvent_t)waitEvent, 0));
+    if (rs->visible_type != e->visBitsOwner) {     // a render state this engine has not been tracking: derive its bitmap
+        launch_rebuild_visbits(e->prefetchStream, e->fs, rs->visible_type, e->total);
+        e->visBitsOwner = rs->visible_type;
+    }
     launch_begin_frame(e->prefetchStream, e->fs, 0, 0, 0, 0, rs->visible_ids, rs->visible_type, rs->visible_capacity);
     launch_alloc_requests(e->prefetchStream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
     CU(cudaGetLastError());
