@@ -804,6 +804,7 @@ struct dsb200_tracker {
     double *partials = nullptr, *result = nullptr, *hostResult = nullptr;
     unsigned *ticket = nullptr;
     int lastPara = 0;
+    double seq = 0.0;                  // evaluation counter echoed by the kernel into hostResult[slots - 1]
 };
 
 int dsb200_tracker_create(dsb200_tracker **out, int32_t width, int32_t height, int32_t levels, void *stream)
@@ -871,9 +872,23 @@ static int tracker_gh(dsb200_tracker *t, const float *depth, int vW, int vH, con
         iterationType != DSB200_TRACKER_ITERATION_BOTH)
         return fail(DSB200_ERR_INVALID, "tracker_compute_g_and_h: unknown iteration type");
     launch_tracker_gh(t->stream, iterationType, approxInvPose, scenePose, vIntr, sIntr, distThresh, depth, vW, vH, points, normals,
-                      sW, sH, t->partials, t->ticket, t->result);
+                      sW, sH, t->partials, t->ticket, t->result, t->seq += 1.0);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(t->stream));      // t->result aliases t->hostResult (mapped)
+    // t->result aliases t->hostResult (mapped pinned memory).  Poll the echoed sequence number; fall back to the stream's
+    // status every few thousand polls so a failed launch surfaces as an error instead of a spin.
+    {
+        volatile double *flag = t->hostResult + tracker_gh_slots() - 1;
+        for (unsigned spins = 0; *flag != t->seq; ) {
+            if ((++spins & 0xfff) == 0) {
+                cudaError_t q = cudaStreamQuery(t->stream);
+                if (q == cudaSuccess) { if (*flag != t->seq) CU(cudaStreamSynchronize(t->stream)); if (*flag != t->seq) return fail(DSB200_ERR_CUDA, "tracker: result never arrived"); break; }
+                if (q != cudaErrorNotReady) return cuda_fail(q, "tracker_compute_g_and_h");
+            }
+#if defined(__x86_64__)
+            __builtin_ia32_pause();
+#endif
+        }
+    }
     const bool shortIt = iterationType != DSB200_TRACKER_ITERATION_BOTH;
     const int noPara = shortIt ? 3 : 6, noParaSQ = shortIt ? 6 : 21;
     t->lastPara = noPara;

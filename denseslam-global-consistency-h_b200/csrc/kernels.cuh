@@ -123,6 +123,6 @@ int tracker_gh_slots();
 void launch_tracker_gh(cudaStream_t st, int iterationType, const float *approxInvPose, const float *scenePose,
                        const float *viewIntr, const float *sceneIntr, float distThresh, const float *depth, int viewW, int viewH,
                        const float *points, const float *normals, int sceneW, int sceneH, double *partials, unsigned *ticket,
-                       double *result);
+                       double *result, double seq);
 
 } // namespace dsb

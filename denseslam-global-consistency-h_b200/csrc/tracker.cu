@@ -121,7 +121,7 @@ template <bool SHORT, bool ROT>
 __global__ void __launch_bounds__(kGhThreads) k_tracker_gh(TrackerParams P, const float *__restrict__ depth,
                                                            const float4 *__restrict__ points, const float4 *__restrict__ normals,
                                                            double *__restrict__ partials, unsigned *__restrict__ ticket,
-                                                           double *__restrict__ result)
+                                                           double *__restrict__ result, double seq)
 {
     constexpr int NP = SHORT ? 3 : 6, NH = SHORT ? 6 : 21, NV = NH + NP + 1;
     double acc[NV];
@@ -181,7 +181,13 @@ __global__ void __launch_bounds__(kGhThreads) k_tracker_gh(TrackerParams P, cons
         result[threadIdx.x] = s;           // mapped host memory
         __threadfence_system();
     }
-    if (threadIdx.x == 0) *ticket = 0;   // re-armed for the next launch on this stream
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *ticket = 0;                       // re-armed for the next launch on this stream
+        // sequence number last: the host polls this word instead of paying a stream synchronisation per evaluation
+        *reinterpret_cast<volatile double *>(result + kGhSlots - 1) = seq;
+        __threadfence_system();
+    }
 }
 
 } // namespace
@@ -202,7 +208,7 @@ int tracker_gh_slots() { return kGhSlots; }
 void launch_tracker_gh(cudaStream_t st, int iterationType, const float *approxInvPose, const float *scenePose,
                        const float *viewIntr, const float *sceneIntr, float distThresh, const float *depth, int viewW, int viewH,
                        const float *points, const float *normals, int sceneW, int sceneH, double *partials, unsigned *ticket,
-                       double *result)
+                       double *result, double seq)
 {
     TrackerParams P;
     for (int i = 0; i < 16; i++) { P.approxInvPose.m[i] = approxInvPose[i]; P.scenePose.m[i] = scenePose[i]; }
@@ -212,11 +218,11 @@ void launch_tracker_gh(cudaStream_t st, int iterationType, const float *approxIn
     if (grid > tracker_gh_max_ctas()) grid = tracker_gh_max_ctas();
     const float4 *pts = reinterpret_cast<const float4 *>(points), *nrm = reinterpret_cast<const float4 *>(normals);
     if (iterationType == DSB200_TRACKER_ITERATION_ROTATION)
-        DSB_LAUNCH((k_tracker_gh<true, true>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result);
+        DSB_LAUNCH((k_tracker_gh<true, true>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result, seq);
     else if (iterationType == DSB200_TRACKER_ITERATION_TRANSLATION)
-        DSB_LAUNCH((k_tracker_gh<true, false>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result);
+        DSB_LAUNCH((k_tracker_gh<true, false>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result, seq);
     else
-        DSB_LAUNCH((k_tracker_gh<false, false>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result);
+        DSB_LAUNCH((k_tracker_gh<false, false>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result, seq);
 }
 
 } // namespace dsb
