@@ -888,6 +888,7 @@ static int tracker_gh(dsb200_tracker *t, const float *depth, int vW, int vH, con
             __builtin_ia32_pause();
 #endif
         }
+        __atomic_thread_fence(__ATOMIC_ACQUIRE);      // the sums below are read after the flag
     }
     const bool shortIt = iterationType != DSB200_TRACKER_ITERATION_BOTH;
     const int noPara = shortIt ? 3 : 6, noParaSQ = shortIt ? 6 : 21;
@@ -931,6 +932,7 @@ int dsb200_tracker_last_sums(const dsb200_tracker *t, double *sums)
 {
     if (!t || !sums) return fail(DSB200_ERR_INVALID, "tracker_last_sums: null argument");
     memcpy(sums, t->hostResult, sizeof(double) * 32);
+    sums[31] = 0.0;                    // the kernel's sequence echo is not part of the result
     return DSB200_OK;
 }
 
