@@ -65,3 +65,36 @@ def test_host_matrix_helpers_match_oracle(lib):
         B = rng.normal(size=16).astype(np.float32)
         lib.dsb200_mat4_multiply(abi.f16(M), abi.f16(B), out)
         assert np.array_equal(np.array(out[:], np.float32).view(np.uint32), o.mat4_multiply(M, B).view(np.uint32))
+
+
+def test_host_pose_helpers_match_reference_fixture_and_oracle(lib):
+    """dsb200_pose_from_params / dsb200_pose_coerce are host code (csrc/tracker_host.cpp): no GPU needed.  Bit-exact with the
+    reference's ITMPose known answers in tests/golden/tiny_tracker_ref.npz and with the oracle over every angle branch."""
+    import importlib
+    import numpy as np
+    eng = importlib.import_module(hz.PKG + ".engine")
+    t = np.load(os.path.join(hz.ROOT, "tests", "golden", "tiny_tracker_ref.npz"))
+    bits = lambda a: np.ascontiguousarray(a, np.float32).view(np.uint32)
+    for p, M, cM, cp in zip(t["pose_params"], t["pose_M"], t["pose_coerced_M"], t["pose_coerced_params"]):
+        assert np.array_equal(bits(eng.pose_from_params(p)), bits(M))
+        m2, p2 = eng.pose_coerce(M)
+        assert np.array_equal(bits(m2), bits(cM)) and np.array_equal(bits(p2), bits(cp))
+    o = hz.po.Oracle()
+    rng = np.random.default_rng(13)
+    for k in range(1200):
+        p = np.concatenate([rng.normal(size=3), rng.normal(size=3) * [1e-5, 5e-4, 0.05, 1.0, 1.8, 3.1][k % 6]]).astype(np.float32)
+        M = eng.pose_from_params(p)
+        assert np.array_equal(bits(M), bits(o.pose_from_params(p)))
+        noisy = M + rng.normal(size=16).astype(np.float32) * np.float32(1e-4) * (np.arange(16) % 4 != 3)
+        a, b = eng.pose_coerce(noisy), o.pose_coerce(noisy)
+        assert np.array_equal(bits(a[0]), bits(b[0])) and np.array_equal(bits(a[1]), bits(b[1]))
+
+
+def test_tracker_entry_points_fail_loudly_without_gpu(lib):
+    if lib.dsb200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    h = C.c_void_p()
+    rc = lib.dsb200_tracker_create(C.byref(h), 64, 48, 3, None)
+    assert rc < 0 and not h.value
+    assert lib.dsb200_tracker_create(C.byref(h), 64, 48, 0, None) == abi.ERR_INVALID      # level count checked before any CUDA call
+    assert lib.dsb200_recon_join_prefetch(None) == abi.ERR_INVALID
