@@ -954,6 +954,24 @@ int dsb200_filter_subsample_with_holes(const float *in, int32_t w, int32_t h, fl
     return DSB200_OK;
 }
 
+int dsb200_view_filter_depth(dsb200_view *view, float *scratch, void *stream)
+{
+    if (!view || !view->depth || !scratch) return fail(DSB200_ERR_INVALID, "view_filter_depth: null argument");
+    const int W = view->depth_w, H = view->depth_h;
+    if (W < 5 || H < 5) return fail(DSB200_ERR_INVALID, "view_filter_depth: image smaller than the 5x5 window");
+    float *depth = const_cast<float *>(view->depth);
+    cudaStream_t st = (cudaStream_t)stream;
+    // 5 steps of bilateral filtering, CPU/ITMViewBuilder_CPU.cpp:49-58
+    launch_filter_depth(st, depth, scratch, W, H);
+    launch_filter_depth(st, scratch, depth, W, H);
+    launch_filter_depth(st, depth, scratch, W, H);
+    launch_filter_depth(st, scratch, depth, W, H);
+    launch_filter_depth(st, depth, scratch, W, H);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(depth, scratch, sizeof(float) * (size_t)W * H, cudaMemcpyDeviceToDevice, st));
+    return DSB200_OK;
+}
+
 // ---------------------------------------------------------------- look-ahead
 int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
                                      dsb200_render_state *rs, void *waitEvent)

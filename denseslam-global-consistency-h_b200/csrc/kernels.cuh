@@ -116,6 +116,8 @@ void launch_forward_render(cudaStream_t st, const RayParams &P, const float *pro
                            const dsb200_hash_entry *hash, const float *rangeImage, const float *raycastResult,
                            const float *depth, float *fwd, int *owner, int *noMissing, uint8_t *rendering);
 
+// view_filter.cu
+void launch_filter_depth(cudaStream_t st, const float *in, float *out, int W, int H);
 // tracker.cu
 void launch_filter_subsample_holes(cudaStream_t st, const float *in, int oldW, int oldH, float *out);
 int tracker_gh_max_ctas();

@@ -128,7 +128,7 @@ class ITMView(object):
         self.rgb.upload(np.asarray(rgb, np.uint8))
         self.c.timestamp = timestamp
 
-    def update_from_raw(self, depth_i16, bgr, timestamp=0.0, scale=0.001, offset=0.0, stream=None):
+    def update_from_raw(self, depth_i16, bgr, timestamp=0.0, scale=0.001, offset=0.0, stream=None, useBilateralFilter=False):
         """ITMViewBuilder::UpdateView (affine calibration) + the driver's BGR -> RGBA conversion, on the device"""
         d = np.ascontiguousarray(depth_i16, np.int16)
         if not hasattr(self, "raw_depth"):
@@ -138,14 +138,25 @@ class ITMView(object):
             self.raw_bgr.upload(np.ascontiguousarray(bgr, np.uint8), stream)
         abi.check(_lib().dsb200_view_from_raw(self.raw_depth.ptr, self.raw_bgr.ptr if bgr is not None else None, scale, offset,
                                               C.byref(self.c), stream))
+        if useBilateralFilter:
+            self.filter_depth(stream)
         abi.check(_lib().dsb200_stream_synchronize(stream))
         self.c.timestamp = timestamp
+
+    def filter_depth(self, stream=None):
+        """UpdateView's useBilateralFilter branch: five 5x5 bilateral passes over the depth image, in place"""
+        if not hasattr(self, "filter_scratch"):
+            self.filter_scratch = DeviceBuffer(self.W * self.H * 4)
+        abi.check(_lib().dsb200_view_filter_depth(C.byref(self.c), self.filter_scratch.ptr, stream))
+        abi.check(_lib().dsb200_stream_synchronize(stream))
 
     def free(self):
         self.depth.free()
         self.rgb.free()
         if hasattr(self, "raw_depth"):
             self.raw_depth.free(); self.raw_bgr.free()
+        if hasattr(self, "filter_scratch"):
+            self.filter_scratch.free()
 
 
 class ITMTrackingState(object):

@@ -282,6 +282,13 @@ int dsb200_stream_synchronize(void *cuda_stream);
 int dsb200_mat4_inverse(const float *M, float *out);
 void dsb200_mat4_multiply(const float *A, const float *B, float *out);
 
+/* ITMViewBuilder::UpdateView's useBilateralFilter branch (CPU/ITMViewBuilder_CPU.cpp:49-58, filterDepth
+ * DeviceAgnostic/ITMViewBuilder.h:30-53): five passes of the 5x5 bilateral depth filter over view->depth, in place;
+ * scratch = DEVICE buffer of depth_w * depth_h floats.  Off in DenseSLAM (ITMLibSettings.cpp:37).  Float arithmetic is the
+ * reference's; its exp() is evaluated in double and rounded (see csrc/view_filter.cu for the parity statement).  Asynchronous
+ * on cuda_stream like dsb200_view_from_raw. */
+int dsb200_view_filter_depth(dsb200_view *view, float *scratch, void *cuda_stream);
+
 /* Look-ahead for streaming callers (asynchronous mode only; no counterpart in the reference).  Enqueues the first half
  * of the NEXT frame's AllocateSceneFromDepth -- setToType3 over the current visible list and the per-pixel request pass
  * (ITMSceneReconstructionEngine_CPU.cpp:185-201), which only READ the hash table -- on an internal stream that waits for

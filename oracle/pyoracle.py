@@ -127,11 +127,19 @@ class Oracle(object):
         L.rst_tracker_compute_g_and_h.restype = C.c_int
         L.rst_tracker_compute_g_and_h.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_int, vp, vp, vp, C.c_float,
                                                   C.c_int, C.c_int, vp, vp, vp, vp]
+        L.rst_view_filter_depth.argtypes = [vp, C.c_int, C.c_int]
         L.rst_pose_coerce.argtypes = [vp, vp]
         L.rst_pose_from_params.argtypes = [vp, vp]
         L.rst_track_camera.argtypes = [P(abi.TrackerConfig), P(abi.View), P(abi.Tracking), vp, C.c_int, C.c_int, C.c_int,
                                        P(abi.TrackerReport)]
         self.L = L
+
+    def view_filter_depth(self, depth):
+        """five bilateral passes (UpdateView with useBilateralFilter) -> filtered copy"""
+        d = np.array(depth, np.float32).copy()
+        h, w = d.shape
+        self.L.rst_view_filter_depth(ptr(d), w, h)
+        return d
 
     def pose_coerce(self, M):
         m = np.array(M, np.float32).copy()
@@ -236,6 +244,8 @@ class RefEngine(object):
             getattr(L, name).argtypes = [vp]
         if hasattr(L, "itmref_update_view_raw"):
             L.itmref_update_view_raw.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double]
+            if hasattr(L, "itmref_update_view_raw_ex"):
+                L.itmref_update_view_raw_ex.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double, C.c_int]
             L.itmref_view_depth.restype = vp
             L.itmref_view_depth.argtypes = [vp]
         if hasattr(L, "itmref_forward_render"):
@@ -322,11 +332,11 @@ class RefEngine(object):
     def create_icp_maps(self):
         self.L.itmref_create_icp_maps(self.h)
 
-    def update_view_raw(self, raw_depth_i16, rgba, scale=0.001, offset=0.0, timestamp=0.0):
+    def update_view_raw(self, raw_depth_i16, rgba, scale=0.001, offset=0.0, timestamp=0.0, use_bilateral_filter=False):
         """ITMViewBuilder_CPU::UpdateView (TRAFO_AFFINE) -> copy of view->depth"""
         d = np.ascontiguousarray(raw_depth_i16, np.int16)
         r = np.ascontiguousarray(rgba, np.uint8)
-        self.L.itmref_update_view_raw(self.h, ptr(d), ptr(r), scale, offset, timestamp)
+        self.L.itmref_update_view_raw_ex(self.h, ptr(d), ptr(r), scale, offset, timestamp, 1 if use_bilateral_filter else 0)
         return self._arr(self.L.itmref_view_depth(self.h), np.float32, self.W * self.H).reshape(self.H, self.W).copy()
 
     def tracker_compute_g_and_h(self, depth, view_intr, points, normals, scene_intr, scene_pose, approx_inv_pose,

@@ -100,7 +100,14 @@ void itmref_set_view(void *h, const float *depth, const uint8_t *rgba, double ti
 
 // ITMViewBuilder_CPU::UpdateView with the affine depth calibration DenseSLAM configures (DS/InfiniTamDriver.cpp:78-81,286):
 // raw int16 depth + RGBA in, view->depth (float) out
+void itmref_update_view_raw_ex(void *h, const short *rawDepth, const uint8_t *rgba, float scale, float offset, double timestamp,
+                               int useBilateralFilter);
 void itmref_update_view_raw(void *h, const short *rawDepth, const uint8_t *rgba, float scale, float offset, double timestamp)
+{
+    itmref_update_view_raw_ex(h, rawDepth, rgba, scale, offset, timestamp, 0);
+}
+void itmref_update_view_raw_ex(void *h, const short *rawDepth, const uint8_t *rgba, float scale, float offset, double timestamp,
+                               int useBilateralFilter)
 {
     RefCtx *c = (RefCtx *)h;
     c->calib.disparityCalib.SetFrom(scale, offset, ITMDisparityCalib::TRAFO_AFFINE);
@@ -111,7 +118,7 @@ void itmref_update_view_raw(void *h, const short *rawDepth, const uint8_t *rgba,
     memcpy(rgb.GetData(MEMORYDEVICE_CPU), rgba, n * 4);
     memcpy(raw.GetData(MEMORYDEVICE_CPU), rawDepth, n * sizeof(short));
     ITMView *built = NULL;        // a fresh view makes the builder allocate its own staging images (UpdateView :12-27)
-    vb.UpdateView(&built, &rgb, &raw, timestamp, false);
+    vb.UpdateView(&built, &rgb, &raw, timestamp, useBilateralFilter != 0);
     memcpy(c->view->depth->GetData(MEMORYDEVICE_CPU), built->depth->GetData(MEMORYDEVICE_CPU), n * sizeof(float));
     memcpy(c->view->rgb->GetData(MEMORYDEVICE_CPU), built->rgb->GetData(MEMORYDEVICE_CPU), n * 4);
     c->view->mTimeStamp = timestamp;

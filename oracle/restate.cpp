@@ -1517,3 +1517,37 @@ void rst_track_camera(const dsb200_tracker_config *cfg, const dsb200_view *view,
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------- view builder: bilateral depth filter
+extern "C" {
+
+// ITMViewBuilder_CPU::UpdateView's useBilateralFilter branch, CPU/ITMViewBuilder_CPU.cpp:49-58 with DepthFiltering :119-130
+// and filterDepth, DA/ITMViewBuilder.h:30-53.  exp on a float argument is the float overload (glibc expf), as in the reference.
+void rst_view_filter_depth(float *depth, int W, int H)
+{
+    std::vector<float> tmp((size_t)W * H);
+    float *bufs[2] = {depth, tmp.data()};
+    for (int pass = 0; pass < 5; pass++) {
+        const float *in = bufs[pass & 1]; float *out = bufs[(pass & 1) ^ 1];
+        memset(out, 0, sizeof(float) * (size_t)W * H);
+        for (int y = 2; y < H - 2; y++) for (int x = 2; x < W - 2; x++) {
+            float z, tmpz, dz, final_depth = 0.0f, w, w_sum = 0.0f;
+            z = in[x + y * W];
+            if (z < 0.0f) { out[x + y * W] = -1.0f; continue; }
+            float sigma_z = 1.0f / (0.0012f + 0.0019f * (z - 0.4f) * (z - 0.4f) + 0.0001f / sqrtf(z) * 0.25f);
+            for (int i = -2; i <= 2; i++) for (int j = -2; j <= 2; j++) {
+                tmpz = in[(x + j) + (y + i) * W];
+                if (tmpz < 0.0f) continue;
+                dz = (tmpz - z); dz *= dz;
+                w = expf(-0.5f * ((abs(i) + abs(j)) * 1.2232f * 1.2232f + dz * sigma_z * sigma_z));
+                w_sum += w;
+                final_depth += w * tmpz;
+            }
+            final_depth /= w_sum;
+            out[x + y * W] = final_depth;
+        }
+    }
+    memcpy(depth, tmp.data(), sizeof(float) * (size_t)W * H);   // five passes end in the staging image; SetFrom copies it back
+}
+
+} // extern "C"

@@ -101,4 +101,9 @@ def test_view_building_matches_reference():
             assert np.array_equal(hz.bits(got), hz.bits(want))
             same = raw == f.depth_mm
             assert np.array_equal(hz.bits(got[same]), hz.bits(f.depth[same]))
+            # useBilateralFilter: five 5x5 passes (CPU/ITMViewBuilder_CPU.cpp:49-58), restated bit for bit
+            got_f = ref.update_view_raw(raw, f.rgb, np.float32(1.0 / 1000.0), 0.0, f.timestamp, use_bilateral_filter=True)
+            want_f = po.Oracle().view_filter_depth(want.reshape(cfg.H, cfg.W))
+            assert np.array_equal(hz.bits(got_f), hz.bits(want_f))
+            assert not np.array_equal(got_f, got) and (got_f[2:-2, 2:-2] > 0).mean() > 0.2
         ref.close()
