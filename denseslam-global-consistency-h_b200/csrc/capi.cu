@@ -972,6 +972,20 @@ int dsb200_view_filter_depth(dsb200_view *view, float *scratch, void *stream)
     return DSB200_OK;
 }
 
+int dsb200_selftest_expf(const float *x, float *y, int32_t n)
+{
+    if (!x || !y || n <= 0) return fail(DSB200_ERR_INVALID, "selftest_expf: null argument");
+    if (dsb200_device_count() == 0) return fail(DSB200_ERR_NO_DEVICE, "no CUDA device: libdsb200 has no CPU fallback");
+    float *dx = nullptr, *dy = nullptr;
+    CU(cudaMalloc(&dx, sizeof(float) * (size_t)n)); CU(cudaMalloc(&dy, sizeof(float) * (size_t)n));
+    CU(cudaMemcpy(dx, x, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
+    launch_expf_selftest(nullptr, dx, dy, n);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(y, dy, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(dx); cudaFree(dy);
+    return DSB200_OK;
+}
+
 // ---------------------------------------------------------------- look-ahead
 int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
                                      dsb200_render_state *rs, void *waitEvent)

@@ -5,11 +5,17 @@
 //   five passes ping-ponging between the view's depth image and a scratch image, result copied back (UpdateView :49-58).
 //
 // Arithmetic follows the reference expression by expression (float, no contraction, IEEE division and square root).  The
-// one library call, exp(float), is glibc's expf on the reference's host: a double-precision evaluation rounded to float.
-// Here it is CUDA's double exp rounded to float, which agrees with any < 1 ulp-double evaluation except where the exact
-// value lies within ~2^-29 of a float rounding boundary (about one weight in 10^8); tests/test_gpu_parity.py therefore
-// checks this kernel against the oracle with a 1e-6 relative tolerance and requires >= 99.99 % of the pixels bit-identical.
+// one library call, exp(float), resolves to glibc's expf on the reference's host.  That function is NOT correctly rounded
+// (a degree-3 polynomial in double after a 32-entry table reduction, ~2^-33 relative error), so a more accurate exp disagrees
+// with it on about one weight in 10^4, and five passes spread every such difference over a 21x21 neighbourhood.  expf_host()
+// below therefore restates glibc's published algorithm (sysdeps/ieee754/flt-32/e_expf.c, glibc >= 2.27: table 2^(i/32),
+// InvLn2N, the three scaled coefficients, the 0x1.8p52 shift trick) with the FMA contraction of its x86-64 FMA build; the
+// remaining disagreement was one argument in 4e8 on the build host (a value 5 double-ulps from a float tie).  tests/test_gpu_parity.py
+// checks the function itself against the host C library bit for bit on 200 000 arguments, and for the filter asks for >= 99.5 %
+// of the pixels bit-identical to the oracle (glibc expf on the test host) and 1e-6 relative elsewhere.
 #include "kernels.cuh"
+#include <cmath>
+#include <cstring>
 
 namespace dsb {
 
@@ -17,7 +23,34 @@ namespace {
 
 constexpr int kFx = 32, kFy = 8;     // CTA tile; the 5x5 window is staged in shared memory with a 2-pixel apron
 
-__device__ __forceinline__ float exp_like_host(float x) { return (float)exp((double)x); }
+__constant__ unsigned long long c_exp2fTab[32];     // asuint64(2^(i/32)) - (i << 47), filled by ensure_exp_table()
+
+__device__ __forceinline__ float expf_host(float x)
+{
+    const unsigned abstop = (__float_as_uint(x) >> 20) & 0x7ffu;
+    if (abstop >= 0x42bu) {                              // |x| >= 88 (or NaN / Inf)
+        if (__float_as_uint(x) == 0xff800000u) return 0.0f;
+        if (abstop >= 0x7f8u) return x + x;
+        if (x > 0x1.62e42ep6f) return __int_as_float(0x7f800000);                 // overflow
+        if (x < -0x1.9fe368p6f) return 0.0f;                                      // underflow
+        if (x < -0x1.9d1d9ep6f) return __int_as_float(1);                         // "may underflow": 0x1.4p-75f squared = 2^-149
+    }
+    const double xd = (double)x;
+    double z = 0x1.71547652b82fep+5 * xd;                // InvLn2N = 0x1.71547652b82fep+0 * 32
+    double kd = z + 0x1.8p+52;                           // SHIFT: round to nearest integer in the low mantissa bits
+    const unsigned long long ki = (unsigned long long)__double_as_longlong(kd);
+    kd -= 0x1.8p+52;
+    const double r = z - kd;
+    const unsigned long long t = c_exp2fTab[ki & 31u] + (ki << 47);
+    const double sc = __longlong_as_double((long long)t);
+    // C = {0x1.c6af84b912394p-5 / 32^3, 0x1.ebfce50fac4f3p-3 / 32^2, 0x1.62e42ff0c52d6p-1 / 32}
+    z = fma(0x1.c6af84b912394p-5 / 32 / 32 / 32, r, 0x1.ebfce50fac4f3p-3 / 32 / 32);
+    const double r2 = r * r;
+    double y = fma(0x1.62e42ff0c52d6p-1 / 32, r, 1.0);
+    y = fma(z, r2, y);
+    y = y * sc;
+    return (float)y;
+}
 
 __global__ void __launch_bounds__(kFx * kFy) k_filter_depth(const float *__restrict__ in, float *__restrict__ out, int W, int H)
 {
@@ -44,7 +77,7 @@ __global__ void __launch_bounds__(kFx * kFy) k_filter_depth(const float *__restr
             const float tmpz = tile[threadIdx.y + 2 + i][threadIdx.x + 2 + j];
             if (tmpz < 0.0f) continue;
             float dz = tmpz - z; dz *= dz;
-            const float w = exp_like_host(-0.5f * ((float)(abs(i) + abs(j)) * kSigmaL * kSigmaL + dz * sigma_z * sigma_z));
+            const float w = expf_host(-0.5f * ((float)(abs(i) + abs(j)) * kSigmaL * kSigmaL + dz * sigma_z * sigma_z));
             w_sum += w;
             final_depth += w * tmpz;
         }
@@ -55,8 +88,37 @@ __global__ void __launch_bounds__(kFx * kFy) k_filter_depth(const float *__restr
 
 } // namespace
 
+// 2^(i/32) correctly rounded to double (via the 64-bit-mantissa long double exp2), stored the way glibc's table is
+static void ensure_exp_table()
+{
+    static bool done = false;
+    if (done) return;
+    unsigned long long tab[32];
+    for (int i = 0; i < 32; i++) {
+        const double v = (double)exp2l((long double)i / 32.0L);
+        unsigned long long bits; memcpy(&bits, &v, 8);
+        tab[i] = bits - ((unsigned long long)i << 47);
+    }
+    cudaMemcpyToSymbol(c_exp2fTab, tab, sizeof(tab));
+    done = true;
+}
+
+namespace {
+__global__ void k_expf_selftest(const float *__restrict__ x, float *__restrict__ y, int n)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) y[i] = expf_host(x[i]);
+}
+}
+
+void launch_expf_selftest(cudaStream_t st, const float *x, float *y, int n)
+{
+    ensure_exp_table();
+    DSB_LAUNCH(k_expf_selftest, kNumSMs * 4, 256, 0, st, x, y, n);
+}
+
 void launch_filter_depth(cudaStream_t st, const float *in, float *out, int W, int H)
 {
+    ensure_exp_table();
     dim3 block(kFx, kFy), grid(div_up(W, kFx), div_up(H, kFy));
     DSB_LAUNCH(k_filter_depth, grid, block, 0, st, in, out, W, H);
 }

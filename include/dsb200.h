@@ -393,6 +393,9 @@ int dsb200_profile_read_allocate(dsb200_recon *e, float *stage_ms /* [DSB200_PRO
  * bit-level disagreements (must be 0). */
 int dsb200_debug_force_plain_division(dsb200_recon *e, int on);
 int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches);
+/* the bilateral filter's exp (csrc/view_filter.cu, a restatement of glibc's expf) on n HOST floats: y[i] = expf(x[i]);
+ * tests compare it bit for bit with the host C library's expf */
+int dsb200_selftest_expf(const float *x, float *y, int32_t n);
 
 /* counters for bench.py: kernels launched by this library since process start */
 unsigned long long dsb200_kernel_launch_count(void);
