@@ -255,3 +255,46 @@ def test_bilateral_depth_filter_vs_oracle():
         assert rel.max() <= 1e-6
         assert (want[2:-2, 2:-2] > 0).mean() > 0.2 and not np.array_equal(want, plain.reshape(cfg.H, cfg.W))
         view.free()
+
+
+def ragged_sequence():
+    """157 x 119 (no multiple of the 4-pixel vectors, 8x4 ray tiles, 8-pixel range-image cells or 16x16 rendering blocks) with
+    empty frames: frame 0 (nothing to allocate, empty visible list), frame 3 (every visible block falls back to the frustum
+    re-test) and a single valid pixel in frame 5."""
+    cfg = synth.Config("odd", 157, 119, (118.3, 118.0, 77.7, 58.9), 0.02, 0.08, 100, 0.2, 3.0, "room")
+    cfg, frames = synth.make_sequence(cfg, 7)
+    for i in (0, 3, 5):
+        keep = frames[i].depth.reshape(cfg.H, cfg.W)[60, 80]
+        frames[i].depth = np.full_like(frames[i].depth, -1.0)
+        frames[i].depth_mm = np.zeros_like(frames[i].depth_mm)
+        if i == 5:
+            frames[i].depth.reshape(cfg.H, cfg.W)[60, 80] = keep
+    return cfg, frames
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_ragged_sizes_and_empty_frames(fused):
+    cfg, frames = ragged_sequence()
+    gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    for i, f in enumerate(frames):
+        gpu.set_frame(f); ora.set_frame(f)
+        if fused:
+            assert gpu.process_frame() == ora.process_frame()
+        else:
+            assert gpu.allocate() == ora.allocate()
+            gpu.integrate(); ora.integrate()
+            gpu.expected_depths(); ora.expected_depths()
+            gpu.icp_maps(); ora.icp_maps()
+        hz.assert_state_equal(ora.state(), gpu.state(), "ragged frame %d" % i)
+        hz.assert_images_equal(ora.images(), gpu.images(), "ragged frame %d" % i)
+        if i == 0:
+            assert gpu.rs.c.no_visible == 0
+    assert gpu.rs.c.no_visible > 50
+    # free-view render of the ragged image size
+    for b in (gpu, ora):
+        b.free_view(frames[4].M, cfg.intr, abi.RENDER_SHADED_GREYSCALE)
+    fg, fo = gpu.free_images(), ora.free_images()
+    assert np.array_equal(fg["visible"], fo["visible"])
+    hz.assert_images_equal(dict(range=fo["range"], raycast=fo["raycast"], image=fo["image"]),
+                           dict(range=fg["range"], raycast=fg["raycast"], image=fg["image"]), "ragged free view")
+    gpu.close(); ora.close()
