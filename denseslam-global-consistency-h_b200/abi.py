@@ -174,6 +174,8 @@ def load():
         "dsb200_stream_synchronize": (C.c_int, [vp]),
         "dsb200_mat4_inverse": (C.c_int, [_P(C.c_float), _P(C.c_float)]),
         "dsb200_mat4_multiply": (None, [_P(C.c_float), _P(C.c_float), _P(C.c_float)]),
+        "dsb200_scene_save": (C.c_int, [_P(Scene), _P(RenderState), cp]),
+        "dsb200_scene_load": (C.c_int, [vp, _P(Scene), _P(RenderState), cp]),
         "dsb200_view_filter_depth": (C.c_int, [_P(View), vp, vp]),
         "dsb200_recon_prefetch_allocation": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), vp]),
         "dsb200_recon_join_prefetch": (C.c_int, [vp]),

@@ -986,6 +986,119 @@ int dsb200_selftest_expf(const float *x, float *y, int32_t n)
     return DSB200_OK;
 }
 
+// ---------------------------------------------------------------- volume checkpoint
+namespace {
+
+// one file per array, MemoryBlockPersister's layout (ORUtils/MemoryBlockPersister.h:88-140): int32 element count, raw elements
+int write_block(const std::string &path, const void *dev, size_t elemSize, size_t count, void *pinned, size_t pinnedBytes)
+{
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) return fail(DSB200_ERR_INVALID, "checkpoint: could not open " + path + " for writing");
+    const int32_t n = (int32_t)count;
+    bool ok = fwrite(&n, 4, 1, f) == 1;
+    const char *src = (const char *)dev;
+    for (size_t off = 0, total = elemSize * count; ok && off < total; off += pinnedBytes) {
+        const size_t chunk = total - off < pinnedBytes ? total - off : pinnedBytes;
+        if (cudaMemcpy(pinned, src + off, chunk, cudaMemcpyDeviceToHost) != cudaSuccess) { fclose(f); return cuda_fail(cudaGetLastError(), "checkpoint copy"); }
+        ok = fwrite(pinned, 1, chunk, f) == chunk;
+    }
+    fclose(f);
+    return ok ? DSB200_OK : fail(DSB200_ERR_INVALID, "checkpoint: short write to " + path);
+}
+
+int read_block(const std::string &path, void *dev, size_t elemSize, size_t count, void *pinned, size_t pinnedBytes)
+{
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) return fail(DSB200_ERR_INVALID, "checkpoint: could not open " + path + " for reading");
+    int32_t n = 0;
+    bool ok = fread(&n, 4, 1, f) == 1;
+    if (ok && (size_t)n != count) { fclose(f); return fail(DSB200_ERR_INVALID, "checkpoint: " + path + " holds a block of a different size (capacities differ)"); }
+    char *dst = (char *)dev;
+    for (size_t off = 0, total = elemSize * count; ok && off < total; off += pinnedBytes) {
+        const size_t chunk = total - off < pinnedBytes ? total - off : pinnedBytes;
+        ok = fread(pinned, 1, chunk, f) == chunk;
+        if (ok && cudaMemcpy(dst + off, pinned, chunk, cudaMemcpyHostToDevice) != cudaSuccess) { fclose(f); return cuda_fail(cudaGetLastError(), "checkpoint copy"); }
+    }
+    fclose(f);
+    return ok ? DSB200_OK : fail(DSB200_ERR_INVALID, "checkpoint: short read from " + path);
+}
+
+} // namespace
+
+int dsb200_scene_save(const dsb200_scene *scene, const dsb200_render_state *rs, const char *directory)
+{
+    if (!scene || !directory || !scene->voxels || !scene->hash) return fail(DSB200_ERR_INVALID, "scene_save: null argument");
+    CU(cudaDeviceSynchronize());
+    const size_t pinnedBytes = (size_t)32 << 20;
+    void *pinned = nullptr;
+    CU(cudaMallocHost(&pinned, pinnedBytes));
+    const std::string d = std::string(directory) + "/";
+    const size_t total = (size_t)scene->bucket_num + scene->excess_size;
+    int rc = write_block(d + "voxel.dat", scene->voxels, sizeof(dsb200_voxel), (size_t)scene->num_blocks * DSB200_BLOCK_SIZE3, pinned, pinnedBytes);
+    if (!rc) rc = write_block(d + "alloc.dat", scene->alloc_list, 4, scene->num_blocks, pinned, pinnedBytes);
+    if (!rc) rc = write_block(d + "hash.dat", scene->hash, sizeof(dsb200_hash_entry), total, pinned, pinnedBytes);
+    if (!rc) rc = write_block(d + "excess.dat", scene->excess_list, 4, scene->excess_size, pinned, pinnedBytes);
+    if (!rc && rs) {
+        rc = write_block(d + "visible.dat", rs->visible_ids, 4, (size_t)(rs->no_visible > 0 ? rs->no_visible : 0), pinned, pinnedBytes);
+        if (!rc) rc = write_block(d + "vistype.dat", rs->visible_type, 1, total, pinned, pinnedBytes);
+    }
+    cudaFreeHost(pinned);
+    if (rc) return rc;
+    FILE *f = fopen((d + "counters.txt").c_str(), "w");
+    if (!f) return fail(DSB200_ERR_INVALID, "checkpoint: could not write counters.txt");
+    fprintf(f, "%d %d %d %d %d %d\n%.9g %.9g %d %.9g %.9g %d\n", scene->num_blocks, scene->bucket_num, scene->excess_size,
+            scene->last_free_block, scene->last_free_excess, rs ? rs->no_visible : -1, scene->params.voxel_size, scene->params.mu,
+            scene->params.max_w, scene->params.vf_min, scene->params.vf_max, scene->params.stop_integrating_at_max_w);
+    fclose(f);
+    return DSB200_OK;
+}
+
+int dsb200_scene_load(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs, const char *directory)
+{
+    if (!scene || !directory || !scene->voxels || !scene->hash) return fail(DSB200_ERR_INVALID, "scene_load: null argument");
+    const std::string d = std::string(directory) + "/";
+    FILE *f = fopen((d + "counters.txt").c_str(), "r");
+    if (!f) return fail(DSB200_ERR_INVALID, "checkpoint: could not read counters.txt");
+    int nb, bn, ex, lfb, lfe, nv, maxW, stop; float vs, mu, vmin, vmax;
+    const int got = fscanf(f, "%d %d %d %d %d %d %g %g %d %g %g %d", &nb, &bn, &ex, &lfb, &lfe, &nv, &vs, &mu, &maxW, &vmin, &vmax, &stop);
+    fclose(f);
+    if (got != 12) return fail(DSB200_ERR_INVALID, "checkpoint: malformed counters.txt");
+    if (nb != scene->num_blocks || bn != scene->bucket_num || ex != scene->excess_size)
+        return fail(DSB200_ERR_INVALID, "checkpoint: capacities differ from the scene's");
+    if (rs && nv < 0) return fail(DSB200_ERR_INVALID, "checkpoint: saved without a render state");
+    if (rs && nv > rs->visible_capacity) return fail(DSB200_ERR_INVALID, "checkpoint: visible list larger than the render state's capacity");
+    CU(cudaDeviceSynchronize());
+    const size_t pinnedBytes = (size_t)32 << 20;
+    void *pinned = nullptr;
+    CU(cudaMallocHost(&pinned, pinnedBytes));
+    const size_t total = (size_t)bn + ex;
+    int rc = read_block(d + "voxel.dat", scene->voxels, sizeof(dsb200_voxel), (size_t)nb * DSB200_BLOCK_SIZE3, pinned, pinnedBytes);
+    if (!rc) rc = read_block(d + "alloc.dat", scene->alloc_list, 4, nb, pinned, pinnedBytes);
+    if (!rc) rc = read_block(d + "hash.dat", scene->hash, sizeof(dsb200_hash_entry), total, pinned, pinnedBytes);
+    if (!rc) rc = read_block(d + "excess.dat", scene->excess_list, 4, ex, pinned, pinnedBytes);
+    if (!rc && rs) {
+        rc = read_block(d + "visible.dat", rs->visible_ids, 4, (size_t)nv, pinned, pinnedBytes);
+        if (!rc) rc = read_block(d + "vistype.dat", rs->visible_type, 1, total, pinned, pinnedBytes);
+    }
+    cudaFreeHost(pinned);
+    if (rc) return rc;
+    scene->last_free_block = lfb; scene->last_free_excess = lfe;
+    scene->params.voxel_size = vs; scene->params.mu = mu; scene->params.max_w = maxW; scene->params.vf_min = vmin; scene->params.vf_max = vmax;
+    scene->params.stop_integrating_at_max_w = stop;
+    if (rs) rs->no_visible = nv;
+    if (e) {
+        // the engine's derived state describes another scene now: counters come from the host mirrors again, the visibility
+        // bitmap and the sdf shadow are rebuilt on first use, the pruning history starts empty, a pending look-ahead is dropped
+        if (e->prefetchPending) { CU(cudaStreamSynchronize(e->prefetchStream)); e->prefetchPending = false; }
+        e->deviceCountersValid = false; e->visBitsOwner = nullptr; e->shadowFor = nullptr; e->lastKnownVisible = nv > 0 ? nv : 0;
+        e->decayQ.clear(); e->slideQ.clear(); e->decayDefusionQ.clear(); e->slideDefusionQ.clear(); e->snapshots.clear(); e->unsynced.clear();
+        CU(cudaMemsetAsync(e->reqKey, 0, sizeof(unsigned) * (size_t)e->total, e->stream));
+        CU(cudaMemsetAsync(e->fs.reqBits, 0, (size_t)e->fs.bitTiles * 8192, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+    }
+    return DSB200_OK;
+}
+
 // ---------------------------------------------------------------- look-ahead
 int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *view, const dsb200_tracking *trk,
                                      dsb200_render_state *rs, void *waitEvent)

@@ -256,6 +256,15 @@ class ITMSceneReconstructionEngine(object):
         _lib().dsb200_history_sizes(self.h, *[C.byref(x) for x in v])
         return tuple(x.value for x in v)
 
+    def SaveCheckpoint(self, scene, renderState, directory):
+        """volume checkpoint: scene arrays (+ visible list / flags) in MemoryBlockPersister's file layout"""
+        abi.check(_lib().dsb200_scene_save(C.byref(scene.c), C.byref(renderState.c) if renderState is not None else None,
+                                           str(directory).encode()))
+
+    def LoadCheckpoint(self, scene, renderState, directory):
+        abi.check(_lib().dsb200_scene_load(self.h, C.byref(scene.c), C.byref(renderState.c) if renderState is not None else None,
+                                           str(directory).encode()))
+
     def PrefetchAllocation(self, scene, nextView, nextTrackingState, renderState, waitEvent=None):
         """Look-ahead (asynchronous mode): the request pass of the NEXT frame's allocation, overlapping this frame's raycast.
         nextView / nextTrackingState may be engine objects or raw abi.View / abi.Tracking structs."""

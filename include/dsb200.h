@@ -304,6 +304,16 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
  * that record timing events or flush caches between frames: bench.py).  dsb200_reset_scene abandons a pending look-ahead. */
 int dsb200_recon_join_prefetch(dsb200_recon *e);
 
+/* Volume checkpoint (the fork never calls ORUtils/MemoryBlockPersister.h, so the reference
+ * has no save / resume): writes voxel.dat, alloc.dat, hash.dat, excess.dat -- and visible.dat, vistype.dat when rs is given --
+ * into an existing directory, each file in MemoryBlockPersister's layout (int32 element count, raw elements; :88-140),
+ * plus counters.txt (capacities, free-list tops, visible count, scene parameters).  Synchronises the device.
+ * load: the scene (and render state) must have the saved capacities; pass the engine that will keep working on the scene so
+ * that its derived state (device counters, visibility bitmap, sdf shadow, pruning history, pending look-ahead) is reset. */
+int dsb200_scene_save(const dsb200_scene *scene, const dsb200_render_state *rs, const char *directory);
+int dsb200_scene_load(dsb200_recon *e /* may be NULL */, dsb200_scene *scene, dsb200_render_state *rs /* may be NULL */,
+                      const char *directory);
+
 /* ---- ICP depth tracker: the device-specific half ----
  * The reference's tracker is a host Levenberg-Marquardt loop (ITMLib/Engine/ITMDepthTracker.cpp:153-211, shared by
  * its CPU and CUDA builds) around ONE device virtual, ComputeGandH (ITMDepthTracker.h:59;

@@ -298,3 +298,37 @@ def test_ragged_sizes_and_empty_frames(fused):
     hz.assert_images_equal(dict(range=fo["range"], raycast=fo["raycast"], image=fo["image"]),
                            dict(range=fg["range"], raycast=fg["raycast"], image=fg["image"]), "ragged free view")
     gpu.close(); ora.close()
+
+
+def test_checkpoint_round_trip(tmp_path):
+    """dsb200_scene_save / dsb200_scene_load: a fresh engine + scene that loads the checkpoint continues the sequence exactly
+    like the engine that wrote it (and like the oracle's uninterrupted run); files follow MemoryBlockPersister's layout."""
+    import os
+    cfg, frames = synth.make_sequence("tiny", 8)
+    a, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    for f in frames[:4]:
+        a.set_frame(f); ora.set_frame(f)
+        assert a.process_frame() == ora.process_frame()
+    a.recon.SaveCheckpoint(a.scene, a.rs, tmp_path)
+    total = hz.SMALL_CAPS["bucket_num"] + hz.SMALL_CAPS["excess_size"]
+    raw = open(os.path.join(str(tmp_path), "hash.dat"), "rb").read()
+    assert int(np.frombuffer(raw[:4], np.int32)[0]) == total and len(raw) == 4 + 20 * total
+    assert os.path.getsize(os.path.join(str(tmp_path), "voxel.dat")) == 4 + 8 * 512 * hz.SMALL_CAPS["num_blocks"]
+    b = hz.GpuBackend(cfg, hz.SMALL_CAPS)
+    b.recon.LoadCheckpoint(b.scene, b.rs, tmp_path)
+    hz.assert_state_equal(ora.state(), b.state(), "state right after loading")
+    for i, f in enumerate(frames[4:]):
+        for x in (a, b, ora):
+            x.set_frame(f)
+        ra, rb, ro = a.process_frame(), b.process_frame(), ora.process_frame()
+        assert ra == rb == ro
+        hz.assert_state_equal(ora.state(), b.state(), "resumed frame %d" % i)
+        hz.assert_images_equal(ora.images(), b.images(), "resumed frame %d" % i)
+        hz.assert_state_equal(a.state(), b.state(), "resumed vs uninterrupted frame %d" % i)
+    # a scene with other capacities refuses the checkpoint
+    other = dict(hz.SMALL_CAPS); other["excess_size"] //= 2
+    c = hz.GpuBackend(cfg, other)
+    with pytest.raises(abi.Dsb200Error):
+        c.recon.LoadCheckpoint(c.scene, c.rs, tmp_path)
+    for x in (a, b, c, ora):
+        x.close()
