@@ -701,6 +701,10 @@ def main():
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    # stdout carries exactly one JSON line: anything libraries print meanwhile (NCCL's version banner ...) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         out = run_reference(args, rank, world)
     elif args.mode == "sharded":
@@ -711,6 +715,9 @@ def main():
         out = run_tracked(args, rank, world, local_rank)
     else:
         out = run_ours(args, rank, world, local_rank)
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    os.close(saved_stdout)
     if out is not None:
         print(json.dumps(out))
 
