@@ -4,6 +4,7 @@
 #include "ITMSceneReconstructionEngine_B200.h"
 #include "ITMVisualisationEngine_B200.h"
 #include "ITMDepthTracker_B200.h"
+#include "ITMViewBuilder_B200.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
 
 using namespace ITMLib::Engine;
@@ -30,3 +31,5 @@ ITMTracker *make_tracker(Vector2i imgSize, TrackerIterationType *regime, const I
 }
 static_assert((int)TRACKER_ITERATION_ROTATION == DSB200_TRACKER_ITERATION_ROTATION && (int)TRACKER_ITERATION_TRANSLATION == DSB200_TRACKER_ITERATION_TRANSLATION &&
               (int)TRACKER_ITERATION_BOTH == DSB200_TRACKER_ITERATION_BOTH && (int)TRACKER_ITERATION_NONE == DSB200_TRACKER_ITERATION_NONE, "TrackerIterationType values");
+// ITMMainEngine.cpp:57-81 / DenseSLAM InfiniTamDriver.cpp:286 with deviceType == DEVICE_B200
+ITMViewBuilder *make_view_builder(const ITMRGBDCalib *calib) { return new ITMViewBuilder_B200(calib); }

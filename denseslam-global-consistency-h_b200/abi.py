@@ -176,6 +176,8 @@ def load():
         "dsb200_mat4_multiply": (None, [_P(C.c_float), _P(C.c_float), _P(C.c_float)]),
         "dsb200_scene_save": (C.c_int, [_P(Scene), _P(RenderState), cp]),
         "dsb200_scene_load": (C.c_int, [vp, _P(Scene), _P(RenderState), cp]),
+        "dsb200_depth_filter_pass": (C.c_int, [vp, vp, i32, i32, vp]),
+        "dsb200_convert_disparity_to_depth": (C.c_int, [vp, vp, i32, i32, C.c_float, C.c_float, C.c_float, vp]),
         "dsb200_view_filter_depth": (C.c_int, [_P(View), vp, vp]),
         "dsb200_recon_prefetch_allocation": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), vp]),
         "dsb200_recon_join_prefetch": (C.c_int, [vp]),

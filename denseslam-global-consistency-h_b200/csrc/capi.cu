@@ -954,6 +954,24 @@ int dsb200_filter_subsample_with_holes(const float *in, int32_t w, int32_t h, fl
     return DSB200_OK;
 }
 
+int dsb200_depth_filter_pass(const float *in, float *out, int32_t w, int32_t h, void *stream)
+{
+    if (!in || !out || in == out) return fail(DSB200_ERR_INVALID, "depth_filter_pass: null or aliased images");
+    if (w < 5 || h < 5) return fail(DSB200_ERR_INVALID, "depth_filter_pass: image smaller than the 5x5 window");
+    launch_filter_depth((cudaStream_t)stream, in, out, w, h);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
+int dsb200_convert_disparity_to_depth(const int16_t *disparity, float *depth, int32_t w, int32_t h, float param_x, float param_y,
+                                      float fx_depth, void *stream)
+{
+    if (!disparity || !depth || w <= 0 || h <= 0) return fail(DSB200_ERR_INVALID, "convert_disparity_to_depth: null argument");
+    launch_disparity_to_depth((cudaStream_t)stream, disparity, depth, param_x, param_y, fx_depth, w * h);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
 int dsb200_view_filter_depth(dsb200_view *view, float *scratch, void *stream)
 {
     if (!view || !view->depth || !scratch) return fail(DSB200_ERR_INVALID, "view_filter_depth: null argument");

@@ -116,6 +116,26 @@ void launch_expf_selftest(cudaStream_t st, const float *x, float *y, int n)
     DSB_LAUNCH(k_expf_selftest, kNumSMs * 4, 256, 0, st, x, y, n);
 }
 
+namespace {
+// convertDisparityToDepth, DeviceAgnostic/ITMViewBuilder.h:7-20 (Kinect-style raw disparities)
+__global__ void __launch_bounds__(256) k_disparity_to_depth(const short *__restrict__ in, float *__restrict__ out, float cx, float cy,
+                                                            float fx, int n)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float t = cx - (float)in[i];
+        const float depth = (t == 0) ? 0.0f : 8.0f * cy * fx / t;
+        out[i] = (depth > 0) ? depth : -1.0f;
+    }
+}
+}
+
+void launch_disparity_to_depth(cudaStream_t st, const short *in, float *out, float paramX, float paramY, float fx, int n)
+{
+    int grid = div_up(n, 256);
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    DSB_LAUNCH(k_disparity_to_depth, grid, 256, 0, st, in, out, paramX, paramY, fx, n);
+}
+
 void launch_filter_depth(cudaStream_t st, const float *in, float *out, int W, int H)
 {
     ensure_exp_table();

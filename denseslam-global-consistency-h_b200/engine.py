@@ -400,6 +400,30 @@ class ITMDepthTracker(object):
         return _download(p.value, np.float32, w.value * h.value).reshape(h.value, w.value), np.array(intr[:], np.float32)
 
 
+def convert_disparity_to_depth(disparity_i16, param_x, param_y, fx_depth):
+    """ITMViewBuilder::ConvertDisparityToDepth on the device (host array in, host array out)"""
+    d = np.ascontiguousarray(disparity_i16, np.int16)
+    h, w = d.shape
+    src, dst = DeviceBuffer(d.nbytes), DeviceBuffer(d.size * 4)
+    src.upload(d)
+    abi.check(_lib().dsb200_convert_disparity_to_depth(src.ptr, dst.ptr, w, h, param_x, param_y, fx_depth, None))
+    out = dst.download(np.float32, d.size).reshape(h, w)
+    src.free(); dst.free()
+    return out
+
+
+def depth_filter_pass(depth):
+    """ITMViewBuilder::DepthFiltering, one pass (host array in, host array out)"""
+    d = np.ascontiguousarray(depth, np.float32)
+    h, w = d.shape
+    src, dst = DeviceBuffer(d.nbytes), DeviceBuffer(d.nbytes)
+    src.upload(d)
+    abi.check(_lib().dsb200_depth_filter_pass(src.ptr, dst.ptr, w, h, None))
+    out = dst.download(np.float32, d.size).reshape(h, w)
+    src.free(); dst.free()
+    return out
+
+
 def pose_coerce(M):
     """ITMPose::SetM + Coerce -> (M float32[16], params (tx, ty, tz, rx, ry, rz))"""
     m, p = abi.f16(M), (C.c_float * 6)()

@@ -288,6 +288,12 @@ void dsb200_mat4_multiply(const float *A, const float *B, float *out);
  * reference's; its exp() is evaluated in double and rounded (see csrc/view_filter.cu for the parity statement).  Asynchronous
  * on cuda_stream like dsb200_view_from_raw. */
 int dsb200_view_filter_depth(dsb200_view *view, float *scratch, void *cuda_stream);
+/* one pass, ITMViewBuilder::DepthFiltering(image_out, image_in) (CPU/ITMViewBuilder_CPU.cpp:119-130); device pointers, in != out */
+int dsb200_depth_filter_pass(const float *in, float *out, int32_t w, int32_t h, void *cuda_stream);
+/* ITMViewBuilder::ConvertDisparityToDepth (CPU/ITMViewBuilder_CPU.cpp:94-106, convertDisparityToDepth
+ * DeviceAgnostic/ITMViewBuilder.h:7-20): depth = 8 * param_y * fx_depth / (param_x - disparity), non-positive -> -1 */
+int dsb200_convert_disparity_to_depth(const int16_t *disparity, float *depth, int32_t w, int32_t h, float param_x,
+                                      float param_y, float fx_depth, void *cuda_stream);
 
 /* Look-ahead for streaming callers (asynchronous mode only; no counterpart in the reference).  Enqueues the first half
  * of the NEXT frame's AllocateSceneFromDepth -- setToType3 over the current visible list and the per-pixel request pass

@@ -128,11 +128,18 @@ class Oracle(object):
         L.rst_tracker_compute_g_and_h.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_int, vp, vp, vp, C.c_float,
                                                   C.c_int, C.c_int, vp, vp, vp, vp]
         L.rst_view_filter_depth.argtypes = [vp, C.c_int, C.c_int]
+        L.rst_convert_disparity_to_depth.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
         L.rst_pose_coerce.argtypes = [vp, vp]
         L.rst_pose_from_params.argtypes = [vp, vp]
         L.rst_track_camera.argtypes = [P(abi.TrackerConfig), P(abi.View), P(abi.Tracking), vp, C.c_int, C.c_int, C.c_int,
                                        P(abi.TrackerReport)]
         self.L = L
+
+    def convert_disparity_to_depth(self, disparity, param_x, param_y, fx):
+        d = np.ascontiguousarray(disparity, np.int16)
+        out = np.zeros(d.shape, np.float32)
+        self.L.rst_convert_disparity_to_depth(ptr(d), ptr(out), d.shape[1], d.shape[0], param_x, param_y, fx)
+        return out
 
     def view_filter_depth(self, depth):
         """five bilateral passes (UpdateView with useBilateralFilter) -> filtered copy"""
@@ -244,6 +251,8 @@ class RefEngine(object):
             getattr(L, name).argtypes = [vp]
         if hasattr(L, "itmref_update_view_raw"):
             L.itmref_update_view_raw.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double]
+            if hasattr(L, "itmref_convert_disparity_to_depth"):
+                L.itmref_convert_disparity_to_depth.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
             if hasattr(L, "itmref_update_view_raw_ex"):
                 L.itmref_update_view_raw_ex.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double, C.c_int]
             L.itmref_view_depth.restype = vp
@@ -331,6 +340,12 @@ class RefEngine(object):
 
     def create_icp_maps(self):
         self.L.itmref_create_icp_maps(self.h)
+
+    def convert_disparity_to_depth(self, disparity, param_x, param_y, fx):
+        d = np.ascontiguousarray(disparity, np.int16)
+        out = np.zeros(d.shape, np.float32)
+        self.L.itmref_convert_disparity_to_depth(ptr(d), ptr(out), d.shape[1], d.shape[0], param_x, param_y, fx)
+        return out
 
     def update_view_raw(self, raw_depth_i16, rgba, scale=0.001, offset=0.0, timestamp=0.0, use_bilateral_filter=False):
         """ITMViewBuilder_CPU::UpdateView (TRAFO_AFFINE) -> copy of view->depth"""

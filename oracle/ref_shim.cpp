@@ -124,6 +124,18 @@ void itmref_update_view_raw_ex(void *h, const short *rawDepth, const uint8_t *rg
     c->view->mTimeStamp = timestamp;
     delete built;
 }
+// ITMViewBuilder_CPU::ConvertDisparityToDepth on raw arrays (Kinect-style disparity calibration)
+void itmref_convert_disparity_to_depth(const short *disparity, float *depth, int W, int H, float paramX, float paramY, float fx)
+{
+    ITMRGBDCalib calib;
+    ITMViewBuilder_CPU vb(&calib);
+    ITMShortImage in(Vector2i(W, H), true, false);
+    ITMFloatImage out(Vector2i(W, H), true, false);
+    memcpy(in.GetData(MEMORYDEVICE_CPU), disparity, sizeof(short) * (size_t)W * H);
+    ITMIntrinsics intr; intr.SetFrom(fx, fx, W * 0.5f, H * 0.5f, W, H);
+    vb.ConvertDisparityToDepth(&out, &in, &intr, Vector2f(paramX, paramY));
+    memcpy(depth, out.GetData(MEMORYDEVICE_CPU), sizeof(float) * (size_t)W * H);
+}
 const float *itmref_view_depth(void *h) { return ((RefCtx *)h)->view->depth->GetData(MEMORYDEVICE_CPU); }
 
 void itmref_set_pose(void *h, const float *M) { ((RefCtx *)h)->tracking->pose_d->SetM(toM(M)); }

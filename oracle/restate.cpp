@@ -1521,6 +1521,19 @@ void rst_track_camera(const dsb200_tracker_config *cfg, const dsb200_view *view,
 // ---------------------------------------------------------------- view builder: bilateral depth filter
 extern "C" {
 
+// ITMViewBuilder_CPU::ConvertDisparityToDepth, CPU/ITMViewBuilder_CPU.cpp:94-106 with convertDisparityToDepth, DA/ITMViewBuilder.h:7-20
+void rst_convert_disparity_to_depth(const short *d_in, float *d_out, int W, int H, float paramX, float paramY, float fx_depth)
+{
+    for (int i = 0; i < W * H; i++) {
+        short disparity = d_in[i];
+        float disparity_tmp = paramX - (float)(disparity);
+        float depth;
+        if (disparity_tmp == 0) depth = 0.0;
+        else depth = 8.0f * paramY * fx_depth / disparity_tmp;
+        d_out[i] = (depth > 0) ? depth : -1.0f;
+    }
+}
+
 // ITMViewBuilder_CPU::UpdateView's useBilateralFilter branch, CPU/ITMViewBuilder_CPU.cpp:49-58 with DepthFiltering :119-130
 // and filterDepth, DA/ITMViewBuilder.h:30-53.  exp on a float argument is the float overload (glibc expf), as in the reference.
 void rst_view_filter_depth(float *depth, int W, int H)

@@ -79,6 +79,7 @@ int rst_tracker_compute_g_and_h(const float *depth, int view_w, int view_h, cons
                                 float dist_thresh, int iteration_type, int double_sums, float *f, float *nabla,
                                 float *hessian, double *sums);
 
+void rst_convert_disparity_to_depth(const short *disparity, float *depth, int w, int h, float param_x, float param_y, float fx_depth);
 void rst_view_filter_depth(float *depth, int w, int h);
 void rst_pose_coerce(float *M, float *params);
 void rst_pose_from_params(const float *params, float *M);

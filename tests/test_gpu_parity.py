@@ -255,6 +255,17 @@ def test_bilateral_depth_filter_vs_oracle():
         assert rel.max() <= 1e-6
         assert (want[2:-2, 2:-2] > 0).mean() > 0.2 and not np.array_equal(want, plain.reshape(cfg.H, cfg.W))
         view.free()
+    # the single-pass entry point (what an ITMViewBuilder subclass forwards DepthFiltering to) composes to the same result
+    d = plain.reshape(cfg.H, cfg.W)
+    for _ in range(5):
+        d = eng.depth_filter_pass(d)
+    assert np.array_equal(hz.bits(d), hz.bits(got))
+    # Kinect-style disparity conversion: bit-exact (one IEEE division per pixel)
+    disp = rng.integers(-200, 1200, (97, 131)).astype(np.int16)
+    disp[0, :8] = 1090
+    a = eng.convert_disparity_to_depth(disp, 1090.0, 0.075, 573.71)
+    b = o.convert_disparity_to_depth(disp, 1090.0, 0.075, 573.71)
+    assert np.array_equal(hz.bits(a), hz.bits(b)) and (a == -1.0).any() and (a > 0).any()
 
 
 def ragged_sequence():

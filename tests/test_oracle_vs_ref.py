@@ -106,4 +106,10 @@ def test_view_building_matches_reference():
             want_f = po.Oracle().view_filter_depth(want.reshape(cfg.H, cfg.W))
             assert np.array_equal(hz.bits(got_f), hz.bits(want_f))
             assert not np.array_equal(got_f, got) and (got_f[2:-2, 2:-2] > 0).mean() > 0.2
+        # Kinect-style disparity calibration (TRAFO_KINECT): zero denominators, negative and non-positive depths included
+        disp = rng.integers(-200, 1200, (cfg.H, cfg.W)).astype(np.int16)
+        disp[0, :8] = 1090
+        a = ref.convert_disparity_to_depth(disp, 1090.0, 0.075, 573.71)
+        b = po.Oracle().convert_disparity_to_depth(disp, 1090.0, 0.075, 573.71)
+        assert np.array_equal(hz.bits(a), hz.bits(b)) and (a == -1.0).any() and (a > 0).any()
         ref.close()
