@@ -404,6 +404,10 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 // A per-tile globaltimer trace (profiles/README.md, r01f) shows why the kernel is hard to shorten: the tickets run out after
 // a third of the kernel's duration and the rest is the tail of ~20 tiles of grazing rays that START in the first 12 us and
 // run for 100-130 us each (>100 dependent one-voxel steps).
+// A two-pass variant (first pass bounded to S steps per ray, unfinished rays queued with their state and finished by a second
+// launch with 1 or 4 rays per warp; results identical) was slower too: S = 16 / 32 / 64 with one ray per warp 0.224 / 0.181 /
+// 0.168 ms, S = 32 with four rays per warp 0.161 ms, against 0.144 ms -- so the stragglers are not slowed by divergence
+// inside their warps; each of their steps simply is several dependent L2 round trips.
 // Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
 // root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
 template <class Tables>
