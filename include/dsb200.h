@@ -5,6 +5,11 @@
  * /root/reference/src/InfiniTAM-Global-Consistency-h/InfiniTAM/):
  *   ITMLib/Engine/ITMSceneReconstructionEngine.h:45-96   (reconstruction engine)
  *   ITMLib/Engine/ITMVisualisationEngine.h:71-124        (visualisation engine)
+ * and, for the two neighbours of that path, one per device step of
+ *   ITMLib/Engine/ITMViewBuilder.h:20-55                 (depth conversions, bilateral filter)
+ *   ITMLib/Engine/ITMDepthTracker.h:26-70                (ComputeGandH; plus a one-call TrackCamera)
+ * Additions without a counterpart in the reference are marked as such: the sharded scene, the fused frame, the look-ahead
+ * allocation, the volume checkpoint.
  * The adapter subclasses shown in INTEGRATION.md pull raw DEVICE pointers out of the
  * reference objects (ITMScene, ITMRenderState_VH, ITMView, ITMTrackingState) into the POD
  * structs below and forward.  No torch / C++ types cross this boundary.
