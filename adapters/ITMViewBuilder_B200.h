@@ -44,69 +44,62 @@ namespace ITMLib
 				throw std::runtime_error("ITMViewBuilder_B200: modelSensorNoise is not supported");
 			}
 
+			// raw int16 depth + RGBA from the host: upload, convert with the view's calibration, optionally filter
 			void UpdateView(ITMView **view_ptr, ITMUChar4Image *rgbImage, ITMShortImage *rawDepthImage, double timestamp, bool useBilateralFilter,
 				bool modelSensorNoise = false)
 			{
 				if (modelSensorNoise) throw std::runtime_error("ITMViewBuilder_B200: modelSensorNoise is not supported");
-				if (*view_ptr == NULL)
-				{
-					*view_ptr = new ITMView(calib, rgbImage->noDims, rawDepthImage->noDims, true);
-					if (this->shortImage != NULL) delete this->shortImage;
-					this->shortImage = new ITMShortImage(rawDepthImage->noDims, true, true);
-					if (this->floatImage != NULL) delete this->floatImage;
-					this->floatImage = new ITMFloatImage(rawDepthImage->noDims, true, true);
-				}
+				const bool fresh = (*view_ptr == NULL);
+				if (fresh) *view_ptr = new ITMView(calib, rgbImage->noDims, rawDepthImage->noDims, true);
+				if (fresh) resizeStaging(rawDepthImage->noDims);
 				ITMView *view = *view_ptr;
 				view->mTimeStamp = timestamp;
 				view->rgb->SetFrom(rgbImage, ORUtils::MemoryBlock<Vector4u>::CPU_TO_CUDA);
-				this->shortImage->SetFrom(rawDepthImage, ORUtils::MemoryBlock<short>::CPU_TO_CUDA);
+				shortImage->SetFrom(rawDepthImage, ORUtils::MemoryBlock<short>::CPU_TO_CUDA);
 
-				switch (view->calib->disparityCalib.type)
-				{
-				case ITMDisparityCalib::TRAFO_KINECT:
-					this->ConvertDisparityToDepth(view->depth, this->shortImage, &(view->calib->intrinsics_d), view->calib->disparityCalib.params);
-					break;
-				case ITMDisparityCalib::TRAFO_AFFINE:
-					this->ConvertDepthAffineToFloat(view->depth, this->shortImage, view->calib->disparityCalib.params);
-					break;
-				default:
-					break;
-				}
+				const ITMDisparityCalib &dc = view->calib->disparityCalib;
+				if (dc.type == ITMDisparityCalib::TRAFO_KINECT) ConvertDisparityToDepth(view->depth, shortImage, &(view->calib->intrinsics_d), dc.params);
+				else if (dc.type == ITMDisparityCalib::TRAFO_AFFINE) ConvertDepthAffineToFloat(view->depth, shortImage, dc.params);
 
 				if (useBilateralFilter)
 				{
-					// five passes + copy back, as one call
+					// the reference's five DepthFiltering passes and the copy back, as one call
 					dsb200_view v; memset(&v, 0, sizeof(v));
 					v.depth = view->depth->GetData(MEMORYDEVICE_CUDA); v.depth_w = view->depth->noDims.x; v.depth_h = view->depth->noDims.y;
-					b200::check(dsb200_view_filter_depth(&v, this->floatImage->GetData(MEMORYDEVICE_CUDA), stream));
+					b200::check(dsb200_view_filter_depth(&v, floatImage->GetData(MEMORYDEVICE_CUDA), stream));
 				}
 				b200::check(dsb200_stream_synchronize(stream));
 			}
 
+			// float depth already in metres: only the two uploads
 			void UpdateView(ITMView **view_ptr, ITMUChar4Image *rgbImage, ITMFloatImage *depthImage)
 			{
 				if (*view_ptr == NULL) *view_ptr = new ITMView(calib, rgbImage->noDims, depthImage->noDims, true);
-				ITMView *view = *view_ptr;
-				view->rgb->UpdateDeviceFromHost();
-				view->depth->UpdateDeviceFromHost();
+				(*view_ptr)->rgb->UpdateDeviceFromHost();
+				(*view_ptr)->depth->UpdateDeviceFromHost();
 			}
 
+			// with an IMU sample attached to the view
 			void UpdateView(ITMView **view_ptr, ITMUChar4Image *rgbImage, ITMShortImage *depthImage, double timestamp, bool useBilateralFilter,
 				ITMIMUMeasurement *imuMeasurement)
 			{
 				if (*view_ptr == NULL)
 				{
 					*view_ptr = new ITMViewIMU(calib, rgbImage->noDims, depthImage->noDims, true);
-					if (this->shortImage != NULL) delete this->shortImage;
-					this->shortImage = new ITMShortImage(depthImage->noDims, true, true);
-					if (this->floatImage != NULL) delete this->floatImage;
-					this->floatImage = new ITMFloatImage(depthImage->noDims, true, true);
+					resizeStaging(depthImage->noDims);
 				}
-				ITMViewIMU *imuView = (ITMViewIMU*)(*view_ptr);
-				imuView->imu->SetFrom(imuMeasurement);
-				this->UpdateView(view_ptr, rgbImage, depthImage, timestamp, useBilateralFilter);
+				static_cast<ITMViewIMU*>(*view_ptr)->imu->SetFrom(imuMeasurement);
+				UpdateView(view_ptr, rgbImage, depthImage, timestamp, useBilateralFilter);
 			}
 
+		private:
+			void resizeStaging(Vector2i size)
+			{
+				delete shortImage; shortImage = new ITMShortImage(size, true, true);
+				delete floatImage; floatImage = new ITMFloatImage(size, true, true);
+			}
+
+		public:
 			explicit ITMViewBuilder_B200(const ITMRGBDCalib *calib, void *cudaStream = NULL) : ITMViewBuilder(calib), stream(cudaStream) { }
 			~ITMViewBuilder_B200(void) { }
 		};
