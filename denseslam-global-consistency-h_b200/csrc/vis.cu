@@ -408,6 +408,8 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 // launch with 1 or 4 rays per warp; results identical) was slower too: S = 16 / 32 / 64 with one ray per warp 0.224 / 0.181 /
 // 0.168 ms, S = 32 with four rays per warp 0.161 ms, against 0.144 ms -- so the stragglers are not slowed by divergence
 // inside their warps; each of their steps simply is several dependent L2 round trips.
+// An adaptive one-round-trip step (after an interpolated step, load the tri-linear cell straight away and take the nearest
+// voxel, which is always one of its eight corners, out of it; results identical) measured 0.163 ms (55 registers instead of 48).
 // Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
 // root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
 template <class Tables>
