@@ -196,8 +196,7 @@ __global__ void __launch_bounds__(kGhThreads) k_tracker_gh(TrackerParams P, cons
     if (threadIdx.x == 0) {
         *ticket = 0;                       // re-armed for the next launch on this stream
         // sequence number last: the host polls this word instead of paying a stream synchronisation per evaluation
-        *reinterpret_cast<volatile double *>(result + kGhSlots - 1) = seq;
-        __threadfence_system();
+        *reinterpret_cast<volatile double *>(result + kGhSlots - 1) = seq;      // ordered after the sums by the fences + barrier above
     }
 }
 
