@@ -38,20 +38,28 @@ namespace ITMLib
 					image_in->noDims.x, image_in->noDims.y, stream));
 			}
 
-			void ComputeNormalAndWeights(ITMFloat4Image *, ITMFloatImage *, const ITMFloatImage *, Vector4f)
+			// the sensor-noise model's depth normals and uncertainties; read only by the weighted-ICP tracker (TRACKER_WICP,
+			// ITMWeightedICPTracker.cpp:67) and the uncertainty preview (ITMMainEngine.cpp:233), neither of which DenseSLAM selects
+			void ComputeNormalAndWeights(ITMFloat4Image *normal_out, ITMFloatImage *sigmaZ_out, const ITMFloatImage *depth_in, Vector4f intrinsic)
 			{
-				// only the weighted-ICP tracker (TRACKER_WICP, ITMLibSettings.cpp:47) asks for sensor-noise modelling; DenseSLAM never does
-				throw std::runtime_error("ITMViewBuilder_B200: modelSensorNoise is not supported");
+				const float k[4] = { intrinsic.x, intrinsic.y, intrinsic.z, intrinsic.w };
+				b200::check(dsb200_compute_normal_and_weights(depth_in->GetData(MEMORYDEVICE_CUDA),
+					reinterpret_cast<float*>(normal_out->GetData(MEMORYDEVICE_CUDA)), sigmaZ_out->GetData(MEMORYDEVICE_CUDA),
+					depth_in->noDims.x, depth_in->noDims.y, k, stream));
 			}
 
 			// raw int16 depth + RGBA from the host: upload, convert with the view's calibration, optionally filter
 			void UpdateView(ITMView **view_ptr, ITMUChar4Image *rgbImage, ITMShortImage *rawDepthImage, double timestamp, bool useBilateralFilter,
 				bool modelSensorNoise = false)
 			{
-				if (modelSensorNoise) throw std::runtime_error("ITMViewBuilder_B200: modelSensorNoise is not supported");
 				const bool fresh = (*view_ptr == NULL);
 				if (fresh) *view_ptr = new ITMView(calib, rgbImage->noDims, rawDepthImage->noDims, true);
 				if (fresh) resizeStaging(rawDepthImage->noDims);
+				if (fresh && modelSensorNoise)
+				{
+					(*view_ptr)->depthNormal = new ITMFloat4Image(rawDepthImage->noDims, true, true);
+					(*view_ptr)->depthUncertainty = new ITMFloatImage(rawDepthImage->noDims, true, true);
+				}
 				ITMView *view = *view_ptr;
 				view->mTimeStamp = timestamp;
 				view->rgb->SetFrom(rgbImage, ORUtils::MemoryBlock<Vector4u>::CPU_TO_CUDA);
@@ -68,6 +76,8 @@ namespace ITMLib
 					v.depth = view->depth->GetData(MEMORYDEVICE_CUDA); v.depth_w = view->depth->noDims.x; v.depth_h = view->depth->noDims.y;
 					b200::check(dsb200_view_filter_depth(&v, floatImage->GetData(MEMORYDEVICE_CUDA), stream));
 				}
+				if (modelSensorNoise)
+					ComputeNormalAndWeights(view->depthNormal, view->depthUncertainty, view->depth, view->calib->intrinsics_d.projectionParamsSimple.all);
 				b200::check(dsb200_stream_synchronize(stream));
 			}
 

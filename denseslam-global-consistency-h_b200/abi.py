@@ -179,6 +179,7 @@ def load():
         "dsb200_depth_filter_pass": (C.c_int, [vp, vp, i32, i32, vp]),
         "dsb200_convert_disparity_to_depth": (C.c_int, [vp, vp, i32, i32, C.c_float, C.c_float, C.c_float, vp]),
         "dsb200_view_filter_depth": (C.c_int, [_P(View), vp, vp]),
+        "dsb200_compute_normal_and_weights": (C.c_int, [vp, vp, vp, i32, i32, _P(C.c_float), vp]),
         "dsb200_recon_prefetch_allocation": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), vp]),
         "dsb200_recon_join_prefetch": (C.c_int, [vp]),
         "dsb200_tracker_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
@@ -201,6 +202,7 @@ def load():
         "dsb200_debug_force_plain_division": (C.c_int, [vp, C.c_int]),
         "dsb200_selftest_division": (C.c_int, [C.c_ulonglong, C.c_ulonglong, _P(C.c_ulonglong)]),
         "dsb200_selftest_expf": (C.c_int, [vp, vp, i32]),
+        "dsb200_selftest_acosf": (C.c_int, [vp, vp, i32]),
         "dsb200_kernel_launch_count": (C.c_ulonglong, []),
     }
     for name, (res, args) in sig.items():

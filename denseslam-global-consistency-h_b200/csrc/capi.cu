@@ -972,6 +972,17 @@ int dsb200_convert_disparity_to_depth(const int16_t *disparity, float *depth, in
     return DSB200_OK;
 }
 
+int dsb200_compute_normal_and_weights(const float *depth, float *normal4, float *sigma_z, int32_t w, int32_t h, const float *intrinsics,
+                                      void *stream)
+{
+    if (!depth || !normal4 || !sigma_z || !intrinsics) return fail(DSB200_ERR_INVALID, "compute_normal_and_weights: null argument");
+    if (w <= 0 || h <= 0) return fail(DSB200_ERR_INVALID, "compute_normal_and_weights: empty image");
+    if (w < 5 || h < 5) return DSB200_OK;                      // no interior pixel: the reference's loops do not run either
+    launch_normal_and_weight((cudaStream_t)stream, depth, normal4, sigma_z, w, h, intrinsics);
+    CU(cudaGetLastError());
+    return DSB200_OK;
+}
+
 int dsb200_view_filter_depth(dsb200_view *view, float *scratch, void *stream)
 {
     if (!view || !view->depth || !scratch) return fail(DSB200_ERR_INVALID, "view_filter_depth: null argument");
@@ -998,6 +1009,20 @@ int dsb200_selftest_expf(const float *x, float *y, int32_t n)
     CU(cudaMalloc(&dx, sizeof(float) * (size_t)n)); CU(cudaMalloc(&dy, sizeof(float) * (size_t)n));
     CU(cudaMemcpy(dx, x, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
     launch_expf_selftest(nullptr, dx, dy, n);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(y, dy, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
+    cudaFree(dx); cudaFree(dy);
+    return DSB200_OK;
+}
+
+int dsb200_selftest_acosf(const float *x, float *y, int32_t n)
+{
+    if (!x || !y || n <= 0) return fail(DSB200_ERR_INVALID, "selftest_acosf: null argument");
+    if (dsb200_device_count() == 0) return fail(DSB200_ERR_NO_DEVICE, "no CUDA device: libdsb200 has no CPU fallback");
+    float *dx = nullptr, *dy = nullptr;
+    CU(cudaMalloc(&dx, sizeof(float) * (size_t)n)); CU(cudaMalloc(&dy, sizeof(float) * (size_t)n));
+    CU(cudaMemcpy(dx, x, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice));
+    launch_acosf_selftest(nullptr, dx, dy, n);
     CU(cudaGetLastError());
     CU(cudaMemcpy(y, dy, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost));
     cudaFree(dx); cudaFree(dy);

@@ -119,6 +119,8 @@ void launch_forward_render(cudaStream_t st, const RayParams &P, const float *pro
 // view_filter.cu
 void launch_filter_depth(cudaStream_t st, const float *in, float *out, int W, int H);
 void launch_disparity_to_depth(cudaStream_t st, const short *in, float *out, float paramX, float paramY, float fx, int n);
+void launch_normal_and_weight(cudaStream_t st, const float *depth, float *normal4, float *sigmaZ, int W, int H, const float *intr);
+void launch_acosf_selftest(cudaStream_t st, const float *x, float *y, int n);
 void launch_expf_selftest(cudaStream_t st, const float *x, float *y, int n);
 // tracker.cu
 void launch_filter_subsample_holes(cudaStream_t st, const float *in, int oldW, int oldH, float *out);

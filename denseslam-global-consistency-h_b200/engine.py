@@ -424,6 +424,23 @@ def depth_filter_pass(depth):
     return out
 
 
+def compute_normal_and_weights(depth, intrinsics, normal4, sigma_z):
+    """ITMViewBuilder::ComputeNormalAndWeights on the device (host arrays; normal4 (H, W, 4) and sigma_z (H, W) hold what the
+    images held before the call and come back updated, since the reference leaves part of them untouched)"""
+    d = np.ascontiguousarray(depth, np.float32)
+    h, w = d.shape
+    n4 = np.ascontiguousarray(normal4, np.float32); sz = np.ascontiguousarray(sigma_z, np.float32)
+    assert n4.shape == (h, w, 4) and sz.shape == (h, w)
+    src, dn, ds = DeviceBuffer(d.nbytes), DeviceBuffer(n4.nbytes), DeviceBuffer(sz.nbytes)
+    src.upload(d); dn.upload(n4); ds.upload(sz)
+    k = (C.c_float * 4)(*[float(np.float32(v)) for v in intrinsics])
+    abi.check(_lib().dsb200_compute_normal_and_weights(src.ptr, dn.ptr, ds.ptr, w, h, k, None))
+    out_n = dn.download(np.float32, n4.size).reshape(h, w, 4)
+    out_s = ds.download(np.float32, sz.size).reshape(h, w)
+    src.free(); dn.free(); ds.free()
+    return out_n, out_s
+
+
 def pose_coerce(M):
     """ITMPose::SetM + Coerce -> (M float32[16], params (tx, ty, tz, rx, ry, rz))"""
     m, p = abi.f16(M), (C.c_float * 6)()

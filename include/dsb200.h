@@ -407,6 +407,17 @@ int dsb200_profile_read(dsb200_recon *e, float *stage_ms /* [DSB200_PROFILE_STAG
 #define DSB200_PROFILE_ALLOC_STAGES 5
 int dsb200_profile_read_allocate(dsb200_recon *e, float *stage_ms /* [DSB200_PROFILE_ALLOC_STAGES] */);
 
+/* ITMViewBuilder::ComputeNormalAndWeights (CPU/ITMViewBuilder_CPU.cpp:132-143, computeNormalAndWeight
+ * DeviceAgnostic/ITMViewBuilder.h:55-112; CUDA/ITMViewBuilder_CUDA.cu:157-171), UpdateView's modelSensorNoise step: per-pixel
+ * depth normal (float4, w = 1 valid / -1 rejected) from central differences of the un-projected neighbours and the depth
+ * uncertainty sigma_z = 0.0012 + 0.0019 (z - 0.4)^2 + 0.0001 / sqrt(z) * (theta / (pi/2 - theta))^2, theta = acos(normal.z).
+ * depth, normal4 (w*h*4 floats) and sigma_z (w*h floats) are DEVICE pointers; intrinsics = HOST {fx, fy, cx, cy}
+ * (projectionParamsSimple.all).  Like the reference it writes only the interior [2, w-2) x [2, h-2), and for a rejected pixel only
+ * normal.w and sigma_z.  Bit-exact with the reference CPU builder (acos restates glibc's acosf, csrc/view_filter.cu).  Consumed
+ * only by the weighted-ICP tracker (ITMWeightedICPTracker.cpp:67), which DenseSLAM does not select. */
+int dsb200_compute_normal_and_weights(const float *depth, float *normal4, float *sigma_z, int32_t w, int32_t h,
+                                      const float *intrinsics, void *cuda_stream);
+
 /* ---- diagnostics of the exact-division fast paths (csrc/exactdiv.cuh) ----
  * force_plain_division: run the integrate / de-integrate kernel variants that use the compiler's `/` everywhere.
  * selftest_division: evaluates every fast-path helper against `/` on n pseudo-random operand tuples drawn from
@@ -417,6 +428,8 @@ int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsi
 /* the bilateral filter's exp (csrc/view_filter.cu, a restatement of glibc's expf) on n HOST floats: y[i] = expf(x[i]);
  * tests compare it bit for bit with the host C library's expf */
 int dsb200_selftest_expf(const float *x, float *y, int32_t n);
+/* the sensor-noise model's acos (csrc/view_filter.cu, a restatement of glibc's fdlibm acosf) on n HOST floats */
+int dsb200_selftest_acosf(const float *x, float *y, int32_t n);
 
 /* counters for bench.py: kernels launched by this library since process start */
 unsigned long long dsb200_kernel_launch_count(void);

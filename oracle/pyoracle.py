@@ -129,6 +129,7 @@ class Oracle(object):
                                                   C.c_int, C.c_int, vp, vp, vp, vp]
         L.rst_view_filter_depth.argtypes = [vp, C.c_int, C.c_int]
         L.rst_convert_disparity_to_depth.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
+        L.rst_compute_normal_and_weights.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp]
         L.rst_pose_coerce.argtypes = [vp, vp]
         L.rst_pose_from_params.argtypes = [vp, vp]
         L.rst_track_camera.argtypes = [P(abi.TrackerConfig), P(abi.View), P(abi.Tracking), vp, C.c_int, C.c_int, C.c_int,
@@ -140,6 +141,13 @@ class Oracle(object):
         out = np.zeros(d.shape, np.float32)
         self.L.rst_convert_disparity_to_depth(ptr(d), ptr(out), d.shape[1], d.shape[0], param_x, param_y, fx)
         return out
+
+    def compute_normal_and_weights(self, depth, intrinsics, normal4, sigma_z):
+        """ComputeNormalAndWeights; normal4 (H, W, 4) and sigma_z (H, W) are updated in place (only part of them is written)"""
+        d = np.ascontiguousarray(depth, np.float32)
+        k = np.ascontiguousarray(intrinsics, np.float32)
+        assert normal4.dtype == np.float32 and sigma_z.dtype == np.float32 and normal4.flags.c_contiguous and sigma_z.flags.c_contiguous
+        self.L.rst_compute_normal_and_weights(ptr(d), ptr(normal4), ptr(sigma_z), d.shape[1], d.shape[0], ptr(k))
 
     def view_filter_depth(self, depth):
         """five bilateral passes (UpdateView with useBilateralFilter) -> filtered copy"""
@@ -253,6 +261,8 @@ class RefEngine(object):
             L.itmref_update_view_raw.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double]
             if hasattr(L, "itmref_convert_disparity_to_depth"):
                 L.itmref_convert_disparity_to_depth.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
+            if hasattr(L, "itmref_compute_normal_and_weights"):
+                L.itmref_compute_normal_and_weights.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp]
             if hasattr(L, "itmref_update_view_raw_ex"):
                 L.itmref_update_view_raw_ex.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double, C.c_int]
             L.itmref_view_depth.restype = vp
@@ -346,6 +356,12 @@ class RefEngine(object):
         out = np.zeros(d.shape, np.float32)
         self.L.itmref_convert_disparity_to_depth(ptr(d), ptr(out), d.shape[1], d.shape[0], param_x, param_y, fx)
         return out
+
+    def compute_normal_and_weights(self, depth, intrinsics, normal4, sigma_z):
+        d = np.ascontiguousarray(depth, np.float32)
+        k = np.ascontiguousarray(intrinsics, np.float32)
+        assert normal4.dtype == np.float32 and sigma_z.dtype == np.float32 and normal4.flags.c_contiguous and sigma_z.flags.c_contiguous
+        self.L.itmref_compute_normal_and_weights(ptr(d), ptr(normal4), ptr(sigma_z), d.shape[1], d.shape[0], ptr(k))
 
     def update_view_raw(self, raw_depth_i16, rgba, scale=0.001, offset=0.0, timestamp=0.0, use_bilateral_filter=False):
         """ITMViewBuilder_CPU::UpdateView (TRAFO_AFFINE) -> copy of view->depth"""

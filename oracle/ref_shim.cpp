@@ -136,6 +136,22 @@ void itmref_convert_disparity_to_depth(const short *disparity, float *depth, int
     vb.ConvertDisparityToDepth(&out, &in, &intr, Vector2f(paramX, paramY));
     memcpy(depth, out.GetData(MEMORYDEVICE_CPU), sizeof(float) * (size_t)W * H);
 }
+// ITMViewBuilder_CPU::ComputeNormalAndWeights on raw arrays; normal4 / sigmaZ come in pre-filled (the reference writes only
+// part of them) and go out updated
+void itmref_compute_normal_and_weights(const float *depth, float *normal4, float *sigmaZ, int W, int H, const float *intr)
+{
+    ITMRGBDCalib calib;
+    ITMViewBuilder_CPU vb(&calib);
+    const size_t n = (size_t)W * H;
+    ITMFloatImage in(Vector2i(W, H), true, false), sz(Vector2i(W, H), true, false);
+    ITMFloat4Image nrm(Vector2i(W, H), true, false);
+    memcpy(in.GetData(MEMORYDEVICE_CPU), depth, sizeof(float) * n);
+    memcpy(sz.GetData(MEMORYDEVICE_CPU), sigmaZ, sizeof(float) * n);
+    memcpy(nrm.GetData(MEMORYDEVICE_CPU), normal4, sizeof(float) * 4 * n);
+    vb.ComputeNormalAndWeights(&nrm, &sz, &in, Vector4f(intr[0], intr[1], intr[2], intr[3]));
+    memcpy(sigmaZ, sz.GetData(MEMORYDEVICE_CPU), sizeof(float) * n);
+    memcpy(normal4, nrm.GetData(MEMORYDEVICE_CPU), sizeof(float) * 4 * n);
+}
 const float *itmref_view_depth(void *h) { return ((RefCtx *)h)->view->depth->GetData(MEMORYDEVICE_CPU); }
 
 void itmref_set_pose(void *h, const float *M) { ((RefCtx *)h)->tracking->pose_d->SetM(toM(M)); }

@@ -1563,4 +1563,39 @@ void rst_view_filter_depth(float *depth, int W, int H)
     memcpy(depth, tmp.data(), sizeof(float) * (size_t)W * H);   // five passes end in the staging image; SetFrom copies it back
 }
 
+// ITMViewBuilder_CPU::ComputeNormalAndWeights, CPU/ITMViewBuilder_CPU.cpp:132-143 with computeNormalAndWeight,
+// DA/ITMViewBuilder.h:55-112.  sqrt and acos on float arguments are the float overloads (glibc sqrtf / acosf), PI is
+// float(3.14159...) (ORUtils/MathUtils.h:28).  Only the interior is written; a rejected pixel gets normal.w = -1 and sigmaZ = -1.
+void rst_compute_normal_and_weights(const float *depth_in, float *normal_out, float *sigmaZ_out, int W, int H, const float *intrinparam)
+{
+    const float ix = intrinparam[0], iy = intrinparam[1], iz = intrinparam[2], iw = intrinparam[3];
+    const float kPI = float(3.1415926535897932384626433832795);
+    for (int y = 2; y < H - 2; y++) for (int x = 2; x < W - 2; x++) {
+        const int idx = x + y * W;
+        float *n4 = normal_out + 4 * (size_t)idx;
+        float z = depth_in[idx];
+        if (z < 0.0f) { n4[3] = -1.0f; sigmaZ_out[idx] = -1; continue; }
+        float xp[3], xm[3], yp[3], ym[3];
+        xp[2] = depth_in[(x + 1) + y * W]; yp[2] = depth_in[x + (y + 1) * W];
+        xm[2] = depth_in[(x - 1) + y * W]; ym[2] = depth_in[x + (y - 1) * W];
+        if (xp[2] <= 0 || yp[2] <= 0 || xm[2] <= 0 || ym[2] <= 0) { n4[3] = -1.0f; sigmaZ_out[idx] = -1; continue; }
+        xp[0] = xp[2] * ((x + 1.0f) - iz) * ix; xp[1] = xp[2] * (y - iw) * iy;
+        xm[0] = xm[2] * ((x - 1.0f) - iz) * ix; xm[1] = xm[2] * (y - iw) * iy;
+        yp[0] = yp[2] * (x - iz) * ix; yp[1] = yp[2] * ((y + 1.0f) - iw) * iy;
+        ym[0] = ym[2] * (x - iz) * ix; ym[1] = ym[2] * ((y - 1.0f) - iw) * iy;
+        float dx[3], dy[3], n[3];
+        for (int k = 0; k < 3; k++) { dx[k] = xp[k] - xm[k]; dy[k] = yp[k] - ym[k]; }
+        n[0] = (dx[1] * dy[2] - dx[2] * dy[1]);
+        n[1] = (dx[2] * dy[0] - dx[0] * dy[2]);
+        n[2] = (dx[0] * dy[1] - dx[1] * dy[0]);
+        if (n[0] == 0.0f && n[1] == 0 && n[2] == 0) { n4[3] = -1.0f; sigmaZ_out[idx] = -1; continue; }
+        float norm = 1.0f / sqrtf(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        n[0] *= norm; n[1] *= norm; n[2] *= norm;
+        n4[0] = n[0]; n4[1] = n[1]; n4[2] = n[2]; n4[3] = 1.0f;
+        float theta = acosf(n[2]);
+        float theta_diff = theta / (kPI * 0.5f - theta);
+        sigmaZ_out[idx] = (0.0012f + 0.0019f * (z - 0.4f) * (z - 0.4f) + 0.0001f / sqrtf(z) * theta_diff * theta_diff);
+    }
+}
+
 } // extern "C"

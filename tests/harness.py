@@ -406,3 +406,29 @@ def view_from_raw_restated(depth_i16, bgr, scale=0.001, offset=0.0):
         b = np.asarray(bgr, np.uint8)
         rgba = np.concatenate([b[..., ::-1], np.full(b.shape[:-1] + (1,), 255, np.uint8)], axis=-1)
     return depth, rgba
+
+
+def normal_and_weight_cases():
+    """depth images and intrinsics for ComputeNormalAndWeights: rendered frames (with holes), a noisy wall seen at grazing angles and
+    white noise, each with the focal length as the reference passes it (fx) and as a pinhole un-projection would (1 / fx) so that
+    acos sees its three branches (|n.z| < 0.5, n.z > 0.5, n.z < -0.5)."""
+    rng = np.random.default_rng(11)
+    out = []
+    for name in ("tiny", "tiny_street"):
+        cfg, frames = synth.make_sequence(name, 1)
+        d = frames[0].depth.reshape(cfg.H, cfg.W).copy()
+        fx, fy, cx, cy = [np.float32(v) for v in cfg.intr]
+        out.append((name, d, (fx, fy, cx, cy)))
+        out.append((name + " 1/f", d, (np.float32(1) / fx, np.float32(1) / fy, cx, cy)))
+    H, W = 61, 83
+    u = np.arange(W, dtype=np.float32)[None, :]
+    for slope in (0.0005, 0.004, 0.02, -0.03):
+        wall = (np.float32(1.5) + np.float32(slope) * u + rng.normal(0, 0.002, (H, W)).astype(np.float32)).astype(np.float32)
+        wall[rng.random((H, W)) < 0.02] = -1.0
+        out.append(("wall %g" % slope, wall, (np.float32(1 / 500.0), np.float32(1 / 500.0), np.float32(W / 2), np.float32(H / 2))))
+    noise = rng.uniform(0.3, 4.0, (H, W)).astype(np.float32)
+    noise[rng.random((H, W)) < 0.05] = -1.0
+    noise[10:14, 10:14] = 2.0                                   # flat patch: zero cross product -> rejected
+    out.append(("noise", noise, (np.float32(525.0), np.float32(525.0), np.float32(41.5), np.float32(30.5))))
+    out.append(("noise 1/f", noise, (np.float32(1 / 525.0), np.float32(1 / 525.0), np.float32(41.5), np.float32(30.5))))
+    return out

@@ -268,6 +268,53 @@ def test_bilateral_depth_filter_vs_oracle():
     assert np.array_equal(hz.bits(a), hz.bits(b)) and (a == -1.0).any() and (a > 0).any()
 
 
+def test_device_acosf_equals_host_c_library():
+    """the sensor-noise model's acos restates glibc's (fdlibm) acosf: bit-identical on every branch, special values included"""
+    import ctypes
+    lib = abi.load()
+    libm = ctypes.CDLL("libm.so.6")
+    libm.acosf.restype, libm.acosf.argtypes = ctypes.c_float, [ctypes.c_float]
+    rng = np.random.default_rng(23)
+    special = [0.0, -0.0, 1.0, -1.0, 0.5, -0.5, np.nextafter(np.float32(0.5), np.float32(0)), np.nextafter(np.float32(1), np.float32(0)),
+               -np.nextafter(np.float32(1), np.float32(0)), 2.0 ** -26, 2.0 ** -27, -(2.0 ** -26), 1e-30, 1.0000001, -3.0, np.inf, np.nan]
+    x = np.concatenate([rng.uniform(-1, 1, 1 << 21), 1.0 - np.exp(-rng.random(1 << 19) * 16), np.exp(-rng.random(1 << 19) * 30) - 1.0,
+                        rng.uniform(-1, 1, 1 << 18) * 1e-6, special]).astype(np.float32)
+    y = np.zeros_like(x)
+    abi.check(lib.dsb200_selftest_acosf(x.ctypes.data, y.ctypes.data, x.size))
+    idx = np.concatenate([rng.integers(0, x.size - len(special), 200000), np.arange(x.size - len(special), x.size)])
+    want = np.array([libm.acosf(float(v)) for v in x[idx]], np.float32)
+    got = y[idx]
+    nan = np.isnan(want)
+    assert np.array_equal(np.isnan(got), nan) and nan.sum() >= 4
+    bad = np.nonzero(hz.bits(got[~nan]) != hz.bits(want[~nan]))[0]
+    assert bad.size == 0, "%d of %d differ, first x=%r: %r vs %r" % (bad.size, idx.size, x[idx][~nan][bad[:3]], got[~nan][bad[:3]], want[~nan][bad[:3]])
+
+
+def test_normal_and_weights_vs_oracle():
+    """dsb200_compute_normal_and_weights (UpdateView's modelSensorNoise step) == oracle bit for bit, untouched elements included"""
+    eng = hz.importlib.import_module(hz.PKG + ".engine")
+    o = hz.po.Oracle()
+    valid = 0
+    for name, depth, intr in hz.normal_and_weight_cases():
+        H, W = depth.shape
+        want_n = np.full((H, W, 4), 7.25, np.float32); want_s = np.full((H, W), -3.5, np.float32)
+        got_n, got_s = eng.compute_normal_and_weights(depth, intr, want_n, want_s)
+        o.compute_normal_and_weights(depth, intr, want_n, want_s)
+        assert np.array_equal(hz.bits(got_n), hz.bits(want_n)), name
+        assert np.array_equal(hz.bits(got_s), hz.bits(want_s)), name
+        valid += int((got_n[..., 3] == 1.0).sum())
+    assert valid > 5000
+    # full-size frame (C1, 640 x 480) and an image with no interior
+    cfg, frames = synth.make_sequence("C1", 1)
+    depth = frames[0].depth.reshape(cfg.H, cfg.W)
+    want_n = np.zeros((cfg.H, cfg.W, 4), np.float32); want_s = np.zeros((cfg.H, cfg.W), np.float32)
+    got_n, got_s = eng.compute_normal_and_weights(depth, cfg.intr, want_n, want_s)
+    o.compute_normal_and_weights(depth, cfg.intr, want_n, want_s)
+    assert np.array_equal(hz.bits(got_n), hz.bits(want_n)) and np.array_equal(hz.bits(got_s), hz.bits(want_s))
+    small_n, small_s = eng.compute_normal_and_weights(np.ones((4, 9), np.float32), cfg.intr, np.zeros((4, 9, 4), np.float32), np.zeros((4, 9), np.float32))
+    assert not small_n.any() and not small_s.any()
+
+
 def ragged_sequence():
     """157 x 119 (no multiple of the 4-pixel vectors, 8x4 ray tiles, 8-pixel range-image cells or 16x16 rendering blocks) with
     empty frames: frame 0 (nothing to allocate, empty visible list), frame 3 (every visible block falls back to the frustum

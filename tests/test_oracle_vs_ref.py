@@ -113,3 +113,26 @@ def test_view_building_matches_reference():
         b = po.Oracle().convert_disparity_to_depth(disp, 1090.0, 0.075, 573.71)
         assert np.array_equal(hz.bits(a), hz.bits(b)) and (a == -1.0).any() and (a > 0).any()
         ref.close()
+
+
+def test_normal_and_weights_match_reference():
+    """ITMViewBuilder_CPU::ComputeNormalAndWeights (UpdateView's modelSensorNoise step): restatement == reference bit for bit,
+    including which elements are left untouched (border, normal.xyz of rejected pixels)."""
+    o = po.Oracle()
+    ref = po.RefEngine(8, 8, synth.make_sequence("tiny", 1)[0].params())
+    seen_valid = seen_rejected = 0
+    for name, depth, intr in hz.normal_and_weight_cases():
+        H, W = depth.shape
+        fill_n = np.full((H, W, 4), 7.25, np.float32); fill_s = np.full((H, W), -3.5, np.float32)
+        n_ref, s_ref = fill_n.copy(), fill_s.copy()
+        n_ora, s_ora = fill_n.copy(), fill_s.copy()
+        ref.compute_normal_and_weights(depth, intr, n_ref, s_ref)
+        o.compute_normal_and_weights(depth, intr, n_ora, s_ora)
+        assert np.array_equal(hz.bits(n_ref), hz.bits(n_ora)), name
+        assert np.array_equal(hz.bits(s_ref), hz.bits(s_ora)), name
+        assert (s_ref[:2] == -3.5).all() and (s_ref[:, -2:] == -3.5).all() and (n_ref[-2:] == 7.25).all(), name
+        seen_valid += int((n_ref[..., 3] == 1.0).sum()); seen_rejected += int((n_ref[..., 3] == -1.0).sum())
+        rej = n_ref[..., 3] == -1.0
+        assert (n_ref[rej][:, :3] == 7.25).all() and (s_ref[rej] == -1.0).all(), name
+    assert seen_valid > 5000 and seen_rejected > 100
+    ref.close()
