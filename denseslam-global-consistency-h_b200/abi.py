@@ -53,6 +53,12 @@ class Scene(C.Structure):
         return self.bucket_num + self.excess_size
 
 
+class SwapCache(C.Structure):
+    """dsb200_swap_cache (ITMGlobalCache): swap states + the host-side block store"""
+    _fields_ = [("states", C.c_void_p), ("has_stored", C.c_void_p), ("stored", C.c_void_p),
+                ("total_entries", C.c_int32), ("transfer_blocks", C.c_int32)]
+
+
 class RenderState(C.Structure):
     _fields_ = [("visible_ids", C.c_void_p), ("visible_type", C.c_void_p), ("visible_capacity", C.c_int32),
                 ("no_visible", C.c_int32), ("range_image", C.c_void_p), ("raycast_result", C.c_void_p),

@@ -418,6 +418,48 @@ int dsb200_profile_read_allocate(dsb200_recon *e, float *stage_ms /* [DSB200_PRO
 int dsb200_compute_normal_and_weights(const float *depth, float *normal4, float *sigma_z, int32_t w, int32_t h,
                                       const float *intrinsics, void *cuda_stream);
 
+/* ---- host <-> device block swapping: ITMSwappingEngine on ITMGlobalCache ----
+ * ITMGlobalCache (Objects/ITMGlobalCache.h:18-129): the per-entry swap states and the host-side block store.
+ * states: ITMHashSwapState (ITMLibDefines.h:76-85), one byte per hash entry: 0 = most recent data on the host, 1 = on the host
+ * and in the volume, not combined yet, 2 = most recent data in the volume.  In a cache obtained from dsb200_swap_cache_of the
+ * states are a DEVICE array and the store is HOST memory. */
+typedef struct dsb200_swap_cache {
+    uint8_t *states;               /* [total_entries] */
+    uint8_t *has_stored;           /* HOST bool[total_entries]            (hasStoredData) */
+    dsb200_voxel *stored;          /* HOST [total_entries * 512]          (storedVoxelBlocks) */
+    int32_t total_entries;         /* bucket_num + excess_size */
+    int32_t transfer_blocks;       /* SDF_TRANSFER_BLOCK_NUM (0x1000, ITMLibDefines.h:42): most blocks moved by one call */
+} dsb200_swap_cache;
+#define DSB200_DEFAULT_TRANSFER_BLOCKS 0x1000
+typedef struct dsb200_swap dsb200_swap;
+/* ITMGlobalCache() + ITMSwappingEngine_CUDA(): states zeroed, store empty.  The store is reserved lazily (untouched pages cost
+ * nothing), the staging buffers (transfer_blocks blocks, pinned + device) eagerly. */
+int dsb200_swap_create(dsb200_swap **out, int32_t total_entries, int32_t transfer_blocks, void *cuda_stream);
+int dsb200_swap_destroy(dsb200_swap *s);
+int dsb200_swap_cache_of(dsb200_swap *s, dsb200_swap_cache *out);
+/* The swap-state pass of AllocateSceneFromDepth when scene->useSwapping (CPU/ITMSceneReconstructionEngine_CPU.cpp:287-299,
+ * CUDA .cu:1730-1733): every entry whose visibility flag is non-zero and whose state is not 2 goes to state 1.  Call it after
+ * dsb200_recon_allocate_from_depth (the flags it reads are that call's final flags). */
+int dsb200_swap_mark_visible(dsb200_swap *s, const dsb200_render_state *rs);
+/* ITMSwappingEngine::IntegrateGlobalIntoLocal (CPU/ITMSwappingEngine_CPU.cpp:22-131, CUDA .cu:263-306): the first
+ * transfer_blocks entries in state 1 (ascending entry index) get their stored block, if any, combined into the volume
+ * (combineVoxelDepthInformation / combineVoxelColorInformation, DeviceAgnostic/ITMSwappingEngine.h:7-45) and go to state 2.
+ * *moved = entries handled.  An entry whose ptr is negative is not combined (the reference indexes the volume with it). */
+int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene, int32_t *moved);
+/* ITMSwappingEngine::SaveToGlobalMemory (CPU .cpp:133-297, CUDA .cu:308-390): the first transfer_blocks entries (ascending)
+ * in state 2 with a block in the volume -- and, with a render state, a visibility flag of 0 -- are copied to the host store,
+ * go to state 0, and while the free list has room (the reference's test vbaIdx < SDF_BUCKET_NUM - 1) their block is reset,
+ * pushed on the free list and the entry's ptr becomes -1.  rs = NULL is the overload DenseSLAM calls to swap a whole local map
+ * out (DS/DenseSlam.h:248-251).  scene->last_free_block is read and updated: synchronise an asynchronous engine first
+ * (dsb200_recon_sync), and tell the engine afterwards (dsb200_recon_notify_scene_modified). */
+int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const dsb200_render_state *rs, int32_t *moved);
+/* ITMGlobalCache::SaveToFile / ReadFromFile (Objects/ITMGlobalCache.h:75-105): bool[total] then total blocks */
+int dsb200_swap_save_file(dsb200_swap *s, const char *path);
+int dsb200_swap_load_file(dsb200_swap *s, const char *path);
+/* Voxels, hash pointers or the free list were changed behind the reconstruction engine's back (swapping): device counters
+ * are re-seeded from the scene's host mirrors, the sdf shadow is rebuilt on first use, a pending look-ahead is dropped. */
+int dsb200_recon_notify_scene_modified(dsb200_recon *e);
+
 /* ---- diagnostics of the exact-division fast paths (csrc/exactdiv.cuh) ----
  * force_plain_division: run the integrate / de-integrate kernel variants that use the compiler's `/` everywhere.
  * selftest_division: evaluates every fast-path helper against `/` on n pseudo-random operand tuples drawn from

@@ -50,6 +50,19 @@ class HostScene(object):
                            1 if use_swapping else 0)
 
 
+class HostSwapCache(object):
+    """Host-memory twin of ITMGlobalCache; the block store is a dict of touched entries behind a sparse numpy buffer."""
+
+    def __init__(self, total_entries, transfer_blocks=0x1000):
+        self.states = np.zeros(total_entries, np.uint8)
+        self.has_stored = np.zeros(total_entries, np.uint8)
+        self.stored = np.zeros(total_entries * abi.BLOCK_SIZE3, dtype=abi.VOXEL_DTYPE)     # untouched pages are never committed
+        self.c = abi.SwapCache(ptr(self.states), ptr(self.has_stored), ptr(self.stored), total_entries, transfer_blocks)
+
+    def stored_block(self, entry):
+        return self.stored[entry * abi.BLOCK_SIZE3:(entry + 1) * abi.BLOCK_SIZE3]
+
+
 class HostRenderState(object):
     def __init__(self, total_entries, width, height, visible_capacity=abi.DEFAULT_LOCAL_BLOCKS):
         self.visible_ids = np.zeros(visible_capacity, dtype=np.int32)
@@ -130,11 +143,25 @@ class Oracle(object):
         L.rst_view_filter_depth.argtypes = [vp, C.c_int, C.c_int]
         L.rst_convert_disparity_to_depth.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
         L.rst_compute_normal_and_weights.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp]
+        L.rst_swap_mark_visible.argtypes = [P(abi.SwapCache), P(abi.RenderState)]
+        L.rst_swap_integrate_global_into_local.restype = C.c_int
+        L.rst_swap_integrate_global_into_local.argtypes = [P(abi.SwapCache), P(abi.Scene)]
+        L.rst_swap_save_to_global_memory.restype = C.c_int
+        L.rst_swap_save_to_global_memory.argtypes = [P(abi.SwapCache), P(abi.Scene), P(abi.RenderState)]
         L.rst_pose_coerce.argtypes = [vp, vp]
         L.rst_pose_from_params.argtypes = [vp, vp]
         L.rst_track_camera.argtypes = [P(abi.TrackerConfig), P(abi.View), P(abi.Tracking), vp, C.c_int, C.c_int, C.c_int,
                                        P(abi.TrackerReport)]
         self.L = L
+
+    def swap_mark_visible(self, cache, rs):
+        self.L.rst_swap_mark_visible(C.byref(cache.c), C.byref(rs.c))
+
+    def swap_integrate_global_into_local(self, cache, scene):
+        return self.L.rst_swap_integrate_global_into_local(C.byref(cache.c), C.byref(scene.c))
+
+    def swap_save_to_global_memory(self, cache, scene, rs=None):
+        return self.L.rst_swap_save_to_global_memory(C.byref(cache.c), C.byref(scene.c), C.byref(rs.c) if rs is not None else None)
 
     def convert_disparity_to_depth(self, disparity, param_x, param_y, fx):
         d = np.ascontiguousarray(disparity, np.int16)
@@ -263,6 +290,15 @@ class RefEngine(object):
                 L.itmref_convert_disparity_to_depth.argtypes = [vp, vp, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
             if hasattr(L, "itmref_compute_normal_and_weights"):
                 L.itmref_compute_normal_and_weights.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp]
+            if hasattr(L, "itmref_swap_states"):
+                L.itmref_swap_integrate_global_into_local.argtypes = [vp]
+                L.itmref_swap_save_to_global_memory.argtypes = [vp, C.c_int]
+                L.itmref_swap_states.restype = vp
+                L.itmref_swap_states.argtypes = [vp]
+                L.itmref_swap_has_stored.argtypes = [vp, C.c_int]
+                L.itmref_swap_has_stored_all.argtypes = [vp, vp]
+                L.itmref_swap_stored_block.restype = vp
+                L.itmref_swap_stored_block.argtypes = [vp, C.c_int]
             if hasattr(L, "itmref_update_view_raw_ex"):
                 L.itmref_update_view_raw_ex.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_double, C.c_int]
             L.itmref_view_depth.restype = vp
@@ -338,6 +374,23 @@ class RefEngine(object):
         o = np.zeros(16, np.float32)
         self.L.itmref_mat4_mul(ptr(a), ptr(b), ptr(o))
         return o
+
+    def swap_integrate_global_into_local(self):
+        self.L.itmref_swap_integrate_global_into_local(self.h)
+
+    def swap_save_to_global_memory(self, with_render_state=True):
+        self.L.itmref_swap_save_to_global_memory(self.h, 1 if with_render_state else 0)
+
+    def swap_states(self):
+        return self._arr(self.L.itmref_swap_states(self.h), np.uint8, self.total).copy()
+
+    def swap_has_stored(self):
+        out = np.zeros(self.total, np.uint8)
+        self.L.itmref_swap_has_stored_all(self.h, ptr(out))
+        return out
+
+    def swap_stored_block(self, entry):
+        return self._arr(self.L.itmref_swap_stored_block(self.h, int(entry)), abi.VOXEL_DTYPE, abi.BLOCK_SIZE3).copy()
 
     def allocate(self, only_visible=False):
         self.L.itmref_allocate(self.h, 1 if only_visible else 0)

@@ -11,6 +11,8 @@
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.cpp:25-342
 //   ITMVisualisationEngine_CPU<ITMVoxel,ITMVoxelBlockHash>
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.cpp:27-180,296-459
+//   ITMSwappingEngine_CPU<ITMVoxel,ITMVoxelBlockHash> on the scene's ITMGlobalCache
+//       ITMLib/Engine/DeviceSpecific/CPU/ITMSwappingEngine_CPU.cpp:22-297, Objects/ITMGlobalCache.h
 //   ITMDepthTracker_CPU (+ the shared host loop ITMLib/Engine/ITMDepthTracker.cpp) and ITMLowLevelEngine_CPU
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMDepthTracker_CPU.cpp:13-79, CPU/ITMLowLevelEngine_CPU.cpp:50-62
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.h"
@@ -19,6 +21,7 @@
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMViewBuilder_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMDepthTracker_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMSwappingEngine_CPU.h"
 
 #include <cstring>
 #include <cstdint>
@@ -152,6 +155,29 @@ void itmref_compute_normal_and_weights(const float *depth, float *normal4, float
     memcpy(sigmaZ, sz.GetData(MEMORYDEVICE_CPU), sizeof(float) * n);
     memcpy(normal4, nrm.GetData(MEMORYDEVICE_CPU), sizeof(float) * 4 * n);
 }
+// ITMSwappingEngine_CPU on the scene's global cache (the context must have been created with useSwapping)
+void itmref_swap_integrate_global_into_local(void *h)
+{
+    RefCtx *c = (RefCtx *)h;
+    ITMSwappingEngine_CPU<ITMVoxel, ITMVoxelBlockHash> sw;
+    sw.IntegrateGlobalIntoLocal(c->scene, c->rs);
+}
+void itmref_swap_save_to_global_memory(void *h, int withRenderState)
+{
+    RefCtx *c = (RefCtx *)h;
+    ITMSwappingEngine_CPU<ITMVoxel, ITMVoxelBlockHash> sw;
+    if (withRenderState) sw.SaveToGlobalMemory(c->scene, c->rs); else sw.SaveToGlobalMemory(c->scene);
+}
+uint8_t *itmref_swap_states(void *h) { return (uint8_t *)((RefCtx *)h)->scene->globalCache->GetSwapStates(false); }
+int itmref_swap_has_stored(void *h, int entry) { return ((RefCtx *)h)->scene->globalCache->HasStoredData(entry) ? 1 : 0; }
+const void *itmref_swap_stored_block(void *h, int entry) { return ((RefCtx *)h)->scene->globalCache->GetStoredVoxelBlock(entry); }
+void itmref_swap_has_stored_all(void *h, uint8_t *out)
+{
+    ITMGlobalCache<ITMVoxel> *g = ((RefCtx *)h)->scene->globalCache;
+    for (int i = 0; i < g->noTotalEntries; i++) out[i] = g->HasStoredData(i) ? 1 : 0;
+}
+int itmref_sizeof_swap_state() { return (int)sizeof(ITMHashSwapState); }
+int itmref_transfer_block_num() { return SDF_TRANSFER_BLOCK_NUM; }
 const float *itmref_view_depth(void *h) { return ((RefCtx *)h)->view->depth->GetData(MEMORYDEVICE_CPU); }
 
 void itmref_set_pose(void *h, const float *M) { ((RefCtx *)h)->tracking->pose_d->SetM(toM(M)); }

@@ -1598,4 +1598,97 @@ void rst_compute_normal_and_weights(const float *depth_in, float *normal_out, fl
     }
 }
 
+// ---------------------------------------------------------------- swapping engine
+// swap-state pass of AllocateSceneFromDepth with useSwapping, CPU/ITMSceneReconstructionEngine_CPU.cpp:287-299
+void rst_swap_mark_visible(dsb200_swap_cache *cache, const dsb200_render_state *rs)
+{
+    for (int targetIdx = 0; targetIdx < cache->total_entries; targetIdx++)
+        if (rs->visible_type[targetIdx] > 0 && cache->states[targetIdx] != 2) cache->states[targetIdx] = 1;
+}
+
+namespace {
+// combineVoxelDepthInformation + combineVoxelColorInformation, DA/ITMSwappingEngine.h:7-45 (ITMVoxel_s_rgb has colour)
+inline void combineVoxel(const dsb200_voxel &src, dsb200_voxel &dst, int maxW)
+{
+    {
+        int newW = dst.w_depth, oldW = src.w_depth;
+        float newF = sdfToFloat(dst.sdf), oldF = sdfToFloat(src.sdf);
+        if (oldW != 0) {
+            newF = oldW * oldF + newW * newF;
+            newW = oldW + newW;
+            newF /= newW;
+            newW = (newW < maxW) ? newW : maxW;
+            dst.w_depth = (uint8_t)newW;
+            dst.sdf = sdfToShort(newF);
+        }
+    }
+    {
+        int newW = dst.w_color, oldW = src.w_color;
+        float newC[3], oldC[3];
+        for (int k = 0; k < 3; k++) { newC[k] = (float)dst.clr[k] / 255.0f; oldC[k] = (float)src.clr[k] / 255.0f; }
+        if (oldW != 0) {
+            for (int k = 0; k < 3; k++) newC[k] = oldC[k] * (float)oldW + newC[k] * (float)newW;
+            newW = oldW + newW;
+            for (int k = 0; k < 3; k++) newC[k] /= (float)newW;
+            newW = (newW < maxW) ? newW : maxW;
+            for (int k = 0; k < 3; k++) dst.clr[k] = toUChar(newC[k] * 255.0f);
+            dst.w_color = (uint8_t)newW;
+        }
+    }
+}
+}
+
+// LoadFromGlobalMemory + IntegrateGlobalIntoLocal, CPU/ITMSwappingEngine_CPU.cpp:22-131
+int rst_swap_integrate_global_into_local(dsb200_swap_cache *cache, dsb200_scene *scene)
+{
+    std::vector<int> needed;
+    for (int entryId = 0; entryId < cache->total_entries; entryId++) {
+        if ((int)needed.size() >= cache->transfer_blocks) break;
+        if (cache->states[entryId] == 1) needed.push_back(entryId);
+    }
+    const int maxW = scene->params.max_w;
+    for (size_t i = 0; i < needed.size(); i++) {
+        const int entryDestId = needed[i];
+        const int ptr = scene->hash[entryDestId].ptr;
+        if (cache->has_stored[entryDestId] && ptr >= 0) {      // ptr < 0: the reference would index the volume with it
+            const dsb200_voxel *srcVB = cache->stored + (size_t)entryDestId * DSB200_BLOCK_SIZE3;
+            dsb200_voxel *dstVB = scene->voxels + (size_t)ptr * DSB200_BLOCK_SIZE3;
+            for (int vIdx = 0; vIdx < DSB200_BLOCK_SIZE3; vIdx++) combineVoxel(srcVB[vIdx], dstVB[vIdx], maxW);
+        }
+        cache->states[entryDestId] = 2;
+    }
+    return (int)needed.size();
+}
+
+// SaveToGlobalMemory(scene) / SaveToGlobalMemory(scene, renderState), CPU/ITMSwappingEngine_CPU.cpp:133-297
+int rst_swap_save_to_global_memory(dsb200_swap_cache *cache, dsb200_scene *scene, const dsb200_render_state *rs)
+{
+    int noNeededEntries = 0;
+    int noAllocatedVoxelEntries = scene->last_free_block;
+    for (int entryDestId = 0; entryDestId < cache->total_entries; entryDestId++) {
+        if (noNeededEntries >= cache->transfer_blocks) break;
+        const int localPtr = scene->hash[entryDestId].ptr;
+        if (cache->states[entryDestId] == 2 && localPtr >= 0 && (!rs || rs->visible_type[entryDestId] == 0)) {
+            dsb200_voxel *loc = scene->voxels + (size_t)localPtr * DSB200_BLOCK_SIZE3;
+            cache->has_stored[entryDestId] = 1;                 // SetStoredData, ITMGlobalCache.h:30-34 (via the staging copy)
+            memcpy(cache->stored + (size_t)entryDestId * DSB200_BLOCK_SIZE3, loc, sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3);
+            cache->states[entryDestId] = 0;
+            const int vbaIdx = noAllocatedVoxelEntries;
+            // the reference compares with SDF_BUCKET_NUM - 1; the second test only matters where it would write past the list
+            if (vbaIdx < scene->bucket_num - 1 && vbaIdx + 1 < scene->num_blocks) {
+                noAllocatedVoxelEntries++;
+                scene->alloc_list[vbaIdx + 1] = localPtr;
+                scene->hash[entryDestId].ptr = -1;
+                for (int i = 0; i < DSB200_BLOCK_SIZE3; i++) {
+                    dsb200_voxel v; memset(&v, 0, sizeof(v)); v.sdf = 32767;       // TVoxel()
+                    loc[i] = v;
+                }
+            }
+            noNeededEntries++;
+        }
+    }
+    scene->last_free_block = noAllocatedVoxelEntries;
+    return noNeededEntries;
+}
+
 } // extern "C"

@@ -82,6 +82,10 @@ int rst_tracker_compute_g_and_h(const float *depth, int view_w, int view_h, cons
 void rst_convert_disparity_to_depth(const short *disparity, float *depth, int w, int h, float param_x, float param_y, float fx_depth);
 void rst_view_filter_depth(float *depth, int w, int h);
 void rst_compute_normal_and_weights(const float *depth, float *normal4, float *sigma_z, int w, int h, const float *intrinsics);
+/* swapping engine on host arrays (cache->states is a HOST array here) */
+void rst_swap_mark_visible(dsb200_swap_cache *cache, const dsb200_render_state *rs);
+int rst_swap_integrate_global_into_local(dsb200_swap_cache *cache, dsb200_scene *scene);
+int rst_swap_save_to_global_memory(dsb200_swap_cache *cache, dsb200_scene *scene, const dsb200_render_state *rs);
 void rst_pose_coerce(float *M, float *params);
 void rst_pose_from_params(const float *params, float *M);
 void rst_track_camera(const dsb200_tracker_config *cfg, const dsb200_view *view, dsb200_tracking *tracking,

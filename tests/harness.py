@@ -432,3 +432,19 @@ def normal_and_weight_cases():
     out.append(("noise", noise, (np.float32(525.0), np.float32(525.0), np.float32(41.5), np.float32(30.5))))
     out.append(("noise 1/f", noise, (np.float32(1 / 525.0), np.float32(1 / 525.0), np.float32(41.5), np.float32(30.5))))
     return out
+
+
+def swap_scenario():
+    """frames and their order for the swapping tests: two stretches of the tiny room trajectory played forwards and then
+    backwards (blocks leave the frustum, are swapped out, come back and are combined with their stored copy), and the index in
+    the order after which the whole map is swapped out as well (SaveToGlobalMemory without a render state, DS/DenseSlam.h:248-251)"""
+    cfg, a = synth.make_sequence("tiny", 3, start=0)
+    _, b = synth.make_sequence("tiny", 3, start=30)
+    frames = a + b
+    order = list(range(len(frames))) + list(range(len(frames) - 2, -1, -1))
+    return cfg, frames, order, 7
+
+
+def voxels_equal_but_pad(a, b):
+    m = np.uint64(0x00ffffffffffffff)      # the 8th byte of ITMVoxel_s_rgb is compiler padding
+    return np.array_equal(a.view(np.uint64) & m, b.view(np.uint64) & m)

@@ -136,3 +136,39 @@ def test_normal_and_weights_match_reference():
         assert (n_ref[rej][:, :3] == 7.25).all() and (s_ref[rej] == -1.0).all(), name
     assert seen_valid > 5000 and seen_rejected > 100
     ref.close()
+
+
+def test_swapping_engine_matches_reference():
+    """ITMSwappingEngine_CPU on ITMGlobalCache (IntegrateGlobalIntoLocal, both SaveToGlobalMemory overloads) and the
+    allocator's swap-state pass: restatement == reference on the volume, the free list, the swap states and the host store."""
+    cfg, frames, order, whole_map_after = hz.swap_scenario()
+    ref = po.RefEngine(cfg.W, cfg.H, cfg.params(), use_swapping=True)
+    ref.set_calib(cfg.intr)
+    ora = hz.OracleBackend(cfg, use_swapping=True)
+    cache = po.HostSwapCache(ora.scene.c.total_entries)
+    moved_in = moved_out = 0
+    for step, k in enumerate(order):
+        f = frames[k]
+        ref.set_view(f.depth, f.rgb, f.timestamp); ref.set_pose(f.M)
+        ref.allocate(); ref.integrate()
+        ref.swap_integrate_global_into_local(); ref.swap_save_to_global_memory(True)
+        ora.set_frame(f); ora.allocate(); ora.o.swap_mark_visible(cache, ora.rs); ora.integrate()
+        moved_in += ora.o.swap_integrate_global_into_local(cache, ora.scene)
+        moved_out += ora.o.swap_save_to_global_memory(cache, ora.scene, ora.rs)
+        if step == whole_map_after:
+            ref.swap_save_to_global_memory(False)
+            n = ora.o.swap_save_to_global_memory(cache, ora.scene, None)
+            assert n > 300 and (ora.scene.hash["ptr"] == -1).sum() >= n
+        what = "swap step %d (frame %d)" % (step, k)
+        s = ora.state()
+        rstate = dict(hash=ref.hash(), visible=ref.visible(), visible_type=ref.visible_type(), last_free=ref.last_free(),
+                      alloc_list=ref.alloc_list(), excess_list=ref.excess_list())
+        hz.assert_state_equal(rstate, s, what, voxels=False)
+        assert hz.voxels_equal_but_pad(ref.voxels(), s["voxels"]), what
+        assert np.array_equal(ref.swap_states(), cache.states), what
+        has = ref.swap_has_stored()
+        assert np.array_equal(has, cache.has_stored), what
+        for e in np.nonzero(has)[0][::7]:
+            assert hz.voxels_equal_but_pad(ref.swap_stored_block(e), cache.stored_block(e)), what
+    assert moved_out > 300 and moved_in > 1000 and (cache.states == 0).any() and (cache.states == 2).any()
+    ref.close(); ora.close()
