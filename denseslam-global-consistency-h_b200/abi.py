@@ -185,6 +185,15 @@ def load():
         "dsb200_depth_filter_pass": (C.c_int, [vp, vp, i32, i32, vp]),
         "dsb200_convert_disparity_to_depth": (C.c_int, [vp, vp, i32, i32, C.c_float, C.c_float, C.c_float, vp]),
         "dsb200_view_filter_depth": (C.c_int, [_P(View), vp, vp]),
+        "dsb200_swap_create": (C.c_int, [_P(vp), i32, i32, vp]),
+        "dsb200_swap_destroy": (C.c_int, [vp]),
+        "dsb200_swap_cache_of": (C.c_int, [vp, _P(SwapCache)]),
+        "dsb200_swap_mark_visible": (C.c_int, [vp, _P(RenderState)]),
+        "dsb200_swap_integrate_global_into_local": (C.c_int, [vp, _P(Scene), _P(i32)]),
+        "dsb200_swap_save_to_global_memory": (C.c_int, [vp, _P(Scene), _P(RenderState), _P(i32)]),
+        "dsb200_swap_save_file": (C.c_int, [vp, cp]),
+        "dsb200_swap_load_file": (C.c_int, [vp, cp]),
+        "dsb200_recon_notify_scene_modified": (C.c_int, [vp]),
         "dsb200_compute_normal_and_weights": (C.c_int, [vp, vp, vp, i32, i32, _P(C.c_float), vp]),
         "dsb200_recon_prefetch_allocation": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), vp]),
         "dsb200_recon_join_prefetch": (C.c_int, [vp]),

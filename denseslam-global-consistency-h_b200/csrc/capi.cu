@@ -1249,6 +1249,17 @@ int dsb200_recon_set_sdf_shadow(dsb200_recon *e, int on)
     e->shadowFor = nullptr;       // re-derived from the voxels at the next use
     return DSB200_OK;
 }
+int dsb200_recon_notify_scene_modified(dsb200_recon *e)
+{
+    if (!e) return fail(DSB200_ERR_INVALID, "notify_scene_modified: null engine");
+    if (e->prefetchPending) { CU(cudaStreamSynchronize(e->prefetchStream)); e->prefetchPending = false; }
+    CU(cudaStreamSynchronize(e->stream));
+    e->deviceCountersValid = false;        // the next call seeds the device counters from the scene's host mirrors
+    e->shadowFor = nullptr;                // the sdf shadow is re-derived from the voxels at the next use
+    e->modEpoch++;
+    return DSB200_OK;
+}
+
 int dsb200_recon_invalidate_sdf_shadow(dsb200_recon *e)
 {
     if (!e) return fail(DSB200_ERR_INVALID, "invalidate_sdf_shadow: null engine");

@@ -400,6 +400,61 @@ class ITMDepthTracker(object):
         return _download(p.value, np.float32, w.value * h.value).reshape(h.value, w.value), np.array(intr[:], np.float32)
 
 
+class ITMSwappingEngine(object):
+    """ITMSwappingEngine + the scene's ITMGlobalCache (Engine/ITMSwappingEngine.h:16-31, Objects/ITMGlobalCache.h): swap states on
+    the device, block store in host memory.  `recon` (optional) is told after every call that changes the volume."""
+
+    def __init__(self, scene, transfer_blocks=0x1000, stream=None, recon=None):
+        self.h = C.c_void_p()
+        abi.check(_lib().dsb200_swap_create(C.byref(self.h), scene.c.total_entries, transfer_blocks, stream))
+        self.c = abi.SwapCache()
+        abi.check(_lib().dsb200_swap_cache_of(self.h, C.byref(self.c)))
+        self.recon = recon
+
+    def close(self):
+        if self.h:
+            _lib().dsb200_swap_destroy(self.h)
+            self.h = None
+
+    def _changed(self):
+        if self.recon is not None:
+            abi.check(_lib().dsb200_recon_notify_scene_modified(self.recon.h))
+
+    def MarkVisible(self, renderState):
+        """the swap-state pass the reference's AllocateSceneFromDepth runs when useSwapping is on"""
+        abi.check(_lib().dsb200_swap_mark_visible(self.h, C.byref(renderState.c)))
+
+    def IntegrateGlobalIntoLocal(self, scene, renderState=None):
+        n = C.c_int32()
+        abi.check(_lib().dsb200_swap_integrate_global_into_local(self.h, C.byref(scene.c), C.byref(n)))
+        self._changed()
+        return n.value
+
+    def SaveToGlobalMemory(self, scene, renderState=None):
+        n = C.c_int32()
+        abi.check(_lib().dsb200_swap_save_to_global_memory(self.h, C.byref(scene.c), C.byref(renderState.c) if renderState is not None else None,
+                                                           C.byref(n)))
+        self._changed()
+        return n.value
+
+    def SaveToFile(self, path):
+        abi.check(_lib().dsb200_swap_save_file(self.h, path.encode()))
+
+    def ReadFromFile(self, path):
+        abi.check(_lib().dsb200_swap_load_file(self.h, path.encode()))
+
+    # state (tests)
+    def states(self):
+        return _download(self.c.states, np.uint8, self.c.total_entries)
+
+    def has_stored(self):
+        return np.frombuffer((C.c_char * self.c.total_entries).from_address(self.c.has_stored), np.uint8).copy()
+
+    def stored_block(self, entry):
+        buf = (C.c_char * (8 * abi.BLOCK_SIZE3)).from_address(self.c.stored + int(entry) * 8 * abi.BLOCK_SIZE3)
+        return np.frombuffer(buf, abi.VOXEL_DTYPE).copy()
+
+
 def convert_disparity_to_depth(disparity_i16, param_x, param_y, fx_depth):
     """ITMViewBuilder::ConvertDisparityToDepth on the device (host array in, host array out)"""
     d = np.ascontiguousarray(disparity_i16, np.int16)

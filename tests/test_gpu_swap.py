@@ -1,0 +1,101 @@
+"""Host <-> device block swapping on the GPU (dsb200_swap_*) against the oracle, which
+tests/test_oracle_vs_ref.py pins to ITMSwappingEngine_CPU: volume, hash pointers, free list, swap states and the host store
+must match bit for bit after every call."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+
+import harness as hz
+from harness import po
+
+pytestmark = pytest.mark.gpu
+
+
+def compare(gpu, ora, swap, cache, what):
+    hz.assert_state_equal(gpu.state(), ora.state(), what)
+    assert np.array_equal(swap.states(), cache.states), what + ": swap states"
+    has = swap.has_stored()
+    assert np.array_equal(has, cache.has_stored), what + ": stored flags"
+    for e in np.nonzero(has)[0][::5]:
+        assert np.array_equal(swap.stored_block(e).view(np.uint64), cache.stored_block(e).view(np.uint64)), what + ": stored block %d" % e
+
+
+SMALL = dict(num_blocks=8192, bucket_num=16384, excess_size=4096)
+WIDE = dict(num_blocks=8192, bucket_num=1 << 21, excess_size=0x20000)     # 1089 candidate tiles: the tile scan takes two trips
+
+
+@pytest.mark.parametrize("transfer,caps", [(0x1000, SMALL), (96, SMALL), (0x1000, WIDE)], ids=["all", "capped", "wide-table"])
+def test_swapping_engine_vs_oracle(transfer, caps):
+    """the reference's per-frame schedule (allocate with useSwapping, integrate, IntegrateGlobalIntoLocal, SaveToGlobalMemory with
+    the render state) over a trajectory that leaves and re-enters parts of the room, a whole-map swap-out in the middle
+    (SaveToGlobalMemory without a render state), then fused frames on the swapped volume.  transfer = 96 makes every call hit the
+    per-call block limit (the first 96 candidates in entry order move); the small table (16 Ki buckets) also puts a good part of
+    the entries on the excess list."""
+    cfg, frames, order, whole_map_after = hz.swap_scenario()
+    gpu = hz.GpuBackend(cfg, caps=caps, use_swapping=True)
+    ora = hz.OracleBackend(cfg, caps=caps, use_swapping=True)
+    swap = gpu.eng.ITMSwappingEngine(gpu.scene, transfer, recon=gpu.recon)
+    cache = po.HostSwapCache(ora.scene.c.total_entries, transfer)
+    moved_in = moved_out = capped = 0
+    for step, k in enumerate(order):
+        f = frames[k]
+        gpu.set_frame(f); ora.set_frame(f)
+        assert gpu.allocate() == ora.allocate()
+        swap.MarkVisible(gpu.rs); ora.o.swap_mark_visible(cache, ora.rs)
+        gpu.integrate(); ora.integrate()
+        a, b = swap.IntegrateGlobalIntoLocal(gpu.scene), ora.o.swap_integrate_global_into_local(cache, ora.scene)
+        assert a == b
+        moved_in += a; capped += int(a == transfer)
+        a, b = swap.SaveToGlobalMemory(gpu.scene, gpu.rs), ora.o.swap_save_to_global_memory(cache, ora.scene, ora.rs)
+        assert a == b
+        moved_out += a; capped += int(a == transfer)
+        if step == whole_map_after:
+            a, b = swap.SaveToGlobalMemory(gpu.scene), ora.o.swap_save_to_global_memory(cache, ora.scene, None)
+            assert a == b and a > 0
+        compare(gpu, ora, swap, cache, "transfer %d step %d (frame %d)" % (transfer, step, k))
+    assert moved_in > 300 and moved_out > 90 and (cache.states == 0).any() and (cache.states == 2).any()
+    assert (capped > 4) if transfer == 96 else (capped == 0)
+    # the fused frame (allocation, integration from / into the sdf shadow, raycast) on a volume the swapping engine has rewritten
+    for k in (2, 3):
+        f = frames[k]
+        gpu.set_frame(f); ora.set_frame(f)
+        assert gpu.process_frame() == ora.process_frame()
+        swap.MarkVisible(gpu.rs); ora.o.swap_mark_visible(cache, ora.rs)
+        assert swap.IntegrateGlobalIntoLocal(gpu.scene) == ora.o.swap_integrate_global_into_local(cache, ora.scene)
+        compare(gpu, ora, swap, cache, "fused frame %d after swapping" % k)
+        hz.assert_images_equal(gpu.images(), ora.images(), "fused frame %d after swapping" % k)
+    gpu.set_frame(frames[3]); ora.set_frame(frames[3])
+    assert gpu.process_frame() == ora.process_frame()
+    hz.assert_images_equal(gpu.images(), ora.images(), "frame after combining the stored blocks")
+    compare(gpu, ora, swap, cache, "frame after combining the stored blocks")
+    swap.close(); gpu.close(); ora.close()
+
+
+def test_swap_store_file_round_trip():
+    """ITMGlobalCache::SaveToFile / ReadFromFile layout: flags then every block; a fresh cache reads the store back"""
+    cfg, frames, order, _ = hz.swap_scenario()
+    caps = dict(num_blocks=4096, bucket_num=8192, excess_size=1024)
+    gpu = hz.GpuBackend(cfg, caps=caps, use_swapping=True)
+    swap = gpu.eng.ITMSwappingEngine(gpu.scene, recon=gpu.recon)
+    gpu.set_frame(frames[0]); gpu.allocate(); swap.MarkVisible(gpu.rs); gpu.integrate()
+    assert swap.IntegrateGlobalIntoLocal(gpu.scene) > 100
+    n = swap.SaveToGlobalMemory(gpu.scene)
+    assert n > 100 and (gpu.scene.hash()["ptr"] == -1).sum() == n
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "cache.dat")
+        swap.SaveToFile(path)
+        total = gpu.scene.c.total_entries
+        assert os.path.getsize(path) == total + total * 512 * 8
+        other = gpu.eng.ITMSwappingEngine(gpu.scene)
+        other.ReadFromFile(path)
+        has = swap.has_stored()
+        assert has.sum() == n and np.array_equal(other.has_stored(), has)
+        fused = 0
+        for e in np.nonzero(has)[0][::9]:
+            assert np.array_equal(other.stored_block(e).view(np.uint64), swap.stored_block(e).view(np.uint64))
+            fused += int((other.stored_block(e)["w_depth"] > 0).any())
+        assert fused > 5
+        other.close()
+    swap.close(); gpu.close()
