@@ -5,12 +5,14 @@
 #include "ITMVisualisationEngine_B200.h"
 #include "ITMDepthTracker_B200.h"
 #include "ITMViewBuilder_B200.h"
+#include "ITMSwappingEngine_B200.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
 
 using namespace ITMLib::Engine;
 
 template class ITMLib::Engine::ITMSceneReconstructionEngine_B200<ITMVoxel, ITMVoxelIndex>;
 template class ITMLib::Engine::ITMVisualisationEngine_B200<ITMVoxel, ITMVoxelIndex>;
+template class ITMLib::Engine::ITMSwappingEngine_B200<ITMVoxel, ITMVoxelIndex>;
 
 static_assert(sizeof(ITMVoxel) == 8, "ITMVoxel_s_rgb");
 static_assert(sizeof(ITMHashEntry) == 20, "ITMHashEntry");
@@ -33,3 +35,6 @@ static_assert((int)TRACKER_ITERATION_ROTATION == DSB200_TRACKER_ITERATION_ROTATI
               (int)TRACKER_ITERATION_BOTH == DSB200_TRACKER_ITERATION_BOTH && (int)TRACKER_ITERATION_NONE == DSB200_TRACKER_ITERATION_NONE, "TrackerIterationType values");
 // ITMMainEngine.cpp:57-81 / DenseSLAM InfiniTamDriver.cpp:286 with deviceType == DEVICE_B200
 ITMViewBuilder *make_view_builder(const ITMRGBDCalib *calib) { return new ITMViewBuilder_B200(calib); }
+// ITMDenseMapper.cpp:20-33 with deviceType == DEVICE_B200 and settings->useSwapping
+ITMSwappingEngine<ITMVoxel, ITMVoxelIndex> *make_swapping() { return new ITMSwappingEngine_B200<ITMVoxel, ITMVoxelIndex>(); }
+static_assert(SDF_TRANSFER_BLOCK_NUM == DSB200_DEFAULT_TRANSFER_BLOCKS && sizeof(ITMHashSwapState) == 1, "swapping constants");
