@@ -188,6 +188,7 @@ def load():
         "dsb200_swap_create": (C.c_int, [_P(vp), i32, i32, vp]),
         "dsb200_swap_destroy": (C.c_int, [vp]),
         "dsb200_swap_cache_of": (C.c_int, [vp, _P(SwapCache)]),
+        "dsb200_swap_stored_block": (vp, [vp, i32]),
         "dsb200_swap_mark_visible": (C.c_int, [vp, _P(RenderState)]),
         "dsb200_swap_integrate_global_into_local": (C.c_int, [vp, _P(Scene), _P(i32)]),
         "dsb200_swap_save_to_global_memory": (C.c_int, [vp, _P(Scene), _P(RenderState), _P(i32)]),

@@ -4,20 +4,27 @@
 //   ITMGlobalCache (Objects/ITMGlobalCache.h:18-129)                   dsb200_swap: device swap states + staging, host store
 //   swap-state pass of AllocateSceneFromDepth (CUDA .cu:1730-1733)     k_swap_mark_visible
 //   LoadFromGlobalMemory / IntegrateGlobalIntoLocal                    k_swap_count<0> -> k_swap_scan -> k_swap_emit<0>,
-//     (CPU/ITMSwappingEngine_CPU.cpp:22-131, CUDA .cu:263-306)           host gather into pinned staging, k_swap_integrate
+//     (CPU/ITMSwappingEngine_CPU.cpp:22-131, CUDA .cu:263-306)           k_swap_integrate reading the stored blocks in place
 //   SaveToGlobalMemory, both overloads (CPU .cpp:133-297,              k_swap_count<1> -> k_swap_scan -> k_swap_emit<1>,
-//     CUDA .cu:308-390)                                                  k_swap_save, host scatter into the store
+//     CUDA .cu:308-390)                                                  k_swap_save writing the blocks into the store
 //
 // The reference's CUDA engine compacts the candidate entries with an atomic per CTA, so which 4096 entries move when more
 // are eligible depends on the schedule; its CPU engine takes the first 4096 in ascending entry order and pushes freed blocks on
 // the free list in that order.  Here the candidates are ranked in entry order (per-tile counts, one scan over the tiles, ranked
-// emit), which makes the result the CPU engine's, bit for bit.  The traffic is PCIe-bound (4 KB per block through pinned
-// staging); the kernels move 4 KB per CTA with 16-byte accesses.
+// emit), which makes the result the CPU engine's, bit for bit.
+//
+// The host store.  The reference keeps total_entries x 4 KB of malloc'd memory indexed by entry and moves blocks through a pinned
+// staging buffer: device -> staging -> memcpy into the store, whose pages are touched for the first time on that memcpy (measured
+// here with that layout: 7.8 ms per 4096-block call, 1.5 GB/s, almost all of it page faults).  Here the store is a compact arena
+// of PINNED 64 MB chunks with one slot index per entry; pinned memory is addressable from the device, so k_swap_save writes each
+// block straight into its slot and k_swap_integrate reads it from there, 16 bytes per thread over PCIe: no staging buffer, no host
+// copy, no page fault on the call path (a chunk is allocated once per 16384 new blocks).
 #include "kernels.cuh"
 #include "scan.cuh"
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace dsb {
 int fail_with(int code, const char *msg);
@@ -149,27 +156,32 @@ __device__ __forceinline__ uint2 combine_voxel(uint2 src, uint2 dst, int maxW)
     return dst;
 }
 
-// one CTA per transferred entry, two voxels per thread
-__global__ void __launch_bounds__(256) k_swap_integrate(int n, const int *__restrict__ needed, const uint8_t *__restrict__ hasSynced,
-                                                        const dsb200_voxel *__restrict__ synced, const dsb200_hash_entry *__restrict__ hash,
-                                                        dsb200_voxel *voxels, uint8_t *states, int maxW)
+// one CTA per transferred entry, two voxels (16 B) per thread; src[i] = the entry's stored block in pinned host memory, or null
+__global__ void __launch_bounds__(256) k_swap_integrate(int n, const int *__restrict__ needed, const uint4 *const *__restrict__ src,
+                                                        const dsb200_hash_entry *__restrict__ hash, dsb200_voxel *voxels, uint8_t *states,
+                                                        int maxW)
 {
     const int i = blockIdx.x;
     if (i >= n) return;
     const int entry = needed[i];
     const int ptr = reinterpret_cast<const int *>(hash)[(size_t)entry * 5 + 3];
-    if (hasSynced[i] && ptr >= 0) {
-        const uint2 *src = reinterpret_cast<const uint2 *>(synced) + (size_t)i * kBlock3;
-        uint2 *dst = reinterpret_cast<uint2 *>(voxels) + (size_t)ptr * kBlock3;
-        for (int v = threadIdx.x; v < kBlock3; v += 256) dst[v] = combine_voxel(src[v], dst[v], maxW);
+    const uint4 *from = src[i];
+    if (from != nullptr && ptr >= 0) {
+        uint4 *dst = reinterpret_cast<uint4 *>(voxels + (size_t)ptr * kBlock3);
+        const uint4 a = from[threadIdx.x];
+        uint4 b = dst[threadIdx.x];
+        const uint2 lo = combine_voxel(make_uint2(a.x, a.y), make_uint2(b.x, b.y), maxW);
+        const uint2 hi = combine_voxel(make_uint2(a.z, a.w), make_uint2(b.z, b.w), maxW);
+        dst[threadIdx.x] = make_uint4(lo.x, lo.y, hi.x, hi.y);
     }
     if (threadIdx.x == 0) states[entry] = 2;
 }
 
-// one CTA per transferred entry: block -> staging, state 0, and while the free list has room: push, ptr = -1, block reset
+// one CTA per transferred entry: block -> its slot of the host store, state 0, and while the free list has room: push, ptr = -1,
+// block reset
 __global__ void __launch_bounds__(256) k_swap_save(int n, const int *__restrict__ needed, dsb200_hash_entry *hash, dsb200_voxel *voxels,
-                                                   dsb200_voxel *__restrict__ synced, uint8_t *__restrict__ hasSynced, uint8_t *states,
-                                                   int *allocList, int lastFree0, int roomLimit)
+                                                   uint4 *const *__restrict__ dstBlocks, uint8_t *states, int *allocList, int lastFree0,
+                                                   int roomLimit)
 {
     const int i = blockIdx.x;
     if (i >= n) return;
@@ -178,13 +190,11 @@ __global__ void __launch_bounds__(256) k_swap_save(int n, const int *__restrict_
     const int ptr = *ptrField;
     __syncthreads();                                           // every thread has read ptr before thread 0 rewrites it
     uint4 *loc = reinterpret_cast<uint4 *>(voxels + (size_t)ptr * kBlock3);
-    uint4 *out = reinterpret_cast<uint4 *>(synced + (size_t)i * kBlock3);
-    out[threadIdx.x] = loc[threadIdx.x];                       // 256 threads x 16 B = one 4 KB block
+    dstBlocks[i][threadIdx.x] = loc[threadIdx.x];              // 256 threads x 16 B = one 4 KB block, written over PCIe
     const int vbaIdx = lastFree0 + i;                          // the serial loop's noAllocatedVoxelEntries at this entry
     const bool room = vbaIdx < roomLimit;
     if (room) loc[threadIdx.x] = make_uint4(0x00007fffu, 0u, 0x00007fffu, 0u);   // two TVoxel(): sdf 32767, everything else 0
     if (threadIdx.x == 0) {
-        hasSynced[i] = 1;
         states[entry] = 0;
         if (room) { allocList[vbaIdx + 1] = ptr; *ptrField = -1; }
     }
@@ -198,14 +208,18 @@ using namespace dsb;
 struct dsb200_swap {
     int total = 0, transfer = 0, nTiles = 0;
     cudaStream_t stream = nullptr;
-    // "global memory": the host store
-    uint8_t *hasStored = nullptr; dsb200_voxel *stored = nullptr;
+    // "global memory": flags + slot per entry, blocks in pinned chunks
+    uint8_t *hasStored = nullptr; int *slotOf = nullptr; int slotsUsed = 0;
+    std::vector<char *> chunks;
     // device
-    uint8_t *states = nullptr, *hasSynced = nullptr; int *needed = nullptr, *tileCount = nullptr, *tileOffset = nullptr, *result = nullptr;
-    dsb200_voxel *synced = nullptr;
-    // pinned staging
-    uint8_t *hasSyncedHost = nullptr; int *neededHost = nullptr, *resultHost = nullptr; dsb200_voxel *syncedHost = nullptr;
+    uint8_t *states = nullptr; int *needed = nullptr, *tileCount = nullptr, *tileOffset = nullptr, *result = nullptr;
+    uint4 **blockPtrs = nullptr;
+    // pinned
+    int *neededHost = nullptr, *resultHost = nullptr; uint4 **blockPtrsHost = nullptr;
 };
+
+static const int kChunkBlocks = 16384;                          // 64 MB of pinned memory per chunk
+static const size_t kBlockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
 
 #define SWCU(call)                                                                                   \
     do {                                                                                             \
@@ -217,7 +231,27 @@ struct dsb200_swap {
         }                                                                                            \
     } while (0)
 
-// rank the candidates in entry order; returns how many will move (<= transfer) with their ids in s->needed
+static char *slot_address(const dsb200_swap *s, int slot) { return s->chunks[slot / kChunkBlocks] + (size_t)(slot % kChunkBlocks) * kBlockBytes; }
+
+static bool add_chunk(dsb200_swap *s)
+{
+    char *c = nullptr;
+    if (cudaHostAlloc(&c, (size_t)kChunkBlocks * kBlockBytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return false; }
+    s->chunks.push_back(c);
+    return true;
+}
+
+// the entry's slot in the store, assigned (and a chunk allocated) on first use; null on allocation failure
+static char *slot_for(dsb200_swap *s, int entry)
+{
+    if (s->slotOf[entry] < 0) {
+        if (s->slotsUsed == (int)s->chunks.size() * kChunkBlocks && !add_chunk(s)) return nullptr;
+        s->slotOf[entry] = s->slotsUsed++;
+    }
+    return slot_address(s, s->slotOf[entry]);
+}
+
+// rank the candidates in entry order; *n = how many will move (<= transfer), their ids in s->needed and s->neededHost
 template <int MODE>
 static int swap_select(dsb200_swap *s, const dsb200_scene *scene, const uint8_t *visType, int *n)
 {
@@ -229,6 +263,10 @@ static int swap_select(dsb200_swap *s, const dsb200_scene *scene, const uint8_t 
     SWCU(cudaMemcpyAsync(s->resultHost, s->result, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
     SWCU(cudaStreamSynchronize(s->stream));
     *n = s->resultHost[0] < s->transfer ? s->resultHost[0] : s->transfer;
+    if (*n > 0) {
+        SWCU(cudaMemcpyAsync(s->neededHost, s->needed, sizeof(int) * (size_t)*n, cudaMemcpyDeviceToHost, s->stream));
+        SWCU(cudaStreamSynchronize(s->stream));
+    }
     return DSB200_OK;
 }
 
@@ -237,10 +275,10 @@ extern "C" {
 int dsb200_swap_destroy(dsb200_swap *s)
 {
     if (!s) return DSB200_OK;
-    free(s->hasStored); free(s->stored);
-    cudaFree(s->states); cudaFree(s->hasSynced); cudaFree(s->needed); cudaFree(s->tileCount); cudaFree(s->tileOffset);
-    cudaFree(s->result); cudaFree(s->synced);
-    cudaFreeHost(s->hasSyncedHost); cudaFreeHost(s->neededHost); cudaFreeHost(s->resultHost); cudaFreeHost(s->syncedHost);
+    free(s->hasStored); free(s->slotOf);
+    for (char *c : s->chunks) cudaFreeHost(c);
+    cudaFree(s->states); cudaFree(s->needed); cudaFree(s->tileCount); cudaFree(s->tileOffset); cudaFree(s->result); cudaFree(s->blockPtrs);
+    cudaFreeHost(s->neededHost); cudaFreeHost(s->resultHost); cudaFreeHost(s->blockPtrsHost);
     delete s;
     return DSB200_OK;
 }
@@ -252,25 +290,24 @@ int dsb200_swap_create(dsb200_swap **out, int32_t total_entries, int32_t transfe
     dsb200_swap *s = new dsb200_swap();
     s->total = total_entries; s->transfer = transfer_blocks; s->stream = (cudaStream_t)stream;
     s->nTiles = div_up(total_entries, kTileSlots);
-    const size_t blockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
-    // calloc of a large range maps untouched zero pages: the store costs memory only for blocks that were swapped out
     s->hasStored = (uint8_t *)calloc((size_t)total_entries, 1);
-    s->stored = (dsb200_voxel *)calloc((size_t)total_entries, blockBytes);
-    if (!s->hasStored || !s->stored) { dsb200_swap_destroy(s); return fail_with(DSB200_ERR_INVALID, "swap_create: host store allocation failed"); }
+    s->slotOf = (int *)malloc(sizeof(int) * (size_t)total_entries);
+    if (!s->hasStored || !s->slotOf) { dsb200_swap_destroy(s); return fail_with(DSB200_ERR_INVALID, "swap_create: host allocation failed"); }
+    for (int i = 0; i < total_entries; i++) s->slotOf[i] = -1;
     cudaError_t e = cudaSuccess;
     if (e == cudaSuccess) e = cudaMalloc(&s->states, (size_t)total_entries);
     if (e == cudaSuccess) e = cudaMemset(s->states, 0, (size_t)total_entries);
-    if (e == cudaSuccess) e = cudaMalloc(&s->hasSynced, (size_t)transfer_blocks);
     if (e == cudaSuccess) e = cudaMalloc(&s->needed, sizeof(int) * (size_t)transfer_blocks);
     if (e == cudaSuccess) e = cudaMalloc(&s->tileCount, sizeof(int) * (size_t)s->nTiles);
     if (e == cudaSuccess) e = cudaMalloc(&s->tileOffset, sizeof(int) * (size_t)s->nTiles);
     if (e == cudaSuccess) e = cudaMalloc(&s->result, sizeof(int) * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&s->synced, blockBytes * (size_t)transfer_blocks);
-    if (e == cudaSuccess) e = cudaMallocHost(&s->hasSyncedHost, (size_t)transfer_blocks);
+    if (e == cudaSuccess) e = cudaMalloc(&s->blockPtrs, sizeof(uint4 *) * (size_t)transfer_blocks);
     if (e == cudaSuccess) e = cudaMallocHost(&s->neededHost, sizeof(int) * (size_t)transfer_blocks);
     if (e == cudaSuccess) e = cudaMallocHost(&s->resultHost, sizeof(int) * 4);
-    if (e == cudaSuccess) e = cudaMallocHost(&s->syncedHost, blockBytes * (size_t)transfer_blocks);
+    if (e == cudaSuccess) e = cudaMallocHost(&s->blockPtrsHost, sizeof(uint4 *) * (size_t)transfer_blocks);
     if (e != cudaSuccess) { dsb200_swap_destroy(s); SWCU(e); }
+    // the first chunk of the store now, so that pinning 64 MB (tens of milliseconds) is not part of the first swap-out
+    if (!add_chunk(s)) { dsb200_swap_destroy(s); return fail_with(DSB200_ERR_CUDA, "swap_create: could not allocate the first pinned chunk of the host store"); }
     *out = s;
     return DSB200_OK;
 }
@@ -278,9 +315,15 @@ int dsb200_swap_create(dsb200_swap **out, int32_t total_entries, int32_t transfe
 int dsb200_swap_cache_of(dsb200_swap *s, dsb200_swap_cache *out)
 {
     if (!s || !out) return fail_with(DSB200_ERR_INVALID, "swap_cache_of: null argument");
-    out->states = s->states; out->has_stored = s->hasStored; out->stored = s->stored;
+    out->states = s->states; out->has_stored = s->hasStored; out->stored = nullptr;     // blocks: dsb200_swap_stored_block
     out->total_entries = s->total; out->transfer_blocks = s->transfer;
     return DSB200_OK;
+}
+
+const dsb200_voxel *dsb200_swap_stored_block(const dsb200_swap *s, int32_t entry)
+{
+    if (!s || entry < 0 || entry >= s->total || !s->hasStored[entry]) return nullptr;
+    return reinterpret_cast<const dsb200_voxel *>(slot_address(s, s->slotOf[entry]));
 }
 
 int dsb200_swap_mark_visible(dsb200_swap *s, const dsb200_render_state *rs)
@@ -302,21 +345,15 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
     if (rc) return rc;
     if (moved) *moved = n;
     if (n == 0) return DSB200_OK;
-    const size_t blockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
-    SWCU(cudaMemcpyAsync(s->neededHost, s->needed, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s->stream));
-    SWCU(cudaStreamSynchronize(s->stream));
-    // LoadFromGlobalMemory: gather the stored blocks of the needed entries into the staging buffer (CPU .cpp:52-68)
+    // LoadFromGlobalMemory (CPU .cpp:52-68) without the copy: the kernel reads the stored blocks where they lie
     for (int i = 0; i < n; i++) {
         const int entry = s->neededHost[i];
-        s->hasSyncedHost[i] = s->hasStored[entry];
-        if (s->hasStored[entry]) memcpy(s->syncedHost + (size_t)i * DSB200_BLOCK_SIZE3, s->stored + (size_t)entry * DSB200_BLOCK_SIZE3, blockBytes);
+        s->blockPtrsHost[i] = s->hasStored[entry] ? reinterpret_cast<uint4 *>(slot_address(s, s->slotOf[entry])) : nullptr;
     }
-    SWCU(cudaMemcpyAsync(s->hasSynced, s->hasSyncedHost, (size_t)n, cudaMemcpyHostToDevice, s->stream));
-    SWCU(cudaMemcpyAsync(s->synced, s->syncedHost, blockBytes * (size_t)n, cudaMemcpyHostToDevice, s->stream));
-    DSB_LAUNCH(k_swap_integrate, n, 256, 0, s->stream, n, s->needed, s->hasSynced, s->synced, scene->hash, scene->voxels, s->states,
-               scene->params.max_w);
+    SWCU(cudaMemcpyAsync(s->blockPtrs, s->blockPtrsHost, sizeof(uint4 *) * (size_t)n, cudaMemcpyHostToDevice, s->stream));
+    DSB_LAUNCH(k_swap_integrate, n, 256, 0, s->stream, n, s->needed, s->blockPtrs, scene->hash, scene->voxels, s->states, scene->params.max_w);
     SWCU(cudaGetLastError());
-    SWCU(cudaStreamSynchronize(s->stream));                    // the staging buffers are free again when the call returns
+    SWCU(cudaStreamSynchronize(s->stream));
     return DSB200_OK;
 }
 
@@ -330,22 +367,21 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
     if (rc) return rc;
     if (moved) *moved = n;
     if (n == 0) return DSB200_OK;
+    for (int i = 0; i < n; i++) {                               // SetStoredData's destination, Objects/ITMGlobalCache.h:30-34
+        char *slot = slot_for(s, s->neededHost[i]);
+        if (!slot) return fail_with(DSB200_ERR_CUDA, "swap_save_to_global_memory: could not allocate a pinned chunk of the host store");
+        s->blockPtrsHost[i] = reinterpret_cast<uint4 *>(slot);
+    }
+    SWCU(cudaMemcpyAsync(s->blockPtrs, s->blockPtrsHost, sizeof(uint4 *) * (size_t)n, cudaMemcpyHostToDevice, s->stream));
     // the reference lets the free list grow while vbaIdx < SDF_BUCKET_NUM - 1 (CPU .cpp:178); the list itself holds num_blocks
     // entries, so the second bound only differs where the reference would write past its end
     const int lastFree0 = scene->last_free_block;
     const int roomLimit = (scene->bucket_num - 1 < scene->num_blocks - 1) ? scene->bucket_num - 1 : scene->num_blocks - 1;
-    DSB_LAUNCH(k_swap_save, n, 256, 0, s->stream, n, s->needed, scene->hash, scene->voxels, s->synced, s->hasSynced, s->states,
-               scene->alloc_list, lastFree0, roomLimit);
+    DSB_LAUNCH(k_swap_save, n, 256, 0, s->stream, n, s->needed, scene->hash, scene->voxels, s->blockPtrs, s->states, scene->alloc_list,
+               lastFree0, roomLimit);
     SWCU(cudaGetLastError());
-    const size_t blockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
-    SWCU(cudaMemcpyAsync(s->neededHost, s->needed, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s->stream));
-    SWCU(cudaMemcpyAsync(s->syncedHost, s->synced, blockBytes * (size_t)n, cudaMemcpyDeviceToHost, s->stream));
-    SWCU(cudaStreamSynchronize(s->stream));
-    for (int i = 0; i < n; i++) {                               // SetStoredData, Objects/ITMGlobalCache.h:30-34
-        const int entry = s->neededHost[i];
-        s->hasStored[entry] = 1;
-        memcpy(s->stored + (size_t)entry * DSB200_BLOCK_SIZE3, s->syncedHost + (size_t)i * DSB200_BLOCK_SIZE3, blockBytes);
-    }
+    SWCU(cudaStreamSynchronize(s->stream));                    // the blocks are in the store when the call returns
+    for (int i = 0; i < n; i++) s->hasStored[s->neededHost[i]] = 1;
     int pushed = roomLimit - lastFree0;
     if (pushed < 0) pushed = 0;
     if (pushed > n) pushed = n;
@@ -358,9 +394,10 @@ int dsb200_swap_save_file(dsb200_swap *s, const char *path)
     if (!s || !path) return fail_with(DSB200_ERR_INVALID, "swap_save_file: null argument");
     FILE *f = fopen(path, "wb");
     if (!f) return fail_with(DSB200_ERR_INVALID, "swap_save_file: could not open the file for writing");
-    const size_t blockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
+    std::vector<char> zeros(kBlockBytes, 0);                    // a block that was never stored is all-zero in the reference's file
     bool ok = fwrite(s->hasStored, 1, (size_t)s->total, f) == (size_t)s->total;
-    for (int i = 0; ok && i < s->total; i++) ok = fwrite(s->stored + (size_t)i * DSB200_BLOCK_SIZE3, blockBytes, 1, f) == 1;
+    for (int i = 0; ok && i < s->total; i++)
+        ok = fwrite(s->hasStored[i] ? slot_address(s, s->slotOf[i]) : zeros.data(), kBlockBytes, 1, f) == 1;
     ok = (fclose(f) == 0) && ok;
     return ok ? DSB200_OK : fail_with(DSB200_ERR_INVALID, "swap_save_file: short write");
 }
@@ -370,13 +407,10 @@ int dsb200_swap_load_file(dsb200_swap *s, const char *path)
     if (!s || !path) return fail_with(DSB200_ERR_INVALID, "swap_load_file: null argument");
     FILE *f = fopen(path, "rb");
     if (!f) return fail_with(DSB200_ERR_INVALID, "swap_load_file: could not open the file");
-    const size_t blockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
     bool ok = fread(s->hasStored, 1, (size_t)s->total, f) == (size_t)s->total;
     for (int i = 0; ok && i < s->total; i++) {
-        // blocks that were never stored are all-zero in the file; skipping them keeps the store sparse
-        dsb200_voxel *dst = s->stored + (size_t)i * DSB200_BLOCK_SIZE3;
-        if (s->hasStored[i]) ok = fread(dst, blockBytes, 1, f) == 1;
-        else ok = fseek(f, (long)blockBytes, SEEK_CUR) == 0;
+        if (s->hasStored[i]) { char *slot = slot_for(s, i); ok = slot != nullptr && fread(slot, kBlockBytes, 1, f) == 1; }
+        else ok = fseek(f, (long)kBlockBytes, SEEK_CUR) == 0;
     }
     fclose(f);
     return ok ? DSB200_OK : fail_with(DSB200_ERR_INVALID, "swap_load_file: file shorter than the cache (other capacities?)");

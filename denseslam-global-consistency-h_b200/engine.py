@@ -451,8 +451,10 @@ class ITMSwappingEngine(object):
         return np.frombuffer((C.c_char * self.c.total_entries).from_address(self.c.has_stored), np.uint8).copy()
 
     def stored_block(self, entry):
-        buf = (C.c_char * (8 * abi.BLOCK_SIZE3)).from_address(self.c.stored + int(entry) * 8 * abi.BLOCK_SIZE3)
-        return np.frombuffer(buf, abi.VOXEL_DTYPE).copy()
+        p = _lib().dsb200_swap_stored_block(self.h, int(entry))
+        if not p:
+            return None
+        return np.frombuffer((C.c_char * (8 * abi.BLOCK_SIZE3)).from_address(p), abi.VOXEL_DTYPE).copy()
 
 
 def convert_disparity_to_depth(disparity_i16, param_x, param_y, fx_depth):

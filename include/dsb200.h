@@ -422,21 +422,25 @@ int dsb200_compute_normal_and_weights(const float *depth, float *normal4, float 
  * ITMGlobalCache (Objects/ITMGlobalCache.h:18-129): the per-entry swap states and the host-side block store.
  * states: ITMHashSwapState (ITMLibDefines.h:76-85), one byte per hash entry: 0 = most recent data on the host, 1 = on the host
  * and in the volume, not combined yet, 2 = most recent data in the volume.  In a cache obtained from dsb200_swap_cache_of the
- * states are a DEVICE array and the store is HOST memory. */
+ * states are a DEVICE array, has_stored is HOST memory and stored is NULL: the library keeps the stored blocks in a compact arena
+ * of pinned chunks that its kernels read and write in place (dsb200_swap_stored_block returns a block's address). */
 typedef struct dsb200_swap_cache {
     uint8_t *states;               /* [total_entries] */
     uint8_t *has_stored;           /* HOST bool[total_entries]            (hasStoredData) */
-    dsb200_voxel *stored;          /* HOST [total_entries * 512]          (storedVoxelBlocks) */
+    dsb200_voxel *stored;          /* HOST [total_entries * 512]          (storedVoxelBlocks); NULL from dsb200_swap_cache_of */
     int32_t total_entries;         /* bucket_num + excess_size */
     int32_t transfer_blocks;       /* SDF_TRANSFER_BLOCK_NUM (0x1000, ITMLibDefines.h:42): most blocks moved by one call */
 } dsb200_swap_cache;
 #define DSB200_DEFAULT_TRANSFER_BLOCKS 0x1000
 typedef struct dsb200_swap dsb200_swap;
-/* ITMGlobalCache() + ITMSwappingEngine_CUDA(): states zeroed, store empty.  The store is reserved lazily (untouched pages cost
- * nothing), the staging buffers (transfer_blocks blocks, pinned + device) eagerly. */
+/* ITMGlobalCache() + ITMSwappingEngine_CUDA(): states zeroed, store empty (it grows by pinned 64 MB chunks as blocks are
+ * swapped out). */
 int dsb200_swap_create(dsb200_swap **out, int32_t total_entries, int32_t transfer_blocks, void *cuda_stream);
 int dsb200_swap_destroy(dsb200_swap *s);
 int dsb200_swap_cache_of(dsb200_swap *s, dsb200_swap_cache *out);
+/* ITMGlobalCache::GetStoredVoxelBlock (Objects/ITMGlobalCache.h:36): HOST address of the entry's 512 stored voxels, NULL when
+ * HasStoredData(entry) is false */
+const dsb200_voxel *dsb200_swap_stored_block(const dsb200_swap *s, int32_t entry);
 /* The swap-state pass of AllocateSceneFromDepth when scene->useSwapping (CPU/ITMSceneReconstructionEngine_CPU.cpp:287-299,
  * CUDA .cu:1730-1733): every entry whose visibility flag is non-zero and whose state is not 2 goes to state 1.  Call it after
  * dsb200_recon_allocate_from_depth (the flags it reads are that call's final flags). */

@@ -130,10 +130,11 @@ def time_swapping(lib, rt):
     def summary(calls):
         blocks = sum(n for n, _ in calls); secs = sum(dt for _, dt in calls)
         return {"calls": len(calls), "blocks": blocks, "ms_per_call": 1e3 * secs / max(len(calls), 1),
+                "per_call": [[n, round(1e3 * dt, 4)] for n, dt in calls],
                 "blocks_per_s": blocks / secs if secs else 0.0, "GBps": blocks * 4096 / secs / 1e9 if secs else 0.0}
     res = {"workload": "C1 640x480, 5 mm voxels, 4 frames fused, transfer limit 4096 blocks per call",
            "save_to_global_memory_whole_map": summary(out_calls), "integrate_global_into_local_visible_part": summary(in_calls),
-           "timing": "host wall clock around each call (selection kernels, block kernel, PCIe copy, host store copy)"}
+           "timing": "host wall clock around each call (selection kernels, id read-back, block kernel moving 4 KB per block over PCIe)"}
     swap.close(); recon.close(); vis.close()
     for o in (scene, rs, view, trk):
         o.free()
