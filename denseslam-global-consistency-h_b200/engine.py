@@ -425,6 +425,9 @@ class ITMSwappingEngine(object):
         abi.check(_lib().dsb200_swap_mark_visible(self.h, C.byref(renderState.c)))
 
     def IntegrateGlobalIntoLocal(self, scene, renderState=None):
+        """with a render state (the reference's signature) the allocator's swap-state pass runs first, as in the C++ adapter"""
+        if renderState is not None:
+            self.MarkVisible(renderState)
         n = C.c_int32()
         abi.check(_lib().dsb200_swap_integrate_global_into_local(self.h, C.byref(scene.c), C.byref(n)))
         self._changed()

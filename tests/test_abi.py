@@ -98,3 +98,23 @@ def test_tracker_entry_points_fail_loudly_without_gpu(lib):
     assert rc < 0 and not h.value
     assert lib.dsb200_tracker_create(C.byref(h), 64, 48, 0, None) == abi.ERR_INVALID      # level count checked before any CUDA call
     assert lib.dsb200_recon_join_prefetch(None) == abi.ERR_INVALID
+
+
+def test_swap_and_view_entry_points_fail_loudly_without_gpu(lib):
+    """argument checks come before any CUDA call; with no device the constructors report it instead of falling back"""
+    assert lib.dsb200_swap_mark_visible(None, None) == abi.ERR_INVALID
+    assert lib.dsb200_swap_integrate_global_into_local(None, None, None) == abi.ERR_INVALID
+    assert lib.dsb200_swap_save_to_global_memory(None, None, None, None) == abi.ERR_INVALID
+    assert lib.dsb200_swap_save_file(None, b"/tmp/x") == abi.ERR_INVALID and lib.dsb200_swap_load_file(None, None) == abi.ERR_INVALID
+    assert not lib.dsb200_swap_stored_block(None, 0)
+    assert lib.dsb200_swap_destroy(None) == abi.OK
+    assert lib.dsb200_recon_notify_scene_modified(None) == abi.ERR_INVALID
+    assert lib.dsb200_compute_normal_and_weights(None, None, None, 64, 48, None, None) == abi.ERR_INVALID
+    h = C.c_void_p()
+    assert lib.dsb200_swap_create(C.byref(h), 0, 16, None) == abi.ERR_INVALID
+    if lib.dsb200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    assert lib.dsb200_swap_create(C.byref(h), 1024, 16, None) == abi.ERR_NO_DEVICE and not h.value
+    assert b"no CPU fallback" in lib.dsb200_last_error()
+    x = (C.c_float * 4)(0.1, 0.2, 0.3, 0.4)
+    assert lib.dsb200_selftest_acosf(x, x, 4) == abi.ERR_NO_DEVICE
