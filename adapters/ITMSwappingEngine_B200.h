@@ -4,7 +4,7 @@
 // GetSwappingEngine()->SaveToGlobalMemory(scene) when it parks a local map in host memory (DenseSLAM/DenseSlam.h:248-251).
 //
 // The reference keeps the swap states and the host block store in scene->globalCache and lets AllocateSceneFromDepth update
-// the states; here each scene gets a dsb200_swap (device states, pinned staging, host store) owned by this engine, and the
+// the states; here each scene gets a dsb200_swap (device states, pinned host store) owned by this engine, and the
 // allocator's swap-state pass (CUDA/ITMSceneReconstructionEngine_CUDA.cu:1730-1733) runs at the start of
 // IntegrateGlobalIntoLocal, the first reader of those states after an allocation.
 #pragma once

@@ -1,7 +1,7 @@
 // swap.cu -- host <-> device voxel-block swapping: ITMSwappingEngine on ITMGlobalCache.
 //
 //   reference                                                          here
-//   ITMGlobalCache (Objects/ITMGlobalCache.h:18-129)                   dsb200_swap: device swap states + staging, host store
+//   ITMGlobalCache (Objects/ITMGlobalCache.h:18-129)                   dsb200_swap: device swap states, pinned host store
 //   swap-state pass of AllocateSceneFromDepth (CUDA .cu:1730-1733)     k_swap_mark_visible
 //   LoadFromGlobalMemory / IntegrateGlobalIntoLocal                    k_swap_count<0> -> k_swap_scan -> k_swap_emit<0>,
 //     (CPU/ITMSwappingEngine_CPU.cpp:22-131, CUDA .cu:263-306)           k_swap_integrate reading the stored blocks in place
@@ -15,7 +15,7 @@
 //
 // The host store.  The reference keeps total_entries x 4 KB of malloc'd memory indexed by entry and moves blocks through a pinned
 // staging buffer: device -> staging -> memcpy into the store, whose pages are touched for the first time on that memcpy (measured
-// here with that layout: 7.8 ms per 4096-block call, 1.5 GB/s, almost all of it page faults).  Here the store is a compact arena
+// here with that layout: 1.4 ms per 4096-block swap-in, 7.8 ms per swap-out call).  Here the store is a compact arena
 // of PINNED 64 MB chunks with one slot index per entry; pinned memory is addressable from the device, so k_swap_save writes each
 // block straight into its slot and k_swap_integrate reads it from there, 16 bytes per thread over PCIe: no staging buffer, no host
 // copy, no page fault on the call path (a chunk is allocated once per 16384 new blocks).
