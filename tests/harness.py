@@ -448,3 +448,129 @@ def swap_scenario():
 def voxels_equal_but_pad(a, b):
     m = np.uint64(0x00ffffffffffffff)      # the 8th byte of ITMVoxel_s_rgb is compiler padding
     return np.array_equal(a.view(np.uint64) & m, b.view(np.uint64) & m)
+
+
+class SwapOnOracle(object):
+    """the swapping calls of the oracle behind the method names SwapOnGpu has (for checks that run on either backend)"""
+
+    def __init__(self, back, transfer=0x1000):
+        self.back = back
+        self.cache = po.HostSwapCache(back.scene.c.total_entries, transfer)
+
+    def mark(self):
+        self.back.o.swap_mark_visible(self.cache, self.back.rs)
+
+    def swap_in(self):
+        return self.back.o.swap_integrate_global_into_local(self.cache, self.back.scene)
+
+    def save(self, with_render_state):
+        return self.back.o.swap_save_to_global_memory(self.cache, self.back.scene, self.back.rs if with_render_state else None)
+
+    def has_stored(self):
+        return self.cache.has_stored.copy()
+
+    def states(self):
+        return self.cache.states.copy()
+
+    def stored_block(self, entry):
+        return self.cache.stored_block(entry).copy()
+
+    def close(self):
+        pass
+
+
+class SwapOnGpu(object):
+    def __init__(self, back, transfer=0x1000):
+        self.back = back
+        self.swap = back.eng.ITMSwappingEngine(back.scene, transfer, recon=back.recon)
+
+    def mark(self):
+        self.swap.MarkVisible(self.back.rs)
+
+    def swap_in(self):
+        return self.swap.IntegrateGlobalIntoLocal(self.back.scene)
+
+    def save(self, with_render_state):
+        return self.swap.SaveToGlobalMemory(self.back.scene, self.back.rs if with_render_state else None)
+
+    def has_stored(self):
+        return self.swap.has_stored()
+
+    def states(self):
+        return self.swap.states()
+
+    def stored_block(self, entry):
+        return self.swap.stored_block(entry)
+
+    def close(self):
+        self.swap.close()
+
+
+def check_swap_round_trip(back, sw, frames, min_blocks):
+    """Size-independent properties of a whole-map swap-out followed by the swap-in of the visible part (any backend, any size):
+    (1) every block whose entry is in state 2 reaches the host store and its hash pointer becomes -1 (entries the allocator put
+        on the excess list in the last frame were never visible, are still in state 0 and stay); the freed part of the volume is
+        back to its reset state, the rest is untouched, and free list + remaining pointers are a permutation of the block indices;
+    (2) after the next allocation has handed blocks back to the visible entries, IntegrateGlobalIntoLocal restores each of them to
+        its stored copy: combining a block of weight w with an empty one is (w * x) / w, so weights come back exactly and the
+        quantised sdf / colours within 1 LSB."""
+    nb = back.scene.c.num_blocks
+    for f in frames:
+        back.set_frame(f)
+        assert back.allocate() == 0
+        sw.mark(); back.integrate()
+        while sw.swap_in():                  # until no entry is left in state 1 (a call moves at most the transfer limit)
+            pass
+    before = back.state()
+    live = np.nonzero(before["hash"]["ptr"] >= 0)[0]
+    moving = live[sw.states()[live] == 2]
+    staying = live[sw.states()[live] != 2]
+    assert moving.size >= min_blocks and staying.size < moving.size
+    total_out = 0
+    while True:
+        n = sw.save(False)
+        if n == 0:
+            break
+        total_out += n
+    assert total_out == moving.size
+    out = back.state()
+    assert (out["hash"]["ptr"][moving] == -1).all()
+    assert np.array_equal(out["hash"]["ptr"][staying], before["hash"]["ptr"][staying])
+    assert np.array_equal(np.nonzero(out["hash"]["ptr"] >= 0)[0], staying)
+    assert out["last_free"][0] == nb - 1 - staying.size
+    held = np.concatenate([out["alloc_list"][:out["last_free"][0] + 1], out["hash"]["ptr"][staying]])
+    assert np.array_equal(np.sort(held), np.arange(nb, dtype=np.int32))
+    reset = np.ones(nb, bool); reset[before["hash"]["ptr"][staying]] = False
+    out_blocks, before_blocks = out["voxels"].reshape(-1, abi.BLOCK_SIZE3), before["voxels"].reshape(-1, abi.BLOCK_SIZE3)
+    assert (out_blocks[reset].view(np.uint64) == np.uint64(0x7fff)).all()
+    assert np.array_equal(out_blocks[~reset].view(np.uint64), before_blocks[~reset].view(np.uint64))
+    has = sw.has_stored()
+    assert np.array_equal(np.nonzero(has)[0], moving) and (sw.states()[moving] == 0).all()
+    for e in moving[::max(1, moving.size // 200)]:
+        assert np.array_equal(sw.stored_block(e).view(np.uint64), before_blocks[before["hash"]["ptr"][e]].view(np.uint64)), "stored block of entry %d" % e
+    # (2) bring the visible part back: allocation only (no integration), swap-state pass, swap-in until nothing is left in state 1
+    back.set_frame(frames[-1])
+    assert back.allocate() == 0
+    sw.mark()
+    total_in = 0
+    while True:
+        n = sw.swap_in()
+        if n == 0:
+            break
+        total_in += n
+    after = back.state()
+    visible = after["visible"]
+    assert total_in >= visible.size - staying.size and visible.size >= min_blocks // 4
+    after_blocks = after["voxels"].reshape(-1, abi.BLOCK_SIZE3)
+    checked = 0
+    for e in visible[::max(1, visible.size // 400)]:
+        if not has[e]:
+            continue
+        got, want = after_blocks[after["hash"]["ptr"][e]], sw.stored_block(e)
+        assert np.array_equal(got["w_depth"], want["w_depth"]) and np.array_equal(got["w_color"], want["w_color"]), "weights of entry %d" % e
+        assert np.abs(got["sdf"].astype(np.int32) - want["sdf"].astype(np.int32)).max() <= 1, "sdf of entry %d" % e
+        assert np.abs(got["clr"].astype(np.int32) - want["clr"].astype(np.int32)).max() <= 1, "colour of entry %d" % e
+        checked += 1
+    assert checked >= 20
+    return moving.size, visible.size
+
