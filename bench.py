@@ -44,8 +44,10 @@ WORKLOADS = {
                text="C3 TUM-RGBD-shaped 640x480 synthetic depth, 5 mm voxels, voxel decay (max weight 3, min age 40) + "
                     "sliding-window block pruning (max age 80) after every frame"),
 }
-REF_SAMPLE_FRAMES = 12      # bounded CPU sample: the reference's capacities are compile-time (262144 blocks)
+REF_BLOCK_RESERVE = 24000   # the reference's capacities are compile-time (262144 blocks): its arms stop before the array runs out
+REF_MAX_FRAMES = 60         # ... and are bounded to this many timed frames (about 25 s of one host core at C2)
 METRIC = "frames/s alloc+integrate+raycast (1242x375, 2 cm voxels)"
+DIGESTS = os.path.join(ROOT, "tests", "golden", "bench_digests.json")
 
 
 def peaks():
@@ -97,21 +99,15 @@ class ClockSampler(object):
 
 
 def ncu_traffic(stage):
-    """DRAM bytes per launch (read + write) of the stage's dominant kernel from the newest committed `ncu --set full`
-    extract under profiles/ (captured on the same bench command; see profiles/README.md).  None if no capture exists."""
-    import csv
-    import glob
-    kernel = {"integrate": "k_fuse", "raycast": "k_raycast", "allocate+visible_list": "k_alloc_requests"}.get(stage)
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_summary.csv")))
-    if not kernel or not files or WORKLOAD != "C2":
-        return None, None
+    """DRAM bytes per launch (read + write) of the stage's dominant kernel from the committed `ncu --set full` extract
+    profiles/ncu_traffic.json = {"captured_at_commit": ..., "command": ..., "kernels": {name: bytes per launch}} (see
+    profiles/README.md).  A capture is a property of the commit it was taken at: the stamp travels with the number."""
+    kernel = {"integrate": "k_fuse_warp", "raycast": "k_raycast", "allocate+visible_list": "k_alloc_requests"}.get(stage)
     try:
-        rows = list(csv.reader(open(files[-1])))
-        hdr, units = rows[0], rows[1]
-        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
-        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-        vals = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]] for r in rows[2:] if kernel in r[0]]
-        return (sum(vals) / len(vals), os.path.basename(files[-1])) if vals else (None, None)
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if WORKLOAD != t.get("workload", "C2") or kernel not in t["kernels"]:
+            return None, None
+        return float(t["kernels"][kernel]), "profiles/ncu_traffic.json captured at commit %s" % t.get("captured_at_commit")
     except Exception:
         return None, None
 
@@ -122,69 +118,141 @@ def make_frames(n, seed):
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
-def run_reference(args, rank, world):
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def time_reference_cpu(frames_all, cfg, first, count, lib_kind):
+    """The reference's own CPU engines (oracle/_ref, unmodified sources) over frames [0, first) untimed and
+    [first, first + count) timed, from a reset scene -- the frames our arm times.  lib_kind: 'serial' (reference default build,
+    1 core) or 'omp' (its WITH_OPENMP option, all host threads; allocation requests race there, timing only).
+    Stops early when the compile-time voxel block array (262144 blocks) is about to run out.  -> (frames/s, frames timed)"""
+    import pyoracle as po
+    path = po.REF_OMP_PATH if lib_kind == "omp" else po.REF_FAST_PATH
+    eng = po.RefEngine(cfg.W, cfg.H, cfg.params(), path=path)
+    eng.set_calib(cfg.intr)
+
+    def step(f):
+        eng.set_view(f.depth, f.rgb, f.timestamp); eng.set_pose(f.M)
+        eng.allocate(); eng.integrate(); eng.create_expected_depths(); eng.create_icp_maps()
+    for f in frames_all[:first]:
+        step(f)
+    total, done = 0.0, 0
+    for f in frames_all[first:first + count]:
+        if eng.L.itmref_last_free_block(eng.h) < REF_BLOCK_RESERVE:
+            break
+        t0 = time.perf_counter()
+        step(f)
+        total += time.perf_counter() - t0
+        done += 1
+    eng.close()
+    return (done / total if total > 0 else 0.0), done
+
+
+def run_reference(args, rank, world, frames=None, cfg=None):
     if rank != 0:
         return None
     import pyoracle as po
     abi = importlib.import_module(PKG + ".abi")
-    cfg, frames = make_frames(REF_SAMPLE_FRAMES, 0)
-    kind, path_ok = "reference", os.path.exists(po.REF_FAST_PATH)
-    cores = 1
-    if path_ok:
-        eng = po.RefEngine(cfg.W, cfg.H, cfg.params(), fast=True)
-        eng.set_calib(cfg.intr)
-
-        def reset():
-            eng.L.itmref_reset(eng.h)
-
-        def step(f):
-            eng.set_view(f.depth, f.rgb, f.timestamp); eng.set_pose(f.M)
-            eng.allocate(); eng.integrate(); eng.create_expected_depths(); eng.create_icp_maps()
+    K = min(args.steps, REF_MAX_FRAMES)
+    if frames is None:
+        cfg, frames = make_frames(args.warmup + K, 0)
+    threads = host_threads()
+    extra = {}
+    if os.path.exists(po.REF_FAST_PATH):
+        kind = "reference"
+        fps1, done = time_reference_cpu(frames, cfg, args.warmup, K, "serial")
+        extra["serial_1_core"] = {"value": fps1, "unit": "frames/s", "frames": done}
+        fps, cores = fps1, 1
+        if os.path.exists(po.REF_OMP_PATH) and threads > 1:
+            os.environ.setdefault("OMP_NUM_THREADS", str(threads))
+            fpsN, doneN = time_reference_cpu(frames, cfg, args.warmup, K, "omp")
+            extra["openmp_all_threads"] = {"value": fpsN, "unit": "frames/s", "frames": doneN, "threads": threads}
+            if fpsN > fps:
+                fps, cores, done = fpsN, threads, doneN
+        sample = ("frames %d..%d of the %s sequence from a reset scene (the frames the GPU arm times%s), frames 0..%d fused untimed; "
+                  "reference CPU engines compiled from the unmodified sources, -O3 -march=x86-64-v3, serial (the reference's default "
+                  "build) and with its WITH_OPENMP option on %d host threads (nproc = %d); the better of the two is the value; the "
+                  "reference CPU integrator ignores the depth-weighting parameters" % (
+                      args.warmup, args.warmup + done - 1, WORKLOAD, "" if done == args.steps else ", bounded to %d: the reference's "
+                      "voxel block array is 262144 blocks at compile time" % done, args.warmup - 1, threads, os.cpu_count() or threads))
     else:   # the oracle port is the only CPU implementation available on this box
         import harness as hz
-        kind = "port"
+        kind, cores = "port", 1
         ora = hz.OracleBackend(cfg, dict(num_blocks=abi.DEFAULT_LOCAL_BLOCKS, bucket_num=abi.DEFAULT_BUCKETS, excess_size=abi.DEFAULT_EXCESS))
-        ora.set_weights(True, 10, 100)
-        reset = ora.reset
-
-        def step(f):
+        ora.set_weights(cfg.depth_weighting, 10, 100)
+        for f in frames[:args.warmup]:
             ora.set_frame(f); ora.process_frame()
-    idx = 0
-
-    def next_frame():
-        nonlocal idx
-        if idx % REF_SAMPLE_FRAMES == 0:
-            reset()     # untimed: the sample wraps, so the map restarts with it
-        f = frames[idx % REF_SAMPLE_FRAMES]
-        idx += 1
-        return f
-    for _ in range(args.warmup):
-        step(next_frame())
-    total = 0.0
-    for _ in range(args.steps):
-        f = next_frame()
         t0 = time.perf_counter()
-        step(f)
-        total += time.perf_counter() - t0
-    fps = args.steps / total
-    sample = "first %d frames of the %s sequence, cycled (scene reset untimed at wrap); %s" % (
-        REF_SAMPLE_FRAMES, WORKLOAD, "reference CPU engines -O3 -march=x86-64-v3, OpenMP off (reference default; its OpenMP build races on "
-        "allocation and was slower in the survey probe); depth weighting is ignored by the reference CPU integrator" if kind == "reference"
-        else "oracle/restate.cpp port")
-    return {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1000.0 * total / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32->i16/u8 voxels", "data": "synthetic",
-            "config": {"workload": "C2 KITTI-stereo-shaped 1242x375, 2 cm voxels, CPU sample"},
-            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
+        done = 0
+        for f in frames[args.warmup:args.warmup + K]:
+            ora.set_frame(f); ora.process_frame(); done += 1
+        fps = done / (time.perf_counter() - t0)
+        sample = "frames %d..%d of the %s sequence, oracle/restate.cpp port on one core" % (args.warmup, args.warmup + done - 1, WORKLOAD)
+    return {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": done,
+            "warmup": args.warmup, "ms_per_step": 1000.0 / fps if fps > 0 else None, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic",
+            "config": {"workload": workload_text()},
+            "cpu_baseline": dict({"value": fps, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}, **extra),
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def workload_text():
+    return WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only; every GPU runs the same synthetic sequence)"
+
+
+def time_reference_cuda(frames, cfg, d_depth, d_rgb, first, count, flush):
+    """SURVEY 8(d) GPU comparator: the reference's own CUDA engines (unmodified sources recompiled for sm_100 with the
+    reference's --use_fast_math, oracle/_ref/libitmref_cuda_fast.so) on the same device-resident frames, same L2 flush between
+    frames.  Their calls are synchronous (legacy stream, blocking 12-byte copies), so a frame is timed both as the sum of its four
+    CUDA-event stage times and by the host clock around the four calls."""
+    import pyoracle as po
+    import torch
+    if not os.path.exists(po.REF_CUDA_FAST_PATH):
+        return {"unavailable": "oracle/_ref/libitmref_cuda_fast.so not built (needs /root/reference at build time)"}
+    eng = po.RefCudaEngine(cfg.W, cfg.H, cfg.params(), use_swapping=False, fast=True)
+    eng.set_calib(cfg.intr)
+    eng.set_weights(cfg.depth_weighting, 10, 100)
+    stage = np.zeros(5)
+    done = 0
+    for i in range(first + count):
+        if eng.last_free()[0] < REF_BLOCK_RESERVE:
+            break
+        eng.set_view_device(d_depth[i].data_ptr(), d_rgb[i].data_ptr(), frames[i].timestamp)
+        eng.set_pose(frames[i].M)
+        if i >= first:
+            flush.zero_()
+            torch.cuda.synchronize()
+        ms = eng.process_frame_timed()
+        if i >= first:
+            stage += ms
+            done += 1
+    visible = eng.L.itmcu_no_visible(eng.h, 0)
+    eng.close()
+    if not done:
+        return {"unavailable": "no frame fitted the reference's compile-time capacities"}
+    dev = float(stage[:4].sum())
+    return {"value": done / (dev * 1e-3), "unit": "frames/s", "frames": done, "ms_per_frame_device": dev / done,
+            "ms_per_frame_host_clock": float(stage[4]) / done, "value_host_clock": done / (float(stage[4]) * 1e-3),
+            "stages_ms": dict(zip(["allocate+visible_list", "integrate", "expected_depths", "raycast+icp_maps"], [float(x) / done for x in stage[:4]])),
+            "final_visible_blocks": int(visible),
+            "what": "reference CUDA engines (ITMSceneReconstructionEngine_CUDA.cu, ITMVisualisationEngine_CUDA.cu, unmodified) recompiled "
+                    "-gencode arch=compute_100,code=sm_100 --use_fast_math; frames %d..%d resident in HBM, L2 flushed between frames; device "
+                    "time = CUDA events around the four engine calls on the legacy stream" % (first, first + done - 1)}
 
 
 # ------------------------------------------------------------------------------------------------ our arm
 def run_ours(args, rank, world, local_rank):
+    """the driver's line: the C2 workload (or --workload), and at N = 1 the other single-GPU BASELINE configs (C1, C3) as
+    `workloads` sub-objects measured the same way (own clocks, own parity check), so the 640x480 half of the metric is in the
+    same record"""
     import torch
     import torch.distributed as dist
+    global WORKLOAD, CAPS, METRIC
     abi = importlib.import_module(PKG + ".abi")
-    eng = importlib.import_module(PKG + ".engine")
     lib = abi.load()          # raises if libdsb200.so is missing: no fallback
     if lib.dsb200_device_count() < 1:
         raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
@@ -193,6 +261,64 @@ def run_ours(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    out = measure_workload(args, rank, world, local_rank, full=True)
+    if world == 1 and out is not None and not args.single_workload:
+        main_wl, main_caps, main_metric = WORKLOAD, CAPS, METRIC
+        out["workloads"] = {}
+        for wl in sorted(WORKLOADS.keys()):
+            if wl == main_wl:
+                continue
+            WORKLOAD, CAPS, METRIC = wl, WORKLOADS[wl]["caps"], metric_text(wl)
+            sub = measure_workload(args, rank, world, local_rank, full=False)
+            out["workloads"][wl] = {k: sub[k] for k in ("metric", "value", "unit", "ms_per_step", "steps", "warmup", "e2e", "clocks", "roofline",
+                                                        "stages", "parity_check", "gpu_launches", "config", "prune_ms_per_frame",
+                                                        "decayed_blocks") if k in sub}
+        WORKLOAD, CAPS, METRIC = main_wl, main_caps, main_metric
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+def metric_text(wl):
+    if wl == "C2":
+        return "frames/s alloc+integrate+raycast (1242x375, 2 cm voxels)"
+    return "frames/s alloc+integrate+raycast (640x480, 5 mm voxels%s)" % (", decay + slide window" if wl == "C3" else "")
+
+
+def state_digest_of(digest, eng_mod, scene, rs, trk, recon):
+    """digest of the map the timed frames left behind (untimed; downloads the allocated part of the voxel array)"""
+    h = scene.hash()
+    nb = scene.c.num_blocks
+
+    def fetch(lo, hi):
+        return eng_mod._download(scene.c.voxels + lo * 512 * 8, eng_mod.abi.VOXEL_DTYPE, (hi - lo) * 512)
+    images = dict(range=rs.range_image(), raycast=rs.raycast_result(), points=trk.icp_points(), normals=trk.icp_normals(),
+                  rendering=rs.raycast_image())
+    d = digest.state_digest(h, (scene.c.last_free_block, scene.c.last_free_excess), rs.visible(), fetch, nb, images)
+    d["no_visible"] = int(rs.c.no_visible)
+    return d
+
+
+def check_digest(got, n_frames):
+    key = "%s:%d" % (WORKLOAD, n_frames)
+    try:
+        table = json.load(open(DIGESTS))
+    except Exception:
+        return "no golden digests (tests/golden/bench_digests.json missing)", key
+    if key not in table:
+        return "no golden digest for %s (tests/golden/make_bench_digests.py %s)" % (key, key), key
+    digest = importlib.import_module(PKG + ".digest")
+    return digest.compare(got, table[key]), key
+
+
+def measure_workload(args, rank, world, local_rank, full):
+    import torch
+    import torch.distributed as dist
+    abi = importlib.import_module(PKG + ".abi")
+    eng = importlib.import_module(PKG + ".engine")
+    digest = importlib.import_module(PKG + ".digest")
+    lib = abi.load()
+    dev = torch.device("cuda", local_rank)
     K, Wm = args.steps, args.warmup
     cfg, frames = make_frames(K + Wm + 1, seed=0)  # replicas: every GPU runs the same sequence (weak scaling, equal work per GPU);
     # one extra frame: the look-ahead issued during the last timed frame has a real successor, so every timed frame carries
@@ -301,6 +427,14 @@ def run_ours(args, rank, world, local_rank):
     dev_ms, _, vis_counts, launches = resident_pass(False)
     clocks = sampler.stop()
     blocks_used = CAPS["num_blocks"] - 1 - scene.c.last_free_block
+    # what did the timed frames build?  (untimed) digest of hash + free lists + visible list + voxels + the last frame's images,
+    # compared with the digest the CPU checker produced for the same frames (tests/golden/bench_digests.json)
+    parity = {}
+    if rank == 0:
+        abi.check(lib.dsb200_recon_join_prefetch(recon.h))
+        abi.check(lib.dsb200_stream_synchronize(None))
+        verdict, key = check_digest(state_digest_of(digest, eng, scene, rs, trk, recon), Wm + K)
+        parity = {"resident_pass": verdict, "golden": key}
     _, stage_ms, _, _ = resident_pass(True)
 
     # ---- leg 2: end to end through the C ABI with pinned host buffers
@@ -382,6 +516,9 @@ def run_ours(args, rank, world, local_rank):
     e2e_wall = time.perf_counter() - t0
     recon.Sync(scene, rs)
     recon.SetAsync(False)
+    if rank == 0:
+        rs.c.raycast_image = imgs_e[(Wm + K - 1) & 1]      # the image buffer the last frame rendered into
+        parity["e2e_pass"] = check_digest(state_digest_of(digest, eng, scene, rs, trk, recon), Wm + K)[0]
     rs.c.raycast_image = imgs_e[0]
     e2e_ms = max(float(e0.elapsed_time(e1)), 1000.0 * e2e_wall)
     if world > 1:
@@ -389,17 +526,25 @@ def run_ours(args, rank, world, local_rank):
         t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, e2e_ms = float(t[0]), float(t[1])
+    def release():
+        recon.close(); vis.close()
+        for o in (scene, rs, view, view2, trk, img2) + tuple(raw_d) + tuple(raw_c):
+            o.free()
+
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        release()
         return None
 
     pk, pk_kind = peaks()
     V = float(np.mean(vis_counts))
+    A = float(blocks_used) / float(Wm + K)          # new blocks per frame (mean over the run)
+    N_tot = float(CAPS["bucket_num"] + CAPS["excess_size"])
     stage_names = ["allocate+visible_list", "integrate", "expected_depths", "raycast", "icp_maps"]
     per_stage = stage_ms / K
     # algorithmic bytes per frame (SURVEY.md section 8d / DESIGN.md), each datum counted once
-    alg = [4.0 * npx + 4.0 * 2 * (CAPS["bucket_num"] + CAPS["excess_size"]) + 24.0 * V,    # keys+visType scans, depth, lists
+    # B_alloc = 4 W H (depth) + 3 N_tot (allocation + visibility flags; the kernels scan 1-bit summaries of them, so real
+    # traffic is lower) + 20 (V + A) (hash reads) + 36 A (block coordinates + hash writes) + 4 (V + V_prev) (visible lists)
+    alg = [4.0 * npx + 3.0 * N_tot + 20.0 * (V + A) + 36.0 * A + 8.0 * V,
            8216.0 * V + 8.0 * npx, 24.0 * V + 16.0 * (W // 8 + 1) * (H // 8 + 1) + 8.0 * npx,
            4116.0 * V + 16.0 * npx, 52.0 * npx]
     dom = int(np.argmax(per_stage))
@@ -410,7 +555,9 @@ def run_ours(args, rank, world, local_rank):
     out = {"metric": METRIC, "value": world * K / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic",
-           "config": {"workload": WORKLOADS[WORKLOAD]["text"] + "; one scene per GPU (replicas only; every GPU runs the same synthetic sequence)",
+           "config": {"workload": workload_text(),
+                      "timed_region": "per frame: CUDA-event pair around the frame's launches (process_frame, pruning, the look-ahead); the L2 "
+                                      "flush and the host's counter read-back between frames are outside the pairs; e2e is one closed wall-clock region",
                       "lookahead": ("request pass of frame k+1 submitted with frame k and joined before frame k's closing event (results bit-identical)"
                                     if lookahead else "off"), "frames": K, "mean_visible_blocks": V,
                       "blocks_allocated": int(blocks_used), "capacity_blocks": CAPS["num_blocks"], "l2": "flushed (256 MiB write) between timed steps"},
@@ -421,18 +568,28 @@ def run_ours(args, rank, world, local_rank):
                                + ("; allocation request pass of frame k+1 overlaps the raycast of frame k (dsb200_recon_prefetch_allocation)" if lookahead else "")},
            "gpu_launches": launches, "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                        "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
+                        "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "traffic_captured_at": traffic_src,
                         "algorithmic_bytes_per_launch": alg[dom], "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"},
            "stages": stages, "prune_ms_per_frame": (prune_ms[0] / K) if prune else None,
            "decayed_blocks": recon.GetDecayedBlockCount() if prune else None,
            "allocate_kernels_ms": dict(zip(["begin_frame", "alloc_requests", "allocate", "recheck_visibility", "visible_list"],
                                            [float(x) / K for x in alloc_stage]))}
-    if world == 1:
-        a2 = argparse.Namespace(gpus=1, steps=REF_SAMPLE_FRAMES, warmup=1)
-        ref = run_reference(a2, 0, 1)
+    out["parity_check"] = parity
+    # integrate + raycast together against the HBM roofline (the north star's 60 % target is on this pair)
+    ir_ms = per_stage[1] + per_stage[3]
+    out["roofline"]["integrate_plus_raycast"] = {"algorithmic_bytes": alg[1] + alg[3], "ms": float(ir_ms),
+                                                 "achieved": (alg[1] + alg[3]) / (ir_ms * 1e-3) / 1e9,
+                                                 "frac": (alg[1] + alg[3]) / (ir_ms * 1e-3) / 1e9 / pk["hbm_gbs"]}
+    if world == 1 and full:
+        out["gpu_comparator"] = time_reference_cuda(frames, cfg, d_depth, d_rgb, Wm, min(K, REF_MAX_FRAMES), flush)
+        if "value" in out["gpu_comparator"]:
+            out["gpu_comparator"]["ours_over_reference_cuda"] = out["value"] / out["gpu_comparator"]["value"]
+        a2 = argparse.Namespace(gpus=1, steps=min(K, 20), warmup=Wm)
+        ref = run_reference(a2, 0, 1, frames=frames, cfg=cfg)
         out["cpu_baseline"] = ref["cpu_baseline"]
-    if world > 1:
-        dist.destroy_process_group()
+    release()
+    del d_depth, d_rgb, flush, h_depth, h_rgb
+    torch.cuda.empty_cache()
     return out
 
 
@@ -691,13 +848,14 @@ def main():
     ap.add_argument("--brick-log2", type=int, default=2)
     ap.add_argument("--no-lookahead", action="store_true",
                     help="do not overlap the next frame's allocation request pass with the current frame's raycast")
+    ap.add_argument("--single-workload", action="store_true",
+                    help="N = 1: report only --workload (skip the `workloads` sub-objects for the other single-GPU configs)")
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS.keys()),
                     help="BASELINE.json config to run (default C2: the configuration the metric is quoted on)")
     args = ap.parse_args()
     global WORKLOAD, CAPS, METRIC
     WORKLOAD, CAPS = args.workload, WORKLOADS[args.workload]["caps"]
-    if WORKLOAD != "C2":
-        METRIC = "frames/s alloc+integrate+raycast (640x480, 5 mm voxels%s)" % (", decay + slide window" if WORKLOAD == "C3" else "")
+    METRIC = metric_text(WORKLOAD)
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

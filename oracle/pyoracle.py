@@ -3,6 +3,8 @@
 ctypes wrappers for the two CPU checkers:
   * Oracle    -> oracle/librestate.so   (our CPU restatement, oracle/restate.cpp)
   * RefEngine -> oracle/_ref/libitmref.so (the unmodified reference CPU engines, oracle/ref_shim.cpp)
+  * RefCudaEngine -> oracle/_ref/libitmref_cuda[_fast].so (the unmodified reference CUDA engines recompiled for sm_100,
+                 oracle/refcuda_shim.cu): set-level pin of decay / slide window / de-integration, and the GPU comparator
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
 """
 import ctypes as C
@@ -22,6 +24,9 @@ abi = importlib.import_module("denseslam-global-consistency-h_b200.abi")
 RESTATE_PATH = os.path.join(HERE, "librestate.so")
 REF_PATH = os.path.join(HERE, "_ref", "libitmref.so")
 REF_FAST_PATH = os.path.join(HERE, "_ref", "libitmref_fast.so")
+REF_OMP_PATH = os.path.join(HERE, "_ref", "libitmref_omp.so")              # reference CPU engines, WITH_OPENMP (timing only)
+REF_CUDA_PATH = os.path.join(HERE, "_ref", "libitmref_cuda.so")            # reference CUDA engines, IEEE build (set-level pin)
+REF_CUDA_FAST_PATH = os.path.join(HERE, "_ref", "libitmref_cuda_fast.so")  # reference CUDA engines, --use_fast_math (comparator)
 
 
 def build(force=False):
@@ -265,8 +270,8 @@ def make_tracking(M, invM, icp_points=None, icp_normals=None, requires_full_rend
 class RefEngine(object):
     """oracle/_ref/libitmref.so: the unmodified reference CPU engines at the reference's fixed capacities."""
 
-    def __init__(self, W, H, params, use_swapping=False, fast=False):
-        path = REF_FAST_PATH if fast else REF_PATH
+    def __init__(self, W, H, params, use_swapping=False, fast=False, path=None):
+        path = path or (REF_FAST_PATH if fast else REF_PATH)
         if not os.path.exists(path):
             raise RuntimeError("reference build %s absent (built only where /root/reference exists)" % path)
         L = C.CDLL(path)
@@ -506,3 +511,197 @@ class RefEngine(object):
 
     def out_image(self):
         return self._arr(self.L.itmref_out_image(self.h), np.uint8, self.W * self.H * 4).reshape(self.H, self.W, 4)
+
+
+class RefCudaEngine(object):
+    """oracle/_ref/libitmref_cuda.so (IEEE build) or libitmref_cuda_fast.so (fast=True, the reference's own flags): the
+    unmodified reference CUDA engines at the reference's fixed capacities.  Needs a GPU.  Every call is synchronous."""
+
+    def __init__(self, W, H, params, use_swapping=False, fast=False):
+        path = REF_CUDA_FAST_PATH if fast else REF_CUDA_PATH
+        if not os.path.exists(path):
+            raise RuntimeError("reference CUDA build %s absent (built only where /root/reference exists)" % path)
+        L = C.CDLL(path)
+        vp = C.c_void_p
+        L.itmcu_create.restype = vp
+        L.itmcu_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int]
+        L.itmcu_last_error.restype = C.c_char_p
+        L.itmcu_last_error.argtypes = [vp]
+        L.itmcu_decayed_block_count.restype = C.c_longlong
+        for name in ("itmcu_destroy", "itmcu_reset", "itmcu_integrate", "itmcu_deintegrate", "itmcu_create_expected_depths",
+                     "itmcu_create_icp_maps", "itmcu_find_surface", "itmcu_last_free_block", "itmcu_last_free_excess",
+                     "itmcu_decayed_block_count"):
+            getattr(L, name).argtypes = [vp]
+        L.itmcu_set_calib.argtypes = [vp, vp, vp, vp]
+        L.itmcu_set_view.argtypes = [vp, vp, vp, C.c_double, C.c_int]
+        L.itmcu_set_pose.argtypes = [vp, vp]
+        L.itmcu_set_requires_full_rendering.argtypes = [vp, C.c_int]
+        L.itmcu_set_weights.argtypes = [vp, C.c_int, C.c_int, C.c_int]
+        L.itmcu_allocate.argtypes = [vp, C.c_int, C.c_int]
+        L.itmcu_decay.argtypes = [vp, C.c_int, C.c_int]
+        L.itmcu_decay_defusion.argtypes = [vp, C.c_int, C.c_int]
+        L.itmcu_slide_window.argtypes = [vp, C.c_int]
+        L.itmcu_slide_window_defusion.argtypes = [vp, C.c_int, C.c_int]
+        L.itmcu_render_free_view.argtypes = [vp, vp, vp, C.c_int]
+        L.itmcu_process_frame_timed.argtypes = [vp, vp]
+        L.itmcu_history_sizes.argtypes = [vp, vp]
+        L.itmcu_no_visible.argtypes = [vp, C.c_int]
+        for name in ("itmcu_get_hash", "itmcu_get_alloc_list", "itmcu_get_visible_type", "itmcu_get_icp_points",
+                     "itmcu_get_icp_normals", "itmcu_get_icp_rendering", "itmcu_get_out_image", "itmcu_get_out_depth"):
+            getattr(L, name).argtypes = [vp, vp]
+        for name in ("itmcu_get_visible_ids", "itmcu_get_range_image", "itmcu_get_raycast_result"):
+            getattr(L, name).argtypes = [vp, C.c_int, vp]
+        L.itmcu_get_blocks.argtypes = [vp, vp, C.c_int, vp]
+        if L.itmcu_device_count() < 1:
+            raise RuntimeError("the reference CUDA engines need a CUDA device")
+        self.L, self.W, self.H, self.fast = L, W, H, bool(L.itmcu_fast_math())
+        self.h = L.itmcu_create(W, H, params.voxel_size, params.mu, params.max_w, params.vf_min, params.vf_max,
+                                params.stop_integrating_at_max_w, 1 if use_swapping else 0)
+        self.total = L.itmcu_no_total_entries()
+        self.num_blocks = L.itmcu_local_block_num()
+        self.bucket_num = L.itmcu_bucket_num()
+        self.excess = L.itmcu_excess_list_size()
+
+    def close(self):
+        if self.h:
+            self.L.itmcu_destroy(self.h)
+            self.h = None
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError("reference CUDA engine: %s" % self.L.itmcu_last_error(self.h).decode())
+
+    def reset(self):
+        self._ck(self.L.itmcu_reset(self.h))
+
+    def set_calib(self, intr_d, intr_rgb=None, rgb2depth=None):
+        a = np.asarray(intr_d, np.float32)
+        b = np.asarray(intr_rgb if intr_rgb is not None else intr_d, np.float32)
+        m = np.asarray(rgb2depth if rgb2depth is not None else abi.IDENTITY16, np.float32)
+        self.L.itmcu_set_calib(self.h, ptr(a), ptr(b), ptr(m))
+
+    def set_view(self, depth, rgb, timestamp=0.0):
+        d = np.ascontiguousarray(depth, np.float32)
+        r = np.ascontiguousarray(rgb, np.uint8)
+        self._ck(self.L.itmcu_set_view(self.h, ptr(d), ptr(r), timestamp, 0))
+
+    def set_view_device(self, depth_ptr, rgb_ptr, timestamp=0.0):
+        self._ck(self.L.itmcu_set_view(self.h, depth_ptr, rgb_ptr, timestamp, 1))
+
+    def set_pose(self, M):
+        m = np.ascontiguousarray(M, np.float32)
+        self.L.itmcu_set_pose(self.h, ptr(m))
+
+    def set_weights(self, depth_weighting, max_new_w=10, max_distance=100):
+        self.L.itmcu_set_weights(self.h, int(depth_weighting), max_new_w, max_distance)
+
+    def set_requires_full_rendering(self, on):
+        self.L.itmcu_set_requires_full_rendering(self.h, 1 if on else 0)
+
+    def allocate(self, only_visible=False, is_defusion=False):
+        self._ck(self.L.itmcu_allocate(self.h, 1 if only_visible else 0, 1 if is_defusion else 0))
+
+    def integrate(self):
+        self._ck(self.L.itmcu_integrate(self.h))
+
+    def deintegrate(self):
+        self._ck(self.L.itmcu_deintegrate(self.h))
+
+    def decay(self, max_weight, min_age):
+        self._ck(self.L.itmcu_decay(self.h, max_weight, min_age))
+
+    def decay_defusion(self, max_weight, min_age):
+        self._ck(self.L.itmcu_decay_defusion(self.h, max_weight, min_age))
+
+    def slide_window(self, max_age):
+        self._ck(self.L.itmcu_slide_window(self.h, max_age))
+
+    def slide_window_defusion(self, max_age, max_size):
+        self._ck(self.L.itmcu_slide_window_defusion(self.h, max_age, max_size))
+
+    def decayed_blocks(self):
+        return int(self.L.itmcu_decayed_block_count(self.h))
+
+    def history_sizes(self):
+        """(decay queue, slide-window queue, decay de-fusion queue, slide de-fusion queue, timestamp map) sizes"""
+        out = np.zeros(5, np.int32)
+        self.L.itmcu_history_sizes(self.h, ptr(out))
+        return tuple(int(x) for x in out)
+
+    def create_expected_depths(self):
+        self._ck(self.L.itmcu_create_expected_depths(self.h))
+
+    def create_icp_maps(self):
+        self._ck(self.L.itmcu_create_icp_maps(self.h))
+
+    def find_surface(self):
+        self._ck(self.L.itmcu_find_surface(self.h))
+
+    def render_free_view(self, M, intr, render_type=0):
+        m = np.ascontiguousarray(M, np.float32)
+        i = np.ascontiguousarray(intr, np.float32)
+        self._ck(self.L.itmcu_render_free_view(self.h, ptr(m), ptr(i), render_type))
+
+    def process_frame_timed(self):
+        """allocate + integrate + expected depths + raycast/ICP maps -> ms of the four stages (device) + host wall ms"""
+        ms = np.zeros(5, np.float32)
+        self._ck(self.L.itmcu_process_frame_timed(self.h, ptr(ms)))
+        return ms
+
+    # ---- state (copies)
+    def last_free(self):
+        return self.L.itmcu_last_free_block(self.h), self.L.itmcu_last_free_excess(self.h)
+
+    def hash(self):
+        out = np.zeros(self.total, abi.HASH_DTYPE)
+        self._ck(self.L.itmcu_get_hash(self.h, ptr(out)))
+        return out
+
+    def alloc_list(self):
+        out = np.zeros(self.num_blocks, np.int32)
+        self._ck(self.L.itmcu_get_alloc_list(self.h, ptr(out)))
+        return out
+
+    def visible(self, free_view=False):
+        n = self.L.itmcu_no_visible(self.h, 1 if free_view else 0)
+        out = np.zeros(max(n, 1), np.int32)
+        self._ck(self.L.itmcu_get_visible_ids(self.h, 1 if free_view else 0, ptr(out)))
+        return out[:n]
+
+    def visible_type(self):
+        out = np.zeros(self.total, np.uint8)
+        self._ck(self.L.itmcu_get_visible_type(self.h, ptr(out)))
+        return out
+
+    def blocks(self, ptrs):
+        p = np.ascontiguousarray(ptrs, np.int32)
+        out = np.zeros((len(p), abi.BLOCK_SIZE3), abi.VOXEL_DTYPE)
+        if len(p):
+            self._ck(self.L.itmcu_get_blocks(self.h, ptr(p), len(p), ptr(out)))
+        return out
+
+    def _img(self, fn, shape, dtype, *pre):
+        out = np.zeros(shape, dtype)
+        self._ck(fn(self.h, *(list(pre) + [ptr(out)])))
+        return out
+
+    def range_image(self, free_view=False):
+        return self._img(self.L.itmcu_get_range_image, (self.H, self.W, 2), np.float32, 1 if free_view else 0)
+
+    def raycast_result(self, free_view=False):
+        return self._img(self.L.itmcu_get_raycast_result, (self.H, self.W, 4), np.float32, 1 if free_view else 0)
+
+    def icp_points(self):
+        return self._img(self.L.itmcu_get_icp_points, (self.H, self.W, 4), np.float32)
+
+    def icp_normals(self):
+        return self._img(self.L.itmcu_get_icp_normals, (self.H, self.W, 4), np.float32)
+
+    def icp_rendering(self):
+        return self._img(self.L.itmcu_get_icp_rendering, (self.H, self.W, 4), np.uint8)
+
+    def out_image(self):
+        return self._img(self.L.itmcu_get_out_image, (self.H, self.W, 4), np.uint8)
+
+    def out_depth(self):
+        return self._img(self.L.itmcu_get_out_depth, (self.H, self.W), np.float32)

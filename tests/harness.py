@@ -30,6 +30,10 @@ def has_ref():
     return os.path.exists(po.REF_PATH)
 
 
+def has_refcuda():
+    return os.path.exists(po.REF_CUDA_PATH)
+
+
 def has_gpu():
     try:
         return abi.load().dsb200_device_count() > 0
@@ -274,6 +278,174 @@ class GpuBackend(object):
         return dict(visible=self.rs_free.visible(), range=self.rs_free.range_image(), raycast=self.rs_free.raycast_result(),
                     image=self.out_img.download(np.uint8, n * 4).reshape(self.cfg.H, self.cfg.W, 4),
                     depth=self.out_depth.download(np.float32, n).reshape(self.cfg.H, self.cfg.W))
+
+
+class RefCudaBackend(object):
+    """oracle/_ref/libitmref_cuda.so: the UNMODIFIED reference CUDA engines recompiled for sm_100 (IEEE build unless
+    fast=True), behind the call names of the other back ends.  Fixed reference capacities.  Allocation there is racy
+    (atomicSub free-list pops, last-writer-wins requests, per-CTA atomicAdd compaction), so its state is compared at SET
+    level: see block_table() / assert_sets_match()."""
+    name = "refcuda"
+
+    def __init__(self, cfg, use_swapping=False, fast=False):
+        self.cfg = cfg
+        self.e = po.RefCudaEngine(cfg.W, cfg.H, cfg.params(), use_swapping=use_swapping, fast=fast)
+        self.e.set_calib(cfg.intr)
+        self.requires_full_rendering = True
+
+    def close(self):
+        self.e.close()
+
+    def reset(self):
+        self.e.reset()
+
+    def set_weights(self, depth_weighting, max_new_w=10, max_distance=100):
+        self.e.set_weights(depth_weighting, max_new_w, max_distance)
+
+    def set_frame(self, f, M=None):
+        self.e.set_view(f.depth, f.rgb, f.timestamp)
+        self.e.set_pose(f.M if M is None else M)
+        self.e.set_requires_full_rendering(self.requires_full_rendering)
+
+    def allocate(self, only_visible=False, is_defusion=False):
+        self.e.allocate(only_visible, is_defusion)
+        return 0
+
+    def integrate(self):
+        self.e.integrate()
+
+    def deintegrate(self):
+        self.e.deintegrate()
+
+    def decay(self, max_weight, min_age):
+        self.e.decay(max_weight, min_age)
+
+    def decay_defusion(self, max_weight, min_age):
+        self.e.decay_defusion(max_weight, min_age)
+
+    def slide_window(self, max_age):
+        self.e.slide_window(max_age)
+
+    def slide_window_defusion(self, max_age, max_size):
+        self.e.slide_window_defusion(max_age, max_size)
+
+    def decayed_blocks(self):
+        return self.e.decayed_blocks()
+
+    def history_sizes(self):
+        return self.e.history_sizes()
+
+    def expected_depths(self):
+        self.e.create_expected_depths()
+
+    def icp_maps(self):
+        self.e.create_icp_maps()
+
+    def process_frame(self):
+        self.allocate(); self.integrate(); self.expected_depths(); self.icp_maps()
+        return 0
+
+    def free_view(self, M, intr, render_type=0):
+        self.e.render_free_view(M, intr, render_type)
+
+    def images(self):
+        return dict(range=self.e.range_image(), raycast=self.e.raycast_result(), points=self.e.icp_points(),
+                    normals=self.e.icp_normals(), rendering=self.e.icp_rendering())
+
+    def block_table(self, voxels=True):
+        h = self.e.hash()
+        return make_block_table(h, self.e.visible(), (lambda ptrs: self.e.blocks(ptrs)) if voxels else None, self.e.last_free(),
+                                self.e.num_blocks)
+
+
+# ---------------------------------------------------------------- set-level state (reference CUDA engine vs ours)
+def pos_key(pos):
+    """(n, 3) int16 block coordinates -> sortable int64 keys"""
+    p = pos.astype(np.int64) + 32768
+    return (p[:, 0] << 32) | (p[:, 1] << 16) | p[:, 2]
+
+
+def make_block_table(hash_table, visible_ids, fetch_blocks, last_free, num_blocks):
+    """What is comparable between two engines whose slot / pointer assignment differs: the SET of allocated block
+    coordinates, each block's 512 voxels, the SET of visible blocks, and the number of free voxel blocks."""
+    live = np.nonzero(hash_table["ptr"] >= 0)[0]
+    keys = pos_key(hash_table["pos"][live])
+    order = np.argsort(keys, kind="stable")
+    keys, live = keys[order], live[order]
+    assert np.unique(keys).size == keys.size, "a block coordinate is allocated twice"
+    t = dict(keys=keys, slots=live, ptrs=hash_table["ptr"][live], free_blocks=last_free[0] + 1, num_blocks=num_blocks)
+    vis = np.asarray(visible_ids)
+    t["visible_keys"] = np.sort(pos_key(hash_table["pos"][vis])) if vis.size else np.zeros(0, np.int64)
+    t["visible_dead"] = int((hash_table["ptr"][vis] < 0).sum()) if vis.size else 0
+    if fetch_blocks is not None:
+        t["voxels"] = fetch_blocks(t["ptrs"])
+    return t
+
+
+def gpu_block_table(gpu, voxels=True):
+    """the same for a GpuBackend / OracleBackend state()"""
+    s = gpu.state(voxels=voxels)
+    fetch = (lambda ptrs: s["voxels"].reshape(-1, abi.BLOCK_SIZE3)[ptrs]) if voxels else None
+    return make_block_table(s["hash"], s["visible"], fetch, s["last_free"], gpu.scene.c.num_blocks)
+
+
+class SetTracker(object):
+    """Follows two engines frame by frame.  A block is COMPARABLE when both engines allocated it in the same frame (its
+    `birth`): the reference CUDA allocator resolves same-frame bucket collisions by a race (CUDA .cu:1521-1531 writes
+    entriesAllocType / blockCoords last-writer-wins; the loser is picked up a frame later, DeviceAgnostic/
+    ITMSceneReconstructionEngine.h:483), the serial CPU engine by scan order, so a few blocks are born a frame apart and have
+    seen one observation less; and its deleteBlock skips a deletion when two blocks of one bucket die in the same launch
+    (try-lock, CUDA .cu:510-515).  Those blocks are counted, bounded, and left out of the payload comparison."""
+
+    def __init__(self):
+        self.birth = [dict(), dict()]
+        self.frame = 0
+
+    def update(self, ta, tb):
+        for side, t in enumerate((ta, tb)):
+            now = set(t["keys"].tolist())
+            b = self.birth[side]
+            for k in list(b.keys()):
+                if k not in now:
+                    del b[k]
+            for k in now:
+                if k not in b:
+                    b[k] = self.frame
+        self.frame += 1
+
+    def comparable(self, keys):
+        a, b = self.birth
+        return np.array([(k in a and k in b and a[k] == b[k]) for k in keys.tolist()], bool)
+
+
+def assert_sets_match(tracker, ours, ref, what, max_odd_fraction=0.01, voxels=True):
+    """ours / ref: block tables taken after the same call sequence.  Returns the number of non-comparable blocks."""
+    tracker.update(ours, ref)
+    both = np.intersect1d(ours["keys"], ref["keys"])
+    union = np.union1d(ours["keys"], ref["keys"])
+    ok = tracker.comparable(both)
+    odd = union.size - int(ok.sum())
+    assert odd <= max(4, max_odd_fraction * union.size), "%s: %d of %d blocks not comparable (only ours %d, only reference %d)" % (
+        what, odd, union.size, np.setdiff1d(ours["keys"], ref["keys"]).size, np.setdiff1d(ref["keys"], ours["keys"]).size)
+    # free-list accounting: allocated + free == capacity in both engines
+    for t, name in ((ours, "ours"), (ref, "reference")):
+        assert t["keys"].size + t["free_blocks"] == t["num_blocks"], "%s: %s leaks voxel blocks (%d allocated + %d free != %d)" % (
+            what, name, t["keys"].size, t["free_blocks"], t["num_blocks"])
+    # visible SET (the reference's list order is schedule-dependent)
+    vdiff = np.setxor1d(ours["visible_keys"], ref["visible_keys"])
+    assert vdiff.size <= odd + ours["visible_dead"] + ref["visible_dead"], "%s: visible sets differ in %d blocks (%d non-comparable)" % (what, vdiff.size, odd)
+    if voxels and both.size:
+        ia = np.searchsorted(ours["keys"], both[ok]); ib = np.searchsorted(ref["keys"], both[ok])
+        va, vb = ours["voxels"][ia], ref["voxels"][ib]
+        m = np.uint64(0x00ffffffffffffff)         # 8th byte = padding
+        ne = (va.view(np.uint64) & m) != (vb.view(np.uint64) & m)
+        if ne.any():
+            blk = np.nonzero(ne.reshape(len(ia), -1).any(axis=1))[0]
+            d = np.abs(va["sdf"].astype(np.int32) - vb["sdf"].astype(np.int32)).max()
+            raise AssertionError("%s: %d of %d comparable blocks differ in %d voxels (max |dsdf| %d LSB); first block key %d: %s vs %s" % (
+                what, blk.size, len(ia), int(ne.sum()), int(d), int(both[ok][blk[0]]),
+                va[blk[0]][ne.reshape(len(ia), -1)[blk[0]]][:3], vb[blk[0]][ne.reshape(len(ia), -1)[blk[0]]][:3]))
+    return odd
 
 
 # ---------------------------------------------------------------- comparators
