@@ -117,7 +117,8 @@ struct dsb200_recon {
     cudaStream_t prefetchStream = nullptr; cudaEvent_t evSceneWritten = nullptr, evPrefetchDone = nullptr;
     unsigned long long modEpoch = 0, epochSceneWritten = ~0ull;   // scene-modifying calls so far / value when evSceneWritten was recorded
     bool prefetchPending = false;
-    struct PrefetchKey { const float *depth; int w, h; float M[16], invM[16], intr[4]; const uint8_t *visType; } prefetchKey{};
+    struct PrefetchKey { const float *depth; int w, h; float M[16], invM[16], intr[4]; const uint8_t *visType;
+                         uint8_t *visTypeRW; const int *visibleIds; const dsb200_hash_entry *hash; } prefetchKey{};
     // SDF shadow: one short per voxel of the scene this engine maintains, kept in step by every kernel that writes voxels
     // (reset, integrate, de-integrate, pruning) and read by the fused frame's raycast instead of the 8-byte voxel records.
     short *sdfShadow = nullptr; const void *shadowFor = nullptr; bool shadowEnabled = true;
@@ -346,6 +347,19 @@ static short *shadow_for(dsb200_recon *e, const dsb200_scene *scene)
     return e->sdfShadow;
 }
 
+// Drop a pending look-ahead: wait for its kernels, then undo what they wrote (request keys / bitmaps, visibility flags) so
+// that the next, un-prefetched allocation starts from the state the look-ahead found.
+static int abandon_prefetch(dsb200_recon *e)
+{
+    if (!e->prefetchPending) return DSB200_OK;
+    const dsb200_recon::PrefetchKey &k = e->prefetchKey;
+    CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));
+    launch_abandon_requests(e->stream, e->fs, k.hash, k.visibleIds, k.visTypeRW, e->reqKey, e->total);
+    CU(cudaGetLastError());
+    e->prefetchPending = false;
+    return DSB200_OK;
+}
+
 // Every scene-modifying entry point passes through here.  consumesPrefetch: the call is an allocation that may pick up a
 // pending look-ahead; any other call while one is pending would invalidate what the look-ahead already wrote.
 static int check_scene(dsb200_recon *e, const dsb200_scene *scene, bool consumesPrefetch = false)
@@ -377,10 +391,14 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     DSB_MARK_A(0);
     if (e->prefetchPending) {
         const dsb200_recon::PrefetchKey &k = e->prefetchKey;
-        e->prefetchPending = false;
         if (k.depth != view->depth || k.w != AP.W || k.h != AP.H || k.visType != rs->visible_type || memcmp(k.M, trk->M_d, 64) ||
-            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost)
-            return fail(DSB200_ERR_INVALID, "the pending prefetched allocation was made for a different view / pose / render state");
+            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost) {
+            // the look-ahead is abandoned and undone (the scene is as it found it); the caller may allocate again
+            int rc = abandon_prefetch(e); if (rc) return rc;
+            return fail(DSB200_ERR_INVALID, "the pending prefetched allocation was made for a different view / pose / render state "
+                                            "(it has been dropped and undone)");
+        }
+        e->prefetchPending = false;
         CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));     // setToType3 + requests already ran on the look-ahead stream
         DSB_MARK_A(1);
     } else {
@@ -1171,6 +1189,7 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
     CU(cudaEventRecord(e->evPrefetchDone, e->prefetchStream));
     dsb200_recon::PrefetchKey &k = e->prefetchKey;
     k.depth = view->depth; k.w = AP.W; k.h = AP.H; k.visType = rs->visible_type;
+    k.visTypeRW = rs->visible_type; k.visibleIds = rs->visible_ids; k.hash = scene->hash;
     memcpy(k.M, trk->M_d, 64); memcpy(k.invM, trk->invM_d, 64); memcpy(k.intr, view->intr_d, 16);
     e->prefetchPending = true;
     return DSB200_OK;
@@ -1252,7 +1271,7 @@ int dsb200_recon_set_sdf_shadow(dsb200_recon *e, int on)
 int dsb200_recon_notify_scene_modified(dsb200_recon *e)
 {
     if (!e) return fail(DSB200_ERR_INVALID, "notify_scene_modified: null engine");
-    if (e->prefetchPending) { CU(cudaStreamSynchronize(e->prefetchStream)); e->prefetchPending = false; }
+    { int rc = abandon_prefetch(e); if (rc) return rc; }   // a pending look-ahead is dropped AND undone (keys, bitmaps, flags)
     CU(cudaStreamSynchronize(e->stream));
     e->deviceCountersValid = false;        // the next call seeds the device counters from the scene's host mirrors
     e->shadowFor = nullptr;                // the sdf shadow is re-derived from the voxels at the next use

@@ -64,6 +64,8 @@ void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeB
                         int hostNoVisible, int useHost, const int *visibleIds, uint8_t *visType, int prevUpperBound);
 void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
                            const dsb200_hash_entry *hash, uint8_t *visType, unsigned *reqKey);
+void launch_abandon_requests(cudaStream_t st, const FrameState &fs, const dsb200_hash_entry *hash, const int *visibleIds,
+                             uint8_t *visType, unsigned *reqKey, int total);
 void launch_recheck_visibility(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
                                const int *prevVisibleIds, uint8_t *visType);
 void launch_rebuild_visbits(cudaStream_t st, const FrameState &fs, const uint8_t *visType, int total);

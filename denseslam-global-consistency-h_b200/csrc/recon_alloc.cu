@@ -377,7 +377,42 @@ __global__ void __launch_bounds__(256) k_rebuild_visbits(const uint8_t *__restri
         visBits[w] = ((w << 5) < total) ? flag_mask32(visType, w, total) : 0u;
 }
 
+// Undo of k_begin_frame + k_alloc_requests for a look-ahead that is being ABANDONED (the scene was modified behind the
+// engine's back, or the next allocation came with another view / pose): request keys and request bitmaps back to all-zero,
+// visibility flags back to "non-zero exactly for the members of the current visible list" (1, or 2 for a swapped-out entry;
+// the 1 / 3 distinction of the last build is not recoverable and no consumer depends on it: the next allocation turns every
+// member into 3 first, CPU .cpp:185-188).
+__global__ void __launch_bounds__(256) k_abandon_requests_clear(FrameState fs, uint8_t *visType, unsigned *reqKey, int total)
+{
+    const int words = fs.bitTiles * 1024;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < words; w += gridDim.x * blockDim.x) {
+        const unsigned rq = fs.reqBits[w];
+        for (unsigned rem = rq; rem; rem &= rem - 1) { const int h = (w << 5) + __ffs(rem) - 1; if (h < total) reqKey[h] = 0u; }
+        if (rq) { fs.reqBits[w] = 0u; fs.reqExBits[w] = 0u; }
+        const unsigned vb = fs.visBits[w];
+        for (unsigned rem = vb; rem; rem &= rem - 1) { const int h = (w << 5) + __ffs(rem) - 1; if (h < total) visType[h] = 0; }
+        if (vb) fs.visBits[w] = 0u;
+    }
+}
+__global__ void __launch_bounds__(256) k_abandon_requests_restore(FrameState fs, const dsb200_hash_entry *__restrict__ hash,
+                                                                  const int *__restrict__ visibleIds, uint8_t *visType)
+{
+    const int n = fs.counters->noVisible;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int h = visibleIds[i];
+        visType[h] = (load_entry(hash, h).ptr == -1) ? 2 : 1;
+        atomicOr(&fs.visBits[h >> 5], 1u << (h & 31));
+    }
+}
+
 // ---------------------------------------------------------------- host launchers
+void launch_abandon_requests(cudaStream_t st, const FrameState &fs, const dsb200_hash_entry *hash, const int *visibleIds,
+                             uint8_t *visType, unsigned *reqKey, int total)
+{
+    DSB_LAUNCH(k_abandon_requests_clear, kNumSMs * 4, 256, 0, st, fs, visType, reqKey, total);
+    DSB_LAUNCH(k_abandon_requests_restore, kNumSMs * 2, 256, 0, st, fs, hash, visibleIds, visType);
+}
+
 void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeBlock, int hostLastFreeExcess,
                         int hostNoVisible, int useHost, const int *visibleIds, uint8_t *visType, int prevUpperBound)
 {

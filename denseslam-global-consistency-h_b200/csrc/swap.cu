@@ -322,7 +322,7 @@ int dsb200_swap_cache_of(dsb200_swap *s, dsb200_swap_cache *out)
 
 const dsb200_voxel *dsb200_swap_stored_block(const dsb200_swap *s, int32_t entry)
 {
-    if (!s || entry < 0 || entry >= s->total || !s->hasStored[entry]) return nullptr;
+    if (!s || entry < 0 || entry >= s->total || !s->hasStored[entry] || s->slotOf[entry] < 0) return nullptr;
     return reinterpret_cast<const dsb200_voxel *>(slot_address(s, s->slotOf[entry]));
 }
 
@@ -348,7 +348,7 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
     // LoadFromGlobalMemory (CPU .cpp:52-68) without the copy: the kernel reads the stored blocks where they lie
     for (int i = 0; i < n; i++) {
         const int entry = s->neededHost[i];
-        s->blockPtrsHost[i] = s->hasStored[entry] ? reinterpret_cast<uint4 *>(slot_address(s, s->slotOf[entry])) : nullptr;
+        s->blockPtrsHost[i] = (s->hasStored[entry] && s->slotOf[entry] >= 0) ? reinterpret_cast<uint4 *>(slot_address(s, s->slotOf[entry])) : nullptr;
     }
     SWCU(cudaMemcpyAsync(s->blockPtrs, s->blockPtrsHost, sizeof(uint4 *) * (size_t)n, cudaMemcpyHostToDevice, s->stream));
     DSB_LAUNCH(k_swap_integrate, n, 256, 0, s->stream, n, s->needed, s->blockPtrs, scene->hash, scene->voxels, s->states, scene->params.max_w);
@@ -407,13 +407,32 @@ int dsb200_swap_load_file(dsb200_swap *s, const char *path)
     if (!s || !path) return fail_with(DSB200_ERR_INVALID, "swap_load_file: null argument");
     FILE *f = fopen(path, "rb");
     if (!f) return fail_with(DSB200_ERR_INVALID, "swap_load_file: could not open the file");
-    bool ok = fread(s->hasStored, 1, (size_t)s->total, f) == (size_t)s->total;
+    // The file is `total` flags followed by `total` blocks (ITMGlobalCache's layout): check its size up front -- a seek past
+    // the end of a truncated file succeeds -- and read the flags into a temporary: a flag is committed to the live cache only
+    // once its block has been read, so a failed load never leaves "stored" entries without a slot.
+    const long long want = (long long)s->total * (1 + (long long)kBlockBytes);
+    bool ok = fseek(f, 0, SEEK_END) == 0 && (long long)ftell(f) == want && fseek(f, 0, SEEK_SET) == 0;
+    if (!ok) { fclose(f); return fail_with(DSB200_ERR_INVALID, "swap_load_file: file size differs from total * (1 + 4096) (other capacities, or truncated)"); }
+    std::vector<unsigned char> flags((size_t)s->total);
+    ok = fread(flags.data(), 1, (size_t)s->total, f) == (size_t)s->total;
+    int failedAt = -1;
     for (int i = 0; ok && i < s->total; i++) {
-        if (s->hasStored[i]) { char *slot = slot_for(s, i); ok = slot != nullptr && fread(slot, kBlockBytes, 1, f) == 1; }
-        else ok = fseek(f, (long)kBlockBytes, SEEK_CUR) == 0;
+        if (flags[i]) {
+            char *slot = slot_for(s, i);
+            ok = slot != nullptr && fread(slot, kBlockBytes, 1, f) == 1;
+            if (ok) s->hasStored[i] = 1; else failedAt = i;
+        } else {
+            ok = fseek(f, (long)kBlockBytes, SEEK_CUR) == 0;
+            if (ok) s->hasStored[i] = 0;
+        }
     }
     fclose(f);
-    return ok ? DSB200_OK : fail_with(DSB200_ERR_INVALID, "swap_load_file: file shorter than the cache (other capacities?)");
+    if (!ok) {
+        if (failedAt >= 0) s->hasStored[failedAt] = 0;       // its slot (if any) holds a partial block: not stored
+        for (int i = 0; i < s->total; i++) if (s->slotOf[i] < 0) s->hasStored[i] = 0;
+        return fail_with(DSB200_ERR_INVALID, "swap_load_file: read failed; entries read so far are kept, the rest are not stored");
+    }
+    return DSB200_OK;
 }
 
 } // extern "C"

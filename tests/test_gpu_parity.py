@@ -390,3 +390,48 @@ def test_checkpoint_round_trip(tmp_path):
         c.recon.LoadCheckpoint(c.scene, c.rs, tmp_path)
     for x in (a, b, c, ora):
         x.close()
+
+
+def test_abandoned_lookahead_is_undone():
+    """A look-ahead that is dropped -- dsb200_recon_notify_scene_modified, or the next allocation arriving with another view /
+    pose -- must leave no trace: its request keys, request bitmaps and visibility flags are undone, and the frame allocated
+    next equals the oracle's plain sequence bit for bit (stale order keys could win the next allocation)."""
+    cfg, frames = synth.make_sequence("tiny", 6)
+    _, far = synth.make_sequence("tiny", 2, start=45)          # a view of another part of the room: many requests of its own
+    gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    eng, lib = gpu.eng, abi.load()
+    other = eng.ITMView(cfg.W, cfg.H, cfg.intr)
+    nxt = eng.ITMTrackingState(cfg.W, cfg.H)
+    gpu.recon.SetAsync(True)
+    for i in range(3):
+        gpu.set_frame(frames[i]); ora.set_frame(frames[i])
+        gpu.process_frame(); ora.process_frame()
+    # (1) look ahead to the far view, then tell the engine the scene was modified: the look-ahead is dropped
+    other.update(far[0].depth, far[0].rgb, far[0].timestamp); nxt.set_pose(far[0].M)
+    gpu.recon.PrefetchAllocation(gpu.scene, other, nxt, gpu.rs)
+    gpu.recon.Sync(gpu.scene, gpu.rs)          # the host mirrors become authoritative again after the notification
+    abi.check(lib.dsb200_recon_notify_scene_modified(gpu.recon.h))
+    gpu.set_frame(frames[3]); ora.set_frame(frames[3])
+    assert gpu.process_frame() == 0
+    ora.process_frame()
+    gpu.recon.Sync(gpu.scene, gpu.rs)
+    hz.assert_state_equal(ora.state(), gpu.state(), "after a look-ahead dropped by notify_scene_modified")
+    hz.assert_images_equal(ora.images(), gpu.images(), "after a look-ahead dropped by notify_scene_modified")
+    # (2) look ahead to the far view, then submit a different frame: refused once (and undone), then accepted
+    other.update(far[1].depth, far[1].rgb, far[1].timestamp); nxt.set_pose(far[1].M)
+    gpu.recon.PrefetchAllocation(gpu.scene, other, nxt, gpu.rs)
+    gpu.set_frame(frames[4]); ora.set_frame(frames[4])
+    with pytest.raises(abi.Dsb200Error):
+        gpu.recon.ProcessFrame(gpu.vis, gpu.scene, gpu.view, gpu.trk, gpu.rs)
+    assert gpu.process_frame() == 0
+    ora.process_frame()
+    gpu.recon.Sync(gpu.scene, gpu.rs)
+    hz.assert_state_equal(ora.state(), gpu.state(), "after a look-ahead dropped by a mismatching allocation")
+    hz.assert_images_equal(ora.images(), gpu.images(), "after a look-ahead dropped by a mismatching allocation")
+    gpu.set_frame(frames[5]); ora.set_frame(frames[5])
+    gpu.process_frame(); ora.process_frame()
+    gpu.recon.Sync(gpu.scene, gpu.rs)
+    hz.assert_state_equal(ora.state(), gpu.state(), "frame after the dropped look-aheads")
+    gpu.recon.SetAsync(False)
+    other.free(); nxt.free()
+    gpu.close(); ora.close()

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import harness as hz
-from harness import po
+from harness import abi, po
 
 pytestmark = pytest.mark.gpu
 
@@ -98,4 +98,13 @@ def test_swap_store_file_round_trip():
             fused += int((other.stored_block(e)["w_depth"] > 0).any())
         assert fused > 5
         other.close()
+        # a truncated file is refused up front and leaves the cache with nothing marked stored
+        with open(path, "r+b") as f:
+            f.truncate(total + (total // 2) * 512 * 8)
+        broken = gpu.eng.ITMSwappingEngine(gpu.scene)
+        with pytest.raises(abi.Dsb200Error):
+            broken.ReadFromFile(path)
+        assert broken.has_stored().sum() == 0
+        assert abi.load().dsb200_swap_stored_block(broken.h, int(np.nonzero(has)[0][0])) in (None, 0)
+        broken.close()
     swap.close(); gpu.close()
