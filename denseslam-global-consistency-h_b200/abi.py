@@ -216,6 +216,7 @@ def load():
         "dsb200_profile_read": (C.c_int, [vp, _P(C.c_float)]),
         "dsb200_profile_read_allocate": (C.c_int, [vp, _P(C.c_float)]),
         "dsb200_debug_force_plain_division": (C.c_int, [vp, C.c_int]),
+        "dsb200_debug_set_tunable": (C.c_int, [C.c_char_p, C.c_int]),
         "dsb200_selftest_division": (C.c_int, [C.c_ulonglong, C.c_ulonglong, _P(C.c_ulonglong)]),
         "dsb200_selftest_expf": (C.c_int, [vp, vp, i32]),
         "dsb200_selftest_acosf": (C.c_int, [vp, vp, i32]),

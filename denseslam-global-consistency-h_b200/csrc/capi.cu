@@ -143,6 +143,7 @@ struct dsb200_vis {
     int *countScratch = nullptr;      // [0] visible count for stand-alone calls, [1] CountVisibleBlocks result
     int *hostInts = nullptr;          // pinned [4]
     float *fwdProjection = nullptr; int *fwdMissing = nullptr; int fwdPixels = 0;
+    RayQueue rayQueue{};              // suspended rays of the bounded first raycast pass (capacity = width * height of creation)
 };
 
 extern "C" {
@@ -623,6 +624,14 @@ int dsb200_vis_create(dsb200_vis **out, int32_t max_visible, int32_t width, int3
     CU(cudaMalloc(&v->countScratch, 4 * sizeof(int)));
     CU(cudaMallocHost(&v->hostCounters, sizeof(Counters)));
     CU(cudaMallocHost(&v->hostInts, 4 * sizeof(int)));
+    // ray queue: one slot per pixel (36 bytes); a larger image than this simply runs the single unbounded raycast pass
+    const size_t npx = (size_t)width * height;
+    CU(cudaMalloc(&v->rayQueue.ctl, 4 * sizeof(int)));
+    CU(cudaMemset(v->rayQueue.ctl, 0, 4 * sizeof(int)));
+    CU(cudaMalloc(&v->rayQueue.pixel, npx * sizeof(int)));
+    CU(cudaMalloc(&v->rayQueue.posLen, npx * sizeof(float4)));
+    CU(cudaMalloc(&v->rayQueue.dirMax, npx * sizeof(float4)));
+    v->rayQueue.capacity = (int)npx;
     *out = v;
     return DSB200_OK;
 }
@@ -633,6 +642,7 @@ int dsb200_vis_destroy(dsb200_vis *v)
     cudaStreamSynchronize(v->stream);
     cudaFree(v->fs.counters); cudaFree(v->fs.tickets); cudaFree(v->fs.scanState); cudaFree(v->countScratch);
     cudaFree(v->fwdProjection); cudaFree(v->fwdMissing);
+    cudaFree(v->rayQueue.ctl); cudaFree(v->rayQueue.pixel); cudaFree(v->rayQueue.posLen); cudaFree(v->rayQueue.dirMax);
     cudaFreeHost(v->hostCounters); cudaFreeHost(v->hostInts);
     delete v;
     return DSB200_OK;
@@ -675,7 +685,7 @@ int dsb200_create_expected_depths(dsb200_vis *v, const dsb200_scene *scene, cons
 int dsb200_find_surface(dsb200_vis *v, const dsb200_scene *scene, const float *invM, const float *intr, dsb200_render_state *rs)
 {
     RayParams P; make_ray_params(P, scene, nullptr, invM, intr, rs->width, rs->height);
-    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, nullptr, &v->rayQueue);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(v->stream));
     return DSB200_OK;
@@ -685,7 +695,7 @@ int dsb200_create_icp_maps(dsb200_vis *v, const dsb200_scene *scene, const dsb20
 {
     if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "create_icp_maps: tracking state has no point cloud buffers");
     RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, nullptr, &v->rayQueue);
     launch_icp_maps(v->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(v->stream));
@@ -698,7 +708,7 @@ int dsb200_render_image(dsb200_vis *v, const dsb200_scene *scene, const float *M
     if (!outRGBA) return fail(DSB200_ERR_INVALID, "render_image: null output image");
     if (type == DSB200_RENDER_COLOURCODED) type = DSB200_RENDER_SHADED_GREYSCALE;   // !TIndex::hasColorCoding
     RayParams P; make_ray_params(P, scene, M, invM, intr, rs->width, rs->height);
-    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2);
+    launch_raycast(v->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, nullptr, &v->rayQueue);
     launch_shade(v->stream, P, type, scene->voxels, scene->hash, rs->raycast_result, outRGBA, outDepth);
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(v->stream));
@@ -729,7 +739,7 @@ int dsb200_raycast_sharded(dsb200_vis *v, const dsb200_scene *scene, const dsb20
         if (!t->hash[i] || !t->voxels[i] || !t->range_image[i]) return fail(DSB200_ERR_INVALID, "raycast_sharded: null table pointer");
     RayParams P; make_ray_params(P, scene, nullptr, invM, intr, width, height);
     launch_raycast_sharded(v->stream, P, t->count, t->rank, t->brick_log2, t->hash, t->voxels, t->range_image, merged_range,
-                           out_raycast, v->fs.tickets + 2);
+                           out_raycast, v->fs.tickets + 2, &v->rayQueue);
     CU(cudaGetLastError());
     return DSB200_OK;
 }
@@ -1249,12 +1259,12 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     if (stages & DSB200_FRAME_ICP_MAPS) {
         if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "process_frame: tracking state has no point cloud buffers");
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene));
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene), &v->rayQueue);
         DSB_MARK(4);
         launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
     } else if (stages & DSB200_FRAME_RAYCAST) {
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene));
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene), &v->rayQueue);
         DSB_MARK(4);
     } else DSB_MARK(4);
     DSB_MARK(5);
@@ -1287,6 +1297,11 @@ int dsb200_recon_invalidate_sdf_shadow(dsb200_recon *e)
 }
 
 int dsb200_debug_force_plain_division(dsb200_recon *e, int on) { e->forceSlowDiv = on != 0; return DSB200_OK; }
+int dsb200_debug_set_tunable(const char *name, int value)
+{
+    if (!name || !set_tunable(name, value)) return fail(DSB200_ERR_INVALID, "debug_set_tunable: unknown name");
+    return DSB200_OK;
+}
 
 int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches)
 {

@@ -59,6 +59,29 @@ struct ProjParams {                  // CreateExpectedDepths
     int W, H, maxRenderBlocks;
 };
 
+// Launch-shape knobs (defaults measured on B200, profiles/README.md).  Initialised from the environment variable of the same name
+// in upper case with the DSB200_ prefix (DSB200_RAY_STEPS ...); dsb200_debug_set_tunable changes them at run time (tools/tune.py).
+// None of them changes a result: every setting is covered by the same bit-exact parity tests.
+struct Tunables {
+    int ray_steps;        // loop bodies per ray in the first raycast pass before the ray is suspended (0: one unbounded pass)
+    int ray_group;        // lanes per suspended ray in the finishing pass: 8, 16 or 32
+    int ray_ctas;         // CTAs per SM of the first raycast pass
+    int ray_finish_ctas;  // CTAs per SM of the finishing pass
+    int ray_bottom_up;    // hand the image tiles out from the last row upwards
+    int fuse_kernel;      // integration kernel variant
+};
+Tunables &tunables();
+bool set_tunable(const char *name, int value);
+
+// Rays the bounded first raycast pass suspends, and the finishing pass completes (vis.cu).  Engine scratch of dsb200_vis.
+struct RayQueue {
+    int *ctl;          // [0] rays queued, [1] hand-out ticket of the finishing pass, [2] warps of the finishing pass that are done
+    int *pixel;        // x + y * W
+    float4 *posLen;    // rx, ry, rz, totalLength (voxel units, at the top of the march loop)
+    float4 *dirMax;    // dx, dy, dz, totalLengthMax
+    int capacity;      // rays (>= W * H of any image raycast through it)
+};
+
 // recon_alloc.cu
 void launch_begin_frame(cudaStream_t st, const FrameState &fs, int hostLastFreeBlock, int hostLastFreeExcess,
                         int hostNoVisible, int useHost, const int *visibleIds, uint8_t *visType, int prevUpperBound);
@@ -102,10 +125,11 @@ void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_h
                             const int *count, float *rangeImage, int *blockTileCounts, Counters *counters);
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
                     const float *rangeImage, float *raycastResult, int *ticketPair /* two zeroed ints, re-armed by the kernel */,
-                    const short *sdfShadowOrNull = nullptr);
+                    const short *sdfShadowOrNull = nullptr, const RayQueue *queueOrNull = nullptr);
 void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank, int brickLog2,
                             const dsb200_hash_entry *const *hash, const dsb200_voxel *const *voxels,
-                            const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair);
+                            const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair,
+                            const RayQueue *queueOrNull = nullptr);
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,
                      uint8_t *rendering);
 void launch_composite_nearest(cudaStream_t st, int n, const float *const *resultsDev, float cx, float cy, float cz, int W,

@@ -141,7 +141,9 @@ __device__ __forceinline__ void fuse_colour(VoxelRegs &vox, float ptx, float pty
     float n0, n1, n2;
     if (!DE) { n0 = oc0 * oldWc + m0 * newWc; n1 = oc1 * oldWc + m1 * newWc; n2 = oc2 * oldWc + m2 * newWc; newWc = oldWc + newWc; }
     else     { n0 = oc0 * oldWc - m0 * newWc; n1 = oc1 * oldWc - m1 * newWc; n2 = oc2 * oldWc - m2 * newWc; newWc = oldWc - newWc; }
-    if (DE && newWc == 0.0f) { vox.r = vox.g = vox.b = 0; vox.wc = 0; return; }   // defined behaviour for x/0
+    // De-fusing the last colour observation divides by zero and de-fusing from weight 0 leaves a weight of -1; the reference's
+    // only implementation is CUDA, so the device's own conversions of inf / NaN / negative values ARE the reference behaviour
+    // (cvt.rzi.s32.f32 saturates, NaN -> 0; `(uchar)float` is cvt.rzi.u32.f32: negative -> 0): nothing is special-cased here.
     if (newWc >= 1.0f) {      // integer-valued, <= 256
         const float y = T.rcp[(int)newWc];
         n0 = X::by_int(n0, newWc, y); n1 = X::by_int(n1, newWc, y); n2 = X::by_int(n2, newWc, y);
@@ -149,7 +151,7 @@ __device__ __forceinline__ void fuse_colour(VoxelRegs &vox, float ptx, float pty
     float mw = (float)(unsigned char)P.maxW;
     newWc = (newWc < mw) ? newWc : mw;
     vox.r = to_uchar(n0 * 255.0f); vox.g = to_uchar(n1 * 255.0f); vox.b = to_uchar(n2 * 255.0f);
-    vox.wc = (unsigned char)(int)newWc;
+    vox.wc = (unsigned char)newWc;        // the reference's `(uchar)newW` on a float (DeviceAgnostic/...:112,214)
 }
 
 // One 4 KiB voxel block per CTA iteration.  Phase A: every thread loads 16 B (two voxels), runs the depth part in
@@ -361,7 +363,7 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
 {
     unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
-    static const int variant = getenv("DSB200_FUSE_KERNEL") ? atoi(getenv("DSB200_FUSE_KERNEL")) : 1;   // 0: CTA per block, 1: warp per block
+    const int variant = tunables().fuse_kernel;   // 0: CTA per block, 1: warp per block
     if (variant == 1) {
         const int g = kNumSMs * 8;
         if (deintegrate) {

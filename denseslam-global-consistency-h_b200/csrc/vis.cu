@@ -12,6 +12,7 @@
 //    fallback that only runs when the cap would be hit;
 //  * nothing returns to the host between stages (counts stay on the device).
 #include <cstdlib>
+#include <cstring>
 #include "kernels.cuh"
 #include "scan.cuh"
 #include "visibility.cuh"
@@ -341,54 +342,92 @@ __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, i
     return ((1.0f - cz) * res1 + cz * res2) / 32767.0f;
 }
 
-// castRay, DeviceAgnostic/ITMVisualisationEngine.h:124-196
-template <class Tables>
-__device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables &T, const RayParams &P, float zmin, float zmax)
+// castRay, DeviceAgnostic/ITMVisualisationEngine.h:124-196, in three pieces so that a march can be suspended and resumed (by
+// another thread, in another kernel) without changing a single operation of it:
+//   ray_setup   :124-158  start point, unit direction, ray length at the near / far expected depth
+//   ray_step    :161-178  ONE pass of the march loop body
+//   ray_finish  :180-195  the two refinement steps and the output
+struct RayState { float rx, ry, rz, total, dx, dy, dz, totalMax; };
+enum RayStep { kStepUnit = 0, kStepJump = 1, kStepHit = 2 };     // unit: stepLength == 1.0f exactly; jump: anything else
+
+__device__ __forceinline__ void ray_setup(RayState &s, int x, int y, const RayParams &P, float zmin, float zmax)
 {
-    const int bucketNum = P.bucketNum, bucketMask = P.bucketMask;
-    const float stepScale = P.mu * P.oneOverVoxel;
     Vec4 pc;
     pc.z = zmin;
     pc.x = pc.z * (((float)x - P.invProj[2]) * P.invProj[0]);
     pc.y = pc.z * (((float)y - P.invProj[3]) * P.invProj[1]);
     pc.w = 1.0f;
-    float totalLength = sqrtf(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z) * P.oneOverVoxel;
+    s.total = sqrtf(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z) * P.oneOverVoxel;
     Vec4 t = mul(P.invM, pc);
     const float sx = t.x * P.oneOverVoxel, sy = t.y * P.oneOverVoxel, sz = t.z * P.oneOverVoxel;
     pc.z = zmax;
     pc.x = pc.z * (((float)x - P.invProj[2]) * P.invProj[0]);
     pc.y = pc.z * (((float)y - P.invProj[3]) * P.invProj[1]);
     pc.w = 1.0f;
-    const float totalLengthMax = sqrtf(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z) * P.oneOverVoxel;
+    s.totalMax = sqrtf(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z) * P.oneOverVoxel;
     t = mul(P.invM, pc);
     float dx = t.x * P.oneOverVoxel - sx, dy = t.y * P.oneOverVoxel - sy, dz = t.z * P.oneOverVoxel - sz;
     const float dn = 1.0f / sqrtf(dx * dx + dy * dy + dz * dz);
-    dx *= dn; dy *= dn; dz *= dn;
-    float rx = sx, ry = sy, rz = sz;
-    BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
-    float sdf = 1.0f, stepLength;
-    bool found, ptFound;
-    while (totalLength < totalLengthMax) {
-        sdf = (float)read_sdf(T, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
-                              (int)round_half_away(rz), found, cache) / 32767.0f;
-        if (!found) stepLength = (float)kBlock;
-        else {
-            if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(T, bucketNum, bucketMask, rx, ry, rz, found, cache);
-            if (!(sdf > 0.0f)) break;
-            stepLength = (sdf * stepScale < 1.0f) ? 1.0f : sdf * stepScale;
-        }
-        rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
-        totalLength += stepLength;
-    }
+    s.dx = dx * dn; s.dy = dy * dn; s.dz = dz * dn;
+    s.rx = sx; s.ry = sy; s.rz = sz;
+}
+
+// one loop body at position (rx, ry, rz): the sample (sdf, as the loop leaves it) and what the loop does next
+template <class Tables>
+__device__ __forceinline__ RayStep ray_step(float rx, float ry, float rz, const Tables &T, const RayParams &P, float stepScale,
+                                            BlockCache &cache, float &sdf, float &stepLength)
+{
+    bool found;
+    sdf = (float)read_sdf(T, P.bucketNum, P.bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
+                          (int)round_half_away(rz), found, cache) / 32767.0f;
+    if (!found) { stepLength = (float)kBlock; return kStepJump; }
+    if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(T, P.bucketNum, P.bucketMask, rx, ry, rz, found, cache);
+    if (!(sdf > 0.0f)) return kStepHit;
+    stepLength = (sdf * stepScale < 1.0f) ? 1.0f : sdf * stepScale;
+    return stepLength == 1.0f ? kStepUnit : kStepJump;
+}
+
+template <class Tables>
+__device__ __forceinline__ float4 ray_finish(float rx, float ry, float rz, float dx, float dy, float dz, float sdf, const Tables &T,
+                                             const RayParams &P, float stepScale, BlockCache &cache)
+{
+    bool ptFound;
     if (sdf <= 0.0f) {
-        stepLength = sdf * stepScale;
+        float stepLength = sdf * stepScale;
         rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
-        sdf = sdf_trilinear(T, bucketNum, bucketMask, rx, ry, rz, ptFound, cache);
+        sdf = sdf_trilinear(T, P.bucketNum, P.bucketMask, rx, ry, rz, ptFound, cache);
         stepLength = sdf * stepScale;
         rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
     } else ptFound = false;
-    out = make_float4(rx, ry, rz, ptFound ? 1.0f : 0.0f);
-    return ptFound;
+    return make_float4(rx, ry, rz, ptFound ? 1.0f : 0.0f);
+}
+
+// the march; returns false when `maxSteps` loop bodies have run and the ray is still marching (state left at the loop top)
+template <class Tables>
+__device__ __forceinline__ bool cast_ray_bounded(float4 &out, RayState &s, const Tables &T, const RayParams &P, int maxSteps)
+{
+    const float stepScale = P.mu * P.oneOverVoxel;
+    BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
+    float sdf = 1.0f, stepLength;
+    int steps = 0;
+    while (s.total < s.totalMax) {
+        if (steps == maxSteps) return false;
+        steps++;
+        if (ray_step(s.rx, s.ry, s.rz, T, P, stepScale, cache, sdf, stepLength) == kStepHit) break;
+        s.rx += stepLength * s.dx; s.ry += stepLength * s.dy; s.rz += stepLength * s.dz;
+        s.total += stepLength;
+    }
+    out = ray_finish(s.rx, s.ry, s.rz, s.dx, s.dy, s.dz, sdf, T, P, stepScale, cache);
+    return true;
+}
+
+template <class Tables>
+__device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables &T, const RayParams &P, float zmin, float zmax)
+{
+    RayState s;
+    ray_setup(s, x, y, P, zmin, zmax);
+    cast_ray_bounded(out, s, T, P, -1);
+    return out.w > 0.0f;
 }
 
 // GenericRaycast (CPU .cpp:296-333; CUDA .cu:807-819).  Ray lengths differ by orders of magnitude across the image (sky
@@ -412,10 +451,13 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 // voxel, which is always one of its eight corners, out of it; results identical) measured 0.163 ms (55 registers instead of 48).
 // Sharded scene: tileStride shards deal the tiles round-robin (tile = ticket * tileStride + tileFirst) and `out` may be the
 // root shard's image (peer memory: the 16-byte stores of a tile row are one 128-byte NVLink write).
+// Rays still marching after `maxSteps` loop bodies are SUSPENDED: their state goes to a queue and k_raycast_finish completes
+// them (the tail described above: a few hundred grazing rays creeping one voxel per step for > 100 dependent steps).
+
 template <class Tables>
 __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_constant__ Tables T,
                                                  const float2 *__restrict__ range, float4 *out, int *ticket, int tileFirst,
-                                                 int tileStride, int bottomUp)
+                                                 int tileStride, int bottomUp, RayQueue q, int maxSteps)
 {
     const int lane = threadIdx.x & 31;
     const int tilesX = (P.W + 7) >> 3, tilesY = (P.H + 3) >> 2, nTiles = tilesX * tilesY;
@@ -427,17 +469,85 @@ __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_const
         if (bottomUp) tile = nTiles - 1 - tile;
         const int ty = tile / tilesX, tx = tile - ty * tilesX;
         const int x = tx * 8 + (lane & 7), y = ty * 4 + (lane >> 3);
+        bool suspended = false;
+        RayState s;
         if (x < P.W && y < P.H) {
             const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
             const float2 mm = __ldg(range + loc2);
             float4 r;
-            cast_ray(r, x, y, T, P, mm.x, mm.y);
-            out[x + y * P.W] = r;
+            ray_setup(s, x, y, P, mm.x, mm.y);
+            if (cast_ray_bounded(r, s, T, P, maxSteps)) out[x + y * P.W] = r;
+            else suspended = true;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, suspended);
+        if (m) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&q.ctl[0], __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (suspended) {
+                const int i = base + __popc(m & ((1u << lane) - 1u));      // capacity = W * H: cannot overflow
+                q.pixel[i] = x + y * P.W;
+                q.posLen[i] = make_float4(s.rx, s.ry, s.rz, s.total);
+                q.dirMax[i] = make_float4(s.dx, s.dy, s.dz, s.totalMax);
+            }
         }
     }
     if (lane == 0) {
         const int nWarps = gridDim.x * (blockDim.x >> 5);
         if (atomicAdd(&ticket[1], 1) == nWarps - 1) { ticket[1] = 0; ticket[0] = 0; }   // all tickets were handed out: re-arm
+    }
+}
+
+// Finishing pass: G lanes (G = 8, 16 or 32) work on ONE suspended ray and evaluate its next G loop bodies TOGETHER, lane j
+// assuming that the j bodies before it all advanced by exactly one voxel -- which is what a creeping ray does
+// (stepLength = max(sdf * mu / voxelSize, 1) is exactly 1.0f inside the quarter of the truncation band next to the surface).
+// Lane j derives its position by the same j additions the sequential loop would perform (rx += 1.0f * dx, ...: bit-identical),
+// samples the volume, and the group commits the bodies up to and including the first one that was NOT a unit step (a longer
+// step, a missing block, the hit, or the end of the range); later lanes' samples are discarded.  Lane 0's body is never
+// speculative, so a round always makes progress, and every committed body is the sequential loop's body on the sequential
+// loop's operands: the result is bit-identical to cast_ray (tests: every raycast parity test runs through here).  What changes
+// is the length of the dependent chain: G bodies per two or three memory round trips instead of one.
+template <class Tables, int G>
+__global__ void __launch_bounds__(128) k_raycast_finish(RayParams P, const __grid_constant__ Tables T, float4 *out, RayQueue q)
+{
+    const int lane = threadIdx.x & 31, j = lane & (G - 1);
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (lane & ~(G - 1)));
+    const int n = q.ctl[0];
+    const float stepScale = P.mu * P.oneOverVoxel;
+    BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
+    while (true) {
+        int i = 0;
+        if (j == 0) i = atomicAdd(&q.ctl[1], 1);
+        i = __shfl_sync(gmask, i, 0, G);
+        if (i >= n) break;
+        const float4 a = q.posLen[i], b = q.dirMax[i];
+        float rx = a.x, ry = a.y, rz = a.z, total = a.w;
+        const float dx = b.x, dy = b.y, dz = b.z, totalMax = b.w;
+        while (true) {
+            // this lane's operands: j unit steps on from the group's committed state
+            float px = rx, py = ry, pz = rz, t = total;
+            for (int k = 0; k < j; k++) { px += dx; py += dy; pz += dz; t += 1.0f; }     // 1.0f * dx == dx: the loop's own additions
+            int kind;                      // RayStep, or 3 = the loop condition fails here (no hit)
+            float sdf = 1.0f, stepLength = 1.0f;
+            if (t < totalMax) kind = ray_step(px, py, pz, T, P, stepScale, cache, sdf, stepLength);
+            else kind = 3;
+            const unsigned stop = __ballot_sync(gmask, kind != kStepUnit) & gmask;
+            const int first = stop ? (__ffs(stop) - 1) & (G - 1) : G - 1;             // the body the group commits last
+            const int fk = __shfl_sync(gmask, kind, first, G);
+            if (fk == kStepHit || fk == 3) {
+                if (j == first) out[q.pixel[i]] = ray_finish(px, py, pz, dx, dy, dz, sdf, T, P, stepScale, cache);
+                break;
+            }
+            // unit or longer step: the committed state after it
+            px += stepLength * dx; py += stepLength * dy; pz += stepLength * dz; t += stepLength;
+            rx = __shfl_sync(gmask, px, first, G); ry = __shfl_sync(gmask, py, first, G); rz = __shfl_sync(gmask, pz, first, G);
+            total = __shfl_sync(gmask, t, first, G);
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        const int nWarps = gridDim.x * (blockDim.x >> 5);
+        if (atomicAdd(&q.ctl[2], 1) == nWarps - 1) { q.ctl[0] = 0; q.ctl[1] = 0; q.ctl[2] = 0; }   // queue drained: re-arm for the next raycast
     }
 }
 
@@ -783,26 +893,62 @@ void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_h
     DSB_LAUNCH(k_range_cap_fallback, 1, 1024, 0, st, P, hash, ids, count, rangeImage, counters);
 }
 
-// tuning knobs (defaults measured on B200, profiles/): tile hand-out order, CTAs launched per SM
+// tuning knobs (kernels.cuh: Tunables)
 static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
-static int ray_bottom_up() { static int v = env_int("DSB200_RAY_BOTTOM_UP", 0); return v != 0; }
-static int ray_ctas_per_sm() { static int v = env_int("DSB200_RAY_CTAS", 12); return v < 1 ? 1 : v; }
+Tunables &tunables()
+{
+    static Tunables t = {env_int("DSB200_RAY_STEPS", 24), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
+                         env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 1)};
+    return t;
+}
+bool set_tunable(const char *name, int value)
+{
+    Tunables &t = tunables();
+    const struct { const char *n; int *p; } table[] = {{"ray_steps", &t.ray_steps}, {"ray_group", &t.ray_group}, {"ray_ctas", &t.ray_ctas},
+        {"ray_finish_ctas", &t.ray_finish_ctas}, {"ray_bottom_up", &t.ray_bottom_up}, {"fuse_kernel", &t.fuse_kernel}};
+    for (const auto &e : table) if (!strcmp(e.n, name)) { *e.p = value; return true; }
+    return false;
+}
+static int ray_bottom_up() { return tunables().ray_bottom_up != 0; }
+static int ray_ctas_per_sm() { const int v = tunables().ray_ctas; return v < 1 ? 1 : v; }
+
+// bounded first pass + finishing pass (k_raycast_finish); DSB200_RAY_STEPS = 0 runs the single unbounded pass,
+// DSB200_RAY_GROUP = lanes per suspended ray in the finishing pass (8, 16 or 32)
+static int ray_max_steps() { return tunables().ray_steps; }
+static int ray_group() { return tunables().ray_group; }
+
+template <class Tables>
+static void launch_raycast_two_pass(cudaStream_t st, const RayParams &P, const Tables &T, const float2 *range, float4 *out,
+                                    int *ticketPair, int tileFirst, int tileStride, int grid, const RayQueue *queue)
+{
+    RayQueue q{};
+    int maxSteps = -1;
+    if (queue && queue->ctl && queue->capacity >= P.W * P.H && ray_max_steps() > 0) { q = *queue; maxSteps = ray_max_steps(); }
+    DSB_LAUNCH(k_raycast<Tables>, grid, 128, 0, st, P, T, range, out, ticketPair, tileFirst, tileStride, ray_bottom_up(), q, maxSteps);
+    if (maxSteps < 0) return;
+    const int g2 = kNumSMs * (tunables().ray_finish_ctas < 1 ? 1 : tunables().ray_finish_ctas);
+    switch (ray_group()) {
+    case 32: DSB_LAUNCH((k_raycast_finish<Tables, 32>), g2, 128, 0, st, P, T, out, q); break;
+    case 16: DSB_LAUNCH((k_raycast_finish<Tables, 16>), g2, 128, 0, st, P, T, out, q); break;
+    default: DSB_LAUNCH((k_raycast_finish<Tables, 8>), g2, 128, 0, st, P, T, out, q); break;
+    }
+}
 
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
-                    const float *rangeImage, float *raycastResult, int *ticketPair, const short *sdfShadow)
+                    const float *rangeImage, float *raycastResult, int *ticketPair, const short *sdfShadow, const RayQueue *queue)
 {
     const int nTiles = div_up(P.W, 8) * div_up(P.H, 4);
     int grid = div_up(nTiles, 4);
     if (grid > kNumSMs * ray_ctas_per_sm()) grid = kNumSMs * ray_ctas_per_sm();
     if (sdfShadow) {
         ShadowTables T; T.sdf = sdfShadow; T.hash = hash;
-        DSB_LAUNCH(k_raycast<ShadowTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(rangeImage),
-                   reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1, ray_bottom_up());
+        launch_raycast_two_pass(st, P, T, reinterpret_cast<const float2 *>(rangeImage), reinterpret_cast<float4 *>(raycastResult),
+                                ticketPair, 0, 1, grid, queue);
         return;
     }
     const SceneTables T = scene_tables(voxels, hash);
-    DSB_LAUNCH(k_raycast<SceneTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(rangeImage),
-               reinterpret_cast<float4 *>(raycastResult), ticketPair, 0, 1, ray_bottom_up());
+    launch_raycast_two_pass(st, P, T, reinterpret_cast<const float2 *>(rangeImage), reinterpret_cast<float4 *>(raycastResult),
+                            ticketPair, 0, 1, grid, queue);
 }
 
 // Expected-depth image of the whole sharded scene = element-wise (min of mins, max of maxes) of the shards' images: what
@@ -822,7 +968,8 @@ __global__ void __launch_bounds__(256) k_range_merge(PeerImages imgs, int n, int
 
 void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank, int brickLog2,
                             const dsb200_hash_entry *const *hash, const dsb200_voxel *const *voxels,
-                            const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair)
+                            const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair,
+                            const RayQueue *queue)
 {
     // only rows [0, H/8] of the full-stride range image are ever read
     PeerImages imgs;
@@ -836,8 +983,8 @@ void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank
     const int nTiles = div_up(div_up(P.W, 8) * div_up(P.H, 4), n);
     int grid = div_up(nTiles, 4);
     if (grid > kNumSMs * ray_ctas_per_sm()) grid = kNumSMs * ray_ctas_per_sm();
-    DSB_LAUNCH(k_raycast<ShardTables>, grid, 128, 0, st, P, T, reinterpret_cast<const float2 *>(mergedRange),
-               reinterpret_cast<float4 *>(raycastResult), ticketPair, rank, n, ray_bottom_up());
+    launch_raycast_two_pass(st, P, T, reinterpret_cast<const float2 *>(mergedRange), reinterpret_cast<float4 *>(raycastResult),
+                            ticketPair, rank, n, grid, queue);
 }
 
 void launch_icp_maps(cudaStream_t st, const RayParams &P, const float *raycastResult, float *points, float *normals,

@@ -470,6 +470,9 @@ int dsb200_recon_notify_scene_modified(dsb200_recon *e);
  * the operand windows the kernels guarantee (plus the out-of-window fall-backs); *mismatches = number of
  * bit-level disagreements (must be 0). */
 int dsb200_debug_force_plain_division(dsb200_recon *e, int on);
+/* launch-shape knobs (csrc/kernels.cuh: Tunables; "ray_steps", "ray_group", "ray_ctas", "ray_finish_ctas", "ray_bottom_up",
+ * "fuse_kernel"): process-wide, results never depend on them (tools/tune.py sweeps them on the GPU) */
+int dsb200_debug_set_tunable(const char *name, int value);
 int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches);
 /* the bilateral filter's exp (csrc/view_filter.cu, a restatement of glibc's expf) on n HOST floats: y[i] = expf(x[i]);
  * tests compare it bit for bit with the host C library's expf */

@@ -402,10 +402,29 @@ inline float sdfToFloat(float x) { return (float)(x) / 32767.0f; }        // SDF
 // the GPU (whose direct float->short conversion saturates) can be written identically.
 inline short sdfToShort(float x) { return (short)(int)((x) * 32767.0f); }
 
+// float -> int as the CUDA hardware converts (cvt.rzi.s32.f32: NaN -> 0, out of range saturates).  The only implementation of
+// de-integration in the reference is its CUDA engine, and de-fusing the last colour observation divides by zero there
+// (DeviceAgnostic/ITMSceneReconstructionEngine.h:204-206), so the device's conversion of inf / NaN IS the reference behaviour
+// (pinned by tests/test_gpu_refcuda.py); for finite in-range values it is the plain C cast.
+inline int deviceFloatToInt(float v)
+{
+    if (v != v) return 0;
+    if (v >= 2147483648.0f) return 2147483647;
+    if (v <= -2147483648.0f) return (-2147483647 - 1);
+    return (int)v;
+}
+// float -> unsigned char as nvcc lowers the reference's `(uchar)newW` (:214): cvt.rzi.u32.f32 (negative -> 0), low byte kept
+inline unsigned char deviceFloatToUChar(float v)
+{
+    if (v != v || v <= 0.0f) return 0;
+    if (v >= 4294967296.0f) return 255;
+    return (unsigned char)(unsigned)v;
+}
+
 // ROUND (ORUtils/MathUtils.h:24) then (int), then CLAMP 0..255: Vector3::toUChar, ORUtils/Vector.h:245-247
 inline unsigned char toUChar(float v)
 {
-    int i = (int)((v < 0) ? (v - 0.5f) : (v + 0.5f));
+    int i = deviceFloatToInt((v < 0) ? (v - 0.5f) : (v + 0.5f));
     int lo = (255 < i) ? 255 : i;       // MIN(255, i)
     return (unsigned char)((0 < lo) ? lo : 0);
 }
@@ -482,14 +501,13 @@ inline void updateColour(dsb200_voxel &vox, V4 pt, const float *Mrgb, const floa
         newC[k] = DE ? (oldC[k] * oldW - meas * newW) : (oldC[k] * oldW + meas * newW);
     }
     newW = DE ? (oldW - newW) : (oldW + newW);
-    if (DE && newW == 0.0f) {   // reference divides by zero and casts inf/NaN to uchar (UB): defined as "no colour left"
-        vox.clr[0] = vox.clr[1] = vox.clr[2] = 0; vox.w_color = 0; return;
-    }
+    // DE with oldW == 1 divides by zero (+-inf, or NaN for 0/0) and DE with oldW == 0 leaves newW = -1: both are converted as
+    // the reference's CUDA build converts them (see deviceFloatToInt / deviceFloatToUChar): a channel becomes 255, 0 or 0, and
+    // the negative weight becomes 0
     for (int k = 0; k < 3; k++) newC[k] /= newW;
     newW = (newW < maxW) ? newW : (float)maxW;
-    // float->uchar of NaN/inf (DE with oldW==1) is UB in the reference; our definition: via toUChar's int cast
     for (int k = 0; k < 3; k++) vox.clr[k] = toUChar(newC[k] * 255.0f);
-    vox.w_color = (unsigned char)(int)newW;
+    vox.w_color = deviceFloatToUChar(newW);
 }
 
 template <bool DE>
