@@ -122,6 +122,7 @@ struct dsb200_recon {
     // SDF shadow: one short per voxel of the scene this engine maintains, kept in step by every kernel that writes voxels
     // (reset, integrate, de-integrate, pruning) and read by the fused frame's raycast instead of the 8-byte voxel records.
     short *sdfShadow = nullptr; const void *shadowFor = nullptr; bool shadowEnabled = true;
+    unsigned char *weightImage = nullptr; size_t weightBytes = 0;   // per-pixel depth weights of the frame being fused (flat kernel)
     dsb200_shard shard{0, 1, 2, 0};      // sharded scene: this engine's block ownership (count <= 1: everything)
     bool forceSlowDiv = false;        // debug: run the plain-division kernel variants (dsb200_debug_force_plain_division)
     // history (CUDA/ITMSceneReconstructionEngine_CUDA.h:41-48)
@@ -216,7 +217,7 @@ int dsb200_recon_destroy(dsb200_recon *e)
     e->arena.release_all();
     cudaFree(e->reqKey); cudaFree(e->slotMark); cudaFree(e->pruneScratch); cudaFree(e->fs.counters);
     cudaFree(e->fs.scanState); cudaFree(e->fs.tickets); cudaFreeHost(e->hostCounters);
-    cudaFree(e->fs.reqBits); cudaFree(e->fs.visBits); cudaFree(e->sdfShadow);
+    cudaFree(e->fs.reqBits); cudaFree(e->fs.visBits); cudaFree(e->sdfShadow); cudaFree(e->weightImage);
     delete e;
     return DSB200_OK;
 }
@@ -359,6 +360,18 @@ static int abandon_prefetch(dsb200_recon *e)
     CU(cudaGetLastError());
     e->prefetchPending = false;
     return DSB200_OK;
+}
+
+// W * H bytes of engine scratch for the per-pixel depth weights (nullptr if the allocation fails: the kernels then compute them per voxel)
+static unsigned char *weight_scratch(dsb200_recon *e, const dsb200_view *view)
+{
+    const size_t need = (size_t)view->depth_w * view->depth_h;
+    if (need > e->weightBytes) {
+        cudaFree(e->weightImage); e->weightImage = nullptr; e->weightBytes = 0;
+        if (cudaMalloc(&e->weightImage, need) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        e->weightBytes = need;
+    }
+    return e->weightImage;
 }
 
 // Every scene-modifying entry point passes through here.  consumesPrefetch: the call is an allocation that may pick up a
@@ -513,7 +526,8 @@ int dsb200_integrate(dsb200_recon *e, dsb200_scene *scene, const dsb200_view *vi
         e->hostCounters->noVisible = rs->no_visible;
         CU(cudaMemcpyAsync(&e->fs.counters->noVisible, &e->hostCounters->noVisible, 4, cudaMemcpyHostToDevice, e->stream));
     }
-    launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene));
+    launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene),
+                weight_scratch(e, view));
     CU(cudaGetLastError());
     if (!e->async) CU(cudaStreamSynchronize(e->stream));
     return DSB200_OK;
@@ -1243,7 +1257,8 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     }
     if (stages & DSB200_FRAME_INTEGRATE) {
         FuseParams FP; make_fuse_params(FP, e, scene, view, trk);
-        launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene));
+        launch_fuse(e->stream, FP, false, scene->voxels, scene->hash, rs->visible_ids, countPtr, view->depth, view->rgb, shadow_for(e, scene),
+                    weight_scratch(e, view));
     }
     if (e->async && !e->profile) {     // nothing after this point writes the scene: a look-ahead may start here
         CU(cudaEventRecord(e->evSceneWritten, e->stream));

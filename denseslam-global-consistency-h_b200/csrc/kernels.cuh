@@ -64,11 +64,13 @@ struct ProjParams {                  // CreateExpectedDepths
 // None of them changes a result: every setting is covered by the same bit-exact parity tests.
 struct Tunables {
     int ray_steps;        // loop bodies per ray in the first raycast pass before the ray is suspended (0: one unbounded pass)
-    int ray_group;        // lanes per suspended ray in the finishing pass: 8, 16 or 32
+    int ray_group;        // lanes per suspended ray in the finishing pass: 2, 4, 8, 16 or 32
     int ray_ctas;         // CTAs per SM of the first raycast pass
     int ray_finish_ctas;  // CTAs per SM of the finishing pass
     int ray_bottom_up;    // hand the image tiles out from the last row upwards
     int fuse_kernel;      // integration kernel variant
+    int fuse_ctas;        // CTAs per SM of the flat integration kernel
+    int fuse_minb;        // ... and its __launch_bounds__ minimum CTAs per SM (4, 6 or 8: 128 / 85 / 64 registers)
 };
 Tunables &tunables();
 bool set_tunable(const char *name, int value);
@@ -102,7 +104,7 @@ void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &
 // recon_integrate.cu
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,
                  const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth,
-                 const uint8_t *rgb, short *sdfShadowOrNull);
+                 const uint8_t *rgb, short *sdfShadowOrNull, unsigned char *weightScratchOrNull = nullptr /* W * H bytes */);
 void launch_reset_scene(cudaStream_t st, dsb200_voxel *voxels, size_t numVoxels, dsb200_hash_entry *hash, int total,
                         int *allocList, int numBlocks, int *excessList, int excessSize, uint8_t *visTypeOrNull,
                         unsigned *reqKey, Counters *counters, short *sdfShadowOrNull);

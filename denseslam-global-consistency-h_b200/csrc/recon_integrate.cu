@@ -357,14 +357,200 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp(FuseParams 
     }
 }
 
+// ---------------------------------------------------------------- flat variant (fuse_kernel = 2)
+// Same decomposition as k_fuse_warp (one warp per block, 8 slices, a voxel pair per lane), but the depth part of both voxels is
+// STRAIGHT-LINE code: every early return of computeUpdatedVoxelDepthInfo (:17-77) becomes a predicate, the depth pixel is always
+// loaded (index 0 when the projection is rejected), and the result is selected at the end.  A warp executes every path of the
+// branchy version anyway as soon as one lane takes it; without the 5-deep nest of divergent branches per voxel the two voxels'
+// dependency chains (13 dependent FMAs for the projection alone) interleave, and the reconvergence bookkeeping disappears.
+// The per-pixel part of the depth weighting, (int)(maxDistance / d + 0.5) clamped to [1, maxNewW] (:52-62), is taken from a byte
+// image computed once per frame (k_depth_weights) instead of once per voxel.  Every operation on data is the one k_fuse_warp
+// performs, in the same order: results are bit-identical (tests: DSB200_FUSE_KERNEL=2 runs the whole parity suite).
+// Fusion (not de-fusion) with the exact-division fast paths only; launch_fuse falls back to k_fuse_warp otherwise.
+__global__ void __launch_bounds__(256) k_depth_weights(const float *__restrict__ depth, unsigned char *wimg, int n, int maxDistance, int maxNewW)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float dm = depth[i];
+        int newW = 1;
+        if (dm > 0.0f) {
+            const float x = (float)maxDistance / dm;
+            if (x < 8388608.0f) { const float tr = truncf(x); newW = (int)tr + ((x - tr >= 0.5f) ? 1 : 0); }
+            else newW = 0x7fffffff;
+            if (newW < 1) newW = 1;
+            if (newW > maxNewW) newW = maxNewW;
+        }
+        wimg[i] = (unsigned char)newW;
+    }
+}
+
+// depth part on the packed low word of a voxel (sdf | w_depth << 16 | clr.r << 24); returns "the colour part must run"
+// `outside` is raised when the voxel's camera-space z lies outside the operand window of the exact-division fast path
+// (|z| < 2^-20 or > 2^20 metres: a voxel within a micrometre of the camera plane); the caller then redoes the slice with the
+// general code.  Keeping that test out of this function keeps it free of branches.
+template <bool WIMG>
+__device__ __forceinline__ bool fuse_depth_flat(unsigned &lo, float pcx, float pcy, float pcz, const FuseParams &P,
+                                                const float *__restrict__ depth, const unsigned char *__restrict__ wimg,
+                                                const FuseTables &T, bool &outside)
+{
+    const int w = (int)((lo >> 16) & 0xffu);
+    bool ok = !(pcz <= 0.0f);
+    if (P.stopMaxW) ok = ok && (w != P.maxW);
+    if (P.approximate) ok = ok && (w == 0);
+    outside = outside || (ok && !div_range_ok(pcz));
+    const float a0 = P.proj_d[0] * pcx, a1 = P.proj_d[1] * pcy;
+    const float y = rcp_refined(pcz);
+    const float qu = div_step2(a0, pcz, y), qv = div_step2(a1, pcz, y);
+    const float u = qu + P.proj_d[2], v = qv + P.proj_d[3];
+    ok = ok && !((u < 1) || (u > P.W - 2) || (v < 1) || (v > P.H - 2));
+    const int idx = ok ? ((int)(u + 0.5f) + (int)(v + 0.5f) * P.W) : 0;
+    const float dm = __ldg(depth + idx);
+    const int newW = WIMG ? (int)__ldg(wimg + idx) : 1;
+    ok = ok && !(dm <= 0.0f);
+    const float eta = dm - pcz;
+    ok = ok && !(eta < -P.mu);
+    const float q = div_step2(eta, P.mu, P.rcpMu);
+    const float oldF = div_step1((float)(short)(lo & 0xffffu), 32767.0f, P.rcp32767);
+    const float newF = (1.0f < q) ? 1.0f : q;
+    const float numer = (float)w * oldF + (float)newW * newF;
+    const int ws = w + newW;                                             // 1 .. 255 + maxNewW <= 510
+    const float F = div_step1(numer, (float)ws, T.rcp[ws]);
+    const int w2 = (ws < P.maxW) ? ws : P.maxW;
+    const unsigned nlo = (lo & 0xff000000u) | (((unsigned)w2 & 0xffu) << 16) | ((unsigned)(int)(F * 32767.0f) & 0xffffu);
+    lo = ok ? nlo : lo;
+    return ok && !((eta > P.mu) || (fabsf(q) > 0.25f));
+}
+
+template <bool WIMG, int MINB>
+__global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FuseParams P, dsb200_voxel *voxels,
+                                                                        const dsb200_hash_entry *__restrict__ hash,
+                                                                        const int *__restrict__ ids, const int *__restrict__ countPtr,
+                                                                        const float *__restrict__ depth, const uchar4 *__restrict__ rgb,
+                                                                        const unsigned char *__restrict__ wimg, unsigned *shadow2)
+{
+    __shared__ FuseWarpSmem S;
+    const int n = *countPtr;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    fill_tables(S.T);
+    if (lane < 8) S.dirty[warp][lane] = 0;
+    __syncthreads();
+    const FuseTables &T = S.T;
+    uint4 *sVox = S.vox[warp];
+    unsigned short *sQueue = S.queue[warp];
+    unsigned *sDirty = S.dirty[warp];
+    const int lx = (lane & 3) * 2, ly = lane >> 2;
+    const int stride = gridDim.x * kFuseWarps;
+    const HashEntry none = {0, 0, 0, 0, 0, -2, 0};
+    int i = blockIdx.x * kFuseWarps + warp;
+    int slot2 = (i + 2 * stride < n) ? __ldg(ids + i + 2 * stride) : -1;
+    HashEntry e1 = (i + stride < n) ? load_entry(hash, __ldg(ids + i + stride)) : none;
+    HashEntry e0 = (i < n) ? load_entry(hash, __ldg(ids + i)) : none;
+    for (; i < n; i += stride) {
+        const int slot3 = (i + 3 * stride < n) ? __ldg(ids + i + 3 * stride) : -1;
+        const HashEntry e2 = (slot2 >= 0) ? load_entry(hash, slot2) : none;
+        if (e1.ptr >= 0) prefetch_l2(reinterpret_cast<const char *>(voxels + (size_t)e1.ptr * kBlock3) + lane * 128);
+        if (e0.ptr >= 0) {
+            const HashEntry e = e0;
+            uint4 *base = reinterpret_cast<uint4 *>(voxels + (size_t)e.ptr * kBlock3);
+            uint4 raw = base[lane];
+            const int gx = e.px * kBlock + lx;
+            const float ptx0 = (float)gx * P.voxelSize, ptx1 = (float)(gx + 1) * P.voxelSize;
+            const float pty = (float)(e.py * kBlock + ly) * P.voxelSize;
+            const float ax0 = P.M_d.m[0] * ptx0 + P.M_d.m[4] * pty, ay0 = P.M_d.m[1] * ptx0 + P.M_d.m[5] * pty, az0 = P.M_d.m[2] * ptx0 + P.M_d.m[6] * pty;
+            const float ax1 = P.M_d.m[0] * ptx1 + P.M_d.m[4] * pty, ay1 = P.M_d.m[1] * ptx1 + P.M_d.m[5] * pty, az1 = P.M_d.m[2] * ptx1 + P.M_d.m[6] * pty;
+            unsigned dirty = 0;
+            int qn = 0;
+#pragma unroll 2
+            for (int z = 0; z < kBlock; z++) {
+                uint4 nxt = raw;
+                if (z + 1 < kBlock) nxt = base[(z + 1) * 32 + lane];
+                const float ptz = (float)(e.pz * kBlock + z) * P.voxelSize;
+                const float bx = P.M_d.m[8] * ptz, by = P.M_d.m[9] * ptz, bz = P.M_d.m[10] * ptz;
+                unsigned lo0 = raw.x, lo1 = raw.z;
+                bool outside = false;
+                bool c0 = fuse_depth_flat<WIMG>(lo0, (ax0 + bx) + P.M_d.m[12], (ay0 + by) + P.M_d.m[13], (az0 + bz) + P.M_d.m[14], P, depth, wimg, T, outside);
+                bool c1 = fuse_depth_flat<WIMG>(lo1, (ax1 + bx) + P.M_d.m[12], (ay1 + by) + P.M_d.m[13], (az1 + bz) + P.M_d.m[14], P, depth, wimg, T, outside);
+                if (__any_sync(0xffffffffu, outside)) {          // (never in practice) the slice again, general code
+                    VoxelRegs v0 = unpack(raw.x, raw.y), v1 = unpack(raw.z, raw.w);
+                    c0 = c1 = false;
+                    if (!((P.stopMaxW && v0.w == P.maxW) || (P.approximate && v0.w != 0))) {
+                        Vec4 pc = {(ax0 + bx) + P.M_d.m[12], (ay0 + by) + P.M_d.m[13], (az0 + bz) + P.M_d.m[14], 1.0f};
+                        c0 = fuse_depth_pc<false, true>(v0, pc, P, depth, T);
+                    }
+                    if (!((P.stopMaxW && v1.w == P.maxW) || (P.approximate && v1.w != 0))) {
+                        Vec4 pc = {(ax1 + bx) + P.M_d.m[12], (ay1 + by) + P.M_d.m[13], (az1 + bz) + P.M_d.m[14], 1.0f};
+                        c1 = fuse_depth_pc<false, true>(v1, pc, P, depth, T);
+                    }
+                    uint4 o = raw;
+                    pack(v0, o.x, o.y); pack(v1, o.z, o.w);
+                    lo0 = o.x; lo1 = o.z;
+                }
+                if (lo0 != raw.x || lo1 != raw.z) {
+                    dirty |= 1u << z;
+                    if (shadow2) shadow2[(size_t)e.ptr * 256 + z * 32 + lane] = (lo0 & 0xffffu) | (lo1 << 16);
+                }
+                raw.x = lo0; raw.z = lo1;
+                sVox[z * 32 + lane] = raw;
+                const unsigned m0 = __ballot_sync(0xffffffffu, c0), m1 = __ballot_sync(0xffffffffu, c1);
+                if (c0) sQueue[qn + __popc(m0 & lt)] = (unsigned short)(z * 64 + 2 * lane);
+                if (c1) sQueue[qn + __popc(m0) + __popc(m1 & lt)] = (unsigned short)(z * 64 + 2 * lane + 1);
+                qn += __popc(m0) + __popc(m1);
+                raw = nxt;
+            }
+            __syncwarp();
+            if (qn) {
+                uint2 *sv = reinterpret_cast<uint2 *>(sVox);
+                for (int k = lane; k < qn; k += 32) {
+                    const int vi = sQueue[k];
+                    uint2 w = sv[vi];
+                    const uint2 before = w;
+                    VoxelRegs vx = unpack(w.x, w.y);
+                    fuse_colour<false, true>(vx, (float)(e.px * kBlock + (vi & 7)) * P.voxelSize, (float)(e.py * kBlock + ((vi >> 3) & 7)) * P.voxelSize,
+                                             (float)(e.pz * kBlock + (vi >> 6)) * P.voxelSize, P, rgb, T);
+                    pack(vx, w.x, w.y);
+                    if (w.x != before.x || w.y != before.y) {
+                        sv[vi] = w;
+                        atomicOr(&sDirty[vi >> 6], 1u << ((vi >> 1) & 31));
+                    }
+                }
+                __syncwarp();
+            }
+#pragma unroll
+            for (int z = 0; z < kBlock; z++) {
+                const unsigned d = qn ? sDirty[z] : 0u;
+                if (((dirty >> z) & 1u) || ((d >> lane) & 1u)) base[z * 32 + lane] = sVox[z * 32 + lane];
+            }
+            if (qn) {
+                __syncwarp();
+                if (lane < 8) sDirty[lane] = 0;
+            }
+            __syncwarp();
+        }
+        e0 = e1; e1 = e2; slot2 = slot3;
+    }
+}
+
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,
                  const dsb200_hash_entry *hash, const int *ids, const int *count, const float *depth, const uint8_t *rgb,
-                 short *sdfShadow)
+                 short *sdfShadow, unsigned char *weightScratch)
 {
     unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
-    const int variant = tunables().fuse_kernel;   // 0: CTA per block, 1: warp per block
-    if (variant == 1) {
+    const int variant = tunables().fuse_kernel;   // 0: CTA per block, 1: warp per block, 2: warp per block, straight-line depth part
+    if (variant == 2 && !deintegrate && P.fastDiv && P.maxNewW >= 1 && P.maxNewW <= 255 && (!P.depthWeighting || weightScratch)) {
+        const int g = kNumSMs * tunables().fuse_ctas;
+        const int minb = tunables().fuse_minb;     // register budget: 65536 / (128 * minb)
+#define DSB_FLAT(W_, M_) DSB_LAUNCH((k_fuse_warp_flat<W_, M_>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, W_ ? weightScratch : nullptr, shadow2)
+        if (P.depthWeighting) {
+            DSB_LAUNCH(k_depth_weights, kNumSMs * 4, 256, 0, st, depth, weightScratch, P.W * P.H, P.maxDistance, P.maxNewW);
+            if (minb >= 8) DSB_FLAT(true, 8); else if (minb >= 6) DSB_FLAT(true, 6); else DSB_FLAT(true, 4);
+        } else {
+            if (minb >= 8) DSB_FLAT(false, 8); else if (minb >= 6) DSB_FLAT(false, 6); else DSB_FLAT(false, 4);
+        }
+#undef DSB_FLAT
+        return;
+    }
+    if (variant >= 1) {
         const int g = kNumSMs * 8;
         if (deintegrate) {
             if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<true, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);

@@ -400,16 +400,31 @@ def gpu_block_table(gpu, voxels=True):
 
 
 class SetTracker(object):
-    """Follows two engines frame by frame.  A block is COMPARABLE when both engines allocated it in the same frame (its
-    `birth`): the reference CUDA allocator resolves same-frame bucket collisions by a race (CUDA .cu:1521-1531 writes
-    entriesAllocType / blockCoords last-writer-wins; the loser is picked up a frame later, DeviceAgnostic/
-    ITMSceneReconstructionEngine.h:483), the serial CPU engine by scan order, so a few blocks are born a frame apart and have
-    seen one observation less; and its deleteBlock skips a deletion when two blocks of one bucket die in the same launch
-    (try-lock, CUDA .cu:510-515).  Those blocks are counted, bounded, and left out of the payload comparison."""
+    """Follows two engines frame by frame and decides which blocks are COMPARABLE voxel by voxel:
+      * both engines allocated the block in the same frame (its `birth`): the reference CUDA allocator resolves same-frame bucket
+        collisions by a race (CUDA .cu:1521-1531 writes entriesAllocType / blockCoords last-writer-wins; the loser is picked up a
+        frame later, DeviceAgnostic/ITMSceneReconstructionEngine.h:483), the serial CPU engine by scan order, so a few blocks are
+        born a frame apart and have seen one observation less;
+      * the block never shared its hash bucket with another live block (`chained`): which slot of the excess list a chain member
+        gets, and which member moves up when the head is deleted (deleteBlock, CUDA .cu:568-586), depend on the order the
+        reference's atomics happened to run in; history snapshots hold SLOT ids, so a pruning pass aimed at a slot reaches whichever
+        block lives there at that time -- chain members can be pruned a pass earlier or later than in the serial order;
+      * the reference's deleteBlock skips a deletion when two blocks of one bucket die in the same launch (try-lock, .cu:510-515).
+    Blocks outside these conditions are counted and bounded, not compared."""
 
-    def __init__(self):
+    def __init__(self, bucket_mask=abi.DEFAULT_BUCKETS - 1):
         self.birth = [dict(), dict()]
+        self.chained = set()
         self.frame = 0
+        self.mask = bucket_mask
+
+    def _buckets(self, keys):
+        k = keys.astype(np.int64)
+        x = ((k >> 32) & 0xffff) - 32768
+        y = ((k >> 16) & 0xffff) - 32768
+        z = (k & 0xffff) - 32768
+        h = ((x.astype(np.uint32) * np.uint32(73856093)) ^ (y.astype(np.uint32) * np.uint32(19349669)) ^ (z.astype(np.uint32) * np.uint32(83492791)))
+        return (h & np.uint32(self.mask)).astype(np.int64)
 
     def update(self, ta, tb):
         for side, t in enumerate((ta, tb)):
@@ -421,26 +436,41 @@ class SetTracker(object):
             for k in now:
                 if k not in b:
                     b[k] = self.frame
+        union = np.union1d(ta["keys"], tb["keys"])
+        alive = set(union.tolist())
+        self.chained &= alive                       # a block that died in both engines starts afresh
+        if union.size:
+            bk = self._buckets(union)
+            order = np.argsort(bk, kind="stable")
+            sb = bk[order]
+            dup = np.zeros(sb.size, bool)
+            dup[1:] |= sb[1:] == sb[:-1]
+            dup[:-1] |= sb[1:] == sb[:-1]
+            self.chained |= set(union[order][dup].tolist())
         self.frame += 1
 
     def comparable(self, keys):
         a, b = self.birth
-        return np.array([(k in a and k in b and a[k] == b[k]) for k in keys.tolist()], bool)
+        return np.array([(k in a and k in b and a[k] == b[k] and k not in self.chained) for k in keys.tolist()], bool)
 
 
-def assert_sets_match(tracker, ours, ref, what, max_odd_fraction=0.01, voxels=True):
+def assert_sets_match(tracker, ours, ref, what, max_odd_fraction=0.03, voxels=True):
     """ours / ref: block tables taken after the same call sequence.  Returns the number of non-comparable blocks."""
     tracker.update(ours, ref)
     both = np.intersect1d(ours["keys"], ref["keys"])
     union = np.union1d(ours["keys"], ref["keys"])
     ok = tracker.comparable(both)
     odd = union.size - int(ok.sum()) + ref["duplicates"]
-    assert odd <= max(4, max_odd_fraction * union.size), "%s: %d of %d blocks not comparable (only ours %d, only reference %d)" % (
+    only = np.setdiff1d(ours["keys"], ref["keys"]).size + np.setdiff1d(ref["keys"], ours["keys"]).size
+    assert odd <= max(8, max_odd_fraction * union.size), "%s: %d of %d blocks not comparable (only ours %d, only reference %d)" % (
         what, odd, union.size, np.setdiff1d(ours["keys"], ref["keys"]).size, np.setdiff1d(ref["keys"], ours["keys"]).size)
-    # free-list accounting: allocated + free == capacity in both engines
-    for t, name in ((ours, "ours"), (ref, "reference")):
-        assert t["allocated"] + t["free_blocks"] == t["num_blocks"], "%s: %s leaks voxel blocks (%d allocated + %d free != %d)" % (
-            what, name, t["allocated"], t["free_blocks"], t["num_blocks"])
+    assert only <= max(8, 0.005 * union.size), "%s: the block sets differ in %d of %d blocks" % (what, only, union.size)
+    # free-list accounting: allocated + free == capacity.  Exact for ours; the reference may double-free a block when a torn
+    # coordinate write left it with two entries for one coordinate (see make_block_table): bounded, reported
+    assert ours["allocated"] + ours["free_blocks"] == ours["num_blocks"], "%s: ours leaks voxel blocks (%d allocated + %d free != %d)" % (
+        what, ours["allocated"], ours["free_blocks"], ours["num_blocks"])
+    ref_leak = ref["allocated"] + ref["free_blocks"] - ref["num_blocks"]
+    assert abs(ref_leak) <= 8, "%s: reference free-list accounting off by %d" % (what, ref_leak)
     # visible SET (the reference's list order is schedule-dependent)
     vdiff = np.setxor1d(ours["visible_keys"], ref["visible_keys"])
     assert vdiff.size <= odd + ours["visible_dead"] + ref["visible_dead"], "%s: visible sets differ in %d blocks (%d non-comparable)" % (what, vdiff.size, odd)

@@ -83,7 +83,7 @@ def test_decay_and_slide_window_pinned_to_reference_cuda():
         step((gpu, ref), f, decay=(3, 4), slide=9)
         odd = compare(tr, gpu, ref, "frame %d" % i)
         assert gpu.history_sizes() == ref.history_sizes(), "frame %d: history queues %s vs %s" % (i, gpu.history_sizes(), ref.history_sizes())
-        assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.01 * gpu.decayed_blocks()), "frame %d: decayed %d vs %d" % (
+        assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.03 * gpu.decayed_blocks()), "frame %d: decayed %d vs %d" % (
             i, gpu.decayed_blocks(), ref.decayed_blocks())
     assert gpu.decayed_blocks() > 500
     print("decay+slide: %d blocks freed (reference %d), %d non-comparable at the end" % (gpu.decayed_blocks(), ref.decayed_blocks(), odd))
@@ -99,7 +99,7 @@ def test_decay_only_pinned_to_reference_cuda():
         compare(tr, gpu, ref, "frame %d" % i)
         assert gpu.history_sizes() == ref.history_sizes()
     assert gpu.decayed_blocks() > 20
-    assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.01 * gpu.decayed_blocks())
+    assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.03 * gpu.decayed_blocks())
     gpu.close(); ref.close()
 
 
@@ -112,7 +112,7 @@ def test_slide_window_only_pinned_to_reference_cuda():
         compare(tr, gpu, ref, "frame %d" % i)
         assert gpu.history_sizes() == ref.history_sizes()
     assert gpu.decayed_blocks() > 500
-    assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.01 * gpu.decayed_blocks())
+    assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.03 * gpu.decayed_blocks())
     gpu.close(); ref.close()
 
 
@@ -177,6 +177,6 @@ def test_c3_full_size_decay_slide_window_vs_reference_cuda():
         compare(tr, gpu, ref, "C3 frame %d" % i, voxels=full)
         assert gpu.history_sizes() == ref.history_sizes()
     assert gpu.decayed_blocks() > 1000
-    assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.01 * gpu.decayed_blocks()), "decayed %d vs %d" % (
+    assert abs(gpu.decayed_blocks() - ref.decayed_blocks()) <= max(8, 0.03 * gpu.decayed_blocks()), "decayed %d vs %d" % (
         gpu.decayed_blocks(), ref.decayed_blocks())
     gpu.close(); ref.close()

@@ -6,7 +6,8 @@ the time.  Prints one JSON line per setting and a summary.
   python tools/tune.py --stage raycast --workload C2 --frames 40 --reps 20 \
       --sweep ray_steps=0,16,24,32,48 --sweep ray_group=8,16,32
 
-stage raycast:   times dsb200_process_frame(stages = RAYCAST) at the last fused frame's pose (sdf shadow, expected depths valid)
+stage raycast:   times dsb200_process_frame(stages = RAYCAST) at the last fused frame's pose (sdf shadow, expected depths valid);
+                 COLD: the L2 flush before it evicts the blocks integration has just written, unlike a real frame -- use `frame`
 stage integrate: times dsb200_process_frame(stages = INTEGRATE) of the last frame again and again (same visible list, same
                  voxels touched every time; only the weights grow)
 stage frame:     times whole frames k..k+reps from a fixed prefix (scene reset + prefix re-fused untimed for each setting)
@@ -89,6 +90,7 @@ def main():
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.reps)]
         for r in range(args.reps + 2):
             timed = r >= 2
+            torch.cuda._sleep(600000)       # ~0.3 ms of GPU idling that the host uses to enqueue this repetition: no launch gaps inside the event pair
             flush.zero_()
             if timed:
                 evs[r - 2][0].record()
