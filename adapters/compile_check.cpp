@@ -6,6 +6,7 @@
 #include "ITMDepthTracker_B200.h"
 #include "ITMViewBuilder_B200.h"
 #include "ITMSwappingEngine_B200.h"
+#include "ITMMeshingEngine_B200.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
 
 using namespace ITMLib::Engine;
@@ -13,6 +14,7 @@ using namespace ITMLib::Engine;
 template class ITMLib::Engine::ITMSceneReconstructionEngine_B200<ITMVoxel, ITMVoxelIndex>;
 template class ITMLib::Engine::ITMVisualisationEngine_B200<ITMVoxel, ITMVoxelIndex>;
 template class ITMLib::Engine::ITMSwappingEngine_B200<ITMVoxel, ITMVoxelIndex>;
+template class ITMLib::Engine::ITMMeshingEngine_B200<ITMVoxel, ITMVoxelIndex>;
 
 static_assert(sizeof(ITMVoxel) == 8, "ITMVoxel_s_rgb");
 static_assert(sizeof(ITMHashEntry) == 20, "ITMHashEntry");
@@ -38,3 +40,5 @@ ITMViewBuilder *make_view_builder(const ITMRGBDCalib *calib) { return new ITMVie
 // ITMDenseMapper.cpp:20-33 with deviceType == DEVICE_B200 and settings->useSwapping
 ITMSwappingEngine<ITMVoxel, ITMVoxelIndex> *make_swapping() { return new ITMSwappingEngine_B200<ITMVoxel, ITMVoxelIndex>(); }
 static_assert(SDF_TRANSFER_BLOCK_NUM == DSB200_DEFAULT_TRANSFER_BLOCKS && sizeof(ITMHashSwapState) == 1, "swapping constants");
+// ITMMainEngine.cpp:57-81 with deviceType == DEVICE_B200 (meshingEngine)
+ITMMeshingEngine<ITMVoxel, ITMVoxelIndex> *make_mesher() { return new ITMMeshingEngine_B200<ITMVoxel, ITMVoxelIndex>(); }

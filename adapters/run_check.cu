@@ -21,9 +21,11 @@
 #include "ITMSceneReconstructionEngine_B200.h"
 #include "ITMVisualisationEngine_B200.h"
 #include "ITMViewBuilder_B200.h"
+#include "ITMMeshingEngine_B200.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMViewBuilder_CPU.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMMeshingEngine_CPU.h"
 
 using namespace ITMLib::Engine;
 using namespace ITMLib::Objects;
@@ -196,6 +198,20 @@ int main(int argc, char **argv)
         EXPECT(vg->mTimeStamp == 1.5, "view builder: timestamp");
         printf("view builder: UpdateView -- CPU builder == B200 adapter\n");
         delete vc; delete vg;
+    }
+
+    // meshing (ITMMainEngine::SaveSceneToMesh path): ITMMesh on the device through the adapter vs ITMMeshingEngine_CPU
+    {
+        ITMMesh *mc = new ITMMesh(MEMORYDEVICE_CPU), *mg = new ITMMesh(MEMORYDEVICE_CUDA);
+        ITMMeshingEngine_CPU<ITMVoxel, ITMVoxelBlockHash> meshCpu; ITMMeshingEngine_B200<ITMVoxel, ITMVoxelBlockHash> meshGpu;
+        meshCpu.MeshScene(mc, cpu.scene);
+        meshGpu.MeshScene(mg, gpu.scene);
+        EXPECT(mc->noTotalTriangles == mg->noTotalTriangles && mc->noTotalTriangles > 100, "meshing: %u vs %u triangles", mc->noTotalTriangles, mg->noTotalTriangles);
+        std::vector<ITMMesh::Triangle> a = pull(mc->triangles->GetData(MEMORYDEVICE_CPU), mc->noTotalTriangles, false),
+                                       b = pull(mg->triangles->GetData(MEMORYDEVICE_CUDA), mc->noTotalTriangles, true);
+        EXPECT(memcmp(a.data(), b.data(), a.size() * sizeof(ITMMesh::Triangle)) == 0, "meshing: triangles differ");
+        printf("meshing: %u triangles -- ITMMeshingEngine_CPU == B200 adapter\n", mg->noTotalTriangles);
+        delete mc; delete mg;
     }
 
     // pruning entry points execute through the adapter and keep the host mirrors valid (the CPU engine throws for these)

@@ -580,7 +580,7 @@ def measure_workload(args, rank, world, local_rank, full):
     out["roofline"]["integrate_plus_raycast"] = {"algorithmic_bytes": alg[1] + alg[3], "ms": float(ir_ms),
                                                  "achieved": (alg[1] + alg[3]) / (ir_ms * 1e-3) / 1e9,
                                                  "frac": (alg[1] + alg[3]) / (ir_ms * 1e-3) / 1e9 / pk["hbm_gbs"]}
-    if world == 1 and full:
+    if world == 1 and full and not args.no_baselines:
         out["gpu_comparator"] = time_reference_cuda(frames, cfg, d_depth, d_rgb, Wm, min(K, REF_MAX_FRAMES), flush)
         if "value" in out["gpu_comparator"]:
             out["gpu_comparator"]["ours_over_reference_cuda"] = out["value"] / out["gpu_comparator"]["value"]
@@ -848,6 +848,7 @@ def main():
     ap.add_argument("--brick-log2", type=int, default=2)
     ap.add_argument("--no-lookahead", action="store_true",
                     help="do not overlap the next frame's allocation request pass with the current frame's raycast")
+    ap.add_argument("--no-baselines", action="store_true", help="skip the gpu_comparator and cpu_baseline legs (tuning runs)")
     ap.add_argument("--single-workload", action="store_true",
                     help="N = 1: report only --workload (skip the `workloads` sub-objects for the other single-GPU configs)")
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS.keys()),

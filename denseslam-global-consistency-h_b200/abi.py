@@ -34,7 +34,9 @@ MAX_SHARDS = 16
 HASH_DTYPE = np.dtype([("pos", "<i2", (3,)), ("pad", "<i2"), ("offset", "<i4"), ("ptr", "<i4"),
                        ("allocated_time", "<i4")])
 VOXEL_DTYPE = np.dtype([("sdf", "<i2"), ("w_depth", "u1"), ("clr", "u1", (3,)), ("w_color", "u1"), ("pad", "u1")])
-assert HASH_DTYPE.itemsize == 20 and VOXEL_DTYPE.itemsize == 8
+TRIANGLE_DTYPE = np.dtype([("p0", "<f4", (3,)), ("p1", "<f4", (3,)), ("p2", "<f4", (3,)), ("c0", "<f4", (3,)), ("c1", "<f4", (3,)),
+                           ("c2", "<f4", (3,))])       # ITMMesh::Triangle (Objects/ITMMesh.h:21-24)
+assert HASH_DTYPE.itemsize == 20 and VOXEL_DTYPE.itemsize == 8 and TRIANGLE_DTYPE.itemsize == 72
 
 
 class SceneParams(C.Structure):
@@ -220,6 +222,9 @@ def load():
         "dsb200_selftest_division": (C.c_int, [C.c_ulonglong, C.c_ulonglong, _P(C.c_ulonglong)]),
         "dsb200_selftest_expf": (C.c_int, [vp, vp, i32]),
         "dsb200_selftest_acosf": (C.c_int, [vp, vp, i32]),
+        "dsb200_mesher_create": (C.c_int, [_P(vp), i32, vp]),
+        "dsb200_mesher_destroy": (C.c_int, [vp]),
+        "dsb200_mesh_scene": (C.c_int, [vp, _P(Scene), vp, C.c_uint32, _P(C.c_uint32)]),
         "dsb200_kernel_launch_count": (C.c_ulonglong, []),
     }
     for name, (res, args) in sig.items():

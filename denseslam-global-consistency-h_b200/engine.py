@@ -512,3 +512,28 @@ def pose_from_params(params):
     m = (C.c_float * 16)()
     abi.check(_lib().dsb200_pose_from_params((C.c_float * 6)(*[float(x) for x in params]), m))
     return np.array(m[:], np.float32)
+
+
+class ITMMeshingEngine(object):
+    """ITMMeshingEngine<ITMVoxel,ITMVoxelBlockHash> (ITMLib/Engine/ITMMeshingEngine.h:19-26): marching cubes over the allocated
+    blocks, triangles in the CPU engine's order."""
+
+    def __init__(self, num_blocks=abi.DEFAULT_LOCAL_BLOCKS, stream=None):
+        self.h = C.c_void_p()
+        abi.check(_lib().dsb200_mesher_create(C.byref(self.h), num_blocks, stream))
+
+    def close(self):
+        if self.h:
+            _lib().dsb200_mesher_destroy(self.h)
+            self.h = None
+
+    def MeshScene(self, scene, max_triangles):
+        """-> (triangles[:n + 1] as abi.TRIANGLE_DTYPE (the slot past the count holds the overflow triangle when capped), n)"""
+        buf = DeviceBuffer(max_triangles * abi.TRIANGLE_DTYPE.itemsize)
+        n = C.c_uint32()
+        try:
+            abi.check(_lib().dsb200_mesh_scene(self.h, C.byref(scene.c), buf.ptr, max_triangles, C.byref(n)))
+            out = buf.download(abi.TRIANGLE_DTYPE, min(n.value + 1, max_triangles))
+        finally:
+            buf.free()
+        return out, int(n.value)

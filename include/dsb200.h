@@ -480,6 +480,21 @@ int dsb200_selftest_expf(const float *x, float *y, int32_t n);
 /* the sensor-noise model's acos (csrc/view_filter.cu, a restatement of glibc's fdlibm acosf) on n HOST floats */
 int dsb200_selftest_acosf(const float *x, float *y, int32_t n);
 
+/* ---- meshing: ITMMeshingEngine<ITMVoxel,ITMVoxelBlockHash>::MeshScene, ITMLib/Engine/ITMMeshingEngine.h:19-26;
+ * CPU ITMLib/Engine/DeviceSpecific/CPU/ITMMeshingEngine_CPU.cpp:20-83, CUDA .../CUDA/ITMMeshingEngine_CUDA.cu:60-195; math in
+ * ITMLib/Engine/DeviceAgnostic/ITMMeshingEngine.h (buildVertList, sdfInterp) and ITMRepresentationAccess.h:699-736 (vertex colours).
+ * Marching cubes over every allocated block: triangles in the CPU engine's order -- hash slot ascending, voxel z / y / x,
+ * table order -- (the reference CUDA engine appends with atomicAdd, i.e. in schedule order), vertices in metres, per-vertex
+ * colours in [0, 1].  `triangles` is DEVICE memory for max_triangles records (ITMMesh::Triangle layout, 72 bytes; the reference
+ * sizes it SDF_LOCAL_BLOCK_NUM * 64); the CPU engine's cap rule is kept: once max_triangles - 1 are stored every further
+ * triangle overwrites the last slot.  *no_triangles = ITMMesh::noTotalTriangles.  Synchronous. */
+typedef struct dsb200_triangle { float p0[3], p1[3], p2[3], c0[3], c1[3], c2[3]; } dsb200_triangle;
+typedef struct dsb200_mesher dsb200_mesher;
+int dsb200_mesher_create(dsb200_mesher **out, int32_t num_blocks, void *stream);
+int dsb200_mesher_destroy(dsb200_mesher *m);
+int dsb200_mesh_scene(dsb200_mesher *m, const dsb200_scene *scene, dsb200_triangle *triangles, uint32_t max_triangles,
+                      uint32_t *no_triangles);
+
 /* counters for bench.py: kernels launched by this library since process start */
 unsigned long long dsb200_kernel_launch_count(void);
 

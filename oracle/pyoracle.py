@@ -138,6 +138,9 @@ class Oracle(object):
         L.rst_raycast_sharded.argtypes = [C.c_int, P(vp), P(vp), C.c_int, fp, fp, C.c_int, C.c_int, vp, vp]
         L.rst_composite_nearest.argtypes = [C.c_int, P(vp), fp, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]
         L.rst_icp_maps_from_raycast.argtypes = [P(abi.Scene), P(abi.View), P(abi.Tracking), vp, vp, C.c_int, C.c_int]
+        L.rst_mesh_scene.restype = C.c_uint
+        L.rst_mesh_scene.argtypes = [P(abi.Scene), vp, C.c_uint]
+        L.rst_mc_tables.argtypes = [vp, vp]
         L.rst_mat4_inverse.restype = C.c_int
         L.rst_mat4_inverse.argtypes = [fp, fp]
         L.rst_mat4_multiply.argtypes = [fp, fp, fp]
@@ -220,6 +223,17 @@ class Oracle(object):
         """ComputeGandH restated -> (noValidPoints, f, nabla[6], hessian[36], sums[32])"""
         return _gh_call(self.L.rst_tracker_compute_g_and_h, depth, view_intr, points, normals, scene_intr, scene_pose,
                         approx_inv_pose, dist_thresh, iteration_type, 1 if double_sums else 0)
+
+    def mesh_scene(self, scene, max_triangles):
+        """ITMMeshingEngine_CPU::MeshScene restated -> (triangles[:n + 1] as TRIANGLE_DTYPE, n)"""
+        buf = np.zeros(max_triangles, abi.TRIANGLE_DTYPE)
+        n = int(self.L.rst_mesh_scene(C.byref(scene.c), ptr(buf), max_triangles))
+        return buf[:min(n + 1, max_triangles)].copy(), n
+
+    def mc_tables(self):
+        edge, tri = np.zeros(256, np.int32), np.zeros((256, 16), np.int32)
+        self.L.rst_mc_tables(ptr(edge), ptr(tri))
+        return edge, tri
 
     def mat4_inverse(self, M):
         out = (C.c_float * 16)()
@@ -379,6 +393,21 @@ class RefEngine(object):
         o = np.zeros(16, np.float32)
         self.L.itmref_mat4_mul(ptr(a), ptr(b), ptr(o))
         return o
+
+    def mesh_scene(self, max_out):
+        """ITMMeshingEngine_CPU::MeshScene on this context's scene -> (triangles[:n + 1], n)"""
+        self.L.itmref_mesh_scene.restype = C.c_uint
+        self.L.itmref_mesh_scene.argtypes = [C.c_void_p, C.c_void_p, C.c_uint]
+        assert self.L.itmref_sizeof_triangle() == abi.TRIANGLE_DTYPE.itemsize
+        buf = np.zeros(max_out, abi.TRIANGLE_DTYPE)
+        n = int(self.L.itmref_mesh_scene(self.h, ptr(buf), max_out))
+        return buf[:min(n + 1, max_out)].copy(), n
+
+    def mc_tables(self):
+        edge, tri = np.zeros(256, np.int32), np.zeros((256, 16), np.int32)
+        self.L.itmref_mc_tables.argtypes = [C.c_void_p, C.c_void_p]
+        self.L.itmref_mc_tables(ptr(edge), ptr(tri))
+        return edge, tri
 
     def swap_integrate_global_into_local(self):
         self.L.itmref_swap_integrate_global_into_local(self.h)

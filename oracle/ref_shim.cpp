@@ -13,6 +13,8 @@
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMVisualisationEngine_CPU.cpp:27-180,296-459
 //   ITMSwappingEngine_CPU<ITMVoxel,ITMVoxelBlockHash> on the scene's ITMGlobalCache
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMSwappingEngine_CPU.cpp:22-297, Objects/ITMGlobalCache.h
+//   ITMMeshingEngine_CPU<ITMVoxel,ITMVoxelBlockHash>
+//       ITMLib/Engine/DeviceSpecific/CPU/ITMMeshingEngine_CPU.cpp:20-83
 //   ITMDepthTracker_CPU (+ the shared host loop ITMLib/Engine/ITMDepthTracker.cpp) and ITMLowLevelEngine_CPU
 //       ITMLib/Engine/DeviceSpecific/CPU/ITMDepthTracker_CPU.cpp:13-79, CPU/ITMLowLevelEngine_CPU.cpp:50-62
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMSceneReconstructionEngine_CPU.h"
@@ -22,6 +24,8 @@
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMDepthTracker_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMLowLevelEngine_CPU.h"
 #include "ITMLib/Engine/DeviceSpecific/CPU/ITMSwappingEngine_CPU.h"
+#include "ITMLib/Engine/DeviceSpecific/CPU/ITMMeshingEngine_CPU.h"
+#include "ITMLib/Engine/DeviceAgnostic/ITMMeshingEngine.h"   // edgeTable / triangleTable (static const: this TU gets its own copy)
 
 #include <cstring>
 #include <cstdint>
@@ -330,3 +334,28 @@ void itmref_track_camera(void *h, int levels, const int *regime, int noICPRunTil
 }
 
 } // extern "C"
+
+
+// ---- meshing: ITMMeshingEngine_CPU::MeshScene on the context's scene.  out: room for maxOut ITMMesh::Triangle records
+// (72 bytes each); returns noTotalTriangles (the reference's own buffer holds SDF_LOCAL_BLOCK_NUM * 64 of them).
+extern "C" {
+int itmref_sizeof_triangle() { return (int)sizeof(ITMMesh::Triangle); }
+unsigned itmref_max_triangles() { return ITMMesh::noMaxTriangles; }
+unsigned itmref_mesh_scene(void *h, void *out, unsigned maxOut)
+{
+    RefCtx *c = (RefCtx *)h;
+    ITMMesh *mesh = new ITMMesh(MEMORYDEVICE_CPU);
+    ITMMeshingEngine_CPU<ITMVoxel, ITMVoxelBlockHash> mesher;
+    mesher.MeshScene(mesh, c->scene);
+    unsigned n = mesh->noTotalTriangles;
+    unsigned copy = n + 1 < maxOut ? n + 1 : maxOut;      // + the slot past the count (holds the overflow triangle when capped)
+    memcpy(out, mesh->triangles->GetData(MEMORYDEVICE_CPU), sizeof(ITMMesh::Triangle) * (size_t)copy);
+    delete mesh;
+    return n;
+}
+// the reference's marching-cubes tables as compiled into its mesher (for tests/test_meshing.py)
+void itmref_mc_tables(int *edge, int *tri)
+{
+    for (int i = 0; i < 256; i++) { edge[i] = edgeTable[i]; for (int k = 0; k < 16; k++) tri[i * 16 + k] = triangleTable[i][k]; }
+}
+}

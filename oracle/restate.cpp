@@ -1710,3 +1710,96 @@ int rst_swap_save_to_global_memory(dsb200_swap_cache *cache, dsb200_scene *scene
 }
 
 } // extern "C"
+
+
+// ================================================================ meshing
+// ITMMeshingEngine_CPU<TVoxel,ITMVoxelBlockHash>::MeshScene, CPU/ITMMeshingEngine_CPU.cpp:20-83; buildVertList /
+// findPointNeighbors / sdfInterp, DeviceAgnostic/ITMMeshingEngine.h:90-160; vertex colours
+// readFromSDF_color4u_interpolated_noalpha, DeviceAgnostic/ITMRepresentationAccess.h:699-736.
+#include "../denseslam-global-consistency-h_b200/csrc/mc_tables.h"
+namespace {
+
+struct F3 { float x, y, z; };
+
+// sdfInterp :83-90
+inline F3 sdfInterp(F3 p1, F3 p2, float valp1, float valp2)
+{
+    if (fabsf(0.0f - valp1) < 0.00001f) return p1;
+    if (fabsf(0.0f - valp2) < 0.00001f) return p2;
+    if (fabsf(valp1 - valp2) < 0.00001f) return p1;
+    const float t = (0.0f - valp1) / (valp2 - valp1);
+    F3 r = {p1.x + t * (p2.x - p1.x), p1.y + t * (p2.y - p1.y), p1.z + t * (p2.z - p1.z)};
+    return r;
+}
+
+// cube corners in the order of findPointNeighbors :40-80
+const int kCorner[8][3] = {{0, 0, 0}, {1, 0, 0}, {1, 1, 0}, {0, 1, 0}, {0, 0, 1}, {1, 0, 1}, {1, 1, 1}, {0, 1, 1}};
+// cube edges (corner pairs) in the order of buildVertList :104-115
+const int kEdge[12][2] = {{0, 1}, {1, 2}, {2, 3}, {3, 0}, {4, 5}, {5, 6}, {6, 7}, {7, 4}, {0, 4}, {1, 5}, {2, 6}, {3, 7}};
+
+inline int buildVertList(F3 *vertList, const dsb200_scene *s, int gx, int gy, int gz)
+{
+    F3 pts[8]; float sdf[8];
+    for (int i = 0; i < 8; i++) {
+        const int x = gx + kCorner[i][0], y = gy + kCorner[i][1], z = gz + kCorner[i][2];
+        bool found;
+        pts[i].x = (float)x; pts[i].y = (float)y; pts[i].z = (float)z;
+        sdf[i] = sdfToFloat(readVoxelNC(s, x, y, z, found).sdf);
+        if (!found || sdf[i] == 1.0f) return -1;
+    }
+    int cube = 0;
+    for (int i = 0; i < 8; i++) if (sdf[i] < 0) cube |= 1 << i;
+    const unsigned edges = dsb::mc_edge_mask(dsb::kMcTrianglesHost[cube]);
+    if (edges == 0) return -1;
+    for (int e = 0; e < 12; e++)
+        if (edges & (1u << e)) vertList[e] = sdfInterp(pts[kEdge[e][0]], pts[kEdge[e][1]], sdf[kEdge[e][0]], sdf[kEdge[e][1]]);
+    return cube;
+}
+
+} // namespace
+
+extern "C" {
+
+void rst_mc_tables(int *edgeTable, int *triangleTable)
+{
+    for (int c = 0; c < 256; c++) {
+        const uint64_t w = dsb::kMcTrianglesHost[c];
+        edgeTable[c] = (int)dsb::mc_edge_mask(w);
+        for (int i = 0; i < 16; i++) { const int e = (int)((w >> (4 * i)) & 0xF); triangleTable[c * 16 + i] = e == 0xF ? -1 : e; }
+    }
+}
+
+unsigned rst_mesh_scene(const dsb200_scene *scene, dsb200_triangle *triangles, unsigned maxTriangles)
+{
+    const int total = scene->bucket_num + scene->excess_size;
+    const float factor = scene->params.voxel_size;
+    memset(triangles, 0, sizeof(dsb200_triangle) * (size_t)maxTriangles);      // mesh->triangles->Clear()
+    unsigned n = 0;
+    for (int entry = 0; entry < total; entry++) {
+        const dsb200_hash_entry &e = scene->hash[entry];
+        if (e.ptr < 0) continue;
+        const int gx = e.pos[0] * DSB200_BLOCK_SIZE, gy = e.pos[1] * DSB200_BLOCK_SIZE, gz = e.pos[2] * DSB200_BLOCK_SIZE;
+        for (int z = 0; z < DSB200_BLOCK_SIZE; z++) for (int y = 0; y < DSB200_BLOCK_SIZE; y++) for (int x = 0; x < DSB200_BLOCK_SIZE; x++) {
+            F3 v[12];
+            const int cube = buildVertList(v, scene, gx + x, gy + y, gz + z);
+            if (cube < 0) continue;
+            const uint64_t w = dsb::kMcTrianglesHost[cube];
+            for (int i = 0; i < 15 && ((w >> (4 * i)) & 0xF) != 0xF; i += 3) {
+                dsb200_triangle &t = triangles[n];
+                for (int k = 0; k < 3; k++) {
+                    const F3 p = v[(w >> (4 * (i + k))) & 0xF];
+                    float *dst = k == 0 ? t.p0 : (k == 1 ? t.p1 : t.p2), *col = k == 0 ? t.c0 : (k == 1 ? t.c1 : t.c2);
+                    dst[0] = p.x * factor; dst[1] = p.y * factor; dst[2] = p.z * factor;
+                    const float pv[3] = {p.x, p.y, p.z};
+                    float c4[4];
+                    colourTrilinear(scene, pv, c4);
+                    col[0] = c4[0]; col[1] = c4[1]; col[2] = c4[2];
+                }
+                if (n < maxTriangles - 1) n++;
+            }
+        }
+    }
+    return n;
+}
+
+} // extern "C"

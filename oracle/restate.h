@@ -94,6 +94,12 @@ void rst_track_camera(const dsb200_tracker_config *cfg, const dsb200_view *view,
 int rst_mat4_inverse(const float *M, float *out);
 void rst_mat4_multiply(const float *A, const float *B, float *out);
 
+/* ITMMeshingEngine_CPU::MeshScene (CPU/ITMMeshingEngine_CPU.cpp:20-83) on a host scene; returns noTotalTriangles.
+ * PINNED: tests/test_meshing.py compares it with the reference CPU mesher bit for bit. */
+unsigned rst_mesh_scene(const dsb200_scene *scene, dsb200_triangle *triangles, unsigned max_triangles);
+/* the marching-cubes tables the restatement uses, decoded (for the table tests) */
+void rst_mc_tables(int *edge_table_256, int *triangle_table_256x16);
+
 #ifdef __cplusplus
 }
 #endif
