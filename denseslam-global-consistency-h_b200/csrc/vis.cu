@@ -301,8 +301,8 @@ __device__ __forceinline__ const short *resolve_block(const Tables &T, int bucke
 // IndexCache; next to a block face the corners alternate between two (up to eight) blocks and every read re-probes the
 // hash table -- on the GPU that is up to 16 dependent memory round trips for one sample (measured: ~6 us per march step).
 // Here the up-to-8 distinct blocks of the 2x2x2 neighbourhood are resolved once each (only the ones the sample really
-// crosses into: 1, 3 or 7 neighbours, in ONE loop in which every lane probes for its next needed neighbour, so that the lanes
-// of a warp run the hash probe together instead of through seven conditional call sites), then the 8 voxels are loaded together.  Same voxels, same arithmetic, same result; a missing block reads as
+// crosses into), then the 8 voxels are loaded together.  (Resolving the 1, 3 or 7 neighbours in one loop over the needed set,
+// so that the lanes of a warp probe together, measured 3.4x SLOWER on B200 -- profiles/README.md r02d -- and was dropped.)  Same voxels, same arithmetic, same result; a missing block reads as
 // the reference's default voxel (sdf 32767).
 template <class Tables>
 __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, int bucketMask, float x, float y, float z, bool &found,
@@ -323,27 +323,14 @@ __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, i
     // The neighbour blocks the sample crosses into: c = dx | dy << 1 | dz << 2 with every set axis a crossing axis, i.e. 0, 1, 3
     // or 7 blocks.  They are resolved in ONE loop (lane by lane its next needed neighbour) instead of seven conditional call
     // sites: the lanes of a warp then run the hash probe together, whichever neighbour each of them is after.
-    const unsigned cross = (ex ? 1u : 0u) | (ey ? 2u : 0u) | (ez ? 4u : 0u);
-    const short *q1 = nullptr, *q2 = nullptr, *q3 = nullptr, *q4 = nullptr, *q5 = nullptr, *q6 = nullptr, *q7 = nullptr;
-    if (cross) {
-        unsigned need = 0;                                               // the non-empty subsets of `cross`
-#pragma unroll
-        for (unsigned c = 1; c < 8; c++) if ((c & ~cross) == 0u) need |= 1u << c;
-        while (need) {
-            const unsigned c = __ffs(need) - 1;
-            need &= need - 1;
-            const short *r = resolve_block(T, bucketNum, bucketMask, bx + (int)(c & 1u), by + (int)((c >> 1) & 1u), bz + (int)(c >> 2));
-            q1 = (c == 1u) ? r : q1; q2 = (c == 2u) ? r : q2; q3 = (c == 3u) ? r : q3; q4 = (c == 4u) ? r : q4;
-            q5 = (c == 5u) ? r : q5; q6 = (c == 6u) ? r : q6; q7 = (c == 7u) ? r : q7;
-        }
-    }
-    const short *p100 = ex ? q1 : p000;
-    const short *p010 = ey ? q2 : p000;
-    const short *p001 = ez ? q4 : p000;
-    const short *p110 = (ex && ey) ? q3 : (ex ? p100 : p010);
-    const short *p101 = (ex && ez) ? q5 : (ex ? p100 : p001);
-    const short *p011 = (ey && ez) ? q6 : (ey ? p010 : p001);
-    const short *p111 = (ex && ey && ez) ? q7 : ((ex && ey) ? p110 : ((ex && ez) ? p101 : ((ey && ez) ? p011 : (ex ? p100 : (ey ? p010 : p001)))));
+    const short *p100 = ex ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz) : p000;
+    const short *p010 = ey ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz) : p000;
+    const short *p001 = ez ? resolve_block(T, bucketNum, bucketMask, bx, by, bz + 1) : p000;
+    const short *p110 = (ex && ey) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by + 1, bz) : (ex ? p100 : p010);
+    const short *p101 = (ex && ez) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz + 1) : (ex ? p100 : p001);
+    const short *p011 = (ey && ez) ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz + 1) : (ey ? p010 : p001);
+    const short *p111 = (ex && ey && ez) ? resolve_block(T, bucketNum, bucketMask, bx + 1, by + 1, bz + 1)
+                                                : ((ex && ey) ? p110 : ((ex && ez) ? p101 : ((ey && ez) ? p011 : (ex ? p100 : (ey ? p010 : p001)))));
     const int x1 = (lx + 1) & 7, y1 = ((ly + 1) & 7) << 3, z1 = ((lz + 1) & 7) << 6, y0 = ly << 3, z0 = lz << 6;
 #define DSB_CORNER(P, L) ((P) ? (float)__ldg((P) + (L) * Tables::kStride) : 32767.0f)
     const float v000 = DSB_CORNER(p000, lx + y0 + z0), v100 = DSB_CORNER(p100, x1 + y0 + z0);
@@ -915,7 +902,7 @@ static int env_int(const char *name, int dflt) { const char *v = getenv(name); r
 Tunables &tunables()
 {
     static Tunables t = {env_int("DSB200_RAY_STEPS", 24), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
-                         env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 1), env_int("DSB200_FUSE_CTAS", 8),
+                         env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 2), env_int("DSB200_FUSE_CTAS", 12),
                          env_int("DSB200_FUSE_MINB", 6)};
     return t;
 }

@@ -410,7 +410,8 @@ class SetTracker(object):
         reference's atomics happened to run in; history snapshots hold SLOT ids, so a pruning pass aimed at a slot reaches whichever
         block lives there at that time -- chain members can be pruned a pass earlier or later than in the serial order;
       * the reference's deleteBlock skips a deletion when two blocks of one bucket die in the same launch (try-lock, .cu:510-515).
-    Blocks outside these conditions are counted and bounded, not compared."""
+    Blocks born in different frames are counted and bounded, not compared; every other block is compared voxel by voxel, and a
+    difference is accepted only in a `chained` block (and only in a bounded number of them)."""
 
     def __init__(self, bucket_mask=abi.DEFAULT_BUCKETS - 1):
         self.birth = [dict(), dict()]
@@ -451,10 +452,13 @@ class SetTracker(object):
 
     def comparable(self, keys):
         a, b = self.birth
-        return np.array([(k in a and k in b and a[k] == b[k] and k not in self.chained) for k in keys.tolist()], bool)
+        return np.array([(k in a and k in b and a[k] == b[k]) for k in keys.tolist()], bool)
+
+    def is_chained(self, keys):
+        return np.array([k in self.chained for k in keys.tolist()], bool)
 
 
-def assert_sets_match(tracker, ours, ref, what, max_odd_fraction=0.12, voxels=True):
+def assert_sets_match(tracker, ours, ref, what, max_odd_fraction=0.03, voxels=True, max_chain_mismatch=0.01):
     """ours / ref: block tables taken after the same call sequence.  Returns the number of non-comparable blocks."""
     tracker.update(ours, ref)
     both = np.intersect1d(ours["keys"], ref["keys"])
@@ -478,13 +482,18 @@ def assert_sets_match(tracker, ours, ref, what, max_odd_fraction=0.12, voxels=Tr
         ia = np.searchsorted(ours["keys"], both[ok]); ib = np.searchsorted(ref["keys"], both[ok])
         va, vb = ours["voxels"][ia], ref["voxels"][ib]
         m = np.uint64(0x00ffffffffffffff)         # 8th byte = padding
-        ne = (va.view(np.uint64) & m) != (vb.view(np.uint64) & m)
-        if ne.any():
-            blk = np.nonzero(ne.reshape(len(ia), -1).any(axis=1))[0]
-            d = np.abs(va["sdf"].astype(np.int32) - vb["sdf"].astype(np.int32)).max()
-            raise AssertionError("%s: %d of %d comparable blocks differ in %d voxels (max |dsdf| %d LSB); first block key %d: %s vs %s" % (
-                what, blk.size, len(ia), int(ne.sum()), int(d), int(both[ok][blk[0]]),
-                va[blk[0]][ne.reshape(len(ia), -1)[blk[0]]][:3], vb[blk[0]][ne.reshape(len(ia), -1)[blk[0]]][:3]))
+        ne = ((va.view(np.uint64) & m) != (vb.view(np.uint64) & m)).reshape(len(ia), -1)
+        bad = ne.any(axis=1)
+        if bad.any():
+            chained = tracker.is_chained(both[ok])
+            loose = np.nonzero(bad & ~chained)[0]       # a differing block that never shared a bucket: a real disagreement
+            if loose.size or int(bad.sum()) > max(4, max_chain_mismatch * len(ia)):
+                blk = loose if loose.size else np.nonzero(bad)[0]
+                d = np.abs(va["sdf"].astype(np.int32) - vb["sdf"].astype(np.int32)).max()
+                raise AssertionError("%s: %d of %d comparable blocks differ (%d of them outside collision chains), %d voxels, max |dsdf| %d LSB; "
+                                     "first block key %d: %s vs %s" % (what, int(bad.sum()), len(ia), loose.size, int(ne.sum()), int(d),
+                                                                       int(both[ok][blk[0]]), va[blk[0]][ne[blk[0]]][:3], vb[blk[0]][ne[blk[0]]][:3]))
+            tracker.chain_mismatches = max(getattr(tracker, "chain_mismatches", 0), int(bad.sum()))
     return odd
 
 
