@@ -94,8 +94,13 @@ class ClockSampler(object):
         mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows if len(r) >= 9 for i in range(4) if r[5 + i].lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+               "samples": len(sm)}
+        gpus = sorted({r[0] for r in self.rows if len(r) >= 9})
+        if len(gpus) > 1:      # one record per GPU of the job
+            out["per_gpu"] = {g: {"sm_mhz": float(np.median([float(r[1]) for r in self.rows if len(r) >= 9 and r[0] == g and r[1].replace(".", "").isdigit()] or [0])),
+                                  "samples": sum(1 for r in self.rows if len(r) >= 9 and r[0] == g)} for g in gpus}
+        return out
 
 
 def ncu_traffic(stage):
@@ -262,6 +267,17 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     out = measure_workload(args, rank, world, local_rank, full=True)
+    if not args.no_sharded:
+        # BASELINE configs[3] next to the replicas line: ONE ~4 M-block scene sharded over the N GPUs (N = 1: the whole map on
+        # one GPU, the denominator of the driver's scaling curve), fast mode and exact mode
+        init_group(world, dev)
+        sh = {}
+        for mode in ("composite", "lookup"):
+            r = measure_sharded(args, rank, world, local_rank, mode)
+            if r is not None:
+                sh[mode] = r
+        if out is not None:
+            out["sharded"] = sh
     if world == 1 and out is not None and not args.single_workload:
         main_wl, main_caps, main_metric = WORKLOAD, CAPS, METRIC
         out["workloads"] = {}
@@ -274,7 +290,7 @@ def run_ours(args, rank, world, local_rank):
                                                         "stages", "parity_check", "gpu_launches", "config", "prune_ms_per_frame",
                                                         "decayed_blocks") if k in sub}
         WORKLOAD, CAPS, METRIC = main_wl, main_caps, main_metric
-    if world > 1:
+    if dist.is_initialized():
         dist.destroy_process_group()
     return out
 
@@ -767,34 +783,51 @@ def run_tracked(args, rank, world, local_rank):
 
 
 # ------------------------------------------------------------------------------------------------ sharded scene
-def run_sharded(args, rank, world, local_rank):
-    """BASELINE configs[3]: ONE scene partitioned by block ownership across the N GPUs (sharded.py).  Rank 0 owns the camera
-    stream (frames resident in its HBM); a step = NCCL broadcast of the frame + per-shard allocate / integrate / expected
-    depths + whole-scene raycast over peer memory + ICP maps on the root.  value = frames/s of the one scene (strong scaling)."""
+C4_CAPS = dict(num_blocks=(1 << 22) + (1 << 20), bucket_num=1 << 23, excess_size=1 << 21)   # ~4 M blocks + margin: 20 GiB of voxels on one GPU
+_FRAME_CACHE = {}
+C4_TEXT = ("C4 large outdoor scene: the C2 camera (1242x375, 2 cm voxels, depth weighting) driven %d m along a street that repeats every "
+           "%d m, fused into ONE scene of ~%.1f M voxel blocks partitioned by block ownership over %d GPU(s)")
+
+
+def measure_sharded(args, rank, world, local_rank, mode, build_frames=None):
+    """BASELINE configs[3]: ONE large scene partitioned by block ownership across the N GPUs (sharded.py).  Rank 0 owns the
+    camera stream (the street's 64 distinct frames resident in its HBM); the map is first BUILT untimed (build_frames frames,
+    ~2.4 k new blocks each), then K frames are timed: NCCL broadcast of the frame + per-shard allocate / integrate / expected
+    depths + raycast (mode `composite`: own blocks, nearest hit per pixel composited slice-wise over peer memory; mode `lookup`:
+    whole-scene march with owner-routed probes, bit-identical to one big scene) + ICP maps on the root.
+    value = frames/s of the one scene.  Needs an initialised process group (world 1 included)."""
     import torch
     import torch.distributed as dist
     abi = importlib.import_module(PKG + ".abi")
     sharded = importlib.import_module(PKG + ".sharded")
+    synth = importlib.import_module(PKG + ".synth")
     lib = abi.load()
-    if lib.dsb200_device_count() < 1:
-        raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
-    abi.check(lib.dsb200_set_device(local_rank))
-    torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    dist.init_process_group("nccl", device_id=dev) if world > 1 else None
-    if world == 1:     # single process: still goes through DistShardedScene (count = 1) so the code path is the same
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29555")
-        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
     K, Wm = args.steps, args.warmup
-    cfg, frames = make_frames(K + Wm, seed=0)          # every rank knows the trajectory; only rank 0 uses the images
-    sc = sharded.DistShardedScene(cfg, CAPS, brick_log2=args.brick_log2, mode=args.shard_mode)
+    build = args.shard_frames if build_frames is None else build_frames
+    total = build + Wm + K
+    cfg = synth.config("C4")
+    poses = [synth.pose_to_M(p) for p in synth.trajectory(cfg, total)]
+    caps = sharded.shard_caps(C4_CAPS, world, args.brick_log2, halo=(mode == "composite"))
+    sc = sharded.DistShardedScene(cfg, caps, brick_log2=args.brick_log2, mode=mode)
     sc.m.recon.SetFusionWeightParams(cfg.depth_weighting, 10, 100)
-    packed = [sc.pack_frame(f).to(dev) for f in frames] if rank == 0 else [None] * len(frames)
+    packed = None
+    if rank == 0:      # only the camera rank renders (64 distinct images, once per process)
+        if "C4" not in _FRAME_CACHE:
+            _FRAME_CACHE["C4"] = synth.make_sequence("C4", cfg.period)[1]
+        packed = [sc.pack_frame(f).to(dev) for f in _FRAME_CACHE["C4"]]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     sc.m.recon.SetAsync(True)
-    for i in range(Wm):
-        sc.process_frame(packed[i], M=frames[i].M, timestamp=frames[i].timestamp)
+
+    def frame(i):
+        sc.process_frame(packed[i % cfg.period] if rank == 0 else None, M=poses[i], timestamp=0.1 * i)
+    for i in range(build + Wm):
+        frame(i)
+        if i % 64 == 63:
+            sc.m.recon.Sync(sc.m.scene, sc.m.rs)       # keeps the snapshot reservations trimmed; raises if a shard ran out of blocks
     sc.m.recon.Sync(sc.m.scene, sc.m.rs)
+    if sc.m.scene.c.last_free_block < 0 or sc.m.scene.c.last_free_excess < 0:
+        raise RuntimeError("shard %d ran out of voxel blocks / excess entries while building the C4 map (capacity %r)" % (rank, caps))
     torch.cuda.synchronize(); dist.barrier()
     l0 = lib.dsb200_kernel_launch_count()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
@@ -803,7 +836,7 @@ def run_sharded(args, rank, world, local_rank):
     for k in range(K):
         flush.zero_()
         evs[k][0].record()
-        sc.process_frame(packed[Wm + k], M=frames[Wm + k].M, timestamp=frames[Wm + k].timestamp)
+        frame(build + Wm + k)
         evs[k][1].record()
         sc.m.recon.Sync(sc.m.scene, sc.m.rs)
         vis_counts.append(sc.m.rs.c.no_visible)
@@ -812,27 +845,59 @@ def run_sharded(args, rank, world, local_rank):
     launches = int(lib.dsb200_kernel_launch_count() - l0)
     dist.barrier()
     ms = float(sum(a.elapsed_time(b) for a, b in evs))
-    blocks = CAPS["num_blocks"] - 1 - sc.m.scene.c.last_free_block
+    blocks = caps["num_blocks"] - 1 - sc.m.scene.c.last_free_block
     t = torch.tensor([ms, float(blocks), float(np.mean(vis_counts))], dtype=torch.float64, device=dev)
     tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    per_shard = [torch.zeros(3, dtype=torch.float64, device=dev) for _ in range(world)]
+    dist.all_gather(per_shard, t)
     sc.m.recon.SetAsync(False)
     sc.close()
-    dist.destroy_process_group()
+    del flush, packed
+    torch.cuda.empty_cache()
     if rank != 0:
         return None
     ms = float(tmax[0])
     npx = cfg.W * cfg.H
-    return {"metric": METRIC, "value": K / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic", "mode": "sharded",
-            "config": {"workload": "C2 street sequence fused into ONE scene sharded by block ownership over %d GPU(s) "
-                                   "(bricks of %d^3 blocks, raycast mode '%s'); camera stream on rank 0" % (world, 1 << args.brick_log2, args.shard_mode),
-                       "frames": K, "visible_blocks_per_shard_mean": float(tsum[2]) / world, "visible_blocks_max_shard": float(tmax[2]),
-                       "blocks_allocated_total": int(tsum[1]), "blocks_allocated_max_shard": int(tmax[1]),
-                       "l2": "flushed (256 MiB write) between timed steps"},
-            "collectives_per_step": {"broadcast_bytes": 8 * npx + 72, "rendezvous_allreduce": 2 if args.shard_mode == "lookup" else 1},
+    return {"metric": "frames/s alloc+integrate+raycast of ONE sharded scene (1242x375, 2 cm voxels, ~4 M blocks)", "value": K / (ms * 1e-3),
+            "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "strong", "mode": "sharded/" + mode,
+            "config": {"workload": C4_TEXT % (total, cfg.period, float(tsum[1]) / 1e6, world), "raycast": mode, "brick_blocks": 1 << args.brick_log2,
+                       "build_frames": build, "per_shard_capacity": caps, "l2": "flushed (256 MiB write) between timed steps"},
+            "blocks_allocated_total": int(tsum[1]), "blocks_allocated_per_shard": [int(x[1]) for x in per_shard],
+            "visible_blocks_per_shard": [float(x[2]) for x in per_shard], "ms_per_shard": [float(x[0]) / K for x in per_shard],
+            "collectives_per_step": {"broadcast_bytes": 8 * npx + 72, "rendezvous_allreduce_4B": 2,
+                                     "peer_reads_bytes_per_gpu": (16 * npx) if mode == "composite" else None},
             "gpu_launches": launches, "clocks": clocks}
+
+
+def run_sharded(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    abi = importlib.import_module(PKG + ".abi")
+    lib = abi.load()
+    if lib.dsb200_device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device; libdsb200 has no CPU fallback")
+    abi.check(lib.dsb200_set_device(local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    init_group(world, dev)
+    out = measure_sharded(args, rank, world, local_rank, args.shard_mode)
+    dist.destroy_process_group()
+    if out is not None:
+        out.update({"vs_baseline": None, "dtype": "f32 math -> i16 sdf / u8 weights", "data": "synthetic"})
+    return out
+
+
+def init_group(world, dev):
+    import torch.distributed as dist
+    if dist.is_initialized():
+        return
+    if world == 1:     # single process: DistShardedScene still goes through the same code path (count = 1)
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29555")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    else:
+        dist.init_process_group("nccl", device_id=dev)
 
 
 def main():
@@ -848,6 +913,8 @@ def main():
     ap.add_argument("--brick-log2", type=int, default=2)
     ap.add_argument("--no-lookahead", action="store_true",
                     help="do not overlap the next frame's allocation request pass with the current frame's raycast")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the `sharded` object (the C4 scene split over the N GPUs)")
+    ap.add_argument("--shard-frames", type=int, default=1650, help="frames fused untimed to build the C4 map (~2.4 k new blocks each)")
     ap.add_argument("--no-baselines", action="store_true", help="skip the gpu_comparator and cpu_baseline legs (tuning runs)")
     ap.add_argument("--single-workload", action="store_true",
                     help="N = 1: report only --workload (skip the `workloads` sub-objects for the other single-GPU configs)")

@@ -406,23 +406,37 @@ __device__ __forceinline__ float4 ray_finish(float rx, float ry, float rz, float
     return make_float4(rx, ry, rz, ptFound ? 1.0f : 0.0f);
 }
 
-// the march; returns false when `maxSteps` loop bodies have run and the ray is still marching (state left at the loop top)
+// the march; returns false when `maxSteps` loop bodies have run and the ray is still marching (state left at the loop top).
+// The loop keeps the shape of the reference's (one condition, one break): with a `return` inside it the compiler no longer
+// reconverges the lanes of a warp per iteration and the kernel runs 3.5x slower (measured, profiles/README.md r02e).
 template <class Tables>
 __device__ __forceinline__ bool cast_ray_bounded(float4 &out, RayState &s, const Tables &T, const RayParams &P, int maxSteps)
 {
+    const int bucketNum = P.bucketNum, bucketMask = P.bucketMask;
     const float stepScale = P.mu * P.oneOverVoxel;
     BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
+    float rx = s.rx, ry = s.ry, rz = s.rz, totalLength = s.total;
+    const float dx = s.dx, dy = s.dy, dz = s.dz, totalLengthMax = s.totalMax;
     float sdf = 1.0f, stepLength;
-    int steps = 0;
-    while (s.total < s.totalMax) {
-        if (steps == maxSteps) return false;
-        steps++;
-        if (ray_step(s.rx, s.ry, s.rz, T, P, stepScale, cache, sdf, stepLength) == kStepHit) break;
-        s.rx += stepLength * s.dx; s.ry += stepLength * s.dy; s.rz += stepLength * s.dz;
-        s.total += stepLength;
+    bool found, stopped = false;
+    int steps = maxSteps;                 // counts down; a negative cap never reaches 0
+    while (totalLength < totalLengthMax && steps != 0) {
+        steps--;
+        sdf = (float)read_sdf(T, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
+                              (int)round_half_away(rz), found, cache) / 32767.0f;
+        if (!found) stepLength = (float)kBlock;
+        else {
+            if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(T, bucketNum, bucketMask, rx, ry, rz, found, cache);
+            if (!(sdf > 0.0f)) { stopped = true; break; }
+            stepLength = (sdf * stepScale < 1.0f) ? 1.0f : sdf * stepScale;
+        }
+        rx += stepLength * dx; ry += stepLength * dy; rz += stepLength * dz;
+        totalLength += stepLength;
     }
-    out = ray_finish(s.rx, s.ry, s.rz, s.dx, s.dy, s.dz, sdf, T, P, stepScale, cache);
-    return true;
+    const bool suspended = !stopped && totalLength < totalLengthMax;     // left the loop on the step cap
+    s.rx = rx; s.ry = ry; s.rz = rz; s.total = totalLength;
+    if (!suspended) out = ray_finish(rx, ry, rz, dx, dy, dz, sdf, T, P, stepScale, cache);
+    return !suspended;
 }
 
 template <class Tables>
@@ -509,8 +523,11 @@ __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_const
 // samples the volume, and the group commits the bodies up to and including the first one that was NOT a unit step (a longer
 // step, a missing block, the hit, or the end of the range); later lanes' samples are discarded.  Lane 0's body is never
 // speculative, so a round always makes progress, and every committed body is the sequential loop's body on the sequential
-// loop's operands: the result is bit-identical to cast_ray (tests: every raycast parity test runs through here).  What changes
-// is the length of the dependent chain: G bodies per two or three memory round trips instead of one.
+// loop's operands: the result is bit-identical to cast_ray (tests/test_gpu_parity.py::test_two_pass_raycast_is_bit_identical).
+// What changes is the length of the dependent chain: G bodies per two or three memory round trips instead of one -- for rays
+// that creep.  Measured on B200 (profiles/README.md r02f): the long rays of the street and room workloads are NOT unit-step
+// creepers; they march inside the truncation band with steps of sdf * 4 voxels in (1, 4), which nothing can predict, so a round
+// commits 1-2 bodies on average and the pass costs more than it saves.  It is therefore OFF by default (ray_steps = 0).
 template <class Tables, int G>
 __global__ void __launch_bounds__(128) k_raycast_finish(RayParams P, const __grid_constant__ Tables T, float4 *out, RayQueue q)
 {
@@ -901,7 +918,7 @@ void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_h
 static int env_int(const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; }
 Tunables &tunables()
 {
-    static Tunables t = {env_int("DSB200_RAY_STEPS", 24), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
+    static Tunables t = {env_int("DSB200_RAY_STEPS", 0), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
                          env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 2), env_int("DSB200_FUSE_CTAS", 12),
                          env_int("DSB200_FUSE_MINB", 6)};
     return t;
@@ -917,7 +934,8 @@ bool set_tunable(const char *name, int value)
 static int ray_bottom_up() { return tunables().ray_bottom_up != 0; }
 static int ray_ctas_per_sm() { const int v = tunables().ray_ctas; return v < 1 ? 1 : v; }
 
-// bounded first pass + finishing pass (k_raycast_finish); DSB200_RAY_STEPS = 0 runs the single unbounded pass,
+// bounded first pass + finishing pass (k_raycast_finish); DSB200_RAY_STEPS = 0 (the default: the two-pass schedule measured
+// SLOWER inside a frame, 0.229-0.276 ms against 0.158 ms at C2, profiles/README.md r02f) runs the single unbounded pass,
 // DSB200_RAY_GROUP = lanes per suspended ray in the finishing pass (8, 16 or 32)
 static int ray_max_steps() { return tunables().ray_steps; }
 static int ray_group() { return tunables().ray_group; }

@@ -31,6 +31,27 @@ def _lib():
     return abi.load()
 
 
+def shard_caps(caps, count, brick_log2=2, halo=False, margin=1.25):
+    """Per-shard capacities for a scene of `caps` split over `count` shards (capacity / N + halo): the voxel block
+    array and the excess list shrink with N (times the halo replication ((B + 1) / B)^3 of bricks of B blocks, times a margin for
+    the imbalance of the ownership hash); the bucket count is the next power of two."""
+    if count <= 1:
+        return dict(caps)
+    rep = ((1 << brick_log2) + 1.0) ** 3 / float(1 << brick_log2) ** 3 if halo else 1.0
+    f = min(1.0, rep * margin / count)
+    nb = max(1024, int(caps["num_blocks"] * f))
+    bn = 1
+    while bn < max(1024, int(caps["bucket_num"] * f)):
+        bn <<= 1
+    return dict(num_blocks=nb, bucket_num=bn, excess_size=max(1024, int(caps["excess_size"] * f)))
+
+
+def row_slice(height, rank, count):
+    """rows [begin, end) of the image that shard `rank` composites (reduce-scatter shape: every shard reads its slice of all
+    the shards' results and writes the nearest hits into the root's image)"""
+    return (height * rank) // count, (height * (rank + 1)) // count
+
+
 class ShardMember(object):
     def __init__(self, cfg, caps, rank, count, brick_log2=2, use_swapping=False, halo=True):
         self.cfg, self.rank, self.count, self.brick_log2 = cfg, rank, count, brick_log2
@@ -55,15 +76,19 @@ class ShardMember(object):
         self.rs.c.raycast_result = self.ray[frame_idx & 1]
         self.recon.ProcessFrame(self.vis, self.scene, self.view, self.trk, self.rs, stages)
 
-    def composite_and_icp(self, result_ptrs, rows=None):
-        """nearest-hit composite of the shards' raycast results (device or IPC-mapped peer pointers), then ICP maps"""
+    def composite_rows(self, result_ptrs, rows=None, out_ptr=None):
+        """nearest-hit composite of rows [r0, r1) of the shards' raycast results (device or IPC-mapped peer pointers) into
+        out_ptr (default: this shard's composite image; the root's image, peer-mapped, in the distributed scene)"""
         n = len(result_ptrs)
         arr = (C.c_void_p * n)(*result_ptrs)
         r0, r1 = rows if rows is not None else (0, self.cfg.H)
         abi.check(_lib().dsb200_composite_nearest(self.vis.h, n, arr, self.trk.c.invM_d, self.cfg.params().voxel_size,
-                                                  self.cfg.W, self.cfg.H, r0, r1, self.composite.ptr))
-        abi.check(_lib().dsb200_icp_maps_from_raycast(self.vis.h, C.byref(self.scene.c), C.byref(self.view.c), C.byref(self.trk.c),
-                                                      self.composite.ptr, self.rs.c.raycast_image, self.cfg.W, self.cfg.H))
+                                                  self.cfg.W, self.cfg.H, r0, r1, out_ptr if out_ptr is not None else self.composite.ptr))
+
+    def composite_and_icp(self, result_ptrs, rows=None):
+        """whole-image composite on this shard, then ICP maps"""
+        self.composite_rows(result_ptrs, rows)
+        self.icp_from_composite()
 
     def tables(self):
         """(hash, voxels, range image) device pointers of this shard, for dsb200_shard_tables"""
@@ -109,7 +134,11 @@ class LocalShardedScene(object):
             m.fuse_and_raycast(self.frame_idx, local | (abi.FRAME_RAYCAST if self.mode == "composite" else 0))
         root = self.members[0]
         if self.mode == "composite":
-            root.composite_and_icp([m.ray[self.frame_idx & 1] for m in self.members])
+            ptrs = [m.ray[self.frame_idx & 1] for m in self.members]
+            for m in self.members:           # every shard composites its row slice into the root's image
+                m.trk.set_pose(f.M)
+                m.composite_rows(ptrs, row_slice(self.cfg.H, m.rank, self.count), root.composite.ptr)
+            root.icp_from_composite()
         else:
             tables = [m.tables() for m in self.members]
             for m in self.members:
@@ -197,8 +226,12 @@ class DistShardedScene(object):
         if self.mode == "composite":
             self.m.fuse_and_raycast(self.frame_idx, local | abi.FRAME_RAYCAST)
             self.rendezvous()                # every shard's raycast of this frame has completed
+            # reduce-scatter shape: shard r composites its row slice from all N results and writes it into the root's image
+            # (each GPU reads 16 W H bytes, 1/N of them locally, instead of the root pulling 16 N W H bytes through one link)
+            self.m.composite_rows(self.peer_ray[self.frame_idx & 1], row_slice(self.cfg.H, self.rank, self.world), self.root_image)
+            self.rendezvous()                # every slice is in the root's image
             if self.rank == self.root:
-                self.m.composite_and_icp(self.peer_ray[self.frame_idx & 1])
+                self.m.icp_from_composite()
         else:
             self.m.fuse_and_raycast(self.frame_idx, local)
             self.rendezvous()                # every shard's tables and range image are final for this frame

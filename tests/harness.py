@@ -382,8 +382,14 @@ def make_block_table(hash_table, visible_ids, fetch_blocks, last_free, num_block
     assert allow_duplicates or dup == 0, "%d block coordinates are allocated twice" % dup
     allocated = int(keys.size)
     keys, live = keys[first], live[first]
-    t = dict(keys=keys, slots=live, ptrs=hash_table["ptr"][live], free_blocks=last_free[0] + 1, num_blocks=num_blocks,
-             duplicates=dup, allocated=allocated)
+    ptrs = hash_table["ptr"][live]
+    # two live entries sharing one voxel block: the aftermath of a double free (the reference frees a block twice when a torn
+    # coordinate left it with two entries for one coordinate; the block is then handed out twice).  Never in ours.
+    up, cnt = np.unique(ptrs, return_counts=True)
+    aliased = keys[np.isin(ptrs, up[cnt > 1])]
+    assert allow_duplicates or aliased.size == 0, "%d live entries share a voxel block" % aliased.size
+    t = dict(keys=keys, slots=live, ptrs=ptrs, free_blocks=last_free[0] + 1, num_blocks=num_blocks,
+             duplicates=dup, allocated=allocated, aliased=aliased)
     vis = np.asarray(visible_ids)
     t["visible_keys"] = np.sort(pos_key(hash_table["pos"][vis])) if vis.size else np.zeros(0, np.int64)
     t["visible_dead"] = int((hash_table["ptr"][vis] < 0).sum()) if vis.size else 0
@@ -416,6 +422,7 @@ class SetTracker(object):
     def __init__(self, bucket_mask=abi.DEFAULT_BUCKETS - 1):
         self.birth = [dict(), dict()]
         self.chained = set()
+        self.aliased = set()          # reference blocks that ever shared their voxel block with another entry (reference defect)
         self.frame = 0
         self.mask = bucket_mask
 
@@ -440,6 +447,7 @@ class SetTracker(object):
         union = np.union1d(ta["keys"], tb["keys"])
         alive = set(union.tolist())
         self.chained &= alive                       # a block that died in both engines starts afresh
+        self.aliased = (self.aliased | set(tb.get("aliased", np.zeros(0, np.int64)).tolist())) & set(tb["keys"].tolist())
         if union.size:
             bk = self._buckets(union)
             order = np.argsort(bk, kind="stable")
@@ -452,7 +460,7 @@ class SetTracker(object):
 
     def comparable(self, keys):
         a, b = self.birth
-        return np.array([(k in a and k in b and a[k] == b[k]) for k in keys.tolist()], bool)
+        return np.array([(k in a and k in b and a[k] == b[k] and k not in self.aliased) for k in keys.tolist()], bool)
 
     def is_chained(self, keys):
         return np.array([k in self.chained for k in keys.tolist()], bool)

@@ -435,3 +435,26 @@ def test_abandoned_lookahead_is_undone():
     gpu.recon.SetAsync(False)
     other.free(); nxt.free()
     gpu.close(); ora.close()
+
+
+def test_two_pass_raycast_is_bit_identical():
+    """the bounded first raycast pass + the group-speculative finishing pass (csrc/vis.cu: k_raycast_finish; off by default)
+    produce the single-pass image bit for bit, for every group size, on the fused frame and on the free-view path"""
+    lib = abi.load()
+    cfg, frames = synth.make_sequence("tiny_street", 5)
+    gpu, ora = hz.GpuBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    gpu.set_weights(True); ora.set_weights(True)
+    try:
+        for i, f in enumerate(frames):
+            abi.check(lib.dsb200_debug_set_tunable(b"ray_steps", (0, 3, 6, 10, 16)[i]))
+            abi.check(lib.dsb200_debug_set_tunable(b"ray_group", (8, 2, 4, 16, 32)[i]))
+            gpu.set_frame(f); ora.set_frame(f)
+            gpu.process_frame(); ora.process_frame()
+            hz.assert_images_equal(ora.images(), gpu.images(), "two-pass raycast, frame %d" % i)
+        abi.check(lib.dsb200_debug_set_tunable(b"ray_steps", 4))
+        gpu.free_view(frames[2].M, cfg.intr, 0); ora.free_view(frames[2].M, cfg.intr, 0)
+        hz.assert_images_equal(ora.free_images(), gpu.free_images(), "two-pass raycast, free view")
+    finally:
+        abi.check(lib.dsb200_debug_set_tunable(b"ray_steps", 0))
+        abi.check(lib.dsb200_debug_set_tunable(b"ray_group", 8))
+    gpu.close(); ora.close()
