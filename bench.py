@@ -107,7 +107,7 @@ def ncu_traffic(stage):
     """DRAM bytes per launch (read + write) of the stage's dominant kernel from the committed `ncu --set full` extract
     profiles/ncu_traffic.json = {"captured_at_commit": ..., "command": ..., "kernels": {name: bytes per launch}} (see
     profiles/README.md).  A capture is a property of the commit it was taken at: the stamp travels with the number."""
-    kernel = {"integrate": "k_fuse_warp", "raycast": "k_raycast", "allocate+visible_list": "k_alloc_requests"}.get(stage)
+    kernel = {"integrate": "k_fuse_warp_flat", "raycast": "k_raycast", "allocate+visible_list": "k_alloc_requests"}.get(stage)
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         if WORKLOAD != t.get("workload", "C2") or kernel not in t["kernels"]:

@@ -8,6 +8,7 @@
 // vector load/store (two voxels per thread, fully coalesced), stores only for lanes whose voxels
 // changed.  Arithmetic order is the reference's (no FMA contraction, IEEE division).
 #include <cstdlib>
+#include <type_traits>
 #include "kernels.cuh"
 #include "exactdiv.cuh"
 
@@ -420,22 +421,63 @@ __device__ __forceinline__ bool fuse_depth_flat(unsigned &lo, float pcx, float p
     return ok && !((eta > P.mu) || (fabsf(q) > 0.25f));
 }
 
-template <bool WIMG, int MINB>
+// ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) of one 4 KiB voxel block global -> shared, completion on an mbarrier.
+// TMA = true: each warp owns a two-stage ring of block buffers; lane 0 issues the copy of the warp's NEXT block as soon as the
+// previous occupant of that stage has been written back, so a block is in flight for a whole block's worth of arithmetic
+// before it is needed, without holding registers (the LDG variant prefetches to L2 and then one slice ahead into registers).
+// The block is updated in place in its stage buffer and dirty 16-byte vectors are written back from there.
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bulk_load_block(void *dstSmem, const void *srcGlobal, unsigned bytes, unsigned long long *bar)
+{
+    // the stage buffer was last touched through the generic proxy (LDS / STS of the previous block): order those accesses before
+    // the async-proxy write
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(dstSmem)), "l"(srcGlobal), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+
+struct FuseTmaSmem {
+    FuseTables T;
+    alignas(128) uint4 stage[kFuseWarps][2][256];      // two 4 KiB block buffers per warp
+    unsigned long long bar[kFuseWarps][2];
+    unsigned short queue[kFuseWarps][kBlock3];
+    unsigned dirty[kFuseWarps][8];
+};
+
+__device__ __forceinline__ uint4 *fuse_stage(FuseWarpSmem &S, int warp, unsigned) { return S.vox[warp]; }
+__device__ __forceinline__ uint4 *fuse_stage(FuseTmaSmem &S, int warp, unsigned s) { return S.stage[warp][s]; }
+__device__ __forceinline__ unsigned long long &fuse_bar(FuseTmaSmem &S, int warp, unsigned s) { return S.bar[warp][s]; }
+__device__ __forceinline__ unsigned long long &fuse_bar(FuseWarpSmem &S, int, unsigned) { return *reinterpret_cast<unsigned long long *>(S.dirty); }   // never used
+
+template <bool WIMG, int MINB, bool TMA>
 __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FuseParams P, dsb200_voxel *voxels,
                                                                         const dsb200_hash_entry *__restrict__ hash,
                                                                         const int *__restrict__ ids, const int *__restrict__ countPtr,
                                                                         const float *__restrict__ depth, const uchar4 *__restrict__ rgb,
                                                                         const unsigned char *__restrict__ wimg, unsigned *shadow2)
 {
-    __shared__ FuseWarpSmem S;
+    typedef typename std::conditional<TMA, FuseTmaSmem, FuseWarpSmem>::type Smem;
+    __shared__ Smem S;
     const int n = *countPtr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
     fill_tables(S.T);
     if (lane < 8) S.dirty[warp][lane] = 0;
+    if (TMA && lane < 2) mbar_init(&fuse_bar(S, warp, lane), 1);
+    if (TMA) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     const FuseTables &T = S.T;
-    uint4 *sVox = S.vox[warp];
     unsigned short *sQueue = S.queue[warp];
     unsigned *sDirty = S.dirty[warp];
     const int lx = (lane & 3) * 2, ly = lane >> 2;
@@ -445,14 +487,24 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FusePa
     int slot2 = (i + 2 * stride < n) ? __ldg(ids + i + 2 * stride) : -1;
     HashEntry e1 = (i + stride < n) ? load_entry(hash, __ldg(ids + i + stride)) : none;
     HashEntry e0 = (i < n) ? load_entry(hash, __ldg(ids + i)) : none;
+    unsigned cur = 0, phase = 0;          // TMA: stage of the current block; bit s of `phase` = parity of stage s's next completion
+    if (TMA && e0.ptr >= 0 && lane == 0)
+        bulk_load_block(fuse_stage(S, warp, 0), voxels + (size_t)e0.ptr * kBlock3, 4096u, &fuse_bar(S, warp, 0));
     for (; i < n; i += stride) {
         const int slot3 = (i + 3 * stride < n) ? __ldg(ids + i + 3 * stride) : -1;
         const HashEntry e2 = (slot2 >= 0) ? load_entry(hash, slot2) : none;
-        if (e1.ptr >= 0) prefetch_l2(reinterpret_cast<const char *>(voxels + (size_t)e1.ptr * kBlock3) + lane * 128);
+        if (TMA) {
+            // the other stage's block was written back in the previous iteration: start the next block's copy into it
+            if (e1.ptr >= 0 && lane == 0)
+                bulk_load_block(fuse_stage(S, warp, cur ^ 1u), voxels + (size_t)e1.ptr * kBlock3, 4096u, &fuse_bar(S, warp, cur ^ 1u));
+        } else if (e1.ptr >= 0) prefetch_l2(reinterpret_cast<const char *>(voxels + (size_t)e1.ptr * kBlock3) + lane * 128);
+        uint4 *sVox = fuse_stage(S, warp, cur);
         if (e0.ptr >= 0) {
             const HashEntry e = e0;
             uint4 *base = reinterpret_cast<uint4 *>(voxels + (size_t)e.ptr * kBlock3);
-            uint4 raw = base[lane];
+            if (TMA) { mbar_wait(&fuse_bar(S, warp, cur), (phase >> cur) & 1u); phase ^= 1u << cur; }
+            const uint4 *src = TMA ? sVox : base;      // where the block's current contents are read from
+            uint4 raw = src[lane];
             const int gx = e.px * kBlock + lx;
             const float ptx0 = (float)gx * P.voxelSize, ptx1 = (float)(gx + 1) * P.voxelSize;
             const float pty = (float)(e.py * kBlock + ly) * P.voxelSize;
@@ -463,7 +515,7 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FusePa
 #pragma unroll 2
             for (int z = 0; z < kBlock; z++) {
                 uint4 nxt = raw;
-                if (z + 1 < kBlock) nxt = base[(z + 1) * 32 + lane];
+                if (z + 1 < kBlock) nxt = src[(z + 1) * 32 + lane];
                 const float ptz = (float)(e.pz * kBlock + z) * P.voxelSize;
                 const float bx = P.M_d.m[8] * ptz, by = P.M_d.m[9] * ptz, bz = P.M_d.m[10] * ptz;
                 unsigned lo0 = raw.x, lo1 = raw.z;
@@ -526,6 +578,7 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FusePa
             }
             __syncwarp();
         }
+        if (TMA) cur ^= 1u;                 // stages alternate with the warp's blocks, processed or not
         e0 = e1; e1 = e2; slot2 = slot3;
     }
 }
@@ -537,15 +590,18 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
     unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
     const int variant = tunables().fuse_kernel;   // 0: CTA per block, 1: warp per block, 2: warp per block, straight-line depth part
-    if (variant == 2 && !deintegrate && P.fastDiv && P.maxNewW >= 1 && P.maxNewW <= 255 && (!P.depthWeighting || weightScratch)) {
+    if (variant >= 2 && !deintegrate && P.fastDiv && P.maxNewW >= 1 && P.maxNewW <= 255 && (!P.depthWeighting || weightScratch)) {
         const int g = kNumSMs * tunables().fuse_ctas;
         const int minb = tunables().fuse_minb;     // register budget: 65536 / (128 * minb)
-#define DSB_FLAT(W_, M_) DSB_LAUNCH((k_fuse_warp_flat<W_, M_>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, W_ ? weightScratch : nullptr, shadow2)
-        if (P.depthWeighting) {
-            DSB_LAUNCH(k_depth_weights, kNumSMs * 4, 256, 0, st, depth, weightScratch, P.W * P.H, P.maxDistance, P.maxNewW);
-            if (minb >= 8) DSB_FLAT(true, 8); else if (minb >= 6) DSB_FLAT(true, 6); else DSB_FLAT(true, 4);
+#define DSB_FLAT(W_, M_, T_) DSB_LAUNCH((k_fuse_warp_flat<W_, M_, T_>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, W_ ? weightScratch : nullptr, shadow2)
+        if (P.depthWeighting) DSB_LAUNCH(k_depth_weights, kNumSMs * 4, 256, 0, st, depth, weightScratch, P.W * P.H, P.maxDistance, P.maxNewW);
+        if (variant == 3) {                // TMA bulk loads: 39 KiB of shared memory per CTA -> at most 5 CTAs per SM
+            if (P.depthWeighting) { if (minb >= 5) DSB_FLAT(true, 5, true); else DSB_FLAT(true, 4, true); }
+            else { if (minb >= 5) DSB_FLAT(false, 5, true); else DSB_FLAT(false, 4, true); }
+        } else if (P.depthWeighting) {
+            if (minb >= 8) DSB_FLAT(true, 8, false); else if (minb >= 6) DSB_FLAT(true, 6, false); else DSB_FLAT(true, 4, false);
         } else {
-            if (minb >= 8) DSB_FLAT(false, 8); else if (minb >= 6) DSB_FLAT(false, 6); else DSB_FLAT(false, 4);
+            if (minb >= 8) DSB_FLAT(false, 8, false); else if (minb >= 6) DSB_FLAT(false, 6, false); else DSB_FLAT(false, 4, false);
         }
 #undef DSB_FLAT
         return;
