@@ -910,7 +910,7 @@ def main():
     ap.add_argument("--mode", default="replicas", choices=["replicas", "sharded", "batched", "tracked"],
                     help="N > 1: independent scenes per GPU (default, weak scaling) or ONE scene sharded by block ownership")
     ap.add_argument("--shard-mode", default="lookup", choices=["lookup", "composite"])
-    ap.add_argument("--brick-log2", type=int, default=2)
+    ap.add_argument("--brick-log2", type=int, default=3, help="sharded scene: ownership bricks of 2^k blocks per axis (halo replication ((B + 1) / B)^3)")
     ap.add_argument("--no-lookahead", action="store_true",
                     help="do not overlap the next frame's allocation request pass with the current frame's raycast")
     ap.add_argument("--no-sharded", action="store_true", help="skip the `sharded` object (the C4 scene split over the N GPUs)")
