@@ -32,11 +32,15 @@ namespace ITMLib
 			dsb200_swap *cacheOf(ITMScene<TVoxel, ITMVoxelBlockHash> *scene)
 			{
 				dsb200_swap *&c = caches[scene];
-				if (c == NULL) b200::check(dsb200_swap_create(&c, SDF_BUCKET_NUM + SDF_EXCESS_LIST_SIZE, SDF_TRANSFER_BLOCK_NUM, stream));
+				if (c == NULL)
+				{
+					b200::check(dsb200_swap_create(&c, SDF_BUCKET_NUM + SDF_EXCESS_LIST_SIZE, SDF_TRANSFER_BLOCK_NUM, stream));
+					b200::check(dsb200_swap_attach_recon(c, recon));   // the library syncs the engine before / notifies it after every swap call
+				}
 				return c;
 			}
 
-			void changed() { if (recon != NULL) b200::check(dsb200_recon_notify_scene_modified(recon)); }
+			void changed() { }   // done inside libdsb200 since dsb200_swap_attach_recon
 
 		public:
 			void IntegrateGlobalIntoLocal(ITMScene<TVoxel, ITMVoxelBlockHash> *scene, ITMRenderState *renderState)

@@ -297,6 +297,15 @@ extern "C" int dsb200_recon_sync(dsb200_recon *e, dsb200_scene *scene, dsb200_re
     return sync_counters(e, scene, rs);
 }
 
+// the same, but only when the DEVICE counters are the authoritative ones (asynchronous engine with frames in flight); between
+// synchronous calls, or after dsb200_recon_notify_scene_modified, the host mirrors already are and must not be overwritten
+extern "C" int dsb200_recon_refresh_mirrors(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs)
+{
+    if (!e) return fail(DSB200_ERR_INVALID, "recon_refresh_mirrors: null engine");
+    if (!(e->async && e->deviceCountersValid)) { CU(cudaStreamSynchronize(e->stream)); return DSB200_OK; }
+    return sync_counters(e, scene, rs);
+}
+
 // ---------------------------------------------------------------- reconstruction engine
 static void make_alloc_params(AllocParams &P, const dsb200_recon *e, const dsb200_scene *scene, const dsb200_view *view,
                               const dsb200_tracking *trk)

@@ -68,7 +68,7 @@ struct Tunables {
     int ray_ctas;         // CTAs per SM of the first raycast pass
     int ray_finish_ctas;  // CTAs per SM of the finishing pass
     int ray_bottom_up;    // hand the image tiles out from the last row upwards
-    int fuse_kernel;      // integration kernel: 0 CTA per block, 1 warp per block, 2 + straight-line depth part, 3 + TMA bulk block loads (default)
+    int fuse_kernel;      // integration kernel: 1 warp per block (round 1), 2 + straight-line depth part, 3 + TMA bulk block loads (default)
     int fuse_ctas;        // CTAs per SM of the flat integration kernel
     int fuse_minb;        // ... and its __launch_bounds__ minimum CTAs per SM (variant 2: 4, 6 or 8; variant 3: 4 or 5)
 };

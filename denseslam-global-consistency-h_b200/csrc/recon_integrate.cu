@@ -155,87 +155,7 @@ __device__ __forceinline__ void fuse_colour(VoxelRegs &vox, float ptx, float pty
     vox.wc = (unsigned char)newWc;        // the reference's `(uchar)newW` on a float (DeviceAgnostic/...:112,214)
 }
 
-// One 4 KiB voxel block per CTA iteration.  Phase A: every thread loads 16 B (two voxels), runs the depth part in
-// registers and queues the voxels that need the colour part; phase B: the CTA drains the queue densely (a voxel per
-// thread, whatever warp it came from) on the shared-memory copy of the block; phase C: 16 B stores where anything changed.
-template <bool DE, bool FAST>
-__global__ void __launch_bounds__(256) k_fuse(FuseParams P, dsb200_voxel *voxels,
-                                              const dsb200_hash_entry *__restrict__ hash,
-                                              const int *__restrict__ ids, const int *__restrict__ countPtr,
-                                              const float *__restrict__ depth, const uchar4 *__restrict__ rgb, unsigned *shadow2)
-{
-    __shared__ FuseTables T;
-    __shared__ uint4 sVox[256];
-    __shared__ unsigned short sQueue[kBlock3];
-    __shared__ int sCount[2];
-    const int n = *countPtr;
-    const int t = threadIdx.x, lane = t & 31;
-    const int lx = (2 * t) & 7, ly = (t >> 2) & 7, lz = t >> 5;     // voxel 2t: x even, same y/z for 2t+1
-    fill_tables(T);
-    if (t < 2) sCount[t] = 0;
-    __syncthreads();
-    int par = 0;
-    // Software pipeline over the CTA's blocks: the chain ids[i] -> hash entry -> voxel block is three dependent global
-    // loads (~2 us); each stage is issued one iteration ahead of its consumer so the chain hides behind the arithmetic.
-    const int stride = gridDim.x;
-    const HashEntry none = {0, 0, 0, 0, 0, -2, 0};
-    int i = blockIdx.x;
-    int slot2 = (i + 2 * stride < n) ? __ldg(ids + i + 2 * stride) : -1;
-    HashEntry e1 = (i + stride < n) ? load_entry(hash, __ldg(ids + i + stride)) : none;
-    HashEntry e0 = (i < n) ? load_entry(hash, __ldg(ids + i)) : none;
-    for (; i < n; i += stride) {
-        const int slot3 = (i + 3 * stride < n) ? __ldg(ids + i + 3 * stride) : -1;      // stage A: list entry, 3 ahead
-        const HashEntry e2 = (slot2 >= 0) ? load_entry(hash, slot2) : none;              // stage B: hash entry, 2 ahead
-        if (e1.ptr >= 0) prefetch_l2(voxels + (size_t)e1.ptr * kBlock3 + 2 * t);         // stage C: voxel block -> L2, 1 ahead
-        if (e0.ptr >= 0) {
-            const HashEntry e = e0;
-            uint4 *p = reinterpret_cast<uint4 *>(voxels + (size_t)e.ptr * kBlock3) + t;
-            const uint4 raw = *p;
-            const float pty = (float)(e.py * kBlock + ly) * P.voxelSize, ptz = (float)(e.pz * kBlock + lz) * P.voxelSize;
-            const int gx = e.px * kBlock + lx;
-            VoxelRegs v0 = unpack(raw.x, raw.y), v1 = unpack(raw.z, raw.w);
-            const bool c0 = fuse_depth<DE, FAST>(v0, (float)gx * P.voxelSize, pty, ptz, P, depth, T);
-            const bool c1 = fuse_depth<DE, FAST>(v1, (float)(gx + 1) * P.voxelSize, pty, ptz, P, depth, T);
-            uint4 out = raw;
-            pack(v0, out.x, out.y); pack(v1, out.z, out.w);
-            // queue the colour work (warp-aggregated)
-            const unsigned m0 = __ballot_sync(0xffffffffu, c0), m1 = __ballot_sync(0xffffffffu, c1);
-            const int cnt = __popc(m0) + __popc(m1);
-            if (cnt) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&sCount[par], cnt);
-                base = __shfl_sync(0xffffffffu, base, 0);
-                const unsigned lt = (1u << lane) - 1u;
-                if (c0) sQueue[base + __popc(m0 & lt)] = (unsigned short)(2 * t);
-                if (c1) sQueue[base + __popc(m0) + __popc(m1 & lt)] = (unsigned short)(2 * t + 1);
-            }
-            sVox[t] = out;
-            if (t == 0) sCount[par ^ 1] = 0;
-            __syncthreads();
-            const int nq = sCount[par];
-            par ^= 1;
-            if (nq) {
-                uint2 *sv = reinterpret_cast<uint2 *>(sVox);
-                for (int k = t; k < nq; k += 256) {
-                    const int vi = sQueue[k];
-                    uint2 w = sv[vi];
-                    VoxelRegs vx = unpack(w.x, w.y);
-                    fuse_colour<DE, FAST>(vx, (float)(e.px * kBlock + (vi & 7)) * P.voxelSize, (float)(e.py * kBlock + ((vi >> 3) & 7)) * P.voxelSize,
-                                          (float)(e.pz * kBlock + (vi >> 6)) * P.voxelSize, P, rgb, T);
-                    pack(vx, w.x, w.y);
-                    sv[vi] = w;
-                }
-                __syncthreads();
-                out = sVox[t];
-            }
-            if (out.x != raw.x || out.y != raw.y || out.z != raw.z || out.w != raw.w) *p = out;
-        }
-        e0 = e1; e1 = e2; slot2 = slot3;
-    }
-}
-
-
-// ---------------------------------------------------------------- warp-per-block variant (default)
+// ---------------------------------------------------------------- warp-per-block kernel (round 1; de-integration and fall-back)
 // One WARP fuses one 4 KiB voxel block: 8 z-slices of 64 voxels, lane l owns the voxel pair (x = 2(l&3), 2(l&3)+1; y = l>>2)
 // of every slice, i.e. 16 voxels per lane per block.  Against the CTA-per-block kernel above this
 //  * removes both CTA barriers per block (20 % of the stall samples in profiles/r01b) -- a warp never waits for another;
@@ -589,7 +509,7 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
 {
     unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
-    const int variant = tunables().fuse_kernel;   // 0: CTA per block, 1: warp per block, 2: warp per block, straight-line depth part
+    const int variant = tunables().fuse_kernel;   // 1: round-1 warp-per-block kernel; 2: + straight-line depth part; 3: + TMA bulk block loads (default)
     if (variant >= 2 && !deintegrate && P.fastDiv && P.maxNewW >= 1 && P.maxNewW <= 255 && (!P.depthWeighting || weightScratch)) {
         const int g = kNumSMs * tunables().fuse_ctas;
         const int minb = tunables().fuse_minb;     // register budget: 65536 / (128 * minb)
@@ -606,7 +526,7 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
 #undef DSB_FLAT
         return;
     }
-    if (variant >= 1) {
+    {
         const int g = kNumSMs * 8;
         if (deintegrate) {
             if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<true, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
@@ -615,15 +535,6 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
             if (P.fastDiv) DSB_LAUNCH((k_fuse_warp<false, true, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
             else DSB_LAUNCH((k_fuse_warp<false, false, 8>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
         }
-        return;
-    }
-    const int grid = kNumSMs * 8;
-    if (deintegrate) {
-        if (P.fastDiv) DSB_LAUNCH((k_fuse<true, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
-        else DSB_LAUNCH((k_fuse<true, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
-    } else {
-        if (P.fastDiv) DSB_LAUNCH((k_fuse<false, true>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
-        else DSB_LAUNCH((k_fuse<false, false>), grid, 256, 0, st, P, voxels, hash, ids, count, depth, rgb4, shadow2);
     }
 }
 

@@ -216,7 +216,15 @@ struct dsb200_swap {
     uint4 **blockPtrs = nullptr;
     // pinned
     int *neededHost = nullptr, *resultHost = nullptr; uint4 **blockPtrsHost = nullptr;
+    // the reconstruction engine working on the same scene (dsb200_swap_attach_recon): synchronised before and notified after every
+    // call here that reads or changes the free list, so a stale host mirror of an asynchronous engine can never be used
+    dsb200_recon *recon = nullptr;
 };
+
+// before a call that reads scene->last_free_block / changes the volume: bring the host mirrors up to date
+static int swap_enter(dsb200_swap *s, dsb200_scene *scene) { return s->recon ? dsb200_recon_refresh_mirrors(s->recon, scene, nullptr) : DSB200_OK; }
+// after it: the engine's device counters, look-ahead and sdf shadow describe the old volume
+static int swap_leave(dsb200_swap *s) { return s->recon ? dsb200_recon_notify_scene_modified(s->recon) : DSB200_OK; }
 
 static const int kChunkBlocks = 16384;                          // 64 MB of pinned memory per chunk
 static const size_t kBlockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
@@ -341,7 +349,9 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
     if (!s || !scene) return fail_with(DSB200_ERR_INVALID, "swap_integrate_global_into_local: null argument");
     if (scene->bucket_num + scene->excess_size != s->total) return fail_with(DSB200_ERR_INVALID, "swap: the cache was sized for another hash table");
     int n = 0;
-    const int rc = swap_select<0>(s, scene, nullptr, &n);
+    int rc = swap_enter(s, scene);
+    if (rc) return rc;
+    rc = swap_select<0>(s, scene, nullptr, &n);
     if (rc) return rc;
     if (moved) *moved = n;
     if (n == 0) return DSB200_OK;
@@ -354,7 +364,7 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
     DSB_LAUNCH(k_swap_integrate, n, 256, 0, s->stream, n, s->needed, s->blockPtrs, scene->hash, scene->voxels, s->states, scene->params.max_w);
     SWCU(cudaGetLastError());
     SWCU(cudaStreamSynchronize(s->stream));
-    return DSB200_OK;
+    return swap_leave(s);
 }
 
 int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const dsb200_render_state *rs, int32_t *moved)
@@ -363,7 +373,9 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
     if (scene->bucket_num + scene->excess_size != s->total) return fail_with(DSB200_ERR_INVALID, "swap: the cache was sized for another hash table");
     if (rs && !rs->visible_type) return fail_with(DSB200_ERR_INVALID, "swap_save_to_global_memory: render state without visibility flags");
     int n = 0;
-    const int rc = swap_select<1>(s, scene, rs ? rs->visible_type : nullptr, &n);
+    int rc = swap_enter(s, scene);                                 // scene->last_free_block below must be the engine's current value
+    if (rc) return rc;
+    rc = swap_select<1>(s, scene, rs ? rs->visible_type : nullptr, &n);
     if (rc) return rc;
     if (moved) *moved = n;
     if (n == 0) return DSB200_OK;
@@ -386,6 +398,13 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
     if (pushed < 0) pushed = 0;
     if (pushed > n) pushed = n;
     scene->last_free_block = lastFree0 + pushed;
+    return swap_leave(s);
+}
+
+int dsb200_swap_attach_recon(dsb200_swap *s, dsb200_recon *recon)
+{
+    if (!s) return fail_with(DSB200_ERR_INVALID, "swap_attach_recon: null cache");
+    s->recon = recon;
     return DSB200_OK;
 }
 

@@ -410,6 +410,8 @@ class ITMSwappingEngine(object):
         self.c = abi.SwapCache()
         abi.check(_lib().dsb200_swap_cache_of(self.h, C.byref(self.c)))
         self.recon = recon
+        if recon is not None:      # the library then synchronises the engine before and notifies it after every swap call
+            abi.check(_lib().dsb200_swap_attach_recon(self.h, recon.h))
 
     def close(self):
         if self.h:
@@ -417,8 +419,7 @@ class ITMSwappingEngine(object):
             self.h = None
 
     def _changed(self):
-        if self.recon is not None:
-            abi.check(_lib().dsb200_recon_notify_scene_modified(self.recon.h))
+        pass        # since dsb200_swap_attach_recon the library notifies the engine itself
 
     def MarkVisible(self, renderState):
         """the swap-state pass the reference's AllocateSceneFromDepth runs when useSwapping is on"""

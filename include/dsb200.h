@@ -457,6 +457,14 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
  * out (DS/DenseSlam.h:248-251).  scene->last_free_block is read and updated: synchronise an asynchronous engine first
  * (dsb200_recon_sync), and tell the engine afterwards (dsb200_recon_notify_scene_modified). */
 int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const dsb200_render_state *rs, int32_t *moved);
+/* Names the reconstruction engine that works on the same scene (NULL detaches).  While attached, IntegrateGlobalIntoLocal and
+ * SaveToGlobalMemory call dsb200_recon_refresh_mirrors before they read the free-list top (an ASYNCHRONOUS engine's host mirrors are stale
+ * until then) and dsb200_recon_notify_scene_modified after they changed the volume (device counters re-seeded, pending look-ahead
+ * undone, sdf shadow rebuilt on next use).  ITMSwappingEngine_B200 attaches the engine it is constructed with. */
+/* dsb200_recon_sync when the device counters are the authoritative ones (asynchronous engine with frames in flight), otherwise
+ * only a stream synchronisation: the host mirrors are then already current and are left alone */
+int dsb200_recon_refresh_mirrors(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs);
+int dsb200_swap_attach_recon(dsb200_swap *s, dsb200_recon *recon);
 /* ITMGlobalCache::SaveToFile / ReadFromFile (Objects/ITMGlobalCache.h:75-105): bool[total] then total blocks */
 int dsb200_swap_save_file(dsb200_swap *s, const char *path);
 int dsb200_swap_load_file(dsb200_swap *s, const char *path);

@@ -108,3 +108,31 @@ def test_swap_store_file_round_trip():
         assert abi.load().dsb200_swap_stored_block(broken.h, int(np.nonzero(has)[0][0])) in (None, 0)
         broken.close()
     swap.close(); gpu.close()
+
+
+def test_swapping_with_an_asynchronous_engine():
+    """SaveToGlobalMemory used the scene's HOST mirror of the free-list top, which is stale while the
+    reconstruction engine runs asynchronously.  With the engine attached (dsb200_swap_attach_recon) the swap calls refresh the
+    mirrors first and notify the engine afterwards, so an asynchronous pipeline with swap-outs in between -- no dsb200_recon_sync
+    by the caller anywhere -- ends in the oracle's state."""
+    cfg, frames, order, _ = hz.swap_scenario()
+    gpu = hz.GpuBackend(cfg, caps=SMALL, use_swapping=True)
+    ora = hz.OracleBackend(cfg, caps=SMALL, use_swapping=True)
+    swap = gpu.eng.ITMSwappingEngine(gpu.scene, 0x1000, recon=gpu.recon)
+    cache = po.HostSwapCache(ora.scene.c.total_entries, 0x1000)
+    gpu.recon.SetAsync(True)
+    for step, k in enumerate(order[:8]):
+        f = frames[k]
+        gpu.set_frame(f); ora.set_frame(f)
+        gpu.recon.ProcessFrame(gpu.vis, gpu.scene, gpu.view, gpu.trk, gpu.rs)      # asynchronous: host mirrors NOT updated
+        ora.process_frame()
+        swap.MarkVisible(gpu.rs); ora.o.swap_mark_visible(cache, ora.rs)
+        a, b = swap.IntegrateGlobalIntoLocal(gpu.scene), ora.o.swap_integrate_global_into_local(cache, ora.scene)
+        assert a == b, step
+        a, b = swap.SaveToGlobalMemory(gpu.scene, gpu.rs), ora.o.swap_save_to_global_memory(cache, ora.scene, ora.rs)
+        assert a == b, step
+    gpu.recon.Sync(gpu.scene, gpu.rs)
+    gpu.recon.SetAsync(False)
+    compare(gpu, ora, swap, cache, "asynchronous engine + swapping")
+    hz.assert_images_equal(gpu.images(), ora.images(), "asynchronous engine + swapping")
+    swap.close(); gpu.close(); ora.close()
