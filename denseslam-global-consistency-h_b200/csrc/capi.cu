@@ -118,7 +118,7 @@ struct dsb200_recon {
     unsigned long long modEpoch = 0, epochSceneWritten = ~0ull;   // scene-modifying calls so far / value when evSceneWritten was recorded
     bool prefetchPending = false;
     struct PrefetchKey { const float *depth; int w, h; float M[16], invM[16], intr[4]; const uint8_t *visType;
-                         uint8_t *visTypeRW; const int *visibleIds; const dsb200_hash_entry *hash; } prefetchKey{};
+                         uint8_t *visTypeRW; const int *visibleIds; const dsb200_hash_entry *hash; int useSwapping; } prefetchKey{};
     // SDF shadow: one short per voxel of the scene this engine maintains, kept in step by every kernel that writes voxels
     // (reset, integrate, de-integrate, pruning) and read by the fused frame's raycast instead of the 8-byte voxel records.
     short *sdfShadow = nullptr; const void *shadowFor = nullptr; bool shadowEnabled = true;
@@ -412,23 +412,30 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     }
 #define DSB_MARK_A(i) do { if (e->profile) cudaEventRecord(e->evAlloc[i], e->stream); } while (0)
     DSB_MARK_A(0);
+    VisParams VP; fill_mat(VP.M, trk->M_d); memcpy(VP.proj, view->intr_d, 16);
+    VP.voxelSize = scene->params.voxel_size; VP.W = AP.W; VP.H = AP.H;
+    VP.useSwapping = (scene->use_swapping && !onlyVisible) ? 1 : 0;
     if (e->prefetchPending) {
         const dsb200_recon::PrefetchKey &k = e->prefetchKey;
         if (k.depth != view->depth || k.w != AP.W || k.h != AP.H || k.visType != rs->visible_type || memcmp(k.M, trk->M_d, 64) ||
-            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost) {
+            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost || k.useSwapping != VP.useSwapping) {
             // the look-ahead is abandoned and undone (the scene is as it found it); the caller may allocate again
             int rc = abandon_prefetch(e); if (rc) return rc;
             return fail(DSB200_ERR_INVALID, "the pending prefetched allocation was made for a different view / pose / render state "
                                             "(it has been dropped and undone)");
         }
         e->prefetchPending = false;
-        CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));     // setToType3 + requests already ran on the look-ahead stream
+        CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));     // setToType3 + requests + frustum re-test already ran on the look-ahead stream
         DSB_MARK_A(1);
     } else {
         launch_begin_frame(e->stream, e->fs, scene->last_free_block, scene->last_free_excess, rs->no_visible, useHost ? 1 : 0,
                            rs->visible_ids, rs->visible_type, useHost ? rs->no_visible : rs->visible_capacity);
         DSB_MARK_A(1);
         launch_alloc_requests(e->stream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
+        // Frustum re-test of last frame's blocks that no depth ray re-observed (flag 3).  It reads only flags and block positions,
+        // so it runs BEFORE the ordered allocation (which then overrides the flag of a stale slot it re-allocates) -- and with
+        // the look-ahead it moves under the previous frame's raycast together with the request pass.
+        launch_recheck_visibility(e->stream, VP, e->fs, scene->hash, rs->visible_ids, rs->visible_type);
     }
     // The host mirrors seeded the device counters above (first asynchronous frame of an engine that has never synchronised);
     // from here on the device copies are the authoritative ones until the next dsb200_recon_sync.
@@ -448,10 +455,6 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     snap->chunk = e->arena.reserve(snap->regionInts, &snap->region);
     if (!snap->chunk) return fail(DSB200_ERR_CUDA, "out of device memory for the visible-list snapshot arena");
     snap->countDev = snap->region; snap->ids = snap->region + 64;
-    VisParams VP; fill_mat(VP.M, trk->M_d); memcpy(VP.proj, view->intr_d, 16);
-    VP.voxelSize = scene->params.voxel_size; VP.W = AP.W; VP.H = AP.H;
-    VP.useSwapping = (scene->use_swapping && !onlyVisible) ? 1 : 0;
-    launch_recheck_visibility(e->stream, VP, e->fs, scene->hash, rs->visible_ids, rs->visible_type);
     DSB_MARK_A(4);
     launch_visible_list(e->stream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, rs->visible_ids,
                         rs->visible_capacity, snap->ids, snap->countDev, (int)snapCap, e->total);
@@ -1218,11 +1221,15 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
     }
     launch_begin_frame(e->prefetchStream, e->fs, 0, 0, 0, 0, rs->visible_ids, rs->visible_type, rs->visible_capacity);
     launch_alloc_requests(e->prefetchStream, AP, e->fs, view->depth, scene->hash, rs->visible_type, e->reqKey);
+    VisParams VP; fill_mat(VP.M, trk->M_d); memcpy(VP.proj, view->intr_d, 16);
+    VP.voxelSize = scene->params.voxel_size; VP.W = AP.W; VP.H = AP.H;
+    VP.useSwapping = scene->use_swapping ? 1 : 0;       // the consuming call must be a full allocation (onlyUpdateVisibleList = false)
+    launch_recheck_visibility(e->prefetchStream, VP, e->fs, scene->hash, rs->visible_ids, rs->visible_type);
     CU(cudaGetLastError());
     CU(cudaEventRecord(e->evPrefetchDone, e->prefetchStream));
     dsb200_recon::PrefetchKey &k = e->prefetchKey;
     k.depth = view->depth; k.w = AP.W; k.h = AP.H; k.visType = rs->visible_type;
-    k.visTypeRW = rs->visible_type; k.visibleIds = rs->visible_ids; k.hash = scene->hash;
+    k.visTypeRW = rs->visible_type; k.visibleIds = rs->visible_ids; k.hash = scene->hash; k.useSwapping = VP.useSwapping;
     memcpy(k.M, trk->M_d, 64); memcpy(k.invM, trk->invM_d, 64); memcpy(k.intr, view->intr_d, 16);
     e->prefetchPending = true;
     return DSB200_OK;

@@ -218,8 +218,9 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
 
 // Frustum re-test of the slots that were visible last frame and were not re-observed by this frame's depth rays (flag 3;
 // CPU .cpp:268-285).  One thread per entry of the previous visible list = perfectly balanced, and the ordered compaction
-// that follows only has to look at flags.  Runs after k_allocate (a freed slot of the old list may just have been
-// re-allocated -> flag 1, no re-test, as in the serial engine).
+// that follows only has to look at flags.  Runs BEFORE k_allocate: it touches flag-3 slots only, and a freed slot of the old list
+// that this frame re-allocates gets its flag 1 from k_allocate afterwards, whatever the re-test of its stale position said
+// (as in the serial engine, where the allocation pass precedes the visibility pass and flag 1 is never re-tested).
 __global__ void __launch_bounds__(256) k_recheck_visibility(VisParams P, FrameState fs, const dsb200_hash_entry *__restrict__ hash,
                                                             const int *__restrict__ prevVisibleIds, uint8_t *visType)
 {
@@ -445,7 +446,7 @@ void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &
                snapshotIds, snapshotCount, snapshotCapacity, total);
 }
 
-// must run between launch_allocate and launch_visible_list: visibleIds still holds the PREVIOUS list at that point
+// must run after launch_alloc_requests and before launch_allocate / launch_visible_list: visibleIds still holds the PREVIOUS list
 void launch_recheck_visibility(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
                                const int *prevVisibleIds, uint8_t *visType)
 {

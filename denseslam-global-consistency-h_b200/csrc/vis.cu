@@ -16,6 +16,7 @@
 #include "kernels.cuh"
 #include "scan.cuh"
 #include "visibility.cuh"
+#include "exactdiv.cuh"
 
 namespace dsb {
 
@@ -280,6 +281,11 @@ __device__ __forceinline__ short read_sdf(const Tables &T, int bucketNum, int bu
     return 32767;
 }
 
+// x / 32767.0f, correctly rounded, in three instructions instead of the compiler's generic division sequence: one Markstein step
+// with the correctly rounded reciprocal is exact for this divisor (verified exhaustively over a full binade of numerators,
+// tests/test_exactdiv.py / oracle/exactdiv_check.c; 0 and every scaling by a power of two follow)
+__device__ __forceinline__ float div_32767(float x) { return div_step1(x, 32767.0f, 1.0f / 32767.0f); }
+
 __device__ __forceinline__ float round_half_away(float x) { return (x < 0) ? (x - 0.5f) : (x + 0.5f); }
 
 // findVoxel's block part: hash probe -> first voxel of the block, or nullptr (ITMRepresentationAccess.h:176-210)
@@ -343,7 +349,7 @@ __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, i
     float res2 = (1.0f - cx) * v001 + cx * v101;
     res2 = (1.0f - cy) * res2 + cy * ((1.0f - cx) * v011 + cx * v111);
     found = true;
-    return ((1.0f - cz) * res1 + cz * res2) / 32767.0f;
+    return div_32767((1.0f - cz) * res1 + cz * res2);
 }
 
 // castRay, DeviceAgnostic/ITMVisualisationEngine.h:124-196, in three pieces so that a march can be suspended and resumed (by
@@ -382,8 +388,8 @@ __device__ __forceinline__ RayStep ray_step(float rx, float ry, float rz, const 
                                             BlockCache &cache, float &sdf, float &stepLength)
 {
     bool found;
-    sdf = (float)read_sdf(T, P.bucketNum, P.bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
-                          (int)round_half_away(rz), found, cache) / 32767.0f;
+    sdf = div_32767((float)read_sdf(T, P.bucketNum, P.bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
+                                    (int)round_half_away(rz), found, cache));
     if (!found) { stepLength = (float)kBlock; return kStepJump; }
     if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(T, P.bucketNum, P.bucketMask, rx, ry, rz, found, cache);
     if (!(sdf > 0.0f)) return kStepHit;
@@ -422,8 +428,8 @@ __device__ __forceinline__ bool cast_ray_bounded(float4 &out, RayState &s, const
     int steps = maxSteps;                 // counts down; a negative cap never reaches 0
     while (totalLength < totalLengthMax && steps != 0) {
         steps--;
-        sdf = (float)read_sdf(T, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
-                              (int)round_half_away(rz), found, cache) / 32767.0f;
+        sdf = div_32767((float)read_sdf(T, bucketNum, bucketMask, (int)round_half_away(rx), (int)round_half_away(ry),
+                                        (int)round_half_away(rz), found, cache));
         if (!found) stepLength = (float)kBlock;
         else {
             if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdf_trilinear(T, bucketNum, bucketMask, rx, ry, rz, found, cache);
