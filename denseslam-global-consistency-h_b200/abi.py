@@ -197,6 +197,7 @@ def load():
         "dsb200_swap_save_file": (C.c_int, [vp, cp]),
         "dsb200_swap_load_file": (C.c_int, [vp, cp]),
         "dsb200_recon_notify_scene_modified": (C.c_int, [vp]),
+        "dsb200_recon_notify_volume_swapped": (C.c_int, [vp, _P(Scene)]),
         "dsb200_compute_normal_and_weights": (C.c_int, [vp, vp, vp, i32, i32, _P(C.c_float), vp]),
         "dsb200_recon_prefetch_allocation": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), vp]),
         "dsb200_recon_join_prefetch": (C.c_int, [vp]),

@@ -1320,6 +1320,23 @@ int dsb200_recon_notify_scene_modified(dsb200_recon *e)
     return DSB200_OK;
 }
 
+// the swapping engine's notification: it changed voxel blocks, entry pointers and scene->last_free_block and nothing else, so
+// only that one device counter is re-seeded -- an asynchronous engine's visible count (whose host mirror the swapping engine
+// never refreshed: it has no render state) and excess-list top stay the device's
+int dsb200_recon_notify_volume_swapped(dsb200_recon *e, const dsb200_scene *scene)
+{
+    if (!e || !scene) return fail(DSB200_ERR_INVALID, "notify_volume_swapped: null argument");
+    { int rc = abandon_prefetch(e); if (rc) return rc; }
+    if (e->async && e->deviceCountersValid) {
+        e->hostCounters->lastFreeBlock = scene->last_free_block;
+        CU(cudaMemcpyAsync(&e->fs.counters->lastFreeBlock, &e->hostCounters->lastFreeBlock, 4, cudaMemcpyHostToDevice, e->stream));
+    }
+    CU(cudaStreamSynchronize(e->stream));
+    e->shadowFor = nullptr;
+    e->modEpoch++;
+    return DSB200_OK;
+}
+
 int dsb200_recon_invalidate_sdf_shadow(dsb200_recon *e)
 {
     if (!e) return fail(DSB200_ERR_INVALID, "invalidate_sdf_shadow: null engine");

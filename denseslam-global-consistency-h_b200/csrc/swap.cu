@@ -224,7 +224,7 @@ struct dsb200_swap {
 // before a call that reads scene->last_free_block / changes the volume: bring the host mirrors up to date
 static int swap_enter(dsb200_swap *s, dsb200_scene *scene) { return s->recon ? dsb200_recon_refresh_mirrors(s->recon, scene, nullptr) : DSB200_OK; }
 // after it: the engine's device counters, look-ahead and sdf shadow describe the old volume
-static int swap_leave(dsb200_swap *s) { return s->recon ? dsb200_recon_notify_scene_modified(s->recon) : DSB200_OK; }
+static int swap_leave(dsb200_swap *s, const dsb200_scene *scene) { return s->recon ? dsb200_recon_notify_volume_swapped(s->recon, scene) : DSB200_OK; }
 
 static const int kChunkBlocks = 16384;                          // 64 MB of pinned memory per chunk
 static const size_t kBlockBytes = sizeof(dsb200_voxel) * DSB200_BLOCK_SIZE3;
@@ -364,7 +364,7 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
     DSB_LAUNCH(k_swap_integrate, n, 256, 0, s->stream, n, s->needed, s->blockPtrs, scene->hash, scene->voxels, s->states, scene->params.max_w);
     SWCU(cudaGetLastError());
     SWCU(cudaStreamSynchronize(s->stream));
-    return swap_leave(s);
+    return swap_leave(s, scene);
 }
 
 int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const dsb200_render_state *rs, int32_t *moved)
@@ -398,7 +398,7 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
     if (pushed < 0) pushed = 0;
     if (pushed > n) pushed = n;
     scene->last_free_block = lastFree0 + pushed;
-    return swap_leave(s);
+    return swap_leave(s, scene);
 }
 
 int dsb200_swap_attach_recon(dsb200_swap *s, dsb200_recon *recon)

@@ -459,8 +459,8 @@ int dsb200_swap_integrate_global_into_local(dsb200_swap *s, dsb200_scene *scene,
 int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const dsb200_render_state *rs, int32_t *moved);
 /* Names the reconstruction engine that works on the same scene (NULL detaches).  While attached, IntegrateGlobalIntoLocal and
  * SaveToGlobalMemory call dsb200_recon_refresh_mirrors before they read the free-list top (an ASYNCHRONOUS engine's host mirrors are stale
- * until then) and dsb200_recon_notify_scene_modified after they changed the volume (device counters re-seeded, pending look-ahead
- * undone, sdf shadow rebuilt on next use).  ITMSwappingEngine_B200 attaches the engine it is constructed with. */
+ * until then) and dsb200_recon_notify_volume_swapped after they changed the volume (free-list top re-seeded on the device, pending
+ * look-ahead undone, sdf shadow rebuilt on next use).  ITMSwappingEngine_B200 attaches the engine it is constructed with. */
 /* dsb200_recon_sync when the device counters are the authoritative ones (asynchronous engine with frames in flight), otherwise
  * only a stream synchronisation: the host mirrors are then already current and are left alone */
 int dsb200_recon_refresh_mirrors(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs);
@@ -471,6 +471,11 @@ int dsb200_swap_load_file(dsb200_swap *s, const char *path);
 /* Voxels, hash pointers or the free list were changed behind the reconstruction engine's back (swapping): device counters
  * are re-seeded from the scene's host mirrors, the sdf shadow is rebuilt on first use, a pending look-ahead is dropped. */
 int dsb200_recon_notify_scene_modified(dsb200_recon *e);
+/* The narrower notification the swapping engine sends (it changes voxel blocks, entry pointers and scene->last_free_block only):
+ * an asynchronous engine keeps its device-side visible count and excess-list top, takes scene->last_free_block, drops a pending
+ * look-ahead and rebuilds the sdf shadow on next use.  (The host mirror of the visible count lives in a render state the
+ * swapping engine never sees, so re-seeding every counter from host mirrors would lose the visible list.) */
+int dsb200_recon_notify_volume_swapped(dsb200_recon *e, const dsb200_scene *scene);
 
 /* ---- diagnostics of the exact-division fast paths (csrc/exactdiv.cuh) ----
  * force_plain_division: run the integrate / de-integrate kernel variants that use the compiler's `/` everywhere.
