@@ -26,6 +26,7 @@ FRAME_ALLOCATE, FRAME_INTEGRATE, FRAME_EXPECTED_DEPTHS, FRAME_ICP_MAPS, FRAME_AL
 FRAME_RAYCAST = 16
 # TrackerIterationType, ITMLib/Utils/ITMLibDefines.h:289-295
 TRACKER_ITERATION_ROTATION, TRACKER_ITERATION_TRANSLATION, TRACKER_ITERATION_BOTH, TRACKER_ITERATION_NONE = 1, 2, 3, 4
+TRACKER_STATIC_MAX_PIXELS = 1 << 22          # dsb200_tracker_compute_g_and_h_static: largest view image
 TRACKER_MAX_LEVELS = 8
 IPC_HANDLE_BYTES = 64
 MAX_SHARDS = 16
@@ -209,6 +210,8 @@ def load():
         "dsb200_tracker_compute_g_and_h_on": (C.c_int, [vp, vp, i32, i32, _P(C.c_float), vp, vp, i32, i32, _P(C.c_float), _P(C.c_float),
                                                         i32, C.c_float, _P(C.c_float), _P(C.c_float), _P(C.c_float), _P(C.c_float), _P(i32)]),
         "dsb200_tracker_last_sums": (C.c_int, [vp, _P(C.c_double)]),
+        "dsb200_tracker_compute_g_and_h_static": (C.c_int, [vp, i32, i32, _P(C.c_float), vp, vp, i32, i32, _P(C.c_float), _P(C.c_float),
+                                                            i32, C.c_float, _P(C.c_float), vp, vp]),
         "dsb200_tracker_level": (C.c_int, [vp, i32, _P(vp), _P(i32), _P(i32), _P(C.c_float)]),
         "dsb200_filter_subsample_with_holes": (C.c_int, [vp, i32, i32, vp, vp]),
         "dsb200_tracker_track_camera": (C.c_int, [vp, _P(TrackerConfig), _P(View), _P(Tracking), _P(C.c_float), i32, i32,

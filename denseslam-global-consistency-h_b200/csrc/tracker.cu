@@ -13,6 +13,8 @@
 // tree: grid-stride pixels per thread, xor-shuffle per warp, warps in order per CTA, CTA partials in eight interleaved
 // chains combined in order by the last CTA to finish.  The result does not depend on scheduling, and is the correctly-rounded sum to about 1e-13 relative,
 // which the parity tests check against the oracle's double-precision serial sum (and, loosely, its float serial sum).
+#include <mutex>
+
 #include "kernels.cuh"
 
 namespace dsb {
@@ -235,4 +237,77 @@ void launch_tracker_gh(cudaStream_t st, int iterationType, const float *approxIn
         DSB_LAUNCH((k_tracker_gh<false, false>), grid, kGhThreads, 0, st, P, depth, pts, nrm, partials, ticket, result, seq);
 }
 
+
+// ---------------------------------------------------------------- the allocation-free evaluation
+// dsb200_tracker_compute_g_and_h_static (include/dsb200.h): the same kernel, its reduction scratch (CTA partials + ticket) in a
+// file-scope device array instead of a dsb200_tracker's cudaMalloc'ed buffers, the sums written to a caller-owned DEVICE buffer
+// instead of the tracker's mapped host memory.  No counterpart in the reference; added for
+// callers that cannot allocate (CUDA graph capture, serving loops).  Every GPU that loads libdsb200 holds the array until exit.
+namespace {
+constexpr int kStaticMaxCtas = kNumSMs * 2;                                   // = tracker_gh_max_ctas(): the grid never exceeds it
+constexpr size_t kStaticPartialBytes = (size_t)kStaticMaxCtas * kGhSlots * sizeof(double);   // 296 * 32 * 8 = 75,776 B
+constexpr size_t kStaticScratchBytes = kStaticPartialBytes + 256;            // + the ticket, on its own 256-byte line
+constexpr int kStaticMaxDevices = 64;
+}
+static __device__ __align__(256) unsigned char g_tracker_static_scratch[kStaticScratchBytes];
+
+int fail_with(int code, const char *msg);      // capi.cu: sets dsb200_last_error
+
+namespace {
+// In host code `g_tracker_static_scratch` names a host-side stand-in, not device memory: the device address is asked for once
+// per device, with that device current, and cached.
+std::mutex g_static_mutex;
+unsigned char *g_static_ptr[kStaticMaxDevices] = {};
+int static_scratch_for_current_device(unsigned char **out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail_with(DSB200_ERR_CUDA, cudaGetErrorString(e));
+    if (dev < 0 || dev >= kStaticMaxDevices) return fail_with(DSB200_ERR_INVALID, "tracker_compute_g_and_h_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_ptr[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_tracker_static_scratch);
+        if (e != cudaSuccess || !p) return fail_with(DSB200_ERR_CUDA, e != cudaSuccess ? cudaGetErrorString(e) : "cudaGetSymbolAddress returned null");
+        g_static_ptr[dev] = static_cast<unsigned char *>(p);
+    }
+    *out = g_static_ptr[dev];
+    return DSB200_OK;
+}
+} // namespace
+
 } // namespace dsb
+
+extern "C" int dsb200_tracker_compute_g_and_h_static(const float *depth, int32_t vW, int32_t vH, const float *vIntr, const float *points,
+                                                     const float *normals, int32_t sW, int32_t sH, const float *sIntr,
+                                                     const float *scenePose, int32_t iterationType, float distThresh,
+                                                     const float *approxInvPose, double *sums, void *stream)
+{
+    using namespace dsb;
+    if (!depth || !vIntr || !points || !normals || !sIntr || !scenePose || !approxInvPose || !sums)
+        return fail_with(DSB200_ERR_INVALID, "tracker_compute_g_and_h_static: null argument");
+    if (vW <= 0 || vH <= 0 || sW < 2 || sH < 2 || sW > 32767 || sH > 32767 || ((uintptr_t)points & 15) || ((uintptr_t)normals & 15) ||
+        ((uintptr_t)sums & 7))
+        return fail_with(DSB200_ERR_INVALID, "tracker_compute_g_and_h_static: bad image size or unaligned maps");
+    if ((long long)vW * vH > (long long)DSB200_TRACKER_STATIC_MAX_PIXELS)
+        return fail_with(DSB200_ERR_INVALID, "tracker_compute_g_and_h_static: view image larger than DSB200_TRACKER_STATIC_MAX_PIXELS (4,194,304 pixels)");
+    if (iterationType != DSB200_TRACKER_ITERATION_ROTATION && iterationType != DSB200_TRACKER_ITERATION_TRANSLATION &&
+        iterationType != DSB200_TRACKER_ITERATION_BOTH)
+        return fail_with(DSB200_ERR_INVALID, "tracker_compute_g_and_h_static: unknown iteration type");
+    static_assert(kStaticMaxCtas * kGhSlots * sizeof(double) + 256 == DSB200_TRACKER_STATIC_SCRATCH_BYTES, "header states the array's size");
+    unsigned char *scratch = nullptr;
+    { int rc = static_scratch_for_current_device(&scratch); if (rc) return rc; }
+    cudaStream_t st = (cudaStream_t)stream;
+    double *partials = reinterpret_cast<double *>(scratch);
+    unsigned *ticket = reinterpret_cast<unsigned *>(scratch + kStaticPartialBytes);
+    // the array keeps the last call's contents: the partials of the CTAs this launch uses are all overwritten before they are
+    // read; the ticket must start at 0 (the kernel re-arms it, but an aborted earlier launch would not have)
+    cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(sums, 0, kGhSlots * sizeof(double), st);    // the slots this iteration type does not use read 0
+    if (e != cudaSuccess) return fail_with(DSB200_ERR_CUDA, cudaGetErrorString(e));
+    launch_tracker_gh(st, iterationType, approxInvPose, scenePose, vIntr, sIntr, distThresh, depth, vW, vH, points, normals, sW, sH,
+                      partials, ticket, sums, 0.0);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail_with(DSB200_ERR_CUDA, cudaGetErrorString(e));
+    return DSB200_OK;
+}

@@ -363,6 +363,26 @@ int dsb200_tracker_compute_g_and_h_on(dsb200_tracker *t, const float *depth, int
                                       const float *scene_pose, int32_t iteration_type, float dist_thresh,
                                       const float *approx_inv_pose, float *f, float *nabla, float *hessian,
                                       int32_t *no_valid_points);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The ComputeGandH evaluation of
+ * dsb200_tracker_compute_g_and_h_on without a dsb200_tracker: it allocates NOTHING (no cudaMalloc / cudaFree / cudaMallocHost, no
+ * allocating library routine), its reduction scratch (CTA partials + ticket) is a file-scope `static __device__` array of
+ * DSB200_TRACKER_STATIC_SCRATCH_BYTES that every GPU loading libdsb200 holds until exit, and it is ASYNCHRONOUS on cuda_stream.
+ * All image / map pointers are DEVICE pointers as above; the matrices and intrinsics are HOST floats read at the call.
+ * sums: caller-owned DEVICE buffer of 32 doubles, 8-byte aligned, written by the kernel: the raw sums in the layout of
+ * dsb200_tracker_last_sums (bit-identical to it: same kernel, same grid, same fixed summation tree); the slots after the valid
+ * count (3-parameter iterations use 11 of them, BOTH uses 29) are 0.
+ * Limits: view_w * view_h <= DSB200_TRACKER_STATIC_MAX_PIXELS (larger -> DSB200_ERR_INVALID); iteration type NONE is rejected
+ * (nothing to launch).  ALL calls on one GPU share the one array: calls that may overlap on the GPU (different streams, or
+ * concurrent graph branches) RACE -- serialise them on one stream.  The ticket word is cleared by a cudaMemsetAsync on the same
+ * stream before every launch; the partials need no clearing (every slot read was written by the same launch). */
+#define DSB200_TRACKER_STATIC_MAX_PIXELS (1 << 22)          /* 2048 x 2048 */
+#define DSB200_TRACKER_STATIC_SCRATCH_BYTES (296 * 32 * 8 + 256)   /* 76,032 B of device memory per GPU */
+int dsb200_tracker_compute_g_and_h_static(const float *depth, int32_t view_w, int32_t view_h, const float *view_intrinsics,
+                                          const float *points, const float *normals, int32_t scene_w, int32_t scene_h,
+                                          const float *scene_intrinsics, const float *scene_pose, int32_t iteration_type,
+                                          float dist_thresh, const float *approx_inv_pose, double *sums /* DEVICE [32] */,
+                                          void *cuda_stream);
 /* raw double sums of the last compute_g_and_h: [0,NH) hessian lower triangle by rows, [NH,NH+NP) nabla, sum b^2, count */
 int dsb200_tracker_last_sums(const dsb200_tracker *t, double *sums /* [32] */);
 /* pyramid level access (device pointer owned by the tracker; level 0 is the caller's image) */
