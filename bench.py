@@ -447,7 +447,7 @@ def measure_workload(args, rank, world, local_rank, full):
     # compared with the digest the CPU checker produced for the same frames (tests/golden/bench_digests.json)
     parity = {}
     if rank == 0:
-        abi.check(lib.dsb200_recon_join_prefetch(recon.h))
+        abi.check(lib.dsb200_recon_abandon_prefetch(recon.h))     # a pending (deep) look-ahead holds frame k+1's entries: undone exactly
         abi.check(lib.dsb200_stream_synchronize(None))
         verdict, key = check_digest(state_digest_of(digest, eng, scene, rs, trk, recon), Wm + K)
         parity = {"resident_pass": verdict, "golden": key}
@@ -488,27 +488,35 @@ def measure_workload(args, rank, world, local_rank, full):
         abi.check(lib.dsb200_view_from_raw(raw_d[b].ptr, raw_c[b].ptr, mm_to_m, 0.0, C.byref(views_e[b].c), s_up.cuda_stream))
         ev_ready[b].record(s_up)
 
+    host_s = {"upload": 0.0, "process_frame": 0.0, "prune": 0.0, "lookahead": 0.0, "readback": 0.0}   # host time spent enqueueing
+
     def frame_e2e(i, last):
         b = i & 1
+        t_a = time.perf_counter()
         if i + 1 < last:
             upload(i + 1)                                    # prefetch the next frame
+        t_b = time.perf_counter(); host_s["upload"] += t_b - t_a
         main.wait_event(ev_ready[b])
         main.wait_event(ev_read[b])                          # image buffer b was read back two frames ago
         views_e[b].c.timestamp = frames[i].timestamp
         trk.set_pose(frames[i].M)
         rs.c.raycast_image = imgs_e[b]
         abi.check(lib.dsb200_process_frame(recon.h, vis.h, C.byref(scene.c), C.byref(views_e[b].c), C.byref(trk.c), C.byref(rs.c), abi.FRAME_ALL))
+        t_c = time.perf_counter(); host_s["process_frame"] += t_c - t_b
         prune_pass()
+        t_d = time.perf_counter(); host_s["prune"] += t_d - t_c
         if lookahead and i + 1 < last:
             nb = (i + 1) & 1                                 # request pass of frame i+1 as soon as its upload has landed
             trk.set_pose(frames[i + 1].M)
             abi.check(lib.dsb200_recon_prefetch_allocation(recon.h, C.byref(scene.c), C.byref(views_e[nb].c), C.byref(trk.c), C.byref(rs.c),
                                                            ev_ready[nb].cuda_event))
+        t_e = time.perf_counter(); host_s["lookahead"] += t_e - t_d
         ev_free[b].record(main)
         ev_done[b].record(main)
         s_down.wait_event(ev_done[b])
         abi.check(lib.dsb200_memcpy_d2h(h_outs[b].data_ptr(), imgs_e[b], npx * 4, s_down.cuda_stream))
         ev_read[b].record(s_down)
+        host_s["readback"] += time.perf_counter() - t_e
 
     recon.SetAsync(True)
     for b in range(2):
@@ -521,6 +529,8 @@ def measure_workload(args, rank, world, local_rank, full):
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for key in host_s:
+        host_s[key] = 0.0
     t0 = time.perf_counter()
     e0.record()
     for k in range(K):
@@ -531,12 +541,15 @@ def measure_workload(args, rank, world, local_rank, full):
     torch.cuda.synchronize()
     e2e_wall = time.perf_counter() - t0
     recon.Sync(scene, rs)
+    abi.check(lib.dsb200_recon_abandon_prefetch(recon.h))         # the successor's look-ahead (outside the timed region: undone)
     recon.SetAsync(False)
     if rank == 0:
         rs.c.raycast_image = imgs_e[(Wm + K - 1) & 1]      # the image buffer the last frame rendered into
         parity["e2e_pass"] = check_digest(state_digest_of(digest, eng, scene, rs, trk, recon), Wm + K)[0]
     rs.c.raycast_image = imgs_e[0]
     e2e_ms = max(float(e0.elapsed_time(e1)), 1000.0 * e2e_wall)
+    e2e_detail = {"device_ms_per_step": float(e0.elapsed_time(e1)) / K, "wall_ms_per_step": 1000.0 * e2e_wall / K,
+                  "host_enqueue_ms_per_step": {key: 1000.0 * v / K for key, v in host_s.items()}}
     if world > 1:
         dist.barrier()
         t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
@@ -574,14 +587,14 @@ def measure_workload(args, rank, world, local_rank, full):
            "config": {"workload": workload_text(),
                       "timed_region": "per frame: CUDA-event pair around the frame's launches (process_frame, pruning, the look-ahead); the L2 "
                                       "flush and the host's counter read-back between frames are outside the pairs; e2e is one closed wall-clock region",
-                      "lookahead": ("request pass of frame k+1 submitted with frame k and joined before frame k's closing event (results bit-identical)"
+                      "lookahead": ("allocation of frame k+1 (request pass, ordered allocation as pending entries, visible list) submitted with frame k and joined before frame k's closing event (results bit-identical)"
                                     if lookahead else "off"), "frames": K, "mean_visible_blocks": V,
                       "blocks_allocated": int(blocks_used), "capacity_blocks": CAPS["num_blocks"], "l2": "flushed (256 MiB write) between timed steps"},
            "e2e": {"value": world * K / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": 5 * npx,
-                   "d2h_bytes_per_step": 4 * npx, "ms_per_step": e2e_ms / K,
+                   "d2h_bytes_per_step": 4 * npx, "ms_per_step": e2e_ms / K, "detail": e2e_detail,
                    "input": "int16 mm depth + packed BGR from pinned host memory, view built on the device (dsb200_view_from_raw)",
                    "pipeline": "double-buffered: upload of frame k+1 and read-back of frame k-1 overlap the fusion of frame k; one host sync at the end"
-                               + ("; allocation request pass of frame k+1 overlaps the raycast of frame k (dsb200_recon_prefetch_allocation)" if lookahead else "")},
+                               + ("; allocation of frame k+1 (request pass, ordered allocation with pending entries, visible list) overlaps the raycast of frame k (dsb200_recon_prefetch_allocation)" if lookahead else "")},
            "gpu_launches": launches, "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": stage_names[dom], "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": achieved / pk["hbm_gbs"], "traffic": traffic, "traffic_captured_at": traffic_src,
@@ -844,7 +857,8 @@ def measure_sharded(args, rank, world, local_rank, mode, build_frames=None):
     clocks = sampler.stop()
     launches = int(lib.dsb200_kernel_launch_count() - l0)
     dist.barrier()
-    ms = float(sum(a.elapsed_time(b) for a, b in evs))
+    step_ms = np.array([a.elapsed_time(b) for a, b in evs])
+    ms = float(step_ms.sum())
     blocks = caps["num_blocks"] - 1 - sc.m.scene.c.last_free_block
     t = torch.tensor([ms, float(blocks), float(np.mean(vis_counts))], dtype=torch.float64, device=dev)
     tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -868,6 +882,8 @@ def measure_sharded(args, rank, world, local_rank, mode, build_frames=None):
             "visible_blocks_per_shard": [float(x[2]) for x in per_shard], "ms_per_shard": [float(x[0]) / K for x in per_shard],
             "collectives_per_step": {"broadcast_bytes": 8 * npx + 72, "rendezvous_allreduce_4B": 2,
                                      "peer_reads_bytes_per_gpu": (16 * npx) if mode == "composite" else None},
+            "step_ms_rank0": {"p10": float(np.percentile(step_ms, 10)), "p50": float(np.percentile(step_ms, 50)),
+                              "p90": float(np.percentile(step_ms, 90)), "max": float(step_ms.max())},
             "gpu_launches": launches, "clocks": clocks}
 
 

@@ -202,6 +202,7 @@ def load():
         "dsb200_compute_normal_and_weights": (C.c_int, [vp, vp, vp, i32, i32, _P(C.c_float), vp]),
         "dsb200_recon_prefetch_allocation": (C.c_int, [vp, _P(Scene), _P(View), _P(Tracking), _P(RenderState), vp]),
         "dsb200_recon_join_prefetch": (C.c_int, [vp]),
+        "dsb200_recon_abandon_prefetch": (C.c_int, [vp]),
         "dsb200_tracker_create": (C.c_int, [_P(vp), i32, i32, i32, vp]),
         "dsb200_tracker_destroy": (C.c_int, [vp]),
         "dsb200_tracker_set_evaluation_data": (C.c_int, [vp, vp, _P(C.c_float), vp, vp, i32, i32, _P(C.c_float), _P(C.c_float)]),

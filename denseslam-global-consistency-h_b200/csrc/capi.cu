@@ -118,7 +118,10 @@ struct dsb200_recon {
     unsigned long long modEpoch = 0, epochSceneWritten = ~0ull;   // scene-modifying calls so far / value when evSceneWritten was recorded
     bool prefetchPending = false;
     struct PrefetchKey { const float *depth; int w, h; float M[16], invM[16], intr[4]; const uint8_t *visType;
-                         uint8_t *visTypeRW; const int *visibleIds; const dsb200_hash_entry *hash; int useSwapping; } prefetchKey{};
+                         uint8_t *visTypeRW; const int *visibleIds; const dsb200_hash_entry *hash; int useSwapping;
+                         bool deep; dsb200_hash_entry *hashRW; } prefetchKey{};
+    // deep look-ahead (recon_alloc.cu): undo / commit list of the ordered allocation, second visible-list buffer
+    int *deepBuf = nullptr; int *nextVisible = nullptr; int nextVisibleCap = 0;
     // SDF shadow: one short per voxel of the scene this engine maintains, kept in step by every kernel that writes voxels
     // (reset, integrate, de-integrate, pruning) and read by the fused frame's raycast instead of the 8-byte voxel records.
     short *sdfShadow = nullptr; const void *shadowFor = nullptr; bool shadowEnabled = true;
@@ -218,6 +221,7 @@ int dsb200_recon_destroy(dsb200_recon *e)
     cudaFree(e->reqKey); cudaFree(e->slotMark); cudaFree(e->pruneScratch); cudaFree(e->fs.counters);
     cudaFree(e->fs.scanState); cudaFree(e->fs.tickets); cudaFreeHost(e->hostCounters);
     cudaFree(e->fs.reqBits); cudaFree(e->fs.visBits); cudaFree(e->sdfShadow); cudaFree(e->weightImage);
+    cudaFree(e->deepBuf); cudaFree(e->nextVisible);
     delete e;
     return DSB200_OK;
 }
@@ -358,6 +362,24 @@ static short *shadow_for(dsb200_recon *e, const dsb200_scene *scene)
     return e->sdfShadow;
 }
 
+// deep look-ahead buffers: 8 ints per voxel block of capacity (slot, parent, 6 saved words) -- a frame cannot allocate more
+// blocks than the free list holds -- and a second visible list as large as the render state's
+static DeepList deep_list(const dsb200_recon *e)
+{
+    DeepList d; d.slot = e->deepBuf; d.parent = e->deepBuf + e->numBlocks; d.old = e->deepBuf + 2 * (size_t)e->numBlocks; d.capacity = e->numBlocks;
+    return d;
+}
+static bool deep_buffers(dsb200_recon *e, int visibleCapacity)
+{
+    if (!e->deepBuf && cudaMalloc(&e->deepBuf, (size_t)e->numBlocks * 8 * sizeof(int)) != cudaSuccess) { cudaGetLastError(); e->deepBuf = nullptr; return false; }
+    if (visibleCapacity > e->nextVisibleCap) {
+        cudaFree(e->nextVisible); e->nextVisible = nullptr; e->nextVisibleCap = 0;
+        if (cudaMalloc(&e->nextVisible, (size_t)visibleCapacity * sizeof(int)) != cudaSuccess) { cudaGetLastError(); return false; }
+        e->nextVisibleCap = visibleCapacity;
+    }
+    return true;
+}
+
 // Drop a pending look-ahead: wait for its kernels, then undo what they wrote (request keys / bitmaps, visibility flags) so
 // that the next, un-prefetched allocation starts from the state the look-ahead found.
 static int abandon_prefetch(dsb200_recon *e)
@@ -365,6 +387,7 @@ static int abandon_prefetch(dsb200_recon *e)
     if (!e->prefetchPending) return DSB200_OK;
     const dsb200_recon::PrefetchKey &k = e->prefetchKey;
     CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));
+    if (k.deep) launch_abandon_allocation(e->stream, e->fs, k.hashRW, deep_list(e));   // the table is bit for bit what the look-ahead found
     launch_abandon_requests(e->stream, e->fs, k.hash, k.visibleIds, k.visTypeRW, e->reqKey, e->total);
     CU(cudaGetLastError());
     e->prefetchPending = false;
@@ -406,6 +429,7 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     // noSteps = ceil(2 * |segment| / blockSize) with |segment| = 2*mu (+ rounding): must fit the 8-bit step field
     if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
     const bool useHost = !(e->async && e->deviceCountersValid);
+    bool deepDone = false;
     if (rs->visible_type != e->visBitsOwner) {     // a render state this engine has not been tracking: derive its bitmap
         launch_rebuild_visbits(e->stream, e->fs, rs->visible_type, e->total);
         e->visBitsOwner = rs->visible_type;
@@ -418,7 +442,8 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     if (e->prefetchPending) {
         const dsb200_recon::PrefetchKey &k = e->prefetchKey;
         if (k.depth != view->depth || k.w != AP.W || k.h != AP.H || k.visType != rs->visible_type || memcmp(k.M, trk->M_d, 64) ||
-            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost || k.useSwapping != VP.useSwapping) {
+            memcmp(k.invM, trk->invM_d, 64) || memcmp(k.intr, view->intr_d, 16) || useHost || k.useSwapping != VP.useSwapping ||
+            (k.deep && (onlyVisible || k.hashRW != scene->hash))) {
             // the look-ahead is abandoned and undone (the scene is as it found it); the caller may allocate again
             int rc = abandon_prefetch(e); if (rc) return rc;
             return fail(DSB200_ERR_INVALID, "the pending prefetched allocation was made for a different view / pose / render state "
@@ -426,6 +451,7 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
         }
         e->prefetchPending = false;
         CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));     // setToType3 + requests + frustum re-test already ran on the look-ahead stream
+        deepDone = k.deep;                                            // ... and so did the ordered allocation and the visible-list build
         DSB_MARK_A(1);
     } else {
         launch_begin_frame(e->stream, e->fs, scene->last_free_block, scene->last_free_excess, rs->no_visible, useHost ? 1 : 0,
@@ -441,8 +467,9 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     // from here on the device copies are the authoritative ones until the next dsb200_recon_sync.
     if (e->async) e->deviceCountersValid = true;
     DSB_MARK_A(2);
-    launch_allocate(e->stream, AP, e->fs, view->depth, scene->hash, scene->alloc_list, scene->excess_list, rs->visible_type,
-                    e->reqKey, e->total, onlyVisible ? 0 : 1);
+    if (!deepDone)
+        launch_allocate(e->stream, AP, e->fs, view->depth, scene->hash, scene->alloc_list, scene->excess_list, rs->visible_type,
+                        e->reqKey, e->total, onlyVisible ? 0 : 1);
     DSB_MARK_A(3);
     // snapshot reservation for decay / slide window / de-fusion (CUDA .cu:257-317)
     SnapPtr snap = std::make_shared<Snapshot>();
@@ -456,8 +483,12 @@ static int enqueue_allocate(dsb200_recon *e, dsb200_scene *scene, const dsb200_v
     if (!snap->chunk) return fail(DSB200_ERR_CUDA, "out of device memory for the visible-list snapshot arena");
     snap->countDev = snap->region; snap->ids = snap->region + 64;
     DSB_MARK_A(4);
-    launch_visible_list(e->stream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, rs->visible_ids,
-                        rs->visible_capacity, snap->ids, snap->countDev, (int)snapCap, e->total);
+    if (deepDone)      // pending entries -> entries, the list built beside the last raycast -> the render state (+ snapshot), counters
+        launch_commit_allocation(e->stream, e->fs, scene->hash, deep_list(e), e->nextVisible, rs->visible_ids, rs->visible_capacity,
+                                 snap->ids, snap->countDev, (int)snapCap);
+    else
+        launch_visible_list(e->stream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, rs->visible_ids,
+                            rs->visible_capacity, snap->ids, snap->countDev, (int)snapCap, e->total);
     DSB_MARK_A(5);
     if (e->profile) e->evAllocRecorded = true;
     e->unsynced.push_back(snap);
@@ -1212,7 +1243,8 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
     if (4.0f * AP.mu * AP.oneOverBlock + 2.0f > 250.0f) return fail(DSB200_ERR_INVALID, "mu / block size ratio too large for the 8-bit step order key");
     // Wait only for the last kernel that wrote the scene when that was the integration of the frame just submitted (its
     // raycast then overlaps the look-ahead); after any other scene call, wait for everything submitted so far.
-    if (e->epochSceneWritten != e->modEpoch) CU(cudaEventRecord(e->evSceneWritten, e->stream));
+    const bool behindIntegration = e->epochSceneWritten == e->modEpoch;
+    if (!behindIntegration) CU(cudaEventRecord(e->evSceneWritten, e->stream));
     CU(cudaStreamWaitEvent(e->prefetchStream, e->evSceneWritten, 0));
     if (waitEvent) CU(cudaStreamWaitEvent(e->prefetchStream, (cudaEvent_t)waitEvent, 0));
     if (rs->visible_type != e->visBitsOwner) {     // a render state this engine has not been tracking: derive its bitmap
@@ -1225,13 +1257,34 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
     VP.voxelSize = scene->params.voxel_size; VP.W = AP.W; VP.H = AP.H;
     VP.useSwapping = scene->use_swapping ? 1 : 0;       // the consuming call must be a full allocation (onlyUpdateVisibleList = false)
     launch_recheck_visibility(e->prefetchStream, VP, e->fs, scene->hash, rs->visible_ids, rs->visible_type);
+    // deep look-ahead (recon_alloc.cu): ordered allocation with PENDING entries + the visible list into the second buffer.  Not with
+    // swapping on (the visible-list pass then hands blocks back to swapped-out entries, which the running raycast would see).
+    // Nor when the look-ahead starts behind everything submitted so far (a pruning pass followed the frame): nothing is left to overlap
+    // with, and the pending / commit detour would only add work.
+    const bool deep = tunables().deep_lookahead != 0 && !VP.useSwapping && behindIntegration && deep_buffers(e, rs->visible_capacity);
+    if (deep) {
+        const DeepList dl = deep_list(e);
+        launch_allocate(e->prefetchStream, AP, e->fs, view->depth, scene->hash, scene->alloc_list, scene->excess_list, rs->visible_type,
+                        e->reqKey, e->total, 1, &dl);
+        launch_visible_list(e->prefetchStream, VP, e->fs, scene->hash, scene->alloc_list, rs->visible_type, e->nextVisible,
+                            rs->visible_capacity, nullptr, nullptr, 0, e->total, 1);
+    }
     CU(cudaGetLastError());
     CU(cudaEventRecord(e->evPrefetchDone, e->prefetchStream));
     dsb200_recon::PrefetchKey &k = e->prefetchKey;
     k.depth = view->depth; k.w = AP.W; k.h = AP.H; k.visType = rs->visible_type;
     k.visTypeRW = rs->visible_type; k.visibleIds = rs->visible_ids; k.hash = scene->hash; k.useSwapping = VP.useSwapping;
     memcpy(k.M, trk->M_d, 64); memcpy(k.invM, trk->invM_d, 64); memcpy(k.intr, view->intr_d, 16);
+    k.deep = deep; k.hashRW = scene->hash;
     e->prefetchPending = true;
+    return DSB200_OK;
+}
+
+int dsb200_recon_abandon_prefetch(dsb200_recon *e)
+{
+    if (!e) return fail(DSB200_ERR_INVALID, "abandon_prefetch: null engine");
+    { int rc = abandon_prefetch(e); if (rc) return rc; }
+    if (!e->async) CU(cudaStreamSynchronize(e->stream));
     return DSB200_OK;
 }
 

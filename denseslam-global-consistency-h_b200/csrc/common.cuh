@@ -120,6 +120,8 @@ struct Counters {
     int lastFreeExcessNew;
     int totalFreed;        // blocks released by all pruning passes since ResetScene (GetDecayedBlockCount)
     int snapshotOverflow;  // a visible-list snapshot did not fit its asynchronous reservation (sticky until the next sync)
+    int noVisibleNext;     // deep look-ahead: length of the NEXT frame's visible list (built beside this frame's raycast)
+    int numNew;            // deep look-ahead: allocation requests ranked by k_allocate (entries of the undo / commit list)
 };
 
 extern unsigned long long g_launches;   // kernels launched by this library (bench.py gpu_launches)

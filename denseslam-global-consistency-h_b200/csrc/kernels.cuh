@@ -71,6 +71,7 @@ struct Tunables {
     int fuse_kernel;      // integration kernel: 1 warp per block (round 1), 2 + straight-line depth part, 3 + TMA bulk block loads (default)
     int fuse_ctas;        // CTAs per SM of the flat integration kernel
     int fuse_minb;        // ... and its __launch_bounds__ minimum CTAs per SM (variant 2: 4, 6 or 8; variant 3: 4 or 5)
+    int deep_lookahead;   // dsb200_recon_prefetch_allocation also runs the ordered allocation and the visible-list build (1 = on)
 };
 Tunables &tunables();
 bool set_tunable(const char *name, int value);
@@ -94,12 +95,23 @@ void launch_abandon_requests(cudaStream_t st, const FrameState &fs, const dsb200
 void launch_recheck_visibility(cudaStream_t st, const VisParams &P, const FrameState &fs, const dsb200_hash_entry *hash,
                                const int *prevVisibleIds, uint8_t *visType);
 void launch_rebuild_visbits(cudaStream_t st, const FrameState &fs, const uint8_t *visType, int total);
+// deep look-ahead (recon_alloc.cu): what k_allocate wrote, by allocation rank
+constexpr int kPendingBase = -3;     // a pending entry's ptr = kPendingBase - block  (<= -3; -1 = swapped out, -2 = unallocated)
+struct DeepList {
+    int *slot;         // the entry written for this rank (ordered slot or excess child); -1: nothing written
+    int *parent;       // excess allocations: the chain end whose offset was set; else -1
+    int *old;          // 6 ints per rank: the entry's previous 5 words + the parent's previous offset
+    int capacity;
+};
 void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
                      dsb200_hash_entry *hash, const int *allocList, const int *excessList, uint8_t *visType,
-                     unsigned *reqKey, int total, int doAllocate);
+                     unsigned *reqKey, int total, int doAllocate, const DeepList *deep = nullptr);
 void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &fs, dsb200_hash_entry *hash,
                          const int *allocList, uint8_t *visType, int *visibleIds, int visibleCapacity, int *snapshotIds,
-                         int *snapshotCount, int snapshotCapacity, int total);
+                         int *snapshotCount, int snapshotCapacity, int total, int defer = 0);
+void launch_commit_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep, const int *nextIds,
+                              int *visibleIds, int visibleCapacity, int *snapshotIds, int *snapshotCount, int snapshotCapacity);
+void launch_abandon_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep);
 
 // recon_integrate.cu
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,

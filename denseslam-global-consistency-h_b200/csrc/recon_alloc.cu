@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(256) k_alloc_requests(AllocParams P, FrameStat
 __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, const float *__restrict__ depth,
                                                   dsb200_hash_entry *hash, const int *__restrict__ allocList,
                                                   const int *__restrict__ excessList, uint8_t *visType,
-                                                  unsigned *reqKey, int total, int doAllocate)
+                                                  unsigned *reqKey, int total, int doAllocate, DeepList deep)
 {
     __shared__ unsigned sScan[16];
     __shared__ int sTile;
@@ -187,20 +187,30 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
                 for (int s = 0; s < step; s++) { px += r.dx; py += r.dy; pz += r.dz; }
                 const short bx = (short)floorf(px), by = (short)floorf(py), bz = (short)floorf(pz);
                 const int vbaIdx = lastFreeBlock0 - (int)ra;
+                int written = -1, parent = -1;                // deep look-ahead: what this rank wrote
                 if (!isExcess) {
-                    if (vbaIdx >= 0) store_entry(hash, h, bx, by, bz, 0, allocList[vbaIdx], 0);
+                    if (vbaIdx >= 0) written = h;
                 } else {
                     const int exlIdx = lastFreeExcess0 - (int)rb;
-                    if (vbaIdx >= 0 && exlIdx >= 0) {
-                        const int exlOffset = excessList[exlIdx];
-                        const int child = P.bucketNum + exlOffset;
-                        reinterpret_cast<int *>(hash)[(size_t)h * 5 + 2] = exlOffset + 1;       // parent.offset
-                        store_entry(hash, child, bx, by, bz, 0, allocList[vbaIdx], 0);
-                        visType[child] = 1;
-                        atomicOr(&fs.visBits[child >> 5], 1u << (child & 31));
-                    }
+                    if (vbaIdx >= 0 && exlIdx >= 0) { written = P.bucketNum + excessList[exlIdx]; parent = h; }
                     rb++;
                 }
+                if (written >= 0) {
+                    int *pw = reinterpret_cast<int *>(hash) + (size_t)written * 5, *pp = reinterpret_cast<int *>(hash) + (size_t)h * 5 + 2;
+                    int ptr = allocList[vbaIdx];
+                    if (deep.slot && (int)ra < deep.capacity) {   // keep the bytes being overwritten (exact undo), publish the entry as PENDING (ra <= lastFreeBlock0 < capacity)
+                        int *o = deep.old + (size_t)ra * 6;
+                        o[0] = pw[0]; o[1] = pw[1]; o[2] = pw[2]; o[3] = pw[3]; o[4] = pw[4]; o[5] = parent >= 0 ? *pp : 0;
+                        ptr = kPendingBase - ptr;
+                    }
+                    if (parent >= 0) {
+                        *pp = written - P.bucketNum + 1;                                         // parent.offset
+                        visType[written] = 1;
+                        atomicOr(&fs.visBits[written >> 5], 1u << (written & 31));
+                    }
+                    store_entry(hash, written, bx, by, bz, 0, ptr, 0);
+                }
+                if (deep.slot && (int)ra < deep.capacity) { deep.slot[ra] = written; deep.parent[ra] = parent; }
                 ra++;
             }
         }
@@ -212,6 +222,7 @@ __global__ void __launch_bounds__(256) k_allocate(AllocParams P, FrameState fs, 
     if (threadIdx.x == 0 && tile == gridDim.x - 1) {
         fs.counters->lastFreeBlockNew = doAllocate ? lastFreeBlock0 - (int)(sEx[0] + totA) : lastFreeBlock0;
         fs.counters->lastFreeExcessNew = doAllocate ? lastFreeExcess0 - (int)(sEx[1] + totB) : lastFreeExcess0;
+        fs.counters->numNew = doAllocate ? (int)(sEx[0] + totA) : 0;
     }
     (void)total;
 }
@@ -262,7 +273,7 @@ __device__ __forceinline__ unsigned flag_mask32(const uint8_t *visType, int w, i
 __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs, dsb200_hash_entry *hash,
                                                       const int *__restrict__ allocList, uint8_t *visType,
                                                       int *visibleIds, int visibleCapacity, int *snapshotIds,
-                                                      int *snapshotCount, int snapshotCapacity, int total)
+                                                      int *snapshotCount, int snapshotCapacity, int total, int defer)
 {
     __shared__ unsigned sScan[16];
     __shared__ int sTile;
@@ -359,6 +370,7 @@ __global__ void __launch_bounds__(256) k_visible_list(VisParams P, FrameState fs
     }
     if (threadIdx.x == 0 && tile == gridDim.x - 1) {
         const int n = (int)(sEx[0] + totA);
+        if (defer) { fs.counters->noVisibleNext = n; return; }     // deep look-ahead: k_commit_allocation publishes the frame
         fs.counters->noVisible = n;
         if (snapshotCount) {
             const int m = n < visibleCapacity ? n : visibleCapacity;
@@ -406,7 +418,67 @@ __global__ void __launch_bounds__(256) k_abandon_requests_restore(FrameState fs,
     }
 }
 
+// DEEP LOOK-AHEAD.  With the request pass, the ordered allocation and the visible-list build of frame k+1 can run beside frame
+// k's raycast too, provided the raycast cannot see them: k_allocate (deep) publishes a new entry with ptr = kPendingBase - block
+// (<= -3: every reader of the table tests ptr >= 0 or ptr >= -1, so a pending entry reads as "no block here", which is the state
+// frame k's raycast must see; a torn read mixes two negative ptr values), keeps the 20 bytes it overwrote and the parent's old
+// offset, and k_visible_list (defer) builds the list into the engine's second buffer and leaves every counter of frame k alone.
+// The consuming allocation call then runs ONE small kernel: pending ptr -> ptr, list -> the render state (+ history snapshot),
+// counters committed.  An abandoned look-ahead restores the saved bytes: the table is bit for bit what it was.
+__global__ void __launch_bounds__(256) k_commit_allocation(FrameState fs, dsb200_hash_entry *hash, DeepList deep, const int *__restrict__ nextIds,
+                                                           int *visibleIds, int visibleCapacity, int *snapshotIds, int *snapshotCount,
+                                                           int snapshotCapacity)
+{
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    const int n = fs.counters->noVisibleNext;
+    int m = fs.counters->numNew; if (m > deep.capacity) m = deep.capacity;
+    for (int i = tid; i < m; i += stride) {
+        const int sl = deep.slot[i];
+        if (sl >= 0) { int *p = reinterpret_cast<int *>(hash) + (size_t)sl * 5 + 3; *p = kPendingBase - *p; }
+    }
+    const int nc = n < visibleCapacity ? n : visibleCapacity;
+    for (int i = tid; i < nc; i += stride) {
+        const int id = nextIds[i];
+        visibleIds[i] = id;
+        if (snapshotIds && i < snapshotCapacity) snapshotIds[i] = id;
+    }
+    if (tid == 0) {          // no thread of this kernel reads the fields written here
+        fs.counters->noVisible = n;
+        if (snapshotCount) {
+            *snapshotCount = nc < snapshotCapacity ? nc : snapshotCapacity;
+            if (nc > snapshotCapacity) fs.counters->snapshotOverflow = 1;
+        }
+        fs.counters->lastFreeBlock = fs.counters->lastFreeBlockNew;
+        fs.counters->lastFreeExcess = fs.counters->lastFreeExcessNew;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_abandon_allocation(FrameState fs, dsb200_hash_entry *hash, DeepList deep)
+{
+    int m = fs.counters->numNew; if (m > deep.capacity) m = deep.capacity;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += gridDim.x * blockDim.x) {
+        const int sl = deep.slot[i];
+        if (sl < 0) continue;
+        const int *o = deep.old + (size_t)i * 6;
+        int *p = reinterpret_cast<int *>(hash) + (size_t)sl * 5;
+        p[0] = o[0]; p[1] = o[1]; p[2] = o[2]; p[3] = o[3]; p[4] = o[4];
+        const int par = deep.parent[i];
+        if (par >= 0) reinterpret_cast<int *>(hash)[(size_t)par * 5 + 2] = o[5];
+    }
+}
+
 // ---------------------------------------------------------------- host launchers
+void launch_commit_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep, const int *nextIds,
+                              int *visibleIds, int visibleCapacity, int *snapshotIds, int *snapshotCount, int snapshotCapacity)
+{
+    DSB_LAUNCH(k_commit_allocation, kNumSMs, 256, 0, st, fs, hash, deep, nextIds, visibleIds, visibleCapacity, snapshotIds, snapshotCount,
+               snapshotCapacity);
+}
+void launch_abandon_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep)
+{
+    DSB_LAUNCH(k_abandon_allocation, kNumSMs, 256, 0, st, fs, hash, deep);
+}
+
 void launch_abandon_requests(cudaStream_t st, const FrameState &fs, const dsb200_hash_entry *hash, const int *visibleIds,
                              uint8_t *visType, unsigned *reqKey, int total)
 {
@@ -432,18 +504,19 @@ void launch_alloc_requests(cudaStream_t st, const AllocParams &P, const FrameSta
 
 void launch_allocate(cudaStream_t st, const AllocParams &P, const FrameState &fs, const float *depth,
                      dsb200_hash_entry *hash, const int *allocList, const int *excessList, uint8_t *visType,
-                     unsigned *reqKey, int total, int doAllocate)
+                     unsigned *reqKey, int total, int doAllocate, const DeepList *deep)
 {
+    DeepList d{}; if (deep) d = *deep;
     DSB_LAUNCH(k_allocate, fs.bitTiles, 256, 0, st, P, fs, depth, hash, allocList, excessList, visType, reqKey, total,
-               doAllocate);
+               doAllocate, d);
 }
 
 void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &fs, dsb200_hash_entry *hash,
                          const int *allocList, uint8_t *visType, int *visibleIds, int visibleCapacity, int *snapshotIds,
-                         int *snapshotCount, int snapshotCapacity, int total)
+                         int *snapshotCount, int snapshotCapacity, int total, int defer)
 {
     DSB_LAUNCH(k_visible_list, fs.bitTiles, 256, 0, st, P, fs, hash, allocList, visType, visibleIds, visibleCapacity,
-               snapshotIds, snapshotCount, snapshotCapacity, total);
+               snapshotIds, snapshotCount, snapshotCapacity, total, defer);
 }
 
 // must run after launch_alloc_requests and before launch_allocate / launch_visible_list: visibleIds still holds the PREVIOUS list

@@ -926,14 +926,14 @@ Tunables &tunables()
 {
     static Tunables t = {env_int("DSB200_RAY_STEPS", 0), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
                          env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 3), env_int("DSB200_FUSE_CTAS", 10),
-                         env_int("DSB200_FUSE_MINB", 5)};
+                         env_int("DSB200_FUSE_MINB", 5), env_int("DSB200_DEEP_LOOKAHEAD", 1)};
     return t;
 }
 bool set_tunable(const char *name, int value)
 {
     Tunables &t = tunables();
     const struct { const char *n; int *p; } table[] = {{"ray_steps", &t.ray_steps}, {"ray_group", &t.ray_group}, {"ray_ctas", &t.ray_ctas},
-        {"ray_finish_ctas", &t.ray_finish_ctas}, {"ray_bottom_up", &t.ray_bottom_up}, {"fuse_kernel", &t.fuse_kernel}, {"fuse_ctas", &t.fuse_ctas}, {"fuse_minb", &t.fuse_minb}};
+        {"ray_finish_ctas", &t.ray_finish_ctas}, {"ray_bottom_up", &t.ray_bottom_up}, {"fuse_kernel", &t.fuse_kernel}, {"fuse_ctas", &t.fuse_ctas}, {"fuse_minb", &t.fuse_minb}, {"deep_lookahead", &t.deep_lookahead}};
     for (const auto &e : table) if (!strcmp(e.n, name)) { *e.p = value; return true; }
     return false;
 }

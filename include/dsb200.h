@@ -314,6 +314,18 @@ int dsb200_recon_prefetch_allocation(dsb200_recon *e, dsb200_scene *scene, const
 /* Orders whatever is submitted next on the engine's stream after the pending look-ahead, without consuming it (for callers
  * that record timing events or flush caches between frames: bench.py).  dsb200_reset_scene abandons a pending look-ahead. */
 int dsb200_recon_join_prefetch(dsb200_recon *e);
+/* DEEP look-ahead (the default when the scene does not swap; tunable "deep_lookahead"): the look-ahead also runs the ordered
+ * allocation and the visible-list build of the next frame beside this frame's raycast.  Its new hash entries are PENDING until the
+ * consuming call: ptr = -3 - block, which every reader of the table (this library's and the reference's: they test ptr >= 0 or
+ * ptr >= -1) takes for "no block here" -- the state the running frame must see; the next visible list is built in an engine-owned
+ * buffer, and no counter of the current frame changes.  The consuming call commits all of it with one small kernel.  So between
+ * dsb200_recon_prefetch_allocation and the consuming call the caller's buffers hold frame k's visible list and counters, and frame
+ * k's table plus pending entries.  To read the table as frame k left it (checkpoints, digests), drop the look-ahead first: */
+/* Drops a pending look-ahead and UNDOES it: hash entries, parent offsets, request keys and bitmaps are restored bit for bit,
+ * visibility flags to "non-zero exactly for the members of the current visible list".  The next allocation then runs
+ * un-prefetched.  A no-op without a pending look-ahead.  (dsb200_recon_notify_scene_modified does the same and also re-seeds the
+ * device counters from the host mirrors.) */
+int dsb200_recon_abandon_prefetch(dsb200_recon *e);
 
 /* Volume checkpoint (the fork never calls ORUtils/MemoryBlockPersister.h, so the reference
  * has no save / resume): writes voxel.dat, alloc.dat, hash.dat, excess.dat -- and visible.dat, vistype.dat when rs is given --
@@ -504,7 +516,7 @@ int dsb200_recon_notify_volume_swapped(dsb200_recon *e, const dsb200_scene *scen
  * bit-level disagreements (must be 0). */
 int dsb200_debug_force_plain_division(dsb200_recon *e, int on);
 /* launch-shape knobs (csrc/kernels.cuh: Tunables; "ray_steps", "ray_group", "ray_ctas", "ray_finish_ctas", "ray_bottom_up",
- * "fuse_kernel"): process-wide, results never depend on them (tools/tune.py sweeps them on the GPU) */
+ * "fuse_kernel", "fuse_ctas", "fuse_minb", "deep_lookahead"): process-wide, results never depend on them (tools/tune.py sweeps them on the GPU) */
 int dsb200_debug_set_tunable(const char *name, int value);
 int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches);
 /* the bilateral filter's exp (csrc/view_filter.cu, a restatement of glibc's expf) on n HOST floats: y[i] = expf(x[i]);

@@ -55,7 +55,7 @@ def run_like_bench(workload, n_frames, checkpoints):
             ora.slide_window(prune["max_age"]); ora.decay(prune["max_weight"], prune["min_age"])
         if (i + 1) in checkpoints:
             gpu.recon.Sync(gpu.scene, gpu.rs)
-            abi.check(lib.dsb200_recon_join_prefetch(gpu.recon.h))
+            abi.check(lib.dsb200_recon_abandon_prefetch(gpu.recon.h))     # the deep look-ahead's pending entries of frame i+1 are undone (exactly)
             abi.check(lib.dsb200_stream_synchronize(None))
             got = bench.state_digest_of(digest, eng, gpu.scene, gpu.rs, gpu.trk, gpu.recon)
             want = oracle_digest(ora)
