@@ -228,6 +228,7 @@ def load():
         "dsb200_selftest_expf": (C.c_int, [vp, vp, i32]),
         "dsb200_selftest_acosf": (C.c_int, [vp, vp, i32]),
         "dsb200_swap_attach_recon": (C.c_int, [vp, vp]),
+        "dsb200_swap_set_store_budget": (C.c_int, [vp, i32]),
         "dsb200_recon_refresh_mirrors": (C.c_int, [vp, _P(Scene), _P(RenderState)]),
         "dsb200_mesher_create": (C.c_int, [_P(vp), i32, vp]),
         "dsb200_mesher_destroy": (C.c_int, [vp]),

@@ -210,6 +210,7 @@ struct dsb200_swap {
     cudaStream_t stream = nullptr;
     // "global memory": flags + slot per entry, blocks in pinned chunks
     uint8_t *hasStored = nullptr; int *slotOf = nullptr; int slotsUsed = 0;
+    int budgetBlocks = 0;          // most blocks the (pinned) host store may hold; 0 = as many as the table has entries
     std::vector<char *> chunks;
     // device
     uint8_t *states = nullptr; int *needed = nullptr, *tileCount = nullptr, *tileOffset = nullptr, *result = nullptr;
@@ -379,11 +380,24 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
     if (rc) return rc;
     if (moved) *moved = n;
     if (n == 0) return DSB200_OK;
-    for (int i = 0; i < n; i++) {                               // SetStoredData's destination, Objects/ITMGlobalCache.h:30-34
-        char *slot = slot_for(s, s->neededHost[i]);
-        if (!slot) return fail_with(DSB200_ERR_CUDA, "swap_save_to_global_memory: could not allocate a pinned chunk of the host store");
+    // Destinations first (SetStoredData, Objects/ITMGlobalCache.h:30-34); nothing has been changed yet.  The store is pinned
+    // memory: when its budget is used up or the next chunk cannot be pinned, the call moves the candidates that still fit (a
+    // shorter transfer, as if the transfer limit were lower) and fails cleanly only when none does.
+    int fit = n;
+    for (int i = 0; i < n; i++) {
+        const int entry = s->neededHost[i];
+        char *slot = nullptr;
+        if (s->slotOf[entry] >= 0 || s->budgetBlocks <= 0 || s->slotsUsed < s->budgetBlocks) slot = slot_for(s, entry);
+        if (!slot) { fit = i; break; }
         s->blockPtrsHost[i] = reinterpret_cast<uint4 *>(slot);
     }
+    if (fit == 0) {
+        if (moved) *moved = 0;
+        return fail_with(DSB200_ERR_CUDA, "swap_save_to_global_memory: the host block store is full (dsb200_swap_set_store_budget, or no more "
+                                          "memory could be pinned); nothing was moved");
+    }
+    n = fit;
+    if (moved) *moved = n;
     SWCU(cudaMemcpyAsync(s->blockPtrs, s->blockPtrsHost, sizeof(uint4 *) * (size_t)n, cudaMemcpyHostToDevice, s->stream));
     // the reference lets the free list grow while vbaIdx < SDF_BUCKET_NUM - 1 (CPU .cpp:178); the list itself holds num_blocks
     // entries, so the second bound only differs where the reference would write past its end
@@ -399,6 +413,13 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
     if (pushed > n) pushed = n;
     scene->last_free_block = lastFree0 + pushed;
     return swap_leave(s, scene);
+}
+
+int dsb200_swap_set_store_budget(dsb200_swap *s, int32_t max_blocks)
+{
+    if (!s || max_blocks < 0) return fail_with(DSB200_ERR_INVALID, "swap_set_store_budget: bad argument");
+    s->budgetBlocks = max_blocks;
+    return DSB200_OK;
 }
 
 int dsb200_swap_attach_recon(dsb200_swap *s, dsb200_recon *recon)

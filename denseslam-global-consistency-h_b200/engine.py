@@ -441,6 +441,10 @@ class ITMSwappingEngine(object):
         self._changed()
         return n.value
 
+    def SetStoreBudget(self, max_blocks):
+        """bound on the pinned host store, in voxel blocks (0 = none); no counterpart in the reference (its store is pageable)"""
+        abi.check(_lib().dsb200_swap_set_store_budget(self.h, int(max_blocks)))
+
     def SaveToFile(self, path):
         abi.check(_lib().dsb200_swap_save_file(self.h, path.encode()))
 

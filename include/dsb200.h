@@ -497,6 +497,12 @@ int dsb200_swap_save_to_global_memory(dsb200_swap *s, dsb200_scene *scene, const
  * only a stream synchronisation: the host mirrors are then already current and are left alone */
 int dsb200_recon_refresh_mirrors(dsb200_recon *e, dsb200_scene *scene, dsb200_render_state *rs);
 int dsb200_swap_attach_recon(dsb200_swap *s, dsb200_recon *recon);
+/* The host block store is a compact arena of PINNED 64 MB chunks that grows with the number of blocks ever swapped out (the
+ * reference's is a lazily touched pageable malloc of the whole table, Objects/ITMGlobalCache.h:75-105).  max_blocks bounds it
+ * (0 = no bound but the table size; DenseSLAM parks many local maps, one cache each).  A SaveToGlobalMemory call that meets the
+ * bound -- or cannot pin another chunk -- moves the candidates that still fit and reports that number; when none fits it
+ * returns DSB200_ERR_CUDA with nothing changed. */
+int dsb200_swap_set_store_budget(dsb200_swap *s, int32_t max_blocks);
 /* ITMGlobalCache::SaveToFile / ReadFromFile (Objects/ITMGlobalCache.h:75-105): bool[total] then total blocks */
 int dsb200_swap_save_file(dsb200_swap *s, const char *path);
 int dsb200_swap_load_file(dsb200_swap *s, const char *path);

@@ -136,3 +136,40 @@ def test_swapping_with_an_asynchronous_engine():
     compare(gpu, ora, swap, cache, "asynchronous engine + swapping")
     hz.assert_images_equal(gpu.images(), ora.images(), "asynchronous engine + swapping")
     swap.close(); gpu.close(); ora.close()
+
+
+def test_host_store_budget_is_enforced_without_damage():
+    """ADVICE round 1 (pinned store growth): with a bound on the host store a swap-out moves what still fits, then fails cleanly
+    with nothing changed; raising the bound lets it finish, and every stored block is the block that was in the volume."""
+    cfg, frames, order, _ = hz.swap_scenario()
+    caps = dict(num_blocks=4096, bucket_num=8192, excess_size=1024)
+    gpu = hz.GpuBackend(cfg, caps=caps, use_swapping=True)
+    swap = gpu.eng.ITMSwappingEngine(gpu.scene, 64, recon=gpu.recon)          # 64 blocks per call
+    gpu.set_frame(frames[0]); gpu.allocate(); swap.MarkVisible(gpu.rs); gpu.integrate()
+    while swap.IntegrateGlobalIntoLocal(gpu.scene):
+        pass
+    before_hash, before_vox = gpu.scene.hash().copy(), gpu.scene.voxels().copy()
+    live = int((before_hash["ptr"] >= 0).sum())
+    assert live > 300
+    swap.SetStoreBudget(100)
+    assert swap.SaveToGlobalMemory(gpu.scene) == 64
+    assert swap.SaveToGlobalMemory(gpu.scene) == 36                            # what still fits: a shorter transfer
+    h1, v1, free1 = gpu.scene.hash().copy(), gpu.scene.voxels().copy(), gpu.scene.c.last_free_block
+    with pytest.raises(abi.Dsb200Error) as err:
+        swap.SaveToGlobalMemory(gpu.scene)
+    assert "host block store is full" in str(err.value)
+    assert gpu.scene.hash().tobytes() == h1.tobytes() and np.array_equal(gpu.scene.voxels().view(np.uint64), v1.view(np.uint64))
+    assert gpu.scene.c.last_free_block == free1 and swap.has_stored().sum() == 100
+    swap.SetStoreBudget(0)
+    moved = 100
+    while True:
+        n = swap.SaveToGlobalMemory(gpu.scene)
+        if n == 0:
+            break
+        moved += n
+    has = swap.has_stored()
+    assert moved == has.sum() and moved >= live - 64                           # entries still in state 0 (never visible) stay
+    for e in np.nonzero(has)[0][::7]:
+        p = int(before_hash["ptr"][e])
+        assert np.array_equal(swap.stored_block(e).view(np.uint64), before_vox[p * 512:(p + 1) * 512].view(np.uint64))
+    swap.close(); gpu.close()
