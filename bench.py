@@ -74,14 +74,20 @@ class ClockSampler(object):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", self.gpu, "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.first = threading.Event()
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            # nvidia-smi's start-up (NVML initialisation, tens of ms) holds driver locks that stall kernel submission: a 40 ms step was
+            # measured 20 ms into a timed region (profiles/r02v).  Wait for its first row so that only the 100 ms polls, which do not
+            # show up in the step times, fall into the timed region.
+            self.first.wait(3.0)
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
+            self.first.set()
 
     def stop(self):
         if not self.enabled:
@@ -669,13 +675,13 @@ def run_batched(args, rank, world, local_rank):
         submit(i)
     for L in lanes:
         L["recon"].Sync(L["scene"], L["rs"])
+    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     l0 = lib.dsb200_kernel_launch_count()
     main = torch.cuda.current_stream()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     e0.record()
     for L in lanes:
         L["st"].wait_event(e0)
@@ -761,12 +767,12 @@ def run_tracked(args, rank, world, local_rank):
     for i in range(Wm):
         frame(i, False)
     recon.Sync(scene, rs)
+    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     l0 = lib.dsb200_kernel_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     e0.record()
     for k in range(K):
         frame(Wm + k, True)
@@ -841,10 +847,10 @@ def measure_sharded(args, rank, world, local_rank, mode, build_frames=None):
     sc.m.recon.Sync(sc.m.scene, sc.m.rs)
     if sc.m.scene.c.last_free_block < 0 or sc.m.scene.c.last_free_excess < 0:
         raise RuntimeError("shard %d ran out of voxel blocks / excess entries while building the C4 map (capacity %r)" % (rank, caps))
+    sampler = ClockSampler(local_rank, rank, world); sampler.start()      # before the barrier: rank 0 waits for nvidia-smi's first row
     torch.cuda.synchronize(); dist.barrier()
     l0 = lib.dsb200_kernel_launch_count()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    sampler = ClockSampler(local_rank, rank, world); sampler.start()
     vis_counts = []
     for k in range(K):
         flush.zero_()
@@ -887,7 +893,8 @@ def measure_sharded(args, rank, world, local_rank, mode, build_frames=None):
             "collectives_per_step": {"broadcast_bytes": 8 * npx + 72, "rendezvous_allreduce_4B": 2,
                                      "peer_reads_bytes_per_gpu": (16 * npx) if mode == "composite" else None},
             "step_ms_rank0": {"p10": float(np.percentile(step_ms, 10)), "p50": float(np.percentile(step_ms, 50)),
-                              "p90": float(np.percentile(step_ms, 90)), "max": float(step_ms.max())},
+                              "p90": float(np.percentile(step_ms, 90)), "max": float(step_ms.max()),
+                              "all": [round(float(x), 3) for x in step_ms]},
             "gpu_launches": launches, "clocks": clocks}
 
 

@@ -77,6 +77,16 @@ struct Arena {
         current->used += ints;
         return current;
     }
+    // called where the caller blocks anyway (counter read-back): have the next chunk ready before the current one runs out, so
+    // that no cudaMalloc (implicitly synchronising) lands between two asynchronous frames
+    void ensure_spare()
+    {
+        if (!freeChunks.empty() || !current || current->used * 2 < current->capacity) return;
+        Chunk *c = new Chunk();
+        c->capacity = chunkInts;
+        if (cudaMalloc(&c->base, c->capacity * sizeof(int)) != cudaSuccess) { cudaGetLastError(); delete c; return; }
+        freeChunks.push_back(c);
+    }
     void release_all()
     {
         current.reset();
@@ -292,6 +302,7 @@ static int sync_counters(dsb200_recon *e, dsb200_scene *scene, dsb200_render_sta
         }
         e->unsynced.clear();
     }
+    e->arena.ensure_spare();
     e->deviceCountersValid = true;
     return DSB200_OK;
 }
