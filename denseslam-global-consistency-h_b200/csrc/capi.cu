@@ -1173,6 +1173,20 @@ int dsb200_scene_save(const dsb200_scene *scene, const dsb200_render_state *rs, 
     CU(cudaMallocHost(&pinned, pinnedBytes));
     const std::string d = std::string(directory) + "/";
     const size_t total = (size_t)scene->bucket_num + scene->excess_size;
+    {   // a deep look-ahead's pending entries belong to a frame that has not happened: never into a checkpoint
+        int *cnt = static_cast<int *>(pinned), *dcnt = nullptr;
+        *cnt = 0;
+        if (cudaMalloc(&dcnt, 4) != cudaSuccess) { cudaFreeHost(pinned); return cuda_fail(cudaGetLastError(), "scene_save"); }
+        cudaMemset(dcnt, 0, 4);
+        launch_count_pending(nullptr, scene->hash, (int)total, dcnt);
+        cudaMemcpy(cnt, dcnt, 4, cudaMemcpyDeviceToHost);
+        cudaFree(dcnt);
+        if (*cnt != 0) {
+            cudaFreeHost(pinned);
+            return fail(DSB200_ERR_INVALID, "scene_save: the hash table holds pending entries of a look-ahead; call dsb200_recon_abandon_prefetch "
+                                            "(or the consuming allocation) first");
+        }
+    }
     int rc = write_block(d + "voxel.dat", scene->voxels, sizeof(dsb200_voxel), (size_t)scene->num_blocks * DSB200_BLOCK_SIZE3, pinned, pinnedBytes);
     if (!rc) rc = write_block(d + "alloc.dat", scene->alloc_list, 4, scene->num_blocks, pinned, pinnedBytes);
     if (!rc) rc = write_block(d + "hash.dat", scene->hash, sizeof(dsb200_hash_entry), total, pinned, pinnedBytes);

@@ -112,6 +112,7 @@ void launch_visible_list(cudaStream_t st, const VisParams &P, const FrameState &
 void launch_commit_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep, const int *nextIds,
                               int *visibleIds, int visibleCapacity, int *snapshotIds, int *snapshotCount, int snapshotCapacity);
 void launch_abandon_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep);
+void launch_count_pending(cudaStream_t st, const dsb200_hash_entry *hash, int total, int *count);
 
 // recon_integrate.cu
 void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_voxel *voxels,

@@ -467,6 +467,20 @@ __global__ void __launch_bounds__(256) k_abandon_allocation(FrameState fs, dsb20
     }
 }
 
+// entries a deep look-ahead has published but not committed (checkpointing refuses to write them)
+__global__ void __launch_bounds__(256) k_count_pending(const dsb200_hash_entry *__restrict__ hash, int total, int *count)
+{
+    int n = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+        n += __ldg(reinterpret_cast<const int *>(hash) + (size_t)i * 5 + 3) <= kPendingBase ? 1 : 0;
+    n = __reduce_add_sync(0xffffffffu, n);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(count, n);
+}
+void launch_count_pending(cudaStream_t st, const dsb200_hash_entry *hash, int total, int *count)
+{
+    DSB_LAUNCH(k_count_pending, kNumSMs * 4, 256, 0, st, hash, total, count);
+}
+
 // ---------------------------------------------------------------- host launchers
 void launch_commit_allocation(cudaStream_t st, const FrameState &fs, dsb200_hash_entry *hash, const DeepList &deep, const int *nextIds,
                               int *visibleIds, int visibleCapacity, int *snapshotIds, int *snapshotCount, int snapshotCapacity)

@@ -258,6 +258,7 @@ class ITMSceneReconstructionEngine(object):
 
     def SaveCheckpoint(self, scene, renderState, directory):
         """volume checkpoint: scene arrays (+ visible list / flags) in MemoryBlockPersister's file layout"""
+        abi.check(_lib().dsb200_recon_abandon_prefetch(self.h))      # a pending look-ahead's entries never go into a checkpoint
         abi.check(_lib().dsb200_scene_save(C.byref(scene.c), C.byref(renderState.c) if renderState is not None else None,
                                            str(directory).encode()))
 

@@ -331,6 +331,7 @@ int dsb200_recon_abandon_prefetch(dsb200_recon *e);
  * has no save / resume): writes voxel.dat, alloc.dat, hash.dat, excess.dat -- and visible.dat, vistype.dat when rs is given --
  * into an existing directory, each file in MemoryBlockPersister's layout (int32 element count, raw elements; :88-140),
  * plus counters.txt (capacities, free-list tops, visible count, scene parameters).  Synchronises the device.
+ * save refuses (DSB200_ERR_INVALID) a table that holds pending entries of a deep look-ahead: dsb200_recon_abandon_prefetch first.
  * load: the scene (and render state) must have the saved capacities; pass the engine that will keep working on the scene so
  * that its derived state (device counters, visibility bitmap, sdf shadow, pruning history, pending look-ahead) is reset. */
 int dsb200_scene_save(const dsb200_scene *scene, const dsb200_render_state *rs, const char *directory);

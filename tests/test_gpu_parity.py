@@ -395,7 +395,7 @@ def test_checkpoint_round_trip(tmp_path):
         x.close()
 
 
-def test_abandoned_lookahead_is_undone():
+def test_abandoned_lookahead_is_undone(tmp_path):
     """A look-ahead that is dropped -- dsb200_recon_notify_scene_modified, or the next allocation arriving with another view /
     pose -- must leave no trace: its request keys, request bitmaps and visibility flags are undone, and the frame allocated
     next equals the oracle's plain sequence bit for bit (stale order keys could win the next allocation)."""
@@ -413,7 +413,19 @@ def test_abandoned_lookahead_is_undone():
     other.update(far[0].depth, far[0].rgb, far[0].timestamp); nxt.set_pose(far[0].M)
     gpu.recon.PrefetchAllocation(gpu.scene, other, nxt, gpu.rs)
     gpu.recon.Sync(gpu.scene, gpu.rs)          # the host mirrors become authoritative again after the notification
+    # the DEEP look-ahead has published the far view's new blocks as pending entries (ptr <= -3: unallocated to every reader);
+    # the counters and the visible list are still frame 2's, and a checkpoint of this table is refused
+    import ctypes as C
+    abi.check(lib.dsb200_recon_join_prefetch(gpu.recon.h)); abi.check(lib.dsb200_stream_synchronize(None))
+    so = ora.state()
+    assert (gpu.scene.hash()["ptr"] <= -3).sum() > 20
+    assert gpu.scene.c.last_free_block == so["last_free"][0] and np.array_equal(gpu.rs.visible(), so["visible"])
+    assert lib.dsb200_scene_save(C.byref(gpu.scene.c), None, str(tmp_path).encode()) == abi.ERR_INVALID
     abi.check(lib.dsb200_recon_notify_scene_modified(gpu.recon.h))
+    abi.check(lib.dsb200_stream_synchronize(None))
+    assert (gpu.scene.hash()["ptr"] <= -3).sum() == 0
+    s = gpu.state(); s["visible_type"] = so["visible_type"]
+    hz.assert_state_equal(so, s, "table after the undo")
     gpu.set_frame(frames[3]); ora.set_frame(frames[3])
     assert gpu.process_frame() == 0
     ora.process_frame()
