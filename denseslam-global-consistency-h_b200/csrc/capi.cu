@@ -158,6 +158,7 @@ struct dsb200_vis {
     int *hostInts = nullptr;          // pinned [4]
     float *fwdProjection = nullptr; int *fwdMissing = nullptr; int fwdPixels = 0;
     RayQueue rayQueue{};              // suspended rays of the bounded first raycast pass (capacity = width * height of creation)
+    int *tileOrder = nullptr; int tileOrderCap = 0;   // fused frame: raycast tiles in descending order of expected-depth span
 };
 
 extern "C" {
@@ -205,7 +206,12 @@ int dsb200_recon_create(dsb200_recon **out, int32_t num_blocks, int32_t bucket_n
     CU(cudaMemset(e->fs.tickets, 0, 4 * sizeof(int)));
     CU(cudaMallocHost(&e->hostCounters, sizeof(Counters)));
     memset(e->hostCounters, 0, sizeof(Counters));
-    CU(cudaStreamCreateWithFlags(&e->sideStream, cudaStreamNonBlocking));
+    {   // the side stream's kernels are small and sit beside the integration, whose grid fills the GPU: highest priority, so that they
+        // get the first SM slots that free up instead of queueing behind the whole grid
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&e->sideStream, cudaStreamNonBlocking, hi));
+    }
     CU(cudaEventCreateWithFlags(&e->evFork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&e->evJoin, cudaEventDisableTiming));
     CU(cudaStreamCreateWithFlags(&e->prefetchStream, cudaStreamNonBlocking));
@@ -699,6 +705,9 @@ int dsb200_vis_create(dsb200_vis **out, int32_t max_visible, int32_t width, int3
     CU(cudaMalloc(&v->rayQueue.pixel, npx * sizeof(int)));
     CU(cudaMalloc(&v->rayQueue.posLen, npx * sizeof(float4)));
     CU(cudaMalloc(&v->rayQueue.dirMax, npx * sizeof(float4)));
+    v->tileOrderCap = div_up(width, 8) * div_up(height, 4);
+    CU(cudaMalloc(&v->tileOrder, (size_t)(4 * v->tileOrderCap + 4) * sizeof(int)));      // 4 class counters + 4 lists (vis.cu: k_tile_order)
+    CU(cudaMemset(v->tileOrder, 0, 4 * sizeof(int)));                    // k_tile_order's two counters (k_range_init zeroes them per frame)
     v->rayQueue.capacity = (int)npx;
     *out = v;
     return DSB200_OK;
@@ -711,7 +720,7 @@ int dsb200_vis_destroy(dsb200_vis *v)
     cudaFree(v->fs.counters); cudaFree(v->fs.tickets); cudaFree(v->fs.scanState); cudaFree(v->countScratch);
     cudaFree(v->fwdProjection); cudaFree(v->fwdMissing);
     cudaFree(v->rayQueue.ctl); cudaFree(v->rayQueue.pixel); cudaFree(v->rayQueue.posLen); cudaFree(v->rayQueue.dirMax);
-    cudaFreeHost(v->hostCounters); cudaFreeHost(v->hostInts);
+    cudaFreeHost(v->hostCounters); cudaFreeHost(v->hostInts); cudaFree(v->tileOrder);
     delete v;
     return DSB200_OK;
 }
@@ -1341,12 +1350,15 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     // Integration (writes voxels) and the expected-depth image (reads hash + visible list, writes the range image) are
     // independent: outside profiling mode the latter runs on a side stream, forked after the visible list and joined
     // before the raycast.
+    // raycast tiles are handed out longest expected-depth span first; the order is derived from this call's range image
+    const int nTiles = div_up(rs->width, 8) * div_up(rs->height, 4);
+    int *tileOrder = (v && (stages & DSB200_FRAME_EXPECTED_DEPTHS) && nTiles <= v->tileOrderCap) ? v->tileOrder : nullptr;
     const bool fork = !e->profile && (stages & DSB200_FRAME_INTEGRATE) && (stages & DSB200_FRAME_EXPECTED_DEPTHS) && e->sideStream;
     if (fork) {
         CU(cudaEventRecord(e->evFork, e->stream));
         CU(cudaStreamWaitEvent(e->sideStream, e->evFork, 0));
         ProjParams P; make_proj_params(P, scene, trk->M_d, view->intr_d, rs->width, rs->height);
-        launch_expected_depths(e->sideStream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, nullptr, e->fs.counters);
+        launch_expected_depths(e->sideStream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, tileOrder, e->fs.counters);
         CU(cudaEventRecord(e->evJoin, e->sideStream));
     }
     if (stages & DSB200_FRAME_INTEGRATE) {
@@ -1362,18 +1374,18 @@ int dsb200_process_frame(dsb200_recon *e, dsb200_vis *v, dsb200_scene *scene, co
     if (fork) CU(cudaStreamWaitEvent(e->stream, e->evJoin, 0));
     else if (stages & DSB200_FRAME_EXPECTED_DEPTHS) {
         ProjParams P; make_proj_params(P, scene, trk->M_d, view->intr_d, rs->width, rs->height);
-        launch_expected_depths(e->stream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, nullptr, e->fs.counters);
+        launch_expected_depths(e->stream, P, scene->hash, rs->visible_ids, countPtr, rs->range_image, tileOrder, e->fs.counters);
     }
     DSB_MARK(3);
     if (stages & DSB200_FRAME_ICP_MAPS) {
         if (!trk->icp_points || !trk->icp_normals) return fail(DSB200_ERR_INVALID, "process_frame: tracking state has no point cloud buffers");
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene), &v->rayQueue);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene), &v->rayQueue, tileOrder);
         DSB_MARK(4);
         launch_icp_maps(e->stream, P, rs->raycast_result, trk->icp_points, trk->icp_normals, rs->raycast_image);
     } else if (stages & DSB200_FRAME_RAYCAST) {
         RayParams P; make_ray_params(P, scene, trk->M_d, trk->invM_d, view->intr_d, rs->width, rs->height);
-        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene), &v->rayQueue);
+        launch_raycast(e->stream, P, scene->voxels, scene->hash, rs->range_image, rs->raycast_result, v->fs.tickets + 2, shadow_for(e, scene), &v->rayQueue, tileOrder);
         DSB_MARK(4);
     } else DSB_MARK(4);
     DSB_MARK(5);

@@ -72,6 +72,7 @@ struct Tunables {
     int fuse_ctas;        // CTAs per SM of the flat integration kernel
     int fuse_minb;        // ... and its __launch_bounds__ minimum CTAs per SM (variant 2: 4, 6 or 8; variant 3: 4 or 5)
     int deep_lookahead;   // dsb200_recon_prefetch_allocation also runs the ordered allocation and the visible-list build (1 = on)
+    int ray_lpt;          // fused frame: raycast tiles dealt by class of expected-depth span: >= this many 8-voxel steps, half, a quarter, rest (0 = off)
 };
 Tunables &tunables();
 bool set_tunable(const char *name, int value);
@@ -137,10 +138,11 @@ void launch_find_visible(cudaStream_t st, const VisParams &P, const FrameState &
 void launch_count_visible(cudaStream_t st, const dsb200_hash_entry *hash, const int *ids, const int *count, int minId,
                           int maxId, int *out);
 void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_hash_entry *hash, const int *ids,
-                            const int *count, float *rangeImage, int *blockTileCounts, Counters *counters);
+                            const int *count, float *rangeImage, int *tileOrderOrNull /* 4 counters + 4 lists of ceil(W/8) * ceil(H/4) ints: raycast tiles by depth-span class */,
+                            Counters *counters);
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
                     const float *rangeImage, float *raycastResult, int *ticketPair /* two zeroed ints, re-armed by the kernel */,
-                    const short *sdfShadowOrNull = nullptr, const RayQueue *queueOrNull = nullptr);
+                    const short *sdfShadowOrNull = nullptr, const RayQueue *queueOrNull = nullptr, const int *tileOrderOrNull = nullptr);
 void launch_raycast_sharded(cudaStream_t st, const RayParams &P, int n, int rank, int brickLog2,
                             const dsb200_hash_entry *const *hash, const dsb200_voxel *const *voxels,
                             const float *const *rangeImages, float *mergedRange, float *raycastResult, int *ticketPair,

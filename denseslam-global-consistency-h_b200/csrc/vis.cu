@@ -114,10 +114,13 @@ __device__ __forceinline__ bool project_block(short bx, short by, short bz, cons
     return true;
 }
 
-__global__ void __launch_bounds__(256) k_range_init(float2 *range, int n, Counters *counters)
+__global__ void __launch_bounds__(256) k_range_init(float2 *range, int n, Counters *counters, int *orderCtl)
 {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) range[i] = make_float2(kFarAway, kVeryClose);
-    if (blockIdx.x == 0 && threadIdx.x == 0) counters->renderBlocks = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        counters->renderBlocks = 0;
+        if (orderCtl) { orderCtl[0] = 0; orderCtl[1] = 0; orderCtl[2] = 0; orderCtl[3] = 0; }      // k_tile_order's class counters
+    }
 }
 
 __device__ __forceinline__ void range_minmax(float *range, int W, int x, int y, float zmin, float zmax)
@@ -221,6 +224,36 @@ __global__ void __launch_bounds__(1024) k_range_cap_fallback(ProjParams P, const
         __syncthreads();
     }
     if (threadIdx.x == 0) counters->renderBlocks = sNum;
+}
+
+// LONG TILES FIRST.  A ray marches from the near to the far expected depth of its 8x8-pixel range cell; on a street the cells at
+// the horizon span tens of metres of mostly free space (tools/ray_trip_stats.py: up to 152 loop trips, against a median of 8) and
+// a warp that draws such a tile late finishes long after everything else -- the kernel lasts as long as "start of the longest tile
+// + its march".  The range image is known before the raycast starts, so the tickets are dealt from a list that holds the tiles
+// whose depth span is worth at least `minTrips` 8-voxel steps at the front (they all start in the first wave) and the others at the
+// back.  Warp-aggregated atomics; k_range_init zeroes the counters.  Only the ORDER of the tickets changes.
+// Four classes by span (>= L, >= L/2, >= L/4, rest; L = `spanLong`), one list each: order = {4 counters, 4 lists of n entries}.
+constexpr int kOrderClasses = 4;
+__global__ void __launch_bounds__(256) k_tile_order(const float2 *__restrict__ range, int W, int H, float spanLong, int *order)
+{
+    const int tilesX = (W + 7) >> 3, tilesY = (H + 3) >> 2, n = tilesX * tilesY;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+    int cls = -1;
+    if (t < n) {
+        const int ty = t / tilesX, tx = t - ty * tilesX;
+        const float2 mm = __ldg(range + tx + ((ty * 4) / kSubsample) * W);
+        const float span = mm.y - mm.x;
+        cls = span >= spanLong ? 0 : (span >= 0.5f * spanLong ? 1 : (span >= 0.25f * spanLong ? 2 : 3));
+    }
+#pragma unroll
+    for (int c = 0; c < kOrderClasses; c++) {
+        const unsigned m = __ballot_sync(0xffffffffu, cls == c);
+        if (!m) continue;
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&order[c], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (cls == c) order[kOrderClasses + (size_t)c * n + base + __popc(m & ((1u << lane) - 1u))] = t;
+    }
 }
 
 // ---------------------------------------------------------------- raycast
@@ -357,7 +390,21 @@ __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, i
 //   ray_setup   :124-158  start point, unit direction, ray length at the near / far expected depth
 //   ray_step    :161-178  ONE pass of the march loop body
 //   ray_finish  :180-195  the two refinement steps and the output
-struct RayState { float rx, ry, rz, total, dx, dy, dz, totalMax; };
+struct RayState {
+    float rx, ry, rz, total, dx, dy, dz, totalMax;
+#ifdef DSB_RAY_TRACE
+    int trips;
+#endif
+};
+#ifdef DSB_RAY_TRACE
+// diagnostic build only (make EXTRA=-DDSB_RAY_TRACE): per raycast tile {start ns, end ns, longest ray's loop trips, SM}
+__device__ unsigned long long *g_rayTrace = nullptr;
+extern "C" int dsb200_debug_ray_trace(unsigned long long *deviceBuffer)
+{
+    return cudaMemcpyToSymbol(g_rayTrace, &deviceBuffer, sizeof(deviceBuffer)) == cudaSuccess ? 0 : -1;
+}
+__device__ __forceinline__ unsigned long long ray_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
 enum RayStep { kStepUnit = 0, kStepJump = 1, kStepHit = 2 };     // unit: stepLength == 1.0f exactly; jump: anything else
 
 __device__ __forceinline__ void ray_setup(RayState &s, int x, int y, const RayParams &P, float zmin, float zmax)
@@ -441,6 +488,9 @@ __device__ __forceinline__ bool cast_ray_bounded(float4 &out, RayState &s, const
     }
     const bool suspended = !stopped && totalLength < totalLengthMax;     // left the loop on the step cap
     s.rx = rx; s.ry = ry; s.rz = rz; s.total = totalLength;
+#ifdef DSB_RAY_TRACE
+    s.trips = maxSteps - steps;
+#endif
     if (!suspended) out = ray_finish(rx, ry, rz, dx, dy, dz, sdf, T, P, stepScale, cache);
     return !suspended;
 }
@@ -452,6 +502,47 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
     ray_setup(s, x, y, P, zmin, zmax);
     cast_ray_bounded(out, s, T, P, -1);
     return out.w > 0.0f;
+}
+
+// GROUP MARCH: G lanes (2 .. 32) work on ONE ray and evaluate its next G loop bodies TOGETHER.  Lane j assumes that the j bodies
+// before it all stepped by S, the step of the last committed body (8 voxels at the start) -- which is what the long rays do:
+// tools/ray_trip_stats.py on the C2 street counts, for the rays with >= 64 loop trips, runs of 26 consecutive 8-voxel steps (no
+// block) and of 12 consecutive 4-voxel steps (allocated, empty: sdf = 1) on average.  Lane j derives its position by the very
+// additions the sequential loop would perform (rx += stepLength * dx with stepLength == S), samples the volume, and the group
+// commits the bodies up to and including the first one that did NOT step by exactly S (another step length, the hit, or the end of
+// the range); later lanes' samples are discarded.  Lane 0's body is never speculative, so a round always makes progress, and
+// every committed body is the sequential loop's body on the sequential loop's operands: the result is bit-identical to cast_ray
+// (tests/test_gpu_parity.py::test_two_pass_raycast_is_bit_identical and every frame test, since the fused frame uses it).
+// What changes is the dependent chain: up to G bodies per memory round trip instead of one.
+template <class Tables, int G>
+__device__ __forceinline__ void cast_ray_group(float4 *dst, float rx, float ry, float rz, float total, float dx, float dy, float dz,
+                                               float totalMax, const Tables &T, const RayParams &P, unsigned gmask, int j, BlockCache &cache)
+{
+    const float stepScale = P.mu * P.oneOverVoxel;
+    float S = (float)kBlock;           // the group's hypothesis: the next bodies all step by S (first guess: free space)
+    while (true) {
+        float px = rx, py = ry, pz = rz, t = total;
+        const float sx = S * dx, sy = S * dy, sz = S * dz;
+        for (int k = 0; k < j; k++) { px += sx; py += sy; pz += sz; t += S; }
+        int kind;                      // RayStep, or 3 = the loop condition fails here (no hit)
+        float sdf = 1.0f, stepLength = 1.0f;
+        if (t < totalMax) kind = ray_step(px, py, pz, T, P, stepScale, cache, sdf, stepLength);
+        else kind = 3;
+        // lane j's body is the sequential loop's body iff every body before it stepped by exactly S
+        const bool asAssumed = (kind == kStepUnit || kind == kStepJump) && stepLength == S;
+        const unsigned stop = __ballot_sync(gmask, !asAssumed) & gmask;
+        const int first = stop ? (__ffs(stop) - 1) & (G - 1) : G - 1;             // the body the group commits last
+        const int fk = __shfl_sync(gmask, kind, first, G);
+        if (fk == kStepHit || fk == 3) {
+            if (j == first) *dst = ray_finish(px, py, pz, dx, dy, dz, sdf, T, P, stepScale, cache);
+            break;
+        }
+        // a step (as assumed or not): the committed state after it, and the next hypothesis
+        px += stepLength * dx; py += stepLength * dy; pz += stepLength * dz; t += stepLength;
+        rx = __shfl_sync(gmask, px, first, G); ry = __shfl_sync(gmask, py, first, G); rz = __shfl_sync(gmask, pz, first, G);
+        total = __shfl_sync(gmask, t, first, G);
+        S = __shfl_sync(gmask, stepLength, first, G);
+    }
 }
 
 // GenericRaycast (CPU .cpp:296-333; CUDA .cu:807-819).  Ray lengths differ by orders of magnitude across the image (sky
@@ -481,20 +572,31 @@ __device__ __forceinline__ bool cast_ray(float4 &out, int x, int y, const Tables
 template <class Tables>
 __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_constant__ Tables T,
                                                  const float2 *__restrict__ range, float4 *out, int *ticket, int tileFirst,
-                                                 int tileStride, int bottomUp, RayQueue q, int maxSteps)
+                                                 int tileStride, int bottomUp, RayQueue q, int maxSteps, const int *order)
 {
     const int lane = threadIdx.x & 31;
     const int tilesX = (P.W + 7) >> 3, tilesY = (P.H + 3) >> 2, nTiles = tilesX * tilesY;
+    // k_tile_order's lists: class 0 (the longest depth spans) .. class 3
+    int c0 = 0, c1 = 0, c2 = 0;
+    if (order) { c0 = order[0]; c1 = order[1]; c2 = order[2]; }
     while (true) {
         int tile = 0;
         if (lane == 0) tile = atomicAdd(&ticket[0], 1);
         tile = __shfl_sync(0xffffffffu, tile, 0) * tileStride + tileFirst;
         if (tile >= nTiles) break;
-        if (bottomUp) tile = nTiles - 1 - tile;
+        if (order) {
+            int c = 0, u = tile;
+            if (u >= c0) { u -= c0; c = 1; if (u >= c1) { u -= c1; c = 2; if (u >= c2) { u -= c2; c = 3; } } }
+            tile = __ldg(order + kOrderClasses + (size_t)c * nTiles + u);
+        } else if (bottomUp) tile = nTiles - 1 - tile;
         const int ty = tile / tilesX, tx = tile - ty * tilesX;
         const int x = tx * 8 + (lane & 7), y = ty * 4 + (lane >> 3);
         bool suspended = false;
         RayState s;
+#ifdef DSB_RAY_TRACE
+        const unsigned long long traceT0 = ray_now();
+        s.trips = 0;
+#endif
         if (x < P.W && y < P.H) {
             const int loc2 = (int)floorf((float)x / (float)kSubsample) + (int)floorf((float)y / (float)kSubsample) * P.W;
             const float2 mm = __ldg(range + loc2);
@@ -503,6 +605,16 @@ __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_const
             if (cast_ray_bounded(r, s, T, P, maxSteps)) out[x + y * P.W] = r;
             else suspended = true;
         }
+#ifdef DSB_RAY_TRACE
+        {
+            const int tr = __reduce_max_sync(0xffffffffu, s.trips);
+            if (lane == 0 && g_rayTrace) {
+                unsigned smid; asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+                unsigned long long *w = g_rayTrace + (size_t)tile * 4;
+                w[0] = traceT0; w[1] = ray_now(); w[2] = (unsigned long long)tr; w[3] = smid;
+            }
+        }
+#endif
         const unsigned m = __ballot_sync(0xffffffffu, suspended);
         if (m) {
             int base = 0;
@@ -522,25 +634,16 @@ __global__ void __launch_bounds__(128) k_raycast(RayParams P, const __grid_const
     }
 }
 
-// Finishing pass: G lanes (G = 2, 4, 8, 16 or 32) work on ONE suspended ray and evaluate its next G loop bodies TOGETHER, lane j
-// assuming that the j bodies before it all advanced by exactly one voxel -- which is what a creeping ray does
-// (stepLength = max(sdf * mu / voxelSize, 1) is exactly 1.0f inside the quarter of the truncation band next to the surface).
-// Lane j derives its position by the same j additions the sequential loop would perform (rx += 1.0f * dx, ...: bit-identical),
-// samples the volume, and the group commits the bodies up to and including the first one that was NOT a unit step (a longer
-// step, a missing block, the hit, or the end of the range); later lanes' samples are discarded.  Lane 0's body is never
-// speculative, so a round always makes progress, and every committed body is the sequential loop's body on the sequential
-// loop's operands: the result is bit-identical to cast_ray (tests/test_gpu_parity.py::test_two_pass_raycast_is_bit_identical).
-// What changes is the length of the dependent chain: G bodies per two or three memory round trips instead of one -- for rays
-// that creep.  Measured on B200 (profiles/README.md r02f): the long rays of the street and room workloads are NOT unit-step
-// creepers; they march inside the truncation band with steps of sdf * 4 voxels in (1, 4), which nothing can predict, so a round
-// commits 1-2 bodies on average and the pass costs more than it saves.  It is therefore OFF by default (ray_steps = 0).
+// Finishing pass of the two-pass schedule (ray_steps > 0; OFF by default): the rays the bounded first pass suspended are marched
+// by groups of G lanes (cast_ray_group).  Measured on B200 (profiles/README.md r02f, r02z): with the "repeat the last step"
+// hypothesis a round commits ~4 bodies but costs ~2.2 us against ~1.1 us for a sequential body, and the first pass keeps a tail of
+// its own: 0.141-0.151 ms against 0.139 ms for the single pass inside a C2 frame (the unit-step hypothesis of r02f: 0.229 ms).
 template <class Tables, int G>
 __global__ void __launch_bounds__(128) k_raycast_finish(RayParams P, const __grid_constant__ Tables T, float4 *out, RayQueue q)
 {
     const int lane = threadIdx.x & 31, j = lane & (G - 1);
     const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (lane & ~(G - 1)));
     const int n = q.ctl[0];
-    const float stepScale = P.mu * P.oneOverVoxel;
     BlockCache cache = {0x7fffffff, 0x7fffffff, 0x7fffffff, nullptr};
     while (true) {
         int i = 0;
@@ -550,26 +653,7 @@ __global__ void __launch_bounds__(128) k_raycast_finish(RayParams P, const __gri
         const float4 a = q.posLen[i], b = q.dirMax[i];
         float rx = a.x, ry = a.y, rz = a.z, total = a.w;
         const float dx = b.x, dy = b.y, dz = b.z, totalMax = b.w;
-        while (true) {
-            // this lane's operands: j unit steps on from the group's committed state
-            float px = rx, py = ry, pz = rz, t = total;
-            for (int k = 0; k < j; k++) { px += dx; py += dy; pz += dz; t += 1.0f; }     // 1.0f * dx == dx: the loop's own additions
-            int kind;                      // RayStep, or 3 = the loop condition fails here (no hit)
-            float sdf = 1.0f, stepLength = 1.0f;
-            if (t < totalMax) kind = ray_step(px, py, pz, T, P, stepScale, cache, sdf, stepLength);
-            else kind = 3;
-            const unsigned stop = __ballot_sync(gmask, kind != kStepUnit) & gmask;
-            const int first = stop ? (__ffs(stop) - 1) & (G - 1) : G - 1;             // the body the group commits last
-            const int fk = __shfl_sync(gmask, kind, first, G);
-            if (fk == kStepHit || fk == 3) {
-                if (j == first) out[q.pixel[i]] = ray_finish(px, py, pz, dx, dy, dz, sdf, T, P, stepScale, cache);
-                break;
-            }
-            // unit or longer step: the committed state after it
-            px += stepLength * dx; py += stepLength * dy; pz += stepLength * dz; t += stepLength;
-            rx = __shfl_sync(gmask, px, first, G); ry = __shfl_sync(gmask, py, first, G); rz = __shfl_sync(gmask, pz, first, G);
-            total = __shfl_sync(gmask, t, first, G);
-        }
+        cast_ray_group<Tables, G>(out + q.pixel[i], rx, ry, rz, total, dx, dy, dz, totalMax, T, P, gmask, j, cache);
     }
     __syncwarp();
     if (lane == 0) {
@@ -913,11 +997,18 @@ void launch_count_visible(cudaStream_t st, const dsb200_hash_entry *hash, const 
 }
 
 void launch_expected_depths(cudaStream_t st, const ProjParams &P, const dsb200_hash_entry *hash, const int *ids,
-                            const int *count, float *rangeImage, int *, Counters *counters)
+                            const int *count, float *rangeImage, int *tileOrder, Counters *counters)
 {
-    DSB_LAUNCH(k_range_init, kNumSMs * 4, 256, 0, st, reinterpret_cast<float2 *>(rangeImage), P.W * P.H, counters);
+    const bool lpt = tileOrder && tunables().ray_lpt > 0;
+    DSB_LAUNCH(k_range_init, kNumSMs * 4, 256, 0, st, reinterpret_cast<float2 *>(rangeImage), P.W * P.H, counters, lpt ? tileOrder : nullptr);
     DSB_LAUNCH(k_project_fill, kNumSMs * 4, 256, 0, st, P, hash, ids, count, rangeImage, counters);
     DSB_LAUNCH(k_range_cap_fallback, 1, 1024, 0, st, P, hash, ids, count, rangeImage, counters);
+    if (lpt) {
+        const int n = div_up(P.W, 8) * div_up(P.H, 4);
+        // a span of ray_lpt 8-voxel steps, in metres (the range image holds camera-space depths)
+        DSB_LAUNCH(k_tile_order, div_up(n, 256), 256, 0, st, reinterpret_cast<const float2 *>(rangeImage), P.W, P.H,
+                   (float)tunables().ray_lpt * 8.0f * P.voxelSize, tileOrder);
+    }
 }
 
 // tuning knobs (kernels.cuh: Tunables)
@@ -926,14 +1017,14 @@ Tunables &tunables()
 {
     static Tunables t = {env_int("DSB200_RAY_STEPS", 0), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
                          env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 3), env_int("DSB200_FUSE_CTAS", 10),
-                         env_int("DSB200_FUSE_MINB", 5), env_int("DSB200_DEEP_LOOKAHEAD", 1)};
+                         env_int("DSB200_FUSE_MINB", 5), env_int("DSB200_DEEP_LOOKAHEAD", 1), env_int("DSB200_RAY_LPT", 48)};
     return t;
 }
 bool set_tunable(const char *name, int value)
 {
     Tunables &t = tunables();
     const struct { const char *n; int *p; } table[] = {{"ray_steps", &t.ray_steps}, {"ray_group", &t.ray_group}, {"ray_ctas", &t.ray_ctas},
-        {"ray_finish_ctas", &t.ray_finish_ctas}, {"ray_bottom_up", &t.ray_bottom_up}, {"fuse_kernel", &t.fuse_kernel}, {"fuse_ctas", &t.fuse_ctas}, {"fuse_minb", &t.fuse_minb}, {"deep_lookahead", &t.deep_lookahead}};
+        {"ray_finish_ctas", &t.ray_finish_ctas}, {"ray_bottom_up", &t.ray_bottom_up}, {"fuse_kernel", &t.fuse_kernel}, {"fuse_ctas", &t.fuse_ctas}, {"fuse_minb", &t.fuse_minb}, {"deep_lookahead", &t.deep_lookahead}, {"ray_lpt", &t.ray_lpt}};
     for (const auto &e : table) if (!strcmp(e.n, name)) { *e.p = value; return true; }
     return false;
 }
@@ -948,12 +1039,13 @@ static int ray_group() { return tunables().ray_group; }
 
 template <class Tables>
 static void launch_raycast_two_pass(cudaStream_t st, const RayParams &P, const Tables &T, const float2 *range, float4 *out,
-                                    int *ticketPair, int tileFirst, int tileStride, int grid, const RayQueue *queue)
+                                    int *ticketPair, int tileFirst, int tileStride, int grid, const RayQueue *queue, const int *order = nullptr)
 {
     RayQueue q{};
     int maxSteps = -1;
     if (queue && queue->ctl && queue->capacity >= P.W * P.H && ray_max_steps() > 0) { q = *queue; maxSteps = ray_max_steps(); }
-    DSB_LAUNCH(k_raycast<Tables>, grid, 128, 0, st, P, T, range, out, ticketPair, tileFirst, tileStride, ray_bottom_up(), q, maxSteps);
+    DSB_LAUNCH(k_raycast<Tables>, grid, 128, 0, st, P, T, range, out, ticketPair, tileFirst, tileStride, ray_bottom_up(), q, maxSteps,
+               (tileStride == 1 && tunables().ray_lpt > 0) ? order : nullptr);
     if (maxSteps < 0) return;
     const int g2 = kNumSMs * (tunables().ray_finish_ctas < 1 ? 1 : tunables().ray_finish_ctas);
     switch (ray_group()) {
@@ -966,7 +1058,8 @@ static void launch_raycast_two_pass(cudaStream_t st, const RayParams &P, const T
 }
 
 void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *voxels, const dsb200_hash_entry *hash,
-                    const float *rangeImage, float *raycastResult, int *ticketPair, const short *sdfShadow, const RayQueue *queue)
+                    const float *rangeImage, float *raycastResult, int *ticketPair, const short *sdfShadow, const RayQueue *queue,
+                    const int *tileOrder)
 {
     const int nTiles = div_up(P.W, 8) * div_up(P.H, 4);
     int grid = div_up(nTiles, 4);
@@ -974,12 +1067,12 @@ void launch_raycast(cudaStream_t st, const RayParams &P, const dsb200_voxel *vox
     if (sdfShadow) {
         ShadowTables T; T.sdf = sdfShadow; T.hash = hash;
         launch_raycast_two_pass(st, P, T, reinterpret_cast<const float2 *>(rangeImage), reinterpret_cast<float4 *>(raycastResult),
-                                ticketPair, 0, 1, grid, queue);
+                                ticketPair, 0, 1, grid, queue, tileOrder);
         return;
     }
     const SceneTables T = scene_tables(voxels, hash);
     launch_raycast_two_pass(st, P, T, reinterpret_cast<const float2 *>(rangeImage), reinterpret_cast<float4 *>(raycastResult),
-                            ticketPair, 0, 1, grid, queue);
+                            ticketPair, 0, 1, grid, queue, tileOrder);
 }
 
 // Expected-depth image of the whole sharded scene = element-wise (min of mins, max of maxes) of the shards' images: what

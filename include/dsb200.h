@@ -522,7 +522,7 @@ int dsb200_recon_notify_volume_swapped(dsb200_recon *e, const dsb200_scene *scen
  * the operand windows the kernels guarantee (plus the out-of-window fall-backs); *mismatches = number of
  * bit-level disagreements (must be 0). */
 int dsb200_debug_force_plain_division(dsb200_recon *e, int on);
-/* launch-shape knobs (csrc/kernels.cuh: Tunables; "ray_steps", "ray_group", "ray_ctas", "ray_finish_ctas", "ray_bottom_up",
+/* launch-shape knobs (csrc/kernels.cuh: Tunables; "ray_steps", "ray_group", "ray_ctas", "ray_finish_ctas", "ray_bottom_up", "ray_lpt",
  * "fuse_kernel", "fuse_ctas", "fuse_minb", "deep_lookahead"): process-wide, results never depend on them (tools/tune.py sweeps them on the GPU) */
 int dsb200_debug_set_tunable(const char *name, int value);
 int dsb200_selftest_division(unsigned long long n, unsigned long long seed, unsigned long long *mismatches);

@@ -628,6 +628,12 @@ inline float sdfTrilinear(const dsb200_scene *s, V3 p, bool &found, BlockCache &
 // analysis hook (profiles/): when set, castRay adds its loop-trip count per pixel here
 static int *g_rayStepCounts = nullptr; static int g_rayStepWidth = 0;
 extern "C" void rst_debug_ray_steps(int *counts, int width) { g_rayStepCounts = counts; g_rayStepWidth = width; }
+// ... and, per pixel, how many of those trips (0) found no block (8-voxel step), (1) took the minimum one-voxel step, (2) sampled
+// tri-linearly, (3) found no block right after a trip that found none either, (4) stepped exactly mu / voxelSize voxels (an empty
+// allocated block: sdf = 1), (5) did so right after a trip of kind (4)
+static int *g_rayStepKinds = nullptr;
+constexpr int kRayKinds = 6;
+extern "C" void rst_debug_ray_kinds(int *kinds6) { g_rayStepKinds = kinds6; }
 
 // castRay, DA/ITMVisualisationEngine.h:124-196
 inline bool castRay(float *out, int x, int y, const dsb200_scene *s, const float *invM, const float *invProj,
@@ -655,14 +661,20 @@ inline bool castRay(float *out, int x, int y, const dsb200_scene *s, const float
     dir.x *= dn; dir.y *= dn; dir.z *= dn;
     pr = ps;
     BlockCache cache;
+    int prevKind = -1;     // analysis hook only
     while (totalLength < totalLengthMax) {
         if (g_rayStepCounts) g_rayStepCounts[x + y * g_rayStepWidth]++;
         sdf = sdfNearest(s, pr, hashFound, cache);
-        if (!hashFound) stepLength = DSB200_BLOCK_SIZE;
+        int *kinds = g_rayStepKinds ? g_rayStepKinds + kRayKinds * (x + y * g_rayStepWidth) : nullptr;
+        if (!hashFound) { stepLength = DSB200_BLOCK_SIZE; if (kinds) { kinds[0]++; if (prevKind == 0) kinds[3]++; prevKind = 0; } }
         else {
-            if ((sdf <= 0.1f) && (sdf >= -0.5f)) sdf = sdfTrilinear(s, pr, hashFound, cache);
+            if ((sdf <= 0.1f) && (sdf >= -0.5f)) { sdf = sdfTrilinear(s, pr, hashFound, cache); if (kinds) kinds[2]++; }
             if (!(sdf > 0.0f)) break;
             stepLength = (sdf * stepScale < 1.0f) ? 1.0f : sdf * stepScale;   // MAX(sdf*stepScale, 1.0f)
+            if (kinds) {
+                if (stepLength == 1.0f) kinds[1]++;
+                if (stepLength == stepScale) { kinds[4]++; if (prevKind == 4) kinds[5]++; prevKind = 4; } else prevKind = -1;
+            }
         }
         pr.x += stepLength * dir.x; pr.y += stepLength * dir.y; pr.z += stepLength * dir.z;
         totalLength += stepLength;
