@@ -343,7 +343,6 @@ static void make_alloc_params(AllocParams &P, const dsb200_recon *e, const dsb20
 }
 
 static bool in_window(float v, int loExp, int hiExp) { float a = fabsf(v); return a >= ldexpf(1.0f, loExp) && a <= ldexpf(1.0f, hiExp); }
-static bool zero_or_in_window(float v, int loExp, int hiExp) { return v == 0.0f || in_window(v, loExp, hiExp); }
 static bool significand_all_ones(float v) { unsigned u; memcpy(&u, &v, 4); return (u & 0x7fffffu) == 0x7fffffu; }
 
 static void make_fuse_params(FuseParams &P, const dsb200_recon *e, const dsb200_scene *scene, const dsb200_view *view,
@@ -359,11 +358,18 @@ static void make_fuse_params(FuseParams &P, const dsb200_recon *e, const dsb200_
     P.depthWeighting = e->weights.depth_weighting; P.maxNewW = e->weights.max_new_w; P.maxDistance = e->weights.max_distance;
     // exact-division support (exactdiv.cuh).  Host IEEE divisions give the correctly rounded reciprocals; fastDiv states
     // that no intermediate of the FMA correction sequences can overflow or go denormal for ANY voxel of ANY block:
-    // |pt| <= 2^18 * voxelSize, so with these windows |proj * pc.xy| stays inside [2^-84, 2^68] or is exactly 0.
+    // |pt| <= 2^18 * voxelSize, so with these windows |proj * pc.xy| stays below 2^68.
     P.rcpMu = 1.0f / P.mu; P.rcp255 = 1.0f / 255.0f; P.rcp32767 = 1.0f / 32767.0f;
+    // Upper side only.  A numerator BELOW the window (|proj * pc.xy| < 2^-84: a voxel within a hair of the optical axis times a
+    // pose entry like cos(pi/2) = 6e-17, which synthetic and axis-aligned trajectories are full of) makes the correction
+    // sequence inexact, but its quotient is then below 2^-64 in magnitude (|pc.z| >= 2^-20 is tested per voxel) and the only use
+    // of the quotient is `q + principal point`, which rounds to the principal point for ANY |q| < 2^-40 when that is >= 1 and
+    // fails the `u >= 1` image test either way when it is smaller: the voxel's fate and value do not depend on it.  (Round 2
+    // until r02ac had a per-factor lower window here that sent every such frame -- most of C1 and C3 -- to the plain-division
+    // kernels; tests/test_gpu_bench_config.py runs those sequences against the CPU checker bit for bit.)
     bool ok = in_window(P.voxelSize, -20, 10) && in_window(P.mu, -20, 20) && !significand_all_ones(P.mu);
-    for (int i = 0; i < 16 && ok; i++) ok = zero_or_in_window(P.M_d.m[i], -30, 20) && zero_or_in_window(P.M_rgb.m[i], -30, 20);
-    for (int i = 0; i < 4 && ok; i++) ok = zero_or_in_window(P.proj_d[i], -10, 20) && zero_or_in_window(P.proj_rgb[i], -10, 20);
+    for (int i = 0; i < 16 && ok; i++) ok = fabsf(P.M_d.m[i]) <= ldexpf(1.0f, 20) && fabsf(P.M_rgb.m[i]) <= ldexpf(1.0f, 20);
+    for (int i = 0; i < 4 && ok; i++) ok = fabsf(P.proj_d[i]) <= ldexpf(1.0f, 20) && fabsf(P.proj_rgb[i]) <= ldexpf(1.0f, 20);
     P.fastDiv = (ok && !e->forceSlowDiv) ? 1 : 0;
 }
 

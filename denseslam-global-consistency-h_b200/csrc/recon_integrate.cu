@@ -341,6 +341,70 @@ __device__ __forceinline__ bool fuse_depth_flat(unsigned &lo, float pcx, float p
     return ok && !((eta > P.mu) || (fabsf(q) > 0.25f));
 }
 
+// PACKED FP32 (sm_100: add / mul / fma .rn.f32x2, SASS FADD2 / FMUL2 / FFMA2): a lane's two voxels of a slice go through the depth
+// part TOGETHER, one instruction per operation for both.  Each half of a packed operation is the IEEE round-to-nearest operation
+// of the scalar code, so the result is bit-identical to two calls of fuse_depth_flat; what changes is the number of issue slots
+// (the kernel is issue-bound): ~40 packed instead of ~80 scalar floating-point instructions per voxel pair.
+__device__ __forceinline__ float2 bc2(float x) { return make_float2(x, x); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+// div_step1 / div_step2 (exactdiv.cuh) on both halves; nb = -b
+__device__ __forceinline__ float2 div_step1_2(float2 a, float2 nb, float2 y)
+{
+    const float2 q = mul2(a, y);
+    return fma2(fma2(nb, q, a), y, q);
+}
+__device__ __forceinline__ float2 div_step2_2(float2 a, float2 nb, float2 y)
+{
+    float2 q = mul2(a, y);
+    q = fma2(fma2(nb, q, a), y, q);
+    return fma2(fma2(nb, q, a), y, q);
+}
+
+template <bool WIMG>
+__device__ __forceinline__ void fuse_depth_flat2(unsigned &loA, unsigned &loB, float2 pcx, float2 pcy, float2 pcz, const FuseParams &P,
+                                                 const float *__restrict__ depth, const unsigned char *__restrict__ wimg,
+                                                 const FuseTables &T, bool &outside, bool &colourA, bool &colourB)
+{
+    const int wA = (int)((loA >> 16) & 0xffu), wB = (int)((loB >> 16) & 0xffu);
+    bool okA = !(pcz.x <= 0.0f), okB = !(pcz.y <= 0.0f);
+    if (P.stopMaxW) { okA = okA && (wA != P.maxW); okB = okB && (wB != P.maxW); }
+    if (P.approximate) { okA = okA && (wA == 0); okB = okB && (wB == 0); }
+    outside = outside || (okA && !div_range_ok(pcz.x)) || (okB && !div_range_ok(pcz.y));
+    const float2 nz = make_float2(-pcz.x, -pcz.y);
+    const float2 a0 = mul2(bc2(P.proj_d[0]), pcx), a1 = mul2(bc2(P.proj_d[1]), pcy);
+    float2 y = make_float2(rcp_approx(pcz.x), rcp_approx(pcz.y));          // rcp_refined on both halves
+    y = fma2(y, fma2(nz, y, bc2(1.0f)), y);
+    const float2 u = add2(div_step2_2(a0, nz, y), bc2(P.proj_d[2])), v = add2(div_step2_2(a1, nz, y), bc2(P.proj_d[3]));
+    okA = okA && !((u.x < 1) || (u.x > P.W - 2) || (v.x < 1) || (v.x > P.H - 2));
+    okB = okB && !((u.y < 1) || (u.y > P.W - 2) || (v.y < 1) || (v.y > P.H - 2));
+    const float2 uh = add2(u, bc2(0.5f)), vh = add2(v, bc2(0.5f));
+    const int idxA = okA ? ((int)uh.x + (int)vh.x * P.W) : 0, idxB = okB ? ((int)uh.y + (int)vh.y * P.W) : 0;
+    const float2 dm = make_float2(__ldg(depth + idxA), __ldg(depth + idxB));
+    const int newWA = WIMG ? (int)__ldg(wimg + idxA) : 1, newWB = WIMG ? (int)__ldg(wimg + idxB) : 1;
+    okA = okA && !(dm.x <= 0.0f); okB = okB && !(dm.y <= 0.0f);
+    const float2 eta = add2(dm, nz);                                       // dm - pcz
+    okA = okA && !(eta.x < -P.mu); okB = okB && !(eta.y < -P.mu);
+    const float2 q = div_step2_2(eta, bc2(-P.mu), bc2(P.rcpMu));
+    const float2 oldF = div_step1_2(make_float2((float)(short)(loA & 0xffffu), (float)(short)(loB & 0xffffu)), bc2(-32767.0f), bc2(P.rcp32767));
+    const float2 newF = make_float2((1.0f < q.x) ? 1.0f : q.x, (1.0f < q.y) ? 1.0f : q.y);
+    // w * oldF + newW * newF: the two products packed, the sums SCALAR -- ptxas contracts a packed product feeding a packed sum into
+    // FFMA2 whatever --fmad says and even for explicit mul.rn.f32x2 / add.rn.f32x2 (measured: 25 % of random operands then differ
+    // from the reference's two roundings); a scalar FADD is left alone.  No other packed product here feeds a sum.
+    const float2 pOld = mul2(make_float2((float)wA, (float)wB), oldF), pNew = mul2(make_float2((float)newWA, (float)newWB), newF);
+    const float2 numer = make_float2(__fadd_rn(pOld.x, pNew.x), __fadd_rn(pOld.y, pNew.y));
+    const int wsA = wA + newWA, wsB = wB + newWB;                          // 1 .. 255 + maxNewW <= 510
+    const float2 F = div_step1_2(numer, make_float2(-(float)wsA, -(float)wsB), make_float2(T.rcp[wsA], T.rcp[wsB]));
+    const float2 Fs = mul2(F, bc2(32767.0f));
+    const int w2A = (wsA < P.maxW) ? wsA : P.maxW, w2B = (wsB < P.maxW) ? wsB : P.maxW;
+    const unsigned nloA = (loA & 0xff000000u) | (((unsigned)w2A & 0xffu) << 16) | ((unsigned)(int)Fs.x & 0xffffu);
+    const unsigned nloB = (loB & 0xff000000u) | (((unsigned)w2B & 0xffu) << 16) | ((unsigned)(int)Fs.y & 0xffffu);
+    loA = okA ? nloA : loA; loB = okB ? nloB : loB;
+    colourA = okA && !((eta.x > P.mu) || (fabsf(q.x) > 0.25f));
+    colourB = okB && !((eta.y > P.mu) || (fabsf(q.y) > 0.25f));
+}
+
 // ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) of one 4 KiB voxel block global -> shared, completion on an mbarrier.
 // TMA = true: each warp owns a two-stage ring of block buffers; lane 0 issues the copy of the warp's NEXT block as soon as the
 // previous occupant of that stage has been written back, so a block is in flight for a whole block's worth of arithmetic
@@ -380,7 +444,7 @@ __device__ __forceinline__ uint4 *fuse_stage(FuseTmaSmem &S, int warp, unsigned 
 __device__ __forceinline__ unsigned long long &fuse_bar(FuseTmaSmem &S, int warp, unsigned s) { return S.bar[warp][s]; }
 __device__ __forceinline__ unsigned long long &fuse_bar(FuseWarpSmem &S, int, unsigned) { return *reinterpret_cast<unsigned long long *>(S.dirty); }   // never used
 
-template <bool WIMG, int MINB, bool TMA>
+template <bool WIMG, int MINB, bool TMA, bool PACKED>
 __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FuseParams P, dsb200_voxel *voxels,
                                                                         const dsb200_hash_entry *__restrict__ hash,
                                                                         const int *__restrict__ ids, const int *__restrict__ countPtr,
@@ -440,8 +504,15 @@ __global__ void __launch_bounds__(kFuseWarps * 32, MINB) k_fuse_warp_flat(FusePa
                 const float bx = P.M_d.m[8] * ptz, by = P.M_d.m[9] * ptz, bz = P.M_d.m[10] * ptz;
                 unsigned lo0 = raw.x, lo1 = raw.z;
                 bool outside = false;
-                bool c0 = fuse_depth_flat<WIMG>(lo0, (ax0 + bx) + P.M_d.m[12], (ay0 + by) + P.M_d.m[13], (az0 + bz) + P.M_d.m[14], P, depth, wimg, T, outside);
-                bool c1 = fuse_depth_flat<WIMG>(lo1, (ax1 + bx) + P.M_d.m[12], (ay1 + by) + P.M_d.m[13], (az1 + bz) + P.M_d.m[14], P, depth, wimg, T, outside);
+                bool c0, c1;
+                if (PACKED)
+                    fuse_depth_flat2<WIMG>(lo0, lo1, add2(add2(make_float2(ax0, ax1), bc2(bx)), bc2(P.M_d.m[12])),
+                                           add2(add2(make_float2(ay0, ay1), bc2(by)), bc2(P.M_d.m[13])),
+                                           add2(add2(make_float2(az0, az1), bc2(bz)), bc2(P.M_d.m[14])), P, depth, wimg, T, outside, c0, c1);
+                else {
+                    c0 = fuse_depth_flat<WIMG>(lo0, (ax0 + bx) + P.M_d.m[12], (ay0 + by) + P.M_d.m[13], (az0 + bz) + P.M_d.m[14], P, depth, wimg, T, outside);
+                    c1 = fuse_depth_flat<WIMG>(lo1, (ax1 + bx) + P.M_d.m[12], (ay1 + by) + P.M_d.m[13], (az1 + bz) + P.M_d.m[14], P, depth, wimg, T, outside);
+                }
                 if (__any_sync(0xffffffffu, outside)) {          // (never in practice) the slice again, general code
                     VoxelRegs v0 = unpack(raw.x, raw.y), v1 = unpack(raw.z, raw.w);
                     c0 = c1 = false;
@@ -509,13 +580,17 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
 {
     unsigned *shadow2 = reinterpret_cast<unsigned *>(sdfShadow);
     const uchar4 *rgb4 = reinterpret_cast<const uchar4 *>(rgb);
-    const int variant = tunables().fuse_kernel;   // 1: round-1 warp-per-block kernel; 2: + straight-line depth part; 3: + TMA bulk block loads (default)
+    const int variant = tunables().fuse_kernel;   // 1: round-1 warp-per-block kernel; 2: + straight-line depth part; 3: + TMA bulk block loads; 4: + packed FP32 (default)
     if (variant >= 2 && !deintegrate && P.fastDiv && P.maxNewW >= 1 && P.maxNewW <= 255 && (!P.depthWeighting || weightScratch)) {
         const int g = kNumSMs * tunables().fuse_ctas;
         const int minb = tunables().fuse_minb;     // register budget: 65536 / (128 * minb)
-#define DSB_FLAT(W_, M_, T_) DSB_LAUNCH((k_fuse_warp_flat<W_, M_, T_>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, W_ ? weightScratch : nullptr, shadow2)
+#define DSB_FLAT4(W_, M_, T_, K_) DSB_LAUNCH((k_fuse_warp_flat<W_, M_, T_, K_>), g, kFuseWarps * 32, 0, st, P, voxels, hash, ids, count, depth, rgb4, W_ ? weightScratch : nullptr, shadow2)
+#define DSB_FLAT(W_, M_, T_) DSB_FLAT4(W_, M_, T_, false)
         if (P.depthWeighting) DSB_LAUNCH(k_depth_weights, kNumSMs * 4, 256, 0, st, depth, weightScratch, P.W * P.H, P.maxDistance, P.maxNewW);
-        if (variant == 3) {                // TMA bulk loads: 39 KiB of shared memory per CTA -> at most 5 CTAs per SM
+        if (variant >= 4) {                // TMA bulk loads + packed FP32 depth part (FADD2 / FMUL2 / FFMA2)
+            if (P.depthWeighting) { if (minb >= 5) DSB_FLAT4(true, 5, true, true); else DSB_FLAT4(true, 4, true, true); }
+            else { if (minb >= 5) DSB_FLAT4(false, 5, true, true); else DSB_FLAT4(false, 4, true, true); }
+        } else if (variant == 3) {         // TMA bulk loads: 39 KiB of shared memory per CTA -> at most 5 CTAs per SM
             if (P.depthWeighting) { if (minb >= 5) DSB_FLAT(true, 5, true); else DSB_FLAT(true, 4, true); }
             else { if (minb >= 5) DSB_FLAT(false, 5, true); else DSB_FLAT(false, 4, true); }
         } else if (P.depthWeighting) {
@@ -524,6 +599,7 @@ void launch_fuse(cudaStream_t st, const FuseParams &P, bool deintegrate, dsb200_
             if (minb >= 8) DSB_FLAT(false, 8, false); else if (minb >= 6) DSB_FLAT(false, 6, false); else DSB_FLAT(false, 4, false);
         }
 #undef DSB_FLAT
+#undef DSB_FLAT4
         return;
     }
     {

@@ -1016,7 +1016,7 @@ static int env_int(const char *name, int dflt) { const char *v = getenv(name); r
 Tunables &tunables()
 {
     static Tunables t = {env_int("DSB200_RAY_STEPS", 0), env_int("DSB200_RAY_GROUP", 8), env_int("DSB200_RAY_CTAS", 12),
-                         env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 3), env_int("DSB200_FUSE_CTAS", 10),
+                         env_int("DSB200_RAY_FINISH_CTAS", 4), env_int("DSB200_RAY_BOTTOM_UP", 0), env_int("DSB200_FUSE_KERNEL", 4), env_int("DSB200_FUSE_CTAS", 10),
                          env_int("DSB200_FUSE_MINB", 5), env_int("DSB200_DEEP_LOOKAHEAD", 1), env_int("DSB200_RAY_LPT", 48)};
     return t;
 }
