@@ -21,6 +21,10 @@ def test_fma_division_sequences_match_ieee_on_host(tmp_path):
     out = subprocess.run([exe, mode], capture_output=True, text=True)
     bad1, bad2, n = [int(x) for x in out.stdout.split()]
     assert out.returncode == 0 and bad1 == 0 and bad2 == 0 and n > 1e7, out.stdout
+    # numerators below the run-time-divisor path's window: the quotient may be inexact, `quotient + principal point` never is
+    out = subprocess.run([exe, "2"], capture_output=True, text=True)
+    bad, inexact, n = [int(x) for x in out.stdout.split()]
+    assert out.returncode == 0 and bad == 0 and n == 20000000, out.stdout
 
 
 @pytest.mark.gpu
