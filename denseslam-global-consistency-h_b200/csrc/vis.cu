@@ -359,9 +359,8 @@ __device__ __forceinline__ float sdf_trilinear(const Tables &T, int bucketNum, i
         p000 = resolve_block(T, bucketNum, bucketMask, bx, by, bz);
         if (p000) { cache.bx = bx; cache.by = by; cache.bz = bz; cache.blk = p000; }
     }
-    // The neighbour blocks the sample crosses into: c = dx | dy << 1 | dz << 2 with every set axis a crossing axis, i.e. 0, 1, 3
-    // or 7 blocks.  They are resolved in ONE loop (lane by lane its next needed neighbour) instead of seven conditional call
-    // sites: the lanes of a warp then run the hash probe together, whichever neighbour each of them is after.
+    // The neighbour blocks the sample crosses into: every crossing axis doubles them, i.e. 0, 1, 3 or 7 blocks, each resolved at its
+    // own conditional call site (the single-loop form measured 3.4x slower, see above).
     const short *p100 = ex ? resolve_block(T, bucketNum, bucketMask, bx + 1, by, bz) : p000;
     const short *p010 = ey ? resolve_block(T, bucketNum, bucketMask, bx, by + 1, bz) : p000;
     const short *p001 = ez ? resolve_block(T, bucketNum, bucketMask, bx, by, bz + 1) : p000;
