@@ -552,8 +552,12 @@ extern "C" {
 int dsb200_reset_scene(dsb200_recon *e, dsb200_scene *scene)
 {
     if (e && e->prefetchPending) {       // a reset abandons a pending look-ahead: let its kernels finish, then wipe what they wrote
-        CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));
-        e->prefetchPending = false;
+        if (scene && e->prefetchKey.hashRW != scene->hash) {      // ... made for ANOTHER scene of this engine: undone there, exactly
+            int rc = abandon_prefetch(e); if (rc) return rc;
+        } else {
+            CU(cudaStreamWaitEvent(e->stream, e->evPrefetchDone, 0));
+            e->prefetchPending = false;
+        }
     }
     int rc = check_scene(e, scene); if (rc) return rc;
     e->totalDecayed = 0;
