@@ -141,12 +141,15 @@ class OracleBackend(object):
         return self.o.L.rst_count_visible_blocks(C.byref(self.scene.c), C.byref(self.rs.c), lo, hi)
 
     # ---- state
-    def state(self, voxels=True):
-        s = dict(hash=self.scene.hash.copy(), visible=self.rs.visible(), visible_type=self.rs.visible_type.copy(),
+    def state(self, voxels=True, copy=True):
+        """copy=False: views of the live arrays (the voxel array alone is 1 GiB at the reference capacities) for callers that
+        compare at once and do not keep the state across a later call"""
+        c = (lambda a: a.copy()) if copy else (lambda a: a)
+        s = dict(hash=c(self.scene.hash), visible=self.rs.visible(), visible_type=c(self.rs.visible_type),
                  last_free=(self.scene.c.last_free_block, self.scene.c.last_free_excess),
-                 alloc_list=self.scene.alloc_list.copy(), excess_list=self.scene.excess_list.copy())
+                 alloc_list=c(self.scene.alloc_list), excess_list=c(self.scene.excess_list))
         if voxels:
-            s["voxels"] = self.scene.voxels.copy()
+            s["voxels"] = c(self.scene.voxels)
         return s
 
     def images(self):

@@ -42,7 +42,7 @@ def check_backend_against_fixture(back, z, cfg, frames):
     for i, f in enumerate(frames):
         back.set_frame(f)
         assert back.process_frame() == 0
-        s = back.state()
+        s = back.state(copy=False) if back.name != "gpu" else back.state()      # oracle: views of the live arrays, digested at once
         d = mg.state_digests(s["hash"], s["voxels"], s["visible"], s["visible_type"], s["last_free"])
         for k, want in zip(skeys, z["state_digests"][i]):
             assert d[k] == want, "frame %d: %s differs from the reference" % (i, k)

@@ -22,7 +22,7 @@ def run_pair(cfg_name, n_frames, use_swapping=False, weights=False):
         assert np.array_equal(iMr.view(np.uint32), ora.o.mat4_inverse(f.M).view(np.uint32))
         ref.allocate(); ref.integrate(); ref.create_expected_depths(); ref.create_icp_maps()
         ora.set_frame(f); ora.process_frame()
-        s = ora.state()
+        s = ora.state(copy=False)
         rstate = dict(hash=ref.hash(), visible=ref.visible(), visible_type=ref.visible_type(), last_free=ref.last_free(),
                       alloc_list=ref.alloc_list(), excess_list=ref.excess_list(), voxels=ref.voxels())
         hz.assert_state_equal(rstate, s, "frame %d ref-vs-oracle" % i)
@@ -160,11 +160,14 @@ def test_swapping_engine_matches_reference():
             n = ora.o.swap_save_to_global_memory(cache, ora.scene, None)
             assert n > 300 and (ora.scene.hash["ptr"] == -1).sum() >= n
         what = "swap step %d (frame %d)" % (step, k)
-        s = ora.state()
+        s = ora.state(copy=False)               # compared at once: no copy of the 1 GiB voxel array
         rstate = dict(hash=ref.hash(), visible=ref.visible(), visible_type=ref.visible_type(), last_free=ref.last_free(),
                       alloc_list=ref.alloc_list(), excess_list=ref.excess_list())
         hz.assert_state_equal(rstate, s, what, voxels=False)
-        assert hz.voxels_equal_but_pad(ref.voxels(), s["voxels"]), what
+        # the 1 GiB voxel arrays at the steps where the swapping paths change (first frame, return of the first stretch, whole-map
+        # swap-out and the frame after it, end); tables, states and store contents at every step
+        if step in (0, 4, whole_map_after, whole_map_after + 1, len(order) - 1):
+            assert hz.voxels_equal_but_pad(ref.voxels(), s["voxels"]), what
         assert np.array_equal(ref.swap_states(), cache.states), what
         has = ref.swap_has_stored()
         assert np.array_equal(has, cache.has_stored), what
