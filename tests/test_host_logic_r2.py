@@ -132,3 +132,27 @@ def test_set_level_comparator_accepts_and_rejects_what_it_should():
     # a different block SET beyond the tolerance is a failure
     with pytest.raises(AssertionError):
         hz.assert_sets_match(hz.SetTracker(), A(vox[:n // 2], keys[:n // 2]), B(), "half the map missing")
+
+
+def test_oracle_ray_trip_hooks_count_consistently():
+    """oracle/restate.cpp's analysis hooks (tools/ray_trip_stats.py): per-pixel loop trips and their kinds are consistent, and
+    switching them on changes nothing the checker computes"""
+    import ctypes as C
+    cfg, frames = hz.synth.make_sequence("tiny", 3)
+    plain, hooked = hz.OracleBackend(cfg, hz.SMALL_CAPS), hz.OracleBackend(cfg, hz.SMALL_CAPS)
+    lib = C.CDLL(hz.po.RESTATE_PATH)
+    lib.rst_debug_ray_steps.argtypes = [C.c_void_p, C.c_int]; lib.rst_debug_ray_kinds.argtypes = [C.c_void_p]
+    n = cfg.W * cfg.H
+    steps, kinds = np.zeros(n, np.int32), np.zeros(6 * n, np.int32)
+    for i, f in enumerate(frames):
+        plain.set_frame(f); plain.process_frame()
+        if i + 1 == len(frames):
+            lib.rst_debug_ray_steps(steps.ctypes.data_as(C.c_void_p), cfg.W); lib.rst_debug_ray_kinds(kinds.ctypes.data_as(C.c_void_p))
+        hooked.set_frame(f); hooked.process_frame()
+        lib.rst_debug_ray_steps(None, 0); lib.rst_debug_ray_kinds(None)
+    k = kinds.reshape(n, 6)
+    assert steps.max() > 8 and (steps > 0).sum() > n // 2
+    assert (k[:, 0] + k[:, 1] <= steps).all() and (k[:, 3] <= k[:, 0]).all() and (k[:, 5] <= k[:, 4]).all() and (k[:, 2] <= steps).all()
+    assert k[:, 0].sum() > 0 and k[:, 2].sum() > 0
+    hz.assert_images_equal(plain.images(), hooked.images(), "hooks on / off")
+    plain.close(); hooked.close()
